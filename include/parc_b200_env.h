@@ -1,0 +1,232 @@
+/* parc_b200 -- C ABI, tracking-env part (observation, reward, termination, RSI reset).
+ * Included by parc_b200.h. Citations are file:line into the reference (CloudEngineHub/PARC). */
+#ifndef PARC_B200_ENV_H
+#define PARC_B200_ENV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PARC_MAX_DOFS 96
+
+/* A [N, A, B] fp32 view with strides in ELEMENTS (mid_stride unused for 2-D buffers). */
+typedef struct {
+    float* ptr;
+    int64_t row_stride;
+    int64_t mid_stride;
+    int64_t elem_stride;
+} parc_view3_t;
+
+/* Static configuration of the tracking env: the knobs of
+ * data/configs/tracker_config/dm_env_default.yaml that change hot-path arithmetic, as parsed by
+ * IGParkourEnv.__init__ (PARC/motion_tracker/envs/ig_parkour/ig_parkour_env.py:43-149) and
+ * RefCharEnv.__init__ (ig_parkour/mgdm_dm_util.py:15-35). */
+typedef struct {
+    int32_t num_tar_steps;                       /* S */
+    float tar_dt[PARC_MAX_TAR_STEPS];            /* fp32(timestep * tar_obs_steps[s]), mgdm_dm_util.py:232 */
+    int32_t num_key_bodies;                      /* K */
+    int32_t key_body_ids[PARC_MAX_KEY_BODIES];
+    int32_t num_ray_points;                      /* P */
+    int32_t global_obs;
+    int32_t root_height_obs;
+    int32_t enable_tar_obs;
+    int32_t use_contact_info;
+    int32_t track_root;
+    int32_t track_root_h;
+    int32_t enable_early_termination;
+    int32_t pose_termination;
+    int32_t num_fall_contact_bodies;             /* len(contact_body_ids); 0 disables the fall test */
+    uint32_t fall_contact_body_mask;             /* bit b set <=> body b in contact_body_ids */
+    int32_t never_done;
+    float timestep;                              /* fp32(1 / control_freq) */
+    float episode_length;
+    float termination_height;
+    float root_pos_termination_dist;
+    float root_rot_termination_angle;
+    float pose_termination_dist[PARC_MAX_BODIES];/* [j-1] for body j = 1..J-1 */
+    float joint_err_w[PARC_MAX_BODIES];          /* [j-1] */
+    float dof_err_w[PARC_MAX_DOFS];
+    float contact_weights[PARC_MAX_BODIES];
+    float pose_w, vel_w, root_pos_w, root_vel_w, key_pos_w;   /* already normalised (:91-101) */
+    float contact_eps;                           /* _get_char_contact_state eps, 1e-5 (:655) */
+    float min_obs_h, max_obs_h;
+    float ema_weight;                            /* DeepMimicEnv._ema_weight, dm_env.py:90 */
+    float ema_keep;                              /* fp32(1.0 - ema_weight) evaluated in double like the Python expression, dm_env.py:654 */
+    float min_motion_weight;                     /* dm_env.py:26 */
+    float rand_root_pos_offset_scale;            /* mgdm_dm_util.py:174 */
+} parc_env_config_t;
+
+/* All per-env buffers the reference injects through RefCharEnv.get_sim_tensor_views /
+ * get_data_buffer_views (mgdm_dm_util.py:37-84) plus the ones DeepMimicEnv owns
+ * (dm_env.py:80-92). The env does not own the views: every write is in place. */
+typedef struct {
+    int64_t num_envs;                            /* N */
+    /* simulator state (inputs; written only by reset) */
+    parc_view3_t char_root_pos;                  /* [N,3]  */
+    parc_view3_t char_root_rot;                  /* [N,4]  */
+    parc_view3_t char_root_vel;                  /* [N,3]  */
+    parc_view3_t char_root_ang_vel;              /* [N,3]  */
+    parc_view3_t char_dof_pos;                   /* [N,D]  */
+    parc_view3_t char_dof_vel;                   /* [N,D]  */
+    parc_view3_t char_contact_forces;            /* [N,J,3] */
+    parc_view3_t char_rigid_body_pos;            /* [N,J,3] */
+    parc_view3_t char_rigid_body_vel;            /* [N,J,3] (zeroed by reset; may be NULL) */
+    parc_view3_t char_rigid_body_ang_vel;        /* [N,J,3] (zeroed by reset; may be NULL) */
+    /* reference-motion state (outputs of _update_ref_motion / reset) */
+    parc_view3_t ref_root_pos, ref_root_rot, ref_root_vel, ref_root_ang_vel;
+    parc_view3_t ref_body_pos;                   /* [N,J,3] */
+    parc_view3_t ref_joint_rot;                  /* [N,J-1,4] */
+    parc_view3_t ref_dof_pos, ref_dof_vel;       /* [N,D] */
+    parc_view3_t ref_contacts;                   /* [N,C] */
+    /* data buffers */
+    float* reward_buf;                           /* [N] */
+    float* reward_terms;                         /* [N,8]: pose_r, vel_r, root_pos_r, root_vel_r, key_pos_r, contact_penalty, total_r, pad */
+    int32_t* done_buf;                           /* [N] */
+    float* time_buf;                             /* [N] */
+    int32_t* timestep_buf;                       /* [N] */
+    uint8_t* actors_need_reset;                  /* [N, actors] bool; column 0 set by reset */
+    int64_t actors_per_env;
+    const float* env_offsets;                    /* [N,3] */
+    const float* ray_xy_points;                  /* [P,2] */
+    float* ray_hfs;                              /* [N,P] or NULL (heights then live only in obs_buf) */
+    float* obs_buf;                              /* [N, obs_dim] */
+    int64_t obs_row_stride;
+    /* DeepMimicEnv-owned bookkeeping */
+    int64_t* motion_ids;                         /* [N] */
+    int64_t* motion_terrain_ids;                 /* [N] */
+    float* motion_time_offsets;                  /* [N] */
+    float* motion_id_fail_rates;                 /* [M] */
+    const float* motion_weights;                 /* [M] MotionLib._motion_weights */
+    const float* dm_motion_offsets;              /* [M, terrains_per_motion, 2] */
+    int32_t terrains_per_motion;
+    /* per-step scratch written by the step kernel, consumed by fail_rate_ema / reset */
+    int32_t* done_count;                         /* [1] */
+    int32_t* done_list;                          /* [N] env ids with done != NULL (unordered) */
+    uint8_t* done_code;                          /* [N] 0 = running, 1 = FAIL before the motion-end override, 2 = TIME/SUCC/motion end */
+} parc_env_buffers_t;
+
+/* Which parts of IGEnv._post_physics_step (PARC/motion_tracker/envs/ig_env.py:368-377) one call
+ * of parc_b200_env_step performs. */
+enum {
+    PARC_STEP_TIME = 1,        /* _update_time, ig_env.py:391-394 */
+    PARC_STEP_REF = 2,         /* DeepMimicEnv._update_ref_motion, dm_env.py:523-545 */
+    PARC_STEP_HEIGHTS = 4,     /* _refresh_obs_hfs, ig_parkour_env.py:518-533 */
+    PARC_STEP_OBS = 8,         /* IGParkourEnv._compute_obs, ig_parkour_env.py:842-965 */
+    PARC_STEP_REWARD = 16,     /* _update_reward, ig_parkour_env.py:984-1044 */
+    PARC_STEP_DONE = 32,       /* _update_done + DeepMimicEnv.update_done flags, ig_parkour_env.py:967-982, dm_env.py:628-665 */
+    PARC_STEP_ALL = 63
+};
+
+/* Observation row width for a model/config (ig_parkour_env.py:842-965). */
+int parc_b200_obs_dim(const parc_char_model_t* h_model, const parc_env_config_t* h_cfg);
+
+/* One fused pass of the post-physics step over all N envs (or over the subset env_ids [n_sub],
+ * i64, when env_ids != NULL -- the reset-time call IGParkourEnv._update_observations(env_ids),
+ * whose rows land at obs_buf[env_ids]). `parts` is a mask of PARC_STEP_*.
+ * With PARC_STEP_DONE the kernel also appends finished envs to done_list/done_count (the count
+ * must be zeroed by the caller, e.g. by parc_b200_fail_rate_ema of the previous step) and writes
+ * done_code for parc_b200_fail_rate_ema. */
+int parc_b200_env_step(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                       const parc_terrain_t* h_terrain, const parc_env_config_t* h_cfg,
+                       const parc_env_buffers_t* h_env, uint32_t parts, const int64_t* env_ids,
+                       int64_t n_sub, void* stream);
+
+/* DeepMimicEnv.compute_tar_obs (dm_env.py:594-626) + fetch_tar_obs_data (mgdm_dm_util.py:221-244):
+ * -> tar_root_pos [n,S,3], tar_root_rot [n,S,4], tar_joint_rot [n,S,J-1,4], tar_key_pos [n,S,K,3],
+ * tar_contacts [n,S,C]; env_ids may be NULL (all envs, n = N). */
+int parc_b200_compute_tar_obs_data(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                                   const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
+                                   const int64_t* env_ids, int64_t n, float* tar_root_pos,
+                                   float* tar_root_rot, float* tar_joint_rot, float* tar_key_pos,
+                                   float* tar_contacts, void* stream);
+
+/* The free jit functions of the reference, on caller-provided contiguous tensors. */
+
+/* compute_char_obs (PARC/motion_tracker/envs/ig_char_env.py:581-625) -> obs [n, char_obs_dim] */
+int parc_b200_compute_char_obs(const parc_char_model_t* h_model, const float* root_pos,
+                               const float* root_rot, const float* root_vel,
+                               const float* root_ang_vel, const float* joint_rot,
+                               const float* dof_vel, const float* key_pos, int32_t num_key,
+                               int32_t global_obs, int32_t root_height_obs, int64_t n, float* obs,
+                               void* stream);
+
+/* compute_tar_obs (mgdm_dm_util.py:404-461) -> obs [n, S, 3+6+6(J-1)+3K] */
+int parc_b200_compute_tar_obs(const parc_char_model_t* h_model, const float* ref_root_pos,
+                              const float* ref_root_rot, const float* tar_root_pos,
+                              const float* tar_root_rot, const float* tar_joint_rot,
+                              const float* tar_key_pos, int32_t num_steps, int32_t num_key,
+                              int32_t global_obs, int32_t global_tar_root_h_obs, int64_t n,
+                              float* obs, void* stream);
+
+/* compute_deepmimic_reward (mgdm_dm_util.py:269-332) -> [n,5] */
+int parc_b200_compute_deepmimic_reward(const parc_char_model_t* h_model, const float* root_pos,
+                                       const float* root_rot, const float* root_vel,
+                                       const float* root_ang_vel, const float* joint_rot,
+                                       const float* dof_vel, const float* key_pos,
+                                       const float* tar_root_pos, const float* tar_root_rot,
+                                       const float* tar_root_vel, const float* tar_root_ang_vel,
+                                       const float* tar_joint_rot, const float* tar_dof_vel,
+                                       const float* tar_key_pos, const float* joint_rot_err_w,
+                                       const float* dof_err_w, int32_t num_key, int32_t track_root_h,
+                                       int32_t track_root, int64_t n, float* reward5, void* stream);
+
+/* compute_contact_reward (mgdm_dm_util.py:497-518): [n,C],[n,C,3],[C] -> [n,C] */
+int parc_b200_compute_contact_reward(const float* tar_contacts, const float* contact_forces,
+                                     const float* contact_weights, int32_t num_contacts, int64_t n,
+                                     float* out, void* stream);
+
+/* compute_done (mgdm_dm_util.py:334-402); termination_heights [n,J] precomputed by the caller as
+ * in RefCharEnv.update_done (:147-172), contact_body_ids i64 [n_cb]. */
+int parc_b200_compute_done(const int32_t* done_buf_in, const float* time, float ep_len,
+                           const float* root_rot, const float* body_pos, const float* tar_root_rot,
+                           const float* tar_body_pos, const float* contact_force,
+                           const int64_t* contact_body_ids, int32_t n_cb,
+                           const float* termination_heights, int32_t pose_termination,
+                           const float* pose_termination_dist, int32_t enable_early_termination,
+                           int32_t track_root, float root_pos_termination_dist,
+                           float root_rot_termination_angle, int32_t num_bodies, int64_t n,
+                           int32_t* done_out, void* stream);
+
+/* Fail-rate EMA of DeepMimicEnv.update_done (dm_env.py:648-660): for every finished env IN
+ * ASCENDING ENV-ID ORDER per motion, rate <- rate*(1-w) + w (FAIL) or rate*(1-w) (otherwise).
+ * Consumes done_list/done_code written by parc_b200_env_step; also refreshes the RSI sampling CDF
+ * cdf [M] = inclusive prefix sum of clamp(rate, min_motion_weight) * motion_weight
+ * (dm_env.py:487-490). scratch must hold 2*M + done capacity int32. Does NOT reset done_count. */
+int parc_b200_fail_rate_ema(const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
+                            int32_t num_motions, float* cdf, int32_t* scratch, void* stream);
+
+/* DeepMimicEnv.reset (dm_env.py:567-592) for env_ids [n] i64 given the random draws the reference
+ * takes from torch's generator: motion_ids [n] i64 (sample_motions / demo-mode ids),
+ * terrain_ids [n] i64 (randint), motion_times [n] f32 (sample_time or len*start_fraction),
+ * xy_noise [n,2] f32 in [-1,1) (add_noise_to_char_state, mgdm_dm_util.py:102-106).
+ * Optional per-env offsets (apply_offsets_to_char_state, :108-126) may be NULL. */
+int parc_b200_env_reset(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                        const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
+                        const int64_t* env_ids, int64_t n, const int64_t* motion_ids,
+                        const int64_t* terrain_ids, const float* motion_times,
+                        const float* xy_noise, const float* root_pos_offset,
+                        const float* root_rot_offset, void* stream);
+
+/* Device-side RSI for the graph-captured loop: for each entry of done_list (count read on the
+ * device) draw motion id (inverse CDF over `cdf`, binary search), terrain id and phase from a
+ * Philox4x32-10 counter keyed by (seed, env id, step), then do everything parc_b200_env_reset does
+ * and re-evaluate heights + observation of the reset envs (IGParkourEnv.reset,
+ * ig_parkour_env.py:809-829). Zeroes done_count when finished iff reset_count != 0. */
+int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                                const parc_terrain_t* h_terrain, const parc_env_config_t* h_cfg,
+                                const parc_env_buffers_t* h_env, const float* cdf,
+                                int32_t num_motions, uint64_t seed, uint64_t step,
+                                int32_t rand_reset, void* stream);
+
+/* Inverse-CDF sampler alone (MotionLib.sample_motions semantics given uniforms u [n] in [0,1)):
+ * ids[i] = first m with cdf[m] > u[i] * cdf[M-1]. */
+int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n,
+                                 int64_t* ids, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* PARC_B200_ENV_H */

@@ -1,0 +1,170 @@
+// extern "C" entry points of env_aux_kernels.cu (included at its end; kept separate for size).
+#pragma once
+
+using namespace parc;
+
+#define G_DISPATCH(kernel, n_groups, ...)                                                              \
+    do {                                                                                               \
+        if (m->num_bodies <= 16) kernel<16><<<blocks_for((n_groups), 16), 256, 0, as_stream(stream)>>>(__VA_ARGS__); \
+        else kernel<32><<<blocks_for((n_groups), 8), 256, 0, as_stream(stream)>>>(__VA_ARGS__);         \
+    } while (0)
+
+extern "C" int parc_b200_compute_tar_obs_data(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_env_config_t* cfg,
+                                              const parc_env_buffers_t* env, const int64_t* env_ids, int64_t n, float* tar_root_pos,
+                                              float* tar_root_rot, float* tar_joint_rot, float* tar_key_pos, float* tar_contacts, void* stream) {
+    if (!model_ok(m, "compute_tar_obs_data")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(lib && lib->interp && cfg && env, "compute_tar_obs_data: NULL descriptor");
+    PARC_REQUIRE(cfg->num_tar_steps > 0 && cfg->num_tar_steps <= PARC_MAX_TAR_STEPS, "compute_tar_obs_data: num_steps must be in [1,%d]", PARC_MAX_TAR_STEPS);
+    PARC_REQUIRE(n >= 0, "compute_tar_obs_data: n < 0");
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(tar_root_pos && tar_root_rot && (tar_joint_rot || m->num_bodies == 1), "compute_tar_obs_data: NULL output");
+    PARC_REQUIRE(tar_contacts == nullptr || lib->num_contacts > 0, "compute_tar_obs_data: library has no contact info");
+    G_DISPATCH(tar_obs_data_kernel, n * cfg->num_tar_steps, *m, *lib, *cfg, *env, (const long long*)env_ids, n, tar_root_pos, tar_root_rot,
+               tar_joint_rot, tar_key_pos, tar_contacts);
+    return check_launch("compute_tar_obs_data");
+}
+
+extern "C" int parc_b200_compute_char_obs(const parc_char_model_t* m, const float* root_pos, const float* root_rot, const float* root_vel,
+                                          const float* root_ang_vel, const float* joint_rot, const float* dof_vel, const float* key_pos,
+                                          int32_t num_key, int32_t global_obs, int32_t root_height_obs, int64_t n, float* obs, void* stream) {
+    if (!model_ok(m, "compute_char_obs")) return PARC_ERR_INVALID_ARG;
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel && obs, "compute_char_obs: NULL pointer");
+    PARC_REQUIRE(num_key == 0 || key_pos, "compute_char_obs: key_pos is NULL");
+    G_DISPATCH(char_obs_kernel, n, *m, root_pos, root_rot, root_vel, root_ang_vel, joint_rot, dof_vel, key_pos, num_key, global_obs,
+               root_height_obs ? 1 : 0, n, obs);
+    return check_launch("compute_char_obs");
+}
+
+extern "C" int parc_b200_compute_tar_obs(const parc_char_model_t* m, const float* ref_root_pos, const float* ref_root_rot,
+                                         const float* tar_root_pos, const float* tar_root_rot, const float* tar_joint_rot,
+                                         const float* tar_key_pos, int32_t num_steps, int32_t num_key, int32_t global_obs,
+                                         int32_t global_tar_root_h_obs, int64_t n, float* obs, void* stream) {
+    if (!model_ok(m, "compute_tar_obs")) return PARC_ERR_INVALID_ARG;
+    if (n == 0 || num_steps == 0) return PARC_OK;
+    PARC_REQUIRE(ref_root_pos && ref_root_rot && tar_root_pos && tar_root_rot && obs, "compute_tar_obs: NULL pointer");
+    PARC_REQUIRE(num_key == 0 || tar_key_pos, "compute_tar_obs: tar_key_pos is NULL");
+    G_DISPATCH(tar_obs_kernel, n * num_steps, *m, ref_root_pos, ref_root_rot, tar_root_pos, tar_root_rot, tar_joint_rot, tar_key_pos,
+               num_steps, num_key, global_obs, global_tar_root_h_obs, n, obs);
+    return check_launch("compute_tar_obs");
+}
+
+extern "C" int parc_b200_compute_deepmimic_reward(const parc_char_model_t* m, const float* root_pos, const float* root_rot,
+                                                  const float* root_vel, const float* root_ang_vel, const float* joint_rot,
+                                                  const float* dof_vel, const float* key_pos, const float* tar_root_pos,
+                                                  const float* tar_root_rot, const float* tar_root_vel, const float* tar_root_ang_vel,
+                                                  const float* tar_joint_rot, const float* tar_dof_vel, const float* tar_key_pos,
+                                                  const float* joint_rot_err_w, const float* dof_err_w, int32_t num_key,
+                                                  int32_t track_root_h, int32_t track_root, int64_t n, float* reward5, void* stream) {
+    if (!model_ok(m, "compute_deepmimic_reward")) return PARC_ERR_INVALID_ARG;
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel && tar_root_pos && tar_root_rot && tar_root_vel &&
+                     tar_root_ang_vel && tar_dof_vel && joint_rot_err_w && dof_err_w && reward5,
+                 "compute_deepmimic_reward: NULL pointer");
+    dm_reward_kernel<<<blocks_for(n, 8), 256, 0, as_stream(stream)>>>(m->num_bodies, m->dof_size, num_key, root_pos, root_rot, root_vel,
+                                                                      root_ang_vel, joint_rot, dof_vel, key_pos, tar_root_pos, tar_root_rot,
+                                                                      tar_root_vel, tar_root_ang_vel, tar_joint_rot, tar_dof_vel, tar_key_pos,
+                                                                      joint_rot_err_w, dof_err_w, track_root_h, track_root, n, reward5);
+    return check_launch("compute_deepmimic_reward");
+}
+
+extern "C" int parc_b200_compute_contact_reward(const float* tar_contacts, const float* contact_forces, const float* contact_weights,
+                                                int32_t num_contacts, int64_t n, float* out, void* stream) {
+    if (n == 0 || num_contacts == 0) return PARC_OK;
+    PARC_REQUIRE(tar_contacts && contact_forces && contact_weights && out, "compute_contact_reward: NULL pointer");
+    contact_reward_kernel<<<blocks_for(n * num_contacts, 256), 256, 0, as_stream(stream)>>>(tar_contacts, contact_forces, contact_weights,
+                                                                                          num_contacts, n, out);
+    return check_launch("compute_contact_reward");
+}
+
+extern "C" int parc_b200_compute_done(const int32_t* done_buf_in, const float* time, float ep_len, const float* root_rot,
+                                      const float* body_pos, const float* tar_root_rot, const float* tar_body_pos,
+                                      const float* contact_force, const int64_t* contact_body_ids, int32_t n_cb,
+                                      const float* termination_heights, int32_t pose_termination, const float* pose_termination_dist,
+                                      int32_t enable_early_termination, int32_t track_root, float root_pos_termination_dist,
+                                      float root_rot_termination_angle, int32_t num_bodies, int64_t n, int32_t* done_out, void* stream) {
+    (void)done_buf_in;   // the reference only uses it for shape/dtype (torch.full_like)
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(time && done_out, "compute_done: NULL pointer");
+    PARC_REQUIRE(num_bodies >= 1 && num_bodies <= PARC_MAX_BODIES, "compute_done: num_bodies out of range");
+    if (enable_early_termination) {
+        PARC_REQUIRE(n_cb == 0 || (contact_force && contact_body_ids && termination_heights && body_pos), "compute_done: fall test inputs missing");
+        PARC_REQUIRE(!pose_termination || (body_pos && tar_body_pos && pose_termination_dist), "compute_done: pose termination inputs missing");
+        PARC_REQUIRE(!(pose_termination && track_root) || (root_rot && tar_root_rot), "compute_done: root rotations missing");
+    }
+    compute_done_kernel<<<blocks_for(n, 8), 256, 0, as_stream(stream)>>>(time, ep_len, root_rot, body_pos, tar_root_rot, tar_body_pos, contact_force,
+                                                                         (const long long*)contact_body_ids, n_cb, termination_heights,
+                                                                         pose_termination, pose_termination_dist, enable_early_termination,
+                                                                         track_root, root_pos_termination_dist, root_rot_termination_angle,
+                                                                         num_bodies, n, done_out);
+    return check_launch("compute_done");
+}
+
+extern "C" int parc_b200_fail_rate_ema(const parc_env_config_t* cfg, const parc_env_buffers_t* env, int32_t num_motions, float* cdf,
+                                       int32_t* scratch, void* stream) {
+    PARC_REQUIRE(cfg && env && num_motions > 0, "fail_rate_ema: bad arguments");
+    PARC_REQUIRE(env->done_count && env->done_list && env->done_code && env->motion_ids && env->motion_id_fail_rates && scratch,
+                 "fail_rate_ema: done/fail-rate buffers not set");
+    PARC_REQUIRE(cdf == nullptr || env->motion_weights, "fail_rate_ema: motion_weights not set");
+    fail_rate_ema_kernel<<<1, EMA_THREADS, 0, as_stream(stream)>>>(*cfg, *env, num_motions, cdf, scratch);
+    return check_launch("fail_rate_ema");
+}
+
+static int check_reset_views(const parc_env_buffers_t* env, const char* who) {
+    PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_root_vel.ptr && env->char_root_ang_vel.ptr &&
+                     env->char_dof_pos.ptr && env->char_dof_vel.ptr && env->ref_root_pos.ptr && env->ref_root_rot.ptr &&
+                     env->ref_root_vel.ptr && env->ref_root_ang_vel.ptr && env->ref_joint_rot.ptr && env->ref_dof_pos.ptr &&
+                     env->ref_dof_vel.ptr,
+                 "%s: state views not set", who);
+    PARC_REQUIRE(env->motion_ids && env->motion_terrain_ids && env->motion_time_offsets && env->timestep_buf && env->time_buf &&
+                     env->done_buf && env->env_offsets && env->dm_motion_offsets,
+                 "%s: bookkeeping buffers not set", who);
+    return PARC_OK;
+}
+
+extern "C" int parc_b200_env_reset(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_env_config_t* cfg,
+                                   const parc_env_buffers_t* env, const int64_t* env_ids, int64_t n, const int64_t* motion_ids,
+                                   const int64_t* terrain_ids, const float* motion_times, const float* xy_noise,
+                                   const float* root_pos_offset, const float* root_rot_offset, void* stream) {
+    if (!model_ok(m, "env_reset")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(lib && lib->interp && cfg && env, "env_reset: NULL descriptor");
+    PARC_REQUIRE(n >= 0, "env_reset: n < 0");
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(env_ids && motion_ids && terrain_ids && motion_times, "env_reset: NULL draw arrays");
+    int rc = check_reset_views(env, "env_reset");
+    if (rc) return rc;
+    G_DISPATCH(env_reset_kernel, n, *m, *lib, *cfg, *env, (const long long*)env_ids, n, (const long long*)motion_ids,
+               (const long long*)terrain_ids, motion_times, xy_noise, root_pos_offset, root_rot_offset);
+    return check_launch("env_reset");
+}
+
+extern "C" int parc_b200_env_reset_sampled(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
+                                           const parc_env_config_t* cfg, const parc_env_buffers_t* env, const float* cdf,
+                                           int32_t num_motions, uint64_t seed, uint64_t step, int32_t rand_reset, void* stream) {
+    if (!model_ok(m, "env_reset_sampled")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(lib && lib->interp && cfg && env && terrain && cdf && num_motions > 0, "env_reset_sampled: NULL descriptor");
+    PARC_REQUIRE(env->done_count && env->done_list, "env_reset_sampled: done list not set");
+    int rc = check_reset_views(env, "env_reset_sampled");
+    if (rc) return rc;
+    if (env->num_envs == 0) return PARC_OK;
+    // sized for the worst case (every env finished); groups beyond the device-side count exit at once
+    G_DISPATCH(env_reset_sampled_kernel, env->num_envs, *m, *lib, *cfg, *env, cdf, num_motions, (unsigned long long)seed,
+               (unsigned long long)step, rand_reset);
+    rc = check_launch("env_reset_sampled(reset)");
+    if (rc) return rc;
+    // IGParkourEnv.reset (ig_parkour_env.py:809-829): heights + observation of the reset envs
+    if (env->obs_buf) {
+        rc = launch_env_step(m, lib, terrain, cfg, env, PARC_STEP_HEIGHTS | PARC_STEP_OBS, nullptr, env->num_envs, env->done_list,
+                             env->done_count, stream);
+        if (rc) return rc;
+    }
+    zero_int_kernel<<<1, 1, 0, as_stream(stream)>>>(env->done_count);
+    return check_launch("env_reset_sampled(clear)");
+}
+
+extern "C" int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n, int64_t* ids, void* stream) {
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(cdf && u && ids && num_motions > 0, "sample_motions_cdf: bad arguments");
+    sample_cdf_kernel<<<blocks_for(n, 256), 256, 0, as_stream(stream)>>>(cdf, num_motions, u, n, (long long*)ids);
+    return check_launch("sample_motions_cdf");
+}

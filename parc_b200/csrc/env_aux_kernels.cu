@@ -1,0 +1,524 @@
+// Stand-alone forms of the reference's per-call functions (same inputs/outputs as the Python
+// methods they replace) and the reset / fail-rate kernels. The fused step lives in env_kernels.cu.
+#include "parc_common.cuh"
+#include "parc_lanes.cuh"
+
+namespace parc {
+
+static int blocks_for(long long items, int per_block) {
+    long long b = (items + per_block - 1) / per_block;
+    const long long cap = (long long)kNumSMs * 32;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+// ---- DeepMimicEnv.compute_tar_obs (dm_env.py:594-626) + fetch_tar_obs_data (mgdm_dm_util.py:221-244)
+// One group of G lanes per (env, target step) sample, env-major like the reference's flatten.
+template <int G>
+__global__ void __launch_bounds__(256) tar_obs_data_kernel(
+    const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
+    const __grid_constant__ parc_env_config_t cfg, const __grid_constant__ parc_env_buffers_t env,
+    const long long* __restrict__ env_ids, long long n, float* __restrict__ tar_root_pos, float* __restrict__ tar_root_rot,
+    float* __restrict__ tar_joint_rot, float* __restrict__ tar_key_pos, float* __restrict__ tar_contacts) {
+    const LaneBody lb = load_lane_body<G>(cm);
+    const int J = cm.num_bodies, C = lib.num_contacts, S = cfg.num_tar_steps, K = cfg.num_key_bodies;
+    const int sub = threadIdx.x & (G - 1);
+    const long long gpb = blockDim.x / G;
+    const long long total = n * S;
+    const long long g0 = (long long)blockIdx.x * gpb + threadIdx.x / G;
+    const long long warp_first = g0 - ((threadIdx.x & 31) / G);
+    for (long long base = warp_first; base < total; base += (long long)gridDim.x * gpb) {
+        const long long i = base + ((threadIdx.x & 31) / G);
+        const bool live = i < total;
+        const long long ii = live ? i : 0;
+        const long long r = ii / S;
+        const int s = (int)(ii - r * S);
+        const long long e = env_ids ? env_ids[r] : r;
+        const long long mid = env.motion_ids[e];
+        const MotionMeta mm = load_motion_meta(lib.meta, mid);
+        const float t0 = __fadd_rn(env.time_buf[e], env.motion_time_offsets[e]);
+        const float t = __fadd_rn(t0, cfg.tar_dt[s]);
+        const FrameBlend fb = calc_frame_blend(mm, t);
+        const PoseSample ps = eval_pose_lane(lib, lb, fb, J);
+        const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + env.motion_terrain_ids[e]) * 2;
+        const float tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3));
+        const float toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
+        const Vec3 rpos = make_vec3(ps.root_pos.x + tox, ps.root_pos.y + toy, ps.root_pos.z);
+        const Quat rrot = group_bcast<G>(ps.q, 0);
+        Vec3 bpos; Quat brot;
+        fk_lanes<G>(lb, ps.q, rpos, rrot, bpos, brot);
+        if (!live) continue;
+        if (sub == 0) {
+            tar_root_pos[ii * 3] = rpos.x; tar_root_pos[ii * 3 + 1] = rpos.y; tar_root_pos[ii * 3 + 2] = rpos.z;
+            reinterpret_cast<float4*>(tar_root_rot)[ii] = quat_to_f4(ps.q);
+        } else if (lb.active) {
+            reinterpret_cast<float4*>(tar_joint_rot)[ii * (J - 1) + sub - 1] = quat_to_f4(ps.q);
+        }
+        if (lb.active && tar_key_pos)
+            for (int k = 0; k < K; ++k)
+                if (cfg.key_body_ids[k] == lb.body) {
+                    float* o = tar_key_pos + (ii * K + k) * 3;
+                    o[0] = bpos.x; o[1] = bpos.y; o[2] = bpos.z;
+                }
+        if (tar_contacts && sub < C) tar_contacts[ii * C + sub] = ps.contact;
+    }
+}
+
+// ---- compute_char_obs (ig_char_env.py:581-625): one group per env --------------------------------
+template <int G>
+__global__ void __launch_bounds__(256) char_obs_kernel(const __grid_constant__ parc_char_model_t cm,
+                                                       const float* __restrict__ root_pos, const float* __restrict__ root_rot,
+                                                       const float* __restrict__ root_vel, const float* __restrict__ root_ang_vel,
+                                                       const float* __restrict__ joint_rot, const float* __restrict__ dof_vel,
+                                                       const float* __restrict__ key_pos, int K, int global_obs, int root_h,
+                                                       long long n, float* __restrict__ obs) {
+    const int J = cm.num_bodies, D = cm.dof_size;
+    const int sub = threadIdx.x & (G - 1);
+    const int dim = root_h + 12 + 6 * (J - 1) + D + 3 * K;
+    const long long gpb = blockDim.x / G;
+    for (long long i = (long long)blockIdx.x * gpb + threadIdx.x / G; i < n; i += (long long)gridDim.x * gpb) {
+        const Quat rr = quat_from_f4(__ldg(reinterpret_cast<const float4*>(root_rot) + i));
+        const Vec3 rp = make_vec3(root_pos[i * 3], root_pos[i * 3 + 1], root_pos[i * 3 + 2]);
+        const Quat hinv = calc_heading_quat_inv(rr);
+        float* o = obs + i * dim + root_h;
+        if (sub == 0) {
+            if (root_h) obs[i * dim] = rp.z;
+            float tn[6];
+            quat_to_tan_norm(global_obs ? rr : quat_mul(hinv, rr), tn);
+            for (int k = 0; k < 6; ++k) o[k] = tn[k];
+            Vec3 v = make_vec3(root_vel[i * 3], root_vel[i * 3 + 1], root_vel[i * 3 + 2]);
+            Vec3 w = make_vec3(root_ang_vel[i * 3], root_ang_vel[i * 3 + 1], root_ang_vel[i * 3 + 2]);
+            if (!global_obs) { v = quat_rotate(hinv, v); w = quat_rotate(hinv, w); }
+            o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
+        } else if (sub < J) {
+            float tn[6];
+            quat_to_tan_norm(quat_from_f4(__ldg(reinterpret_cast<const float4*>(joint_rot) + i * (J - 1) + sub - 1)), tn);
+            for (int k = 0; k < 6; ++k) o[12 + 6 * (sub - 1) + k] = tn[k];
+        }
+        for (int k = sub; k < D; k += G) o[12 + 6 * (J - 1) + k] = dof_vel[i * D + k];
+        for (int k = sub; k < K; k += G) {
+            Vec3 kp = make_vec3(key_pos[(i * K + k) * 3] - rp.x, key_pos[(i * K + k) * 3 + 1] - rp.y, key_pos[(i * K + k) * 3 + 2] - rp.z);
+            if (!global_obs) kp = quat_rotate(hinv, kp);
+            float* kd = o + 12 + 6 * (J - 1) + D + 3 * k;
+            kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+        }
+    }
+}
+
+// ---- compute_tar_obs (mgdm_dm_util.py:404-461): one group per (env, step) -------------------------
+template <int G>
+__global__ void __launch_bounds__(256) tar_obs_kernel(const __grid_constant__ parc_char_model_t cm,
+                                                      const float* __restrict__ ref_root_pos, const float* __restrict__ ref_root_rot,
+                                                      const float* __restrict__ tar_root_pos, const float* __restrict__ tar_root_rot,
+                                                      const float* __restrict__ tar_joint_rot, const float* __restrict__ tar_key_pos,
+                                                      int S, int K, int global_obs, int global_h, long long n, float* __restrict__ obs) {
+    const int J = cm.num_bodies;
+    const int sub = threadIdx.x & (G - 1);
+    const int dim = 9 + 6 * (J - 1) + 3 * K;
+    const long long gpb = blockDim.x / G;
+    const long long total = n * S;
+    for (long long i = (long long)blockIdx.x * gpb + threadIdx.x / G; i < total; i += (long long)gridDim.x * gpb) {
+        const long long r = i / S;
+        const Quat rr = quat_from_f4(__ldg(reinterpret_cast<const float4*>(ref_root_rot) + r));
+        const Quat hinv = calc_heading_quat_inv(rr);
+        const Vec3 trp = make_vec3(tar_root_pos[i * 3], tar_root_pos[i * 3 + 1], tar_root_pos[i * 3 + 2]);
+        Vec3 rp_obs = make_vec3(trp.x - ref_root_pos[r * 3], trp.y - ref_root_pos[r * 3 + 1], trp.z - ref_root_pos[r * 3 + 2]);
+        if (!global_obs) rp_obs = quat_rotate(hinv, rp_obs);
+        float* o = obs + i * dim;
+        if (sub == 0) {
+            o[0] = rp_obs.x; o[1] = rp_obs.y; o[2] = global_h ? trp.z : rp_obs.z;
+            Quat q = quat_from_f4(__ldg(reinterpret_cast<const float4*>(tar_root_rot) + i));
+            if (!global_obs) q = quat_mul(hinv, q);
+            float tn[6];
+            quat_to_tan_norm(q, tn);
+            for (int k = 0; k < 6; ++k) o[3 + k] = tn[k];
+        } else if (sub < J) {
+            float tn[6];
+            quat_to_tan_norm(quat_from_f4(__ldg(reinterpret_cast<const float4*>(tar_joint_rot) + i * (J - 1) + sub - 1)), tn);
+            for (int k = 0; k < 6; ++k) o[9 + 6 * (sub - 1) + k] = tn[k];
+        }
+        for (int k = sub; k < K; k += G) {
+            Vec3 kp = make_vec3(tar_key_pos[(i * K + k) * 3] - trp.x, tar_key_pos[(i * K + k) * 3 + 1] - trp.y, tar_key_pos[(i * K + k) * 3 + 2] - trp.z);
+            // the key offsets use root_pos_obs BEFORE the optional global-height overwrite (:437-446)
+            if (!global_obs) kp = quat_rotate(hinv, kp) + rp_obs;
+            float* kd = o + 9 + 6 * (J - 1) + 3 * k;
+            kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+        }
+    }
+}
+
+// ---- compute_deepmimic_reward (mgdm_dm_util.py:269-332): one warp per env --------------------------
+__global__ void __launch_bounds__(256) dm_reward_kernel(int J, int D, int K, const float* __restrict__ root_pos,
+                                                        const float* __restrict__ root_rot, const float* __restrict__ root_vel,
+                                                        const float* __restrict__ root_ang_vel, const float* __restrict__ joint_rot,
+                                                        const float* __restrict__ dof_vel, const float* __restrict__ key_pos,
+                                                        const float* __restrict__ t_root_pos, const float* __restrict__ t_root_rot,
+                                                        const float* __restrict__ t_root_vel, const float* __restrict__ t_root_ang_vel,
+                                                        const float* __restrict__ t_joint_rot, const float* __restrict__ t_dof_vel,
+                                                        const float* __restrict__ t_key_pos, const float* __restrict__ jw,
+                                                        const float* __restrict__ dw, int track_root_h, int track_root, long long n,
+                                                        float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long wpb = blockDim.x / 32;
+    for (long long i = (long long)blockIdx.x * wpb + threadIdx.x / 32; i < n; i += (long long)gridDim.x * wpb) {
+        float pose_t = 0.f, vel_t = 0.f, key_t = 0.f;
+        for (int j = lane; j < J - 1; j += 32) {
+            const Quat a = quat_from_f4(__ldg(reinterpret_cast<const float4*>(joint_rot) + i * (J - 1) + j));
+            const Quat b = quat_from_f4(__ldg(reinterpret_cast<const float4*>(t_joint_rot) + i * (J - 1) + j));
+            const float ang = quat_diff_angle(a, b);
+            pose_t += jw[j] * ang * ang;
+        }
+        for (int k = lane; k < D; k += 32) {
+            const float d = t_dof_vel[i * D + k] - dof_vel[i * D + k];
+            vel_t += dw[k] * d * d;
+        }
+        const Vec3 rp = make_vec3(root_pos[i * 3], root_pos[i * 3 + 1], root_pos[i * 3 + 2]);
+        const Vec3 trp = make_vec3(t_root_pos[i * 3], t_root_pos[i * 3 + 1], t_root_pos[i * 3 + 2]);
+        Quat a_rot = quat_from_f4(__ldg(reinterpret_cast<const float4*>(root_rot) + i));
+        Quat b_rot = quat_from_f4(__ldg(reinterpret_cast<const float4*>(t_root_rot) + i));
+        const Quat ha = calc_heading_quat_inv(a_rot), hb = calc_heading_quat_inv(b_rot);
+        for (int k = lane; k < K; k += 32) {
+            Vec3 kp = make_vec3(key_pos[(i * K + k) * 3] - rp.x, key_pos[(i * K + k) * 3 + 1] - rp.y, key_pos[(i * K + k) * 3 + 2] - rp.z);
+            Vec3 tk = make_vec3(t_key_pos[(i * K + k) * 3] - trp.x, t_key_pos[(i * K + k) * 3 + 1] - trp.y, t_key_pos[(i * K + k) * 3 + 2] - trp.z);
+            if (!track_root) { kp = quat_rotate(ha, kp); tk = quat_rotate(hb, tk); }
+            const Vec3 d = tk - kp;
+            key_t += d.x * d.x + d.y * d.y + d.z * d.z;
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            pose_t += __shfl_xor_sync(FULL_MASK, pose_t, o);
+            vel_t += __shfl_xor_sync(FULL_MASK, vel_t, o);
+            key_t += __shfl_xor_sync(FULL_MASK, key_t, o);
+        }
+        if (lane == 0) {
+            Vec3 rpd = trp - rp;
+            if (!track_root) { rpd.x = 0.f; rpd.y = 0.f; }
+            if (!track_root_h) rpd.z = 0.f;
+            const float root_pos_err = rpd.x * rpd.x + rpd.y * rpd.y + rpd.z * rpd.z;
+            Vec3 av = make_vec3(root_vel[i * 3], root_vel[i * 3 + 1], root_vel[i * 3 + 2]);
+            Vec3 bv = make_vec3(t_root_vel[i * 3], t_root_vel[i * 3 + 1], t_root_vel[i * 3 + 2]);
+            Vec3 aw = make_vec3(root_ang_vel[i * 3], root_ang_vel[i * 3 + 1], root_ang_vel[i * 3 + 2]);
+            Vec3 bw = make_vec3(t_root_ang_vel[i * 3], t_root_ang_vel[i * 3 + 1], t_root_ang_vel[i * 3 + 2]);
+            if (!track_root) {
+                av = quat_rotate(ha, av); aw = quat_rotate(ha, aw); bv = quat_rotate(hb, bv); bw = quat_rotate(hb, bw);
+                a_rot = quat_mul(ha, a_rot); b_rot = quat_mul(hb, b_rot);
+            }
+            const float rra = quat_diff_angle(a_rot, b_rot);
+            const Vec3 dv = bv - av, dwv = bw - aw;
+            const float rve = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
+            const float rae = dwv.x * dwv.x + dwv.y * dwv.y + dwv.z * dwv.z;
+            float* o = out + i * 5;
+            o[0] = expf(-0.25f * pose_t);
+            o[1] = expf(-0.01f * vel_t);
+            o[2] = expf(-5.0f * (root_pos_err + 0.1f * rra * rra));
+            o[3] = expf(-1.0f * (rve + 0.1f * rae));
+            o[4] = expf(-10.0f * key_t);
+        }
+    }
+}
+
+// ---- compute_contact_reward (mgdm_dm_util.py:497-518) ------------------------------------------------
+__global__ void contact_reward_kernel(const float* __restrict__ tar, const float* __restrict__ f, const float* __restrict__ w, int C,
+                                      long long n, float* __restrict__ out) {
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n * C; k += (long long)gridDim.x * blockDim.x) {
+        const float fx = f[k * 3], fy = f[k * 3 + 1], fz = f[k * 3 + 2];
+        const float m = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
+        const float c = tar[k];
+        float r = -(1.0f - c) * m;
+        r += c * m;
+        out[k] = w[k % C] * r;
+    }
+}
+
+// ---- compute_done (mgdm_dm_util.py:334-402): one warp per env, lanes over bodies ---------------------
+__global__ void __launch_bounds__(256) compute_done_kernel(const float* __restrict__ time, float ep_len, const float* __restrict__ root_rot,
+                                                           const float* __restrict__ body_pos, const float* __restrict__ tar_root_rot,
+                                                           const float* __restrict__ tar_body_pos, const float* __restrict__ contact_force,
+                                                           const long long* __restrict__ cb_ids, int n_cb, const float* __restrict__ term_h,
+                                                           int pose_termination, const float* __restrict__ pose_dist, int early, int track_root,
+                                                           float root_pos_dist_sq, float root_rot_angle, int J, long long n, int* __restrict__ done_out) {
+    const int lane = threadIdx.x & 31;
+    const long long wpb = blockDim.x / 32;
+    for (long long i = (long long)blockIdx.x * wpb + threadIdx.x / 32; i < n; i += (long long)gridDim.x * wpb) {
+        int done = PARC_DONE_NULL;
+        const float t = time[i];
+        if (t >= ep_len) done = PARC_DONE_TIME;
+        if (early) {
+            bool failed = false;
+            if (n_cb > 0) {
+                bool fc = false, fh = false;
+                for (int b = lane; b < J; b += 32) {
+                    bool is_cb = false;
+                    for (int k = 0; k < n_cb; ++k) is_cb = is_cb || (cb_ids[k] == b);
+                    if (is_cb) continue;
+                    const float* f = contact_force + (i * J + b) * 3;
+                    fc = fc || fabsf(f[0]) > 0.1f || fabsf(f[1]) > 0.1f || fabsf(f[2]) > 0.1f;
+                    fh = fh || (body_pos[(i * J + b) * 3 + 2] < term_h[i * J + b]);
+                }
+                failed = __any_sync(FULL_MASK, fc) && __any_sync(FULL_MASK, fh);
+            }
+            if (pose_termination) {
+                bool pf = false;
+                const float* b0 = body_pos + i * J * 3;
+                const float* t0 = tar_body_pos + i * J * 3;
+                for (int b = lane + 1; b < J; b += 32) {
+                    const Vec3 a = make_vec3(__fsub_rn(b0[b * 3], b0[0]), __fsub_rn(b0[b * 3 + 1], b0[1]), __fsub_rn(b0[b * 3 + 2], b0[2]));
+                    const Vec3 c = make_vec3(__fsub_rn(t0[b * 3], t0[0]), __fsub_rn(t0[b * 3 + 1], t0[1]), __fsub_rn(t0[b * 3 + 2], t0[2]));
+                    const Vec3 d = make_vec3(__fsub_rn(c.x, a.x), __fsub_rn(c.y, a.y), __fsub_rn(c.z, a.z));
+                    const float td = pose_dist[b - 1];
+                    pf = pf || (sqnorm3_seq(d) > __fmul_rn(td, td));
+                }
+                pf = __any_sync(FULL_MASK, pf);
+                if (track_root) {
+                    const Vec3 d = make_vec3(__fsub_rn(b0[0], t0[0]), __fsub_rn(b0[1], t0[1]), __fsub_rn(b0[2], t0[2]));
+                    pf = pf || (sqnorm3_seq(d) > root_pos_dist_sq);
+                    const Quat a = quat_from_f4(__ldg(reinterpret_cast<const float4*>(root_rot) + i));
+                    const Quat b = quat_from_f4(__ldg(reinterpret_cast<const float4*>(tar_root_rot) + i));
+                    pf = pf || (fabsf(quat_diff_angle(a, b)) > root_rot_angle);
+                }
+                failed = failed || pf;
+            }
+            failed = failed && (t > 1e-5f);
+            if (failed) done = PARC_DONE_FAIL;
+        }
+        if (lane == 0) done_out[i] = done;
+    }
+}
+
+}  // namespace parc
+
+namespace parc {
+
+// ---- DeepMimicEnv.reset (dm_env.py:567-592) --------------------------------------------------------
+// Shared by the explicit-draw entry point and the device-sampled one: one group of G lanes per
+// reset env writes the ids, evaluates the clip at the start time and copies ref -> char state.
+template <int G>
+__device__ __forceinline__ void reset_one_env(const parc_char_model_t& cm, const parc_motion_lib_t& lib, const parc_env_config_t& cfg,
+                                              const parc_env_buffers_t& env, const LaneBody& lb, long long e, long long mid, long long tid,
+                                              float mtime, float nx, float ny, const float* root_pos_offset, const float* root_rot_offset) {
+    const int J = cm.num_bodies, D = cm.dof_size, C = lib.num_contacts;
+    const int sub = threadIdx.x & (G - 1);
+    const MotionMeta mm = load_motion_meta(lib.meta, mid);
+    const FrameBlend fb = calc_frame_blend(mm, mtime);
+    const PoseSample ps = eval_pose_lane(lib, lb, fb, J);
+    // _move_to_motion_terrain (dm_env.py:554-565)
+    const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tid) * 2;
+    const float tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3));
+    const float toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
+    const Vec3 rpos = make_vec3(ps.root_pos.x + tox, ps.root_pos.y + toy, ps.root_pos.z);
+    if (sub == 0) {
+        env.motion_ids[e] = mid;                                   // _reset_ref_motion, dm_env.py:504-506
+        env.motion_terrain_ids[e] = tid;
+        env.motion_time_offsets[e] = mtime;
+        view_st_vec3(env.ref_root_pos, e, rpos);
+        view_st_quat(env.ref_root_rot, e, ps.q);
+        // _char_state_init_from_ref (mgdm_dm_util.py:89-100) + add_noise_to_char_state (:102-106)
+        Vec3 cp = rpos;
+        cp.x += cfg.rand_root_pos_offset_scale * nx;
+        cp.y += cfg.rand_root_pos_offset_scale * ny;
+        Quat cr = ps.q;
+        if (root_pos_offset) { cp.x += root_pos_offset[e * 3]; cp.y += root_pos_offset[e * 3 + 1]; cp.z += root_pos_offset[e * 3 + 2]; }
+        if (root_rot_offset) cr = quat_multiply(quat_from_f4(reinterpret_cast<const float4*>(root_rot_offset)[e]), cr);   // :112-113
+        view_st_vec3(env.char_root_pos, e, cp);
+        view_st_quat(env.char_root_rot, e, cr);
+        env.timestep_buf[e] = 0;                                   // dm_env.py:586-590
+        env.time_buf[e] = 0.f;
+        env.done_buf[e] = PARC_DONE_NULL;
+        if (env.actors_need_reset) env.actors_need_reset[e * env.actors_per_env] = 1;
+    } else if (lb.active) {
+        float* jr = env.ref_joint_rot.ptr + e * env.ref_joint_rot.row_stride + (sub - 1) * env.ref_joint_rot.mid_stride;
+        const long long es = env.ref_joint_rot.elem_stride;
+        jr[0] = ps.q.x; jr[es] = ps.q.y; jr[2 * es] = ps.q.z; jr[3 * es] = ps.q.w;
+        float dd[3];
+        const int nd = rot_to_dof_lane(lb, ps.q, dd);
+        for (int k = 0; k < nd; ++k) {
+            view_st(env.ref_dof_pos, e, lb.dof_idx + k, dd[k]);
+            view_st(env.char_dof_pos, e, lb.dof_idx + k, dd[k]);
+        }
+    }
+    if (sub < C && env.ref_contacts.ptr) view_st(env.ref_contacts, e, sub, ps.contact);
+    const float* v = lib.vel + fb.idx0 * lib.vrec;
+    for (int k = sub; k < 6 + D; k += G) {
+        const float x = __ldg(v + k);
+        if (k < 3) { view_st(env.ref_root_vel, e, k, x); view_st(env.char_root_vel, e, k, x); }
+        else if (k < 6) { view_st(env.ref_root_ang_vel, e, k - 3, x); view_st(env.char_root_ang_vel, e, k - 3, x); }
+        else { view_st(env.ref_dof_vel, e, k - 6, x); view_st(env.char_dof_vel, e, k - 6, x); }
+    }
+    if (lb.active) {
+        for (int k = 0; k < 3; ++k) {
+            if (env.char_rigid_body_vel.ptr) view_st3(env.char_rigid_body_vel, e, sub, k, 0.f);
+            if (env.char_rigid_body_ang_vel.ptr) view_st3(env.char_rigid_body_ang_vel, e, sub, k, 0.f);
+        }
+    }
+}
+
+template <int G>
+__global__ void __launch_bounds__(256) env_reset_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
+                                                        const __grid_constant__ parc_env_config_t cfg, const __grid_constant__ parc_env_buffers_t env,
+                                                        const long long* __restrict__ env_ids, long long n, const long long* __restrict__ motion_ids,
+                                                        const long long* __restrict__ terrain_ids, const float* __restrict__ motion_times,
+                                                        const float* __restrict__ xy_noise, const float* __restrict__ root_pos_offset,
+                                                        const float* __restrict__ root_rot_offset) {
+    const LaneBody lb = load_lane_body<G>(cm);
+    const long long gpb = blockDim.x / G;
+    for (long long i = (long long)blockIdx.x * gpb + threadIdx.x / G; i < n; i += (long long)gridDim.x * gpb) {
+        const float nx = xy_noise ? xy_noise[i * 2] : 0.f, ny = xy_noise ? xy_noise[i * 2 + 1] : 0.f;
+        reset_one_env<G>(cm, lib, cfg, env, lb, env_ids[i], motion_ids[i], terrain_ids[i], motion_times[i], nx, ny, root_pos_offset, root_rot_offset);
+    }
+}
+
+// ---- device-side RSI draws: Philox4x32-10 keyed by (seed, env id, step) -----------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+    const unsigned M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+        const unsigned hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += W0; key.y += W1;
+    }
+    return ctr;
+}
+__device__ __forceinline__ float u01(unsigned x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+// first m with cdf[m] > u * cdf[M-1]  (inverse-CDF form of a weighted draw with replacement)
+__device__ __forceinline__ int sample_cdf(const float* __restrict__ cdf, int M, float u) {
+    const float target = u * __ldg(cdf + M - 1);
+    int lo = 0, hi = M - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(cdf + mid) > target) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+template <int G>
+__global__ void __launch_bounds__(256) env_reset_sampled_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
+                                                                const __grid_constant__ parc_env_config_t cfg, const __grid_constant__ parc_env_buffers_t env,
+                                                                const float* __restrict__ cdf, int M, unsigned long long seed, unsigned long long step, int rand_reset) {
+    const LaneBody lb = load_lane_body<G>(cm);
+    const long long gpb = blockDim.x / G;
+    const long long n = *env.done_count;
+    for (long long i = (long long)blockIdx.x * gpb + threadIdx.x / G; i < n; i += (long long)gridDim.x * gpb) {
+        const long long e = env.done_list[i];
+        if (env.done_buf[e] == PARC_DONE_NULL) continue;   // never_done: counted for the EMA, not reset
+        const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
+        const uint4 r0 = philox4x32_10(make_uint4((unsigned)e, (unsigned)(e >> 32), (unsigned)step, (unsigned)(step >> 32)), key);
+        const long long mid = sample_cdf(cdf, M, u01(r0.x));                                       // sample_motions, motion_lib.py:56-60
+        const long long tid = (long long)(r0.y % (unsigned)env.terrains_per_motion);               // randint, dm_env.py:496
+        const float len = __int_as_float(__ldg(lib.meta + 8 * mid + 2));
+        const float mtime = rand_reset ? u01(r0.z) * len : 0.f;                                    // sample_time, motion_lib.py:62-71
+        const uint4 r1 = philox4x32_10(make_uint4((unsigned)e, (unsigned)(e >> 32), (unsigned)step, (unsigned)(step >> 32) ^ 0x80000000u), key);
+        const float nx = u01(r1.x) * 2.0f - 1.0f, ny = u01(r1.y) * 2.0f - 1.0f;                    // mgdm_dm_util.py:103
+        reset_one_env<G>(cm, lib, cfg, env, lb, e, mid, tid, mtime, nx, ny, nullptr, nullptr);
+    }
+}
+
+__global__ void sample_cdf_kernel(const float* __restrict__ cdf, int M, const float* __restrict__ u, long long n, long long* __restrict__ ids) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        ids[i] = sample_cdf(cdf, M, u[i]);
+}
+
+}  // namespace parc
+
+namespace parc {
+
+// ---- fail-rate EMA (dm_env.py:648-660) --------------------------------------------------------------
+// The reference walks the finished envs on the host IN ENV-ID ORDER and applies, per motion,
+//   rate <- rate*(1-w) + w   (FAIL)      or      rate <- rate*(1-w)   (TIME / SUCC / motion end)
+// as separately rounded fp32 operations. Order matters (w^2 = 1e-4 between a fail-then-pass and a
+// pass-then-fail), so the updates of one motion are applied sequentially in ascending env id by
+// one thread; different motions proceed in parallel. One block:
+//   histogram per motion -> exclusive scan -> bucket scatter -> per-motion sort + apply -> RSI CDF.
+constexpr int EMA_THREADS = 1024;
+
+__device__ void block_exclusive_scan_int(const int* __restrict__ in, int* __restrict__ out, int M, int* smem_partials) {
+    const int t = threadIdx.x, T = blockDim.x;
+    const int chunk = (M + T - 1) / T;
+    const int b = min(t * chunk, M), e = min(b + chunk, M);
+    int s = 0;
+    for (int k = b; k < e; ++k) s += in[k];
+    smem_partials[t] = s;
+    __syncthreads();
+    if (t == 0) {
+        int run = 0;
+        for (int k = 0; k < T; ++k) { const int v = smem_partials[k]; smem_partials[k] = run; run += v; }
+    }
+    __syncthreads();
+    int run = smem_partials[t];
+    for (int k = b; k < e; ++k) { const int v = in[k]; out[k] = run; run += v; }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid_constant__ parc_env_config_t cfg,
+                                                                    const __grid_constant__ parc_env_buffers_t env, int M,
+                                                                    float* __restrict__ cdf, int* __restrict__ scratch) {
+    __shared__ int partial_i[EMA_THREADS];
+    __shared__ float partial_f[EMA_THREADS];
+    const int t = threadIdx.x, T = blockDim.x;
+    const int n = *env.done_count;
+    int* hist = scratch;            // [M]
+    int* offs = scratch + M;        // [M]
+    int* bucket = scratch + 2 * M;  // [n]
+    if (n > 0) {
+        for (int m = t; m < M; m += T) hist[m] = 0;
+        __syncthreads();
+        for (int i = t; i < n; i += T) atomicAdd(&hist[(int)env.motion_ids[env.done_list[i]]], 1);
+        __syncthreads();
+        block_exclusive_scan_int(hist, offs, M, partial_i);
+        for (int m = t; m < M; m += T) hist[m] = 0;   // reuse as per-motion cursor
+        __syncthreads();
+        for (int i = t; i < n; i += T) {
+            const int e = env.done_list[i];
+            const int m = (int)env.motion_ids[e];
+            bucket[offs[m] + atomicAdd(&hist[m], 1)] = e;
+        }
+        __syncthreads();
+        const float w = cfg.ema_weight;
+        const float keep = cfg.ema_keep;   // Python double (1.0 - 0.01) cast to fp32 when it meets the fp32 tensor
+        for (int m = t; m < M; m += T) {
+            const int cnt = hist[m];
+            if (cnt == 0) continue;
+            int* seg = bucket + offs[m];
+            for (int a = 1; a < cnt; ++a) {   // insertion sort by env id (segments are short)
+                const int v = seg[a];
+                int b = a - 1;
+                while (b >= 0 && seg[b] > v) { seg[b + 1] = seg[b]; --b; }
+                seg[b + 1] = v;
+            }
+            float r = env.motion_id_fail_rates[m];
+            for (int a = 0; a < cnt; ++a) {
+                const unsigned char code = env.done_code[seg[a]];
+                r = __fmul_rn(r, keep);
+                if (code == 1) r = __fadd_rn(r, w);
+            }
+            env.motion_id_fail_rates[m] = r;
+        }
+        __syncthreads();
+    }
+    // RSI sampling CDF (dm_env.py:487-490): clamp(fail_rate, min_motion_weight) * motion_weight
+    if (cdf) {
+        const int chunk = (M + T - 1) / T;
+        const int b = min(t * chunk, M), e = min(b + chunk, M);
+        float s = 0.f;
+        for (int k = b; k < e; ++k) s += fmaxf(env.motion_id_fail_rates[k], cfg.min_motion_weight) * env.motion_weights[k];
+        partial_f[t] = s;
+        __syncthreads();
+        if (t == 0) {
+            float run = 0.f;
+            for (int k = 0; k < T; ++k) { const float v = partial_f[k]; partial_f[k] = run; run += v; }
+        }
+        __syncthreads();
+        float run = partial_f[t];
+        for (int k = b; k < e; ++k) {
+            run += fmaxf(env.motion_id_fail_rates[k], cfg.min_motion_weight) * env.motion_weights[k];
+            cdf[k] = run;
+        }
+    }
+}
+
+__global__ void zero_int_kernel(int* p) { *p = 0; }
+
+}  // namespace parc
+
+#include "env_aux_api.cuh"

@@ -1,0 +1,174 @@
+// Quaternion / exp-map / heading arithmetic for the PARC tracking hot path (sm_100a).
+// Quaternions are (x, y, z, w) everywhere, as in the reference (PARC/util/torch_util.py:46-47).
+//
+// Every function states the reference lines whose *arithmetic and branch thresholds* it follows.
+// Index- and flag-critical expressions use __fmul_rn/__fadd_rn/__fdiv_rn so nvcc cannot contract
+// them into FMAs or approximate divisions; the remaining fp32 math is allowed to contract
+// (tolerance 1e-5 relative, BASELINE.json north_star).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+namespace parc {
+
+struct Quat { float x, y, z, w; };
+struct Vec3 { float x, y, z; };
+
+__device__ __forceinline__ Quat make_quat(float x, float y, float z, float w) { Quat q; q.x = x; q.y = y; q.z = z; q.w = w; return q; }
+__device__ __forceinline__ Vec3 make_vec3(float x, float y, float z) { Vec3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ Quat quat_from_f4(float4 v) { return make_quat(v.x, v.y, v.z, v.w); }
+__device__ __forceinline__ float4 quat_to_f4(Quat q) { return make_float4(q.x, q.y, q.z, q.w); }
+__device__ __forceinline__ Quat quat_identity() { return make_quat(0.f, 0.f, 0.f, 1.f); }
+
+__device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return make_vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return make_vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { return make_vec3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ Vec3 cross(Vec3 a, Vec3 b) {
+    return make_vec3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+// torch.sum(a*b, dim=-1) over 3 / 4 trailing elements: separately rounded products added left to
+// right (measured against torch 2.11 CPU: ((p0+p1)+p2)+p3 is bit-identical, pairwise is not).
+__device__ __forceinline__ float dot3_seq(Vec3 a, Vec3 b) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z));
+}
+__device__ __forceinline__ float dot4_seq(Quat a, Quat b) {
+    return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z)),
+                     __fmul_rn(a.w, b.w));
+}
+__device__ __forceinline__ float sqnorm3_seq(Vec3 a) { return dot3_seq(a, a); }
+
+// quat_conjugate, torch_util.py:30-32
+__device__ __forceinline__ Quat quat_conj(Quat q) { return make_quat(-q.x, -q.y, -q.z, q.w); }
+
+// quat_pos, torch_util.py:34-39: q * (1 - 2*[w < 0])
+__device__ __forceinline__ Quat quat_pos(Quat q) {
+    float s = (q.w < 0.f) ? -1.f : 1.f;
+    return make_quat(s * q.x, s * q.y, s * q.z, s * q.w);
+}
+
+// quat_mul, torch_util.py:41-59 (Hamilton product a (x) b; the reference's 8-multiplication
+// factoring and this 16-FMA form agree to ~1 ulp of |a||b|).
+__device__ __forceinline__ Quat quat_mul(Quat a, Quat b) {
+    Quat r;
+    r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+    r.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+    r.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+    r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+    return r;
+}
+
+// quat_rotate, torch_util.py:61-67: t = 2 q_v x v; v + w t + q_v x t
+__device__ __forceinline__ Vec3 quat_rotate(Quat q, Vec3 v) {
+    Vec3 qv = make_vec3(q.x, q.y, q.z);
+    Vec3 t = 2.f * cross(qv, v);
+    return v + q.w * t + cross(qv, t);
+}
+
+// normalize, torch_util.py:10-13: x / max(||x||, 1e-9)
+__device__ __forceinline__ Vec3 normalize3(Vec3 v) {
+    float n = fmaxf(sqrtf(v.x * v.x + v.y * v.y + v.z * v.z), 1e-9f);
+    return make_vec3(v.x / n, v.y / n, v.z / n);
+}
+__device__ __forceinline__ Quat quat_unit(Quat q) {
+    float n = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-9f);
+    return make_quat(q.x / n, q.y / n, q.z / n, q.w / n);
+}
+// quat_normalize, torch_util.py:469-472: unit(pos(q))
+__device__ __forceinline__ Quat quat_normalize(Quat q) { return quat_unit(quat_pos(q)); }
+
+// quat_to_axis_angle, torch_util.py:69-91: eps 1e-5 on ||xyz||, safe length 1e-6, default axis z.
+__device__ __forceinline__ void quat_to_axis_angle(Quat q, Vec3& axis, float& angle) {
+    q = quat_pos(q);
+    float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
+    float a = 2.0f * atan2f(len, q.w);
+    float safe = fmaxf(len, 1e-6f);
+    bool mask = len > 1e-5f;
+    angle = mask ? a : 0.f;
+    axis = mask ? make_vec3(q.x / safe, q.y / safe, q.z / safe) : make_vec3(0.f, 0.f, 1.f);
+}
+
+// quat_to_exp_map, torch_util.py:371-376
+__device__ __forceinline__ Vec3 quat_to_exp_map(Quat q) {
+    Vec3 axis; float angle;
+    quat_to_axis_angle(q, axis, angle);
+    return angle * axis;
+}
+
+// normalize_angle, torch_util.py:5-8
+__device__ __forceinline__ float normalize_angle(float x) { return atan2f(sinf(x), cosf(x)); }
+
+// axis_angle_to_quat, torch_util.py:336-342: normalises the axis AND the resulting quaternion.
+__device__ __forceinline__ Quat axis_angle_to_quat(Vec3 axis, float angle) {
+    float s, c;
+    sincosf(angle * 0.5f, &s, &c);
+    Vec3 n = normalize3(axis);
+    return quat_unit(make_quat(n.x * s, n.y * s, n.z * s, c));
+}
+
+// exp_map_to_axis_angle + exp_map_to_quat, torch_util.py:425-450: min_theta 1e-5, default axis z.
+__device__ __forceinline__ Quat exp_map_to_quat(Vec3 e) {
+    float ang = sqrtf(e.x * e.x + e.y * e.y + e.z * e.z);
+    float nang = normalize_angle(ang);
+    bool mask = fabsf(nang) > 1e-5f;
+    Vec3 axis = mask ? make_vec3(e.x / ang, e.y / ang, e.z / ang) : make_vec3(0.f, 0.f, 1.f);
+    float angle = mask ? nang : 0.f;
+    return axis_angle_to_quat(axis, angle);
+}
+
+// quat_diff_angle, torch_util.py:453-462: angle of q1 (x) conj(q0)
+__device__ __forceinline__ float quat_diff_angle(Quat q0, Quat q1) {
+    Quat dq = quat_mul(q1, quat_conj(q0));
+    Vec3 axis; float angle;
+    quat_to_axis_angle(dq, axis, angle);
+    return angle;
+}
+
+// slerp, torch_util.py:474-499. Branches are taken on the SAME fp32 values as the reference
+// (dot product summed left to right, 1 - c*c unfused); the result is not re-normalised and the
+// |sin| < 0.001 fallback is the un-normalised midpoint, exactly as upstream.
+__device__ __forceinline__ Quat slerp(Quat q0, Quat q1, float t) {
+    float c = dot4_seq(q0, q1);
+    if (c < 0.f) q1 = make_quat(-q1.x, -q1.y, -q1.z, -q1.w);
+    c = fabsf(c);
+    float half_theta = acosf(c);
+    float s = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(c, c)));
+    float ra = sinf((1.f - t) * half_theta) / s;
+    float rb = sinf(t * half_theta) / s;
+    Quat r = make_quat(ra * q0.x + rb * q1.x, ra * q0.y + rb * q1.y, ra * q0.z + rb * q1.z, ra * q0.w + rb * q1.w);
+    if (fabsf(s) < 0.001f)
+        r = make_quat(0.5f * q0.x + 0.5f * q1.x, 0.5f * q0.y + 0.5f * q1.y, 0.5f * q0.z + 0.5f * q1.z, 0.5f * q0.w + 0.5f * q1.w);
+    if (c >= 1.f) r = q0;
+    return r;
+}
+
+// calc_heading, torch_util.py:501-510: atan2 of the rotated x axis.
+__device__ __forceinline__ float calc_heading(Quat q) {
+    Vec3 d = quat_rotate(q, make_vec3(1.f, 0.f, 0.f));
+    return atan2f(d.y, d.x);
+}
+// calc_heading_quat_inv, torch_util.py:522-530: axis_angle_to_quat(z, -heading)
+__device__ __forceinline__ Quat calc_heading_quat_inv(Quat q) {
+    return axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -calc_heading(q));
+}
+
+// quat_to_tan_norm, torch_util.py:392-404: [R x_hat, R z_hat]
+__device__ __forceinline__ void quat_to_tan_norm(Quat q, float out[6]) {
+    Vec3 t = quat_rotate(q, make_vec3(1.f, 0.f, 0.f));
+    Vec3 n = quat_rotate(q, make_vec3(0.f, 0.f, 1.f));
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = n.x; out[4] = n.y; out[5] = n.z;
+}
+
+// quat_multiply, torch_util.py:607-625 (Hamilton form used only for the reset rotation offset)
+__device__ __forceinline__ Quat quat_multiply(Quat a, Quat b) { return quat_mul(a, b); }
+
+// Nearest-cell index of SubTerrain.get_grid_index (PARC/util/terrain_util.py:143-152):
+// clamp(round_half_even((p - min) / d), 0, dim - 1); rintf is half-to-even like torch.round.
+__device__ __forceinline__ int grid_index(float p, float mn, float d, int dim) {
+    float u = rintf(__fdiv_rn(__fsub_rn(p, mn), d));
+    // (long) conversion of values beyond int range: clamp in float first (dims << 2^24)
+    u = fminf(fmaxf(u, 0.f), (float)(dim - 1));
+    return (int)u;
+}
+
+}  // namespace parc

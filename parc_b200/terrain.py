@@ -1,0 +1,126 @@
+"""SubTerrain -- heightfield container of the tracking env (reference: PARC/util/terrain_util.py:18-156).
+
+Holds `hf [X, Y]` fp32 (row-major, x-major), `min_point [2]`, `dxdy [2]`, `dims [2]` i64 exactly
+like the reference; the per-step lookups (`get_hf_val_from_points`, the ray-height observation)
+run in the CUDA kernels, which receive the grid through `cstruct()`.
+"""
+import copy
+
+import numpy as np
+import torch
+
+from . import _lib
+from .file_io import MSTerrainData
+
+
+class SubTerrain:
+    def __init__(self, terrain_name="terrain", x_dim=256, y_dim=256, dx=1.0, dy=1.0, min_x=-1.0, min_y=-1.0,
+                 device="cuda:0"):
+        self.terrain_name = terrain_name
+        self.hf = torch.zeros(size=(x_dim, y_dim), dtype=torch.float32, device=device)
+        self.dims = torch.tensor([x_dim, y_dim], dtype=torch.int64, device=device)
+        self.min_point = torch.tensor([min_x, min_y], dtype=torch.float32, device=device)
+        self.dxdy = torch.tensor([dx, dy], dtype=torch.float32, device=device)
+        self.hf_mask = torch.zeros(size=(x_dim, y_dim), dtype=torch.bool, device=device)
+        self.hf_maxmin = torch.zeros(size=(x_dim, y_dim, 2), dtype=torch.float32, device=device)
+        self.hf_maxmin[..., 0] = 1.0
+        self.hf_maxmin[..., 1] = -1.0
+
+    @classmethod
+    def from_ms_terrain_data(cls, terrain_data: MSTerrainData, device):
+        hf = terrain_data.hf
+        mp = terrain_data.min_point
+        inst = cls(x_dim=hf.shape[0], y_dim=hf.shape[1], dx=terrain_data.dx, dy=terrain_data.dx,
+                   min_x=float(mp[0]), min_y=float(mp[1]), device=device)
+        inst.hf = torch.as_tensor(hf).clone().to(dtype=torch.float32, device=device)
+        if terrain_data.hf_maxmin is not None:
+            inst.hf_maxmin = torch.as_tensor(terrain_data.hf_maxmin).to(dtype=torch.float32, device=device)
+        return inst
+
+    def to_ms_terrain_data(self):
+        return MSTerrainData(hf=self.hf.cpu().numpy(), hf_maxmin=self.hf_maxmin.cpu().numpy(),
+                             min_point=self.min_point.cpu().numpy(), dx=self.dxdy[0].item())
+
+    def set_device(self, device):
+        for name in ("hf", "dims", "min_point", "dxdy", "hf_mask", "hf_maxmin"):
+            setattr(self, name, getattr(self, name).to(device=device))
+
+    def torch_copy(self):
+        new = copy.copy(self)
+        for name in ("hf", "dims", "min_point", "dxdy", "hf_mask", "hf_maxmin"):
+            setattr(new, name, getattr(self, name).clone())
+        return new
+
+    def get_real_size(self):
+        return self.dims * self.dxdy
+
+    def get_max_point(self):
+        return self.min_point + self.get_real_size() - self.dxdy
+
+    def get_point(self, ij):
+        return self.min_point + ij * self.dxdy
+
+    def pad(self, padding_size, height=0.0):
+        """Reference: terrain_util.py:243-262 (host setup, once per clip)."""
+        p = padding_size
+        self.hf = torch.nn.functional.pad(self.hf, [p, p, p, p], value=height)
+        new_mask = torch.zeros((self.hf_mask.shape[0] + 2 * p, self.hf_mask.shape[1] + 2 * p), dtype=torch.bool,
+                               device=self.hf.device)
+        if p > 0:
+            new_mask[p:-p, p:-p] = self.hf_mask
+        else:
+            new_mask[:] = self.hf_mask
+        self.hf_mask = new_mask
+        max_val = torch.max(self.hf_maxmin[..., 0]).item()
+        min_val = torch.min(self.hf_maxmin[..., 1]).item()
+        hi = torch.nn.functional.pad(self.hf_maxmin[..., 0], [p, p, p, p], value=max_val)
+        lo = torch.nn.functional.pad(self.hf_maxmin[..., 1], [p, p, p, p], value=min_val)
+        self.hf_maxmin = torch.stack([hi, lo], dim=-1)
+        self.min_point = self.min_point - self.dxdy * p
+        self.dims = self.dims + 2 * p
+
+    # ---- C-ABI descriptor -------------------------------------------------------------------
+    def cstruct(self):
+        hf = self.hf
+        assert hf.dtype == torch.float32 and hf.is_contiguous(), "hf must be contiguous fp32"
+        t = _lib.TerrainStruct()
+        t.hf = _lib.ptr(hf)
+        t.dim_x, t.dim_y = int(hf.shape[0]), int(hf.shape[1])
+        mp = self.min_point.detach().cpu()
+        dd = self.dxdy.detach().cpu()
+        t.min_x, t.min_y = float(mp[0]), float(mp[1])
+        t.dx, t.dy = float(dd[0]), float(dd[1])
+        return t
+
+    # ---- kernel-backed lookups ----------------------------------------------------------------
+    def get_grid_index(self, point: torch.Tensor):
+        """clamp(round_half_even((p - min) / dxdy), 0, dims - 1) -> i64 [...,2] (:143-152)."""
+        lead = point.shape[:-1]
+        pts = point.reshape(-1, 2).contiguous().float()
+        n = pts.shape[0]
+        # each point is its own "env" with a single zero ray: reuses the ray-height kernel
+        root = torch.cat([pts, torch.zeros((n, 1), dtype=torch.float32, device=pts.device)], dim=-1).contiguous()
+        heading = torch.zeros((n,), dtype=torch.float32, device=pts.device)
+        ray = torch.zeros((1, 2), dtype=torch.float32, device=pts.device)
+        out = torch.empty((n, 1), dtype=torch.float32, device=pts.device)
+        idx = torch.empty((n, 1, 2), dtype=torch.int64, device=pts.device)
+        ts = self.cstruct()
+        _lib.check(_lib.lib().parc_b200_ray_heights(ts, _lib.ptr(root), _lib.ptr(heading), _lib.ptr(ray), 1, n,
+                                                  -3.0e38, 3.0e38, _lib.ptr(out), 1, _lib.ptr(idx),
+                                                  _lib.stream_ptr(pts.device)))
+        return idx.reshape(*lead, 2)
+
+    def get_hf_val_from_points(self, xy_points):
+        """Nearest-cell height of each xy point (:154-156)."""
+        lead = xy_points.shape[:-1]
+        pts = xy_points.reshape(-1, 2).contiguous().float()
+        n = pts.shape[0]
+        root = torch.cat([pts, torch.zeros((n, 1), dtype=torch.float32, device=pts.device)], dim=-1).contiguous()
+        heading = torch.zeros((n,), dtype=torch.float32, device=pts.device)
+        ray = torch.zeros((1, 2), dtype=torch.float32, device=pts.device)
+        out = torch.empty((n, 1), dtype=torch.float32, device=pts.device)
+        ts = self.cstruct()
+        _lib.check(_lib.lib().parc_b200_ray_heights(ts, _lib.ptr(root), _lib.ptr(heading), _lib.ptr(ray), 1, n,
+                                                  -3.0e38, 3.0e38, _lib.ptr(out), 1, None,
+                                                  _lib.stream_ptr(pts.device)))
+        return out.reshape(lead)
