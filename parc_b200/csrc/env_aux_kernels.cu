@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) tar_obs_data_kernel(
         const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + env.motion_terrain_ids[e]) * 2;
         const float tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3));
         const float toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
-        const Vec3 rpos = make_vec3(ps.root_pos.x + tox, ps.root_pos.y + toy, ps.root_pos.z);
+        const Vec3 rpos = make_vec3(__fadd_rn(ps.root_pos.x, tox), __fadd_rn(ps.root_pos.y, toy), ps.root_pos.z);
         const Quat rrot = group_bcast<G>(ps.q, 0);
         Vec3 bpos; Quat brot;
         fk_lanes<G>(lb, ps.q, rpos, rrot, bpos, brot);
@@ -305,7 +305,7 @@ __device__ __forceinline__ void reset_one_env(const parc_char_model_t& cm, const
     const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tid) * 2;
     const float tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3));
     const float toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
-    const Vec3 rpos = make_vec3(ps.root_pos.x + tox, ps.root_pos.y + toy, ps.root_pos.z);
+    const Vec3 rpos = make_vec3(__fadd_rn(ps.root_pos.x, tox), __fadd_rn(ps.root_pos.y, toy), ps.root_pos.z);
     if (sub == 0) {
         env.motion_ids[e] = mid;                                   // _reset_ref_motion, dm_env.py:504-506
         env.motion_terrain_ids[e] = tid;
@@ -314,8 +314,8 @@ __device__ __forceinline__ void reset_one_env(const parc_char_model_t& cm, const
         view_st_quat(env.ref_root_rot, e, ps.q);
         // _char_state_init_from_ref (mgdm_dm_util.py:89-100) + add_noise_to_char_state (:102-106)
         Vec3 cp = rpos;
-        cp.x += cfg.rand_root_pos_offset_scale * nx;
-        cp.y += cfg.rand_root_pos_offset_scale * ny;
+        cp.x = __fadd_rn(cp.x, __fmul_rn(cfg.rand_root_pos_offset_scale, nx));
+        cp.y = __fadd_rn(cp.y, __fmul_rn(cfg.rand_root_pos_offset_scale, ny));
         Quat cr = ps.q;
         if (root_pos_offset) { cp.x += root_pos_offset[e * 3]; cp.y += root_pos_offset[e * 3 + 1]; cp.z += root_pos_offset[e * 3 + 2]; }
         if (root_rot_offset) cr = quat_multiply(quat_from_f4(reinterpret_cast<const float4*>(root_rot_offset)[e]), cr);   // :112-113
@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(256) env_reset_sampled_kernel(const __grid_con
                                                                 const float* __restrict__ cdf, int M, unsigned long long seed, unsigned long long step, int rand_reset) {
     const LaneBody lb = load_lane_body<G>(cm);
     const long long gpb = blockDim.x / G;
-    const long long n = *env.done_count;
+    const long long n = min((long long)*env.done_count, (long long)env.num_envs);
     for (long long i = (long long)blockIdx.x * gpb + threadIdx.x / G; i < n; i += (long long)gridDim.x * gpb) {
         const long long e = env.done_list[i];
         if (env.done_buf[e] == PARC_DONE_NULL) continue;   // never_done: counted for the EMA, not reset
@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
     __shared__ int partial_i[EMA_THREADS];
     __shared__ float partial_f[EMA_THREADS];
     const int t = threadIdx.x, T = blockDim.x;
-    const int n = *env.done_count;
+    const int n = min(*env.done_count, (int)env.num_envs);
     int* hist = scratch;            // [M]
     int* offs = scratch + M;        // [M]
     int* bucket = scratch + 2 * M;  // [n]

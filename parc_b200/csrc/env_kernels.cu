@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(STEP_THREADS) env_step_kernel(
     const long long n_rows_host, const int bulk_ok, const int* __restrict__ env_ids32, const int* __restrict__ n_rows_dev) {
     extern __shared__ __align__(16) float smem[];
     // row count either from the host or (graph-captured reset path) from the device-side done counter
-    const long long n_rows = n_rows_dev ? (long long)*n_rows_dev : n_rows_host;
+    const long long n_rows = n_rows_dev ? min((long long)*n_rows_dev, n_rows_host) : n_rows_host;
     if ((long long)blockIdx.x * TILE >= n_rows) return;
     constexpr int HALVES = 32 / G;
     const int lane = threadIdx.x & 31;
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(STEP_THREADS) env_step_kernel(
                 const FrameBlend fb = calc_frame_blend(mm, t);
                 const PoseSample ps = eval_pose_lane(lib, lb, fb, J);
                 q = ps.q;
-                rpos = make_vec3(ps.root_pos.x + tox, ps.root_pos.y + toy, ps.root_pos.z);
+                rpos = make_vec3(__fadd_rn(ps.root_pos.x, tox), __fadd_rn(ps.root_pos.y, toy), ps.root_pos.z);
                 contact = ps.contact;
                 idx0 = fb.idx0;
             } else if (is_char) {
@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(STEP_THREADS) env_step_kernel(
                 if (env.done_code) env.done_code[e] = (unsigned char)code;
                 if (code != 0 && env.done_list) {
                     const int slot = atomicAdd(env.done_count, 1);
-                    env.done_list[slot] = (int)e;
+                    if (slot < env.num_envs) env.done_list[slot] = (int)e;   // a stale (un-zeroed) count must not overrun the list
                 }
             }
         }

@@ -195,13 +195,18 @@ struct PoseSample {
     float contact;   // lane c < C
 };
 
+// (1 - b) * x0 + b * x1 with each product and the sum rounded on its own (torch elementwise ops)
+__device__ __forceinline__ float lerp_exact(float omb, float x0, float b, float x1) {
+    return __fadd_rn(__fmul_rn(omb, x0), __fmul_rn(b, x1));
+}
+
 __device__ __forceinline__ PoseSample eval_pose_lane(const parc_motion_lib_t& lib, const LaneBody& lb,
                                                      const FrameBlend& fb, int J) {
     PoseSample ps;
     const float* r0 = lib.interp + fb.idx0 * lib.irec;
     const float* r1 = lib.interp + fb.idx1 * lib.irec;
     const float b = fb.blend;
-    const float omb = 1.0f - b;
+    const float omb = __fsub_rn(1.0f, b);
     Quat q0 = quat_identity(), q1 = quat_identity();
     if (lb.active) {
         q0 = quat_from_f4(__ldg(reinterpret_cast<const float4*>(r0) + lb.body));
@@ -213,12 +218,13 @@ __device__ __forceinline__ PoseSample eval_pose_lane(const parc_motion_lib_t& li
     if (lb.body < lib.num_contacts) {
         float c0 = __ldg(r0 + interp_contact_off(J) + lb.body);
         float c1 = __ldg(r1 + interp_contact_off(J) + lb.body);
-        ps.contact = omb * c0 + b * c1;                    // :121
+        ps.contact = lerp_exact(omb, c0, b, c1);           // :121
     }
     ps.q = slerp(q0, q1, b);                               // :113-115
-    ps.root_pos = make_vec3(omb * p0.x + b * p1.x + fb.loop_offset.x,     // :112, :117-118
-                            omb * p0.y + b * p1.y + fb.loop_offset.y,
-                            omb * p0.z + b * p1.z + fb.loop_offset.z);
+    // :112, :117-118 -- root positions live at world-coordinate magnitude: same rounding steps as torch
+    ps.root_pos = make_vec3(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x),
+                            __fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y),
+                            __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
     return ps;
 }
 

@@ -291,6 +291,8 @@ class TrackingEnv:
         RSI sampling CDF (dm_env.py:648-660, 487-490) in one more."""
         km = self._kin_char_model._cstruct()
         L = _lib.lib()
+        if parts & _lib.STEP_DONE:
+            self._done_count.zero_()      # the step kernel appends finished envs to done_list
         _lib.check(L.parc_b200_env_step(km, self._mlib.cstruct(), self._terrain_cs, self._cfg, self._bufs, parts, None, 0,
                                         self._stream()))
         if (parts & _lib.STEP_DONE) and update_fail_rates:

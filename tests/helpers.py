@@ -176,3 +176,24 @@ def randomize_oracle_state(oenv, seed=99, fail_fraction=0.15):
     oenv.char_dof_pos[:], oenv.char_dof_vel[:] = sim["dof_pos"], sim["dof_vel"]
     oenv.char_rigid_body_pos[:], oenv.char_contact_forces[:] = sim["body_pos"], sim["contact_forces"]
     oenv.fail_rates[:] = 0.25 + 0.5 * torch.rand(lib.num_motions(), generator=g)
+
+
+def assert_close_world(a, b, world_mag, rtol=1e-5, atol=3e-6, strict_fraction=0.999, ulps=2.0, what=""):
+    """For values derived from WORLD coordinates (positions, and observations that are differences
+    of positions): env offsets and terrain-tile offsets put world coordinates at |x| ~ world_mag, so
+    one fp32 rounding step of such a coordinate is ulp(world_mag) in absolute terms -- in the
+    reference too. Every element must be within 2 ulp(world_mag) (+ the usual tolerance), and at
+    least `strict_fraction` of them within the usual tolerance alone."""
+    a = torch.as_tensor(a).detach().cpu().double()
+    b = torch.as_tensor(b).detach().cpu().double()
+    assert a.shape == b.shape, "%s: shape %s vs %s" % (what, tuple(a.shape), tuple(b.shape))
+    ulp = float(np.spacing(np.float32(world_mag)))
+    err = (a - b).abs()
+    strict = err <= atol + rtol * b.abs()
+    frac = float(strict.double().mean())
+    assert frac >= strict_fraction, "%s: only %.5f of elements within rtol=%g atol=%g" % (what, frac, rtol, atol)
+    loose = err <= atol + ulps * ulp + rtol * b.abs()
+    if not bool(loose.all()):
+        i = torch.argmax(err)
+        raise AssertionError("%s: worst |%g - %g| = %g exceeds %g ulp(%g) = %g (strict fraction %.5f)" %
+                             (what, a.flatten()[i], b.flatten()[i], err.flatten()[i], ulps, world_mag, ulps * ulp, frac))
