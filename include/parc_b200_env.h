@@ -225,6 +225,12 @@ int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_mot
 int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n,
                                  int64_t* ids, void* stream);
 
+/* Self-test of the heightmap index arithmetic: the fused step divides by the (uniform) cell size
+ * with q = x*rc; r = fma(-q, d, x); q' = fma(r, rc, q), rc = RN(1/d), instead of div.rn. This entry
+ * evaluates both on x [n] so that a test can demand bit-identical quotients (the nearest-cell
+ * index of SubTerrain.get_grid_index, PARC/util/terrain_util.py:143-152, must be bit-exact). */
+int parc_b200_selftest_div(const float* x, int64_t n, float d, float* q_fast, float* q_ieee, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,15 +1,29 @@
 // Fused post-physics step of the DeepMimic-style tracking env:
 //   heights -> time -> reference motion -> observation -> reward -> termination
 // i.e. IGEnv._post_physics_step (PARC/motion_tracker/envs/ig_env.py:368-377) minus PhysX, in ONE
-// launch. One warp per env; a block owns a tile of TILE consecutive envs whose observation rows
-// are assembled in shared memory and leave the SM as one bulk (TMA) shared->global copy.
+// launch that reads every input once and writes every output once.
+//
+// Work decomposition (a block owns TILE = 8 consecutive envs, 256 threads):
+//   A  per-env uniforms (heading, time, clip meta) by 8 lanes; character dof -> quaternion by
+//      one thread per (env, joint)
+//   B  warps 0..1: one thread per (env, pose) -- pose 0 = reference, 1..S = target steps,
+//      S+1 = simulated character -- walks the joint list once: slerp of the two frame records,
+//      forward kinematics against the parent transform kept in shared memory, observation
+//      features straight into the staged row;   warps 2..7 meanwhile: heightmap samples, one
+//      thread per sample point, written straight into the observation rows (coalesced)
+//   C  one thread per (env, joint | dof | body | key body): rot_to_dof, reward / termination terms
+//   D  8 lanes: ordered sums, exponentials, reward, done flag, done-list append
+//   E  all threads: staged rows (observation minus heights, ref_* buffers) -> global, coalesced
+// The v1 kernel (one warp per env, level-by-level FK with warp shuffles) executed 9.8k warp
+// instructions per env and sat at 10 % of the HBM roofline, issue-bound with 22 % of the lanes
+// doing FK work; this layout keeps every lane on its own pose and needs ~2k.
 #include "parc_common.cuh"
 #include "parc_lanes.cuh"
 
 namespace parc {
 
-constexpr int TILE = 8;                 // envs (= warps) per block
-constexpr int STEP_THREADS = TILE * 32;
+constexpr int TILE = 8;                 // envs per block (== warps per block)
+constexpr int STEP_THREADS = 256;
 
 // Column layout of one observation row (IGParkourEnv._compute_obs, ig_parkour_env.py:842-965;
 // compute_char_obs ig_char_env.py:581-625; compute_tar_obs mgdm_dm_util.py:404-461).
@@ -35,23 +49,78 @@ __host__ __device__ inline ObsLayout make_layout(int J, int D, int C, const parc
     return L;
 }
 
-// bulk shared->global copy (TMA, SASS UBLKCP); bytes % 16 == 0, both addresses 16-byte aligned
-__device__ __forceinline__ void bulk_store_s2g(void* gdst, const void* ssrc, unsigned bytes) {
-    unsigned s = (unsigned)__cvta_generic_to_shared(ssrc);
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(s), "r"(bytes) : "memory");
+// Reference-motion outputs staged behind the observation columns of a row (DeepMimicEnv.
+// _update_ref_motion, dm_env.py:523-545): offsets relative to the start of the section.
+struct RefLayout {
+    int root_pos, root_rot, root_vel, root_ang_vel, body_pos, joint_rot, dof_pos, dof_vel, contacts, width;
+};
+__host__ __device__ inline RefLayout make_ref_layout(int J, int D, int C) {
+    RefLayout R;
+    R.root_pos = 0; R.root_rot = 3; R.root_vel = 7; R.root_ang_vel = 10; R.body_pos = 13;
+    R.joint_rot = R.body_pos + 3 * J;
+    R.dof_pos = R.joint_rot + 4 * (J - 1);
+    R.dof_vel = R.dof_pos + D;
+    R.contacts = R.dof_vel + D;
+    R.width = R.contacts + C;
+    return R;
 }
-__device__ __forceinline__ void bulk_commit_wait_read() {
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ __forceinline__ int find_key_slot(const parc_env_config_t& cfg, int body) {
-    int slot = -1;
-    for (int k = 0; k < cfg.num_key_bodies; ++k)
-        if (cfg.key_body_ids[k] == body) slot = k;   // a body listed twice keeps the last slot (and see write loop)
-    return slot;
+// Per-env uniforms computed once (phase A) and read by every later phase.
+struct EnvU {
+    long long e;             // env index of this row
+    long long mid;           // motion id
+    const float* vel_rec;    // velocity record of the reference pose's frame idx0 (set by phase B)
+    Vec3 c_pos; Quat c_rot; Vec3 c_vel; Vec3 c_avel;
+    Quat hinv;               // inverse heading rotation of the CHARACTER root
+    Vec3 eo;                 // env offset
+    Vec3 g;                  // global root position (c_pos + env offset)
+    float sh, ch;            // sin / cos of the character heading
+    float time, t0, tox, toy;
+    MotionMeta mm;
+    int live;
+    int flags;               // phase C: bit0 fall contact, bit1 fall height, bit2 pose failure
+};
+
+// Shared-memory plan (dynamic): sized on the host by step_smem_bytes().
+struct SmemPlan {
+    int row_pitch;           // floats per staged row: o_hf + ref width, forced odd
+    int n_pose;              // poses per env: S + 2
+    int n_pose_threads;      // TILE * n_pose
+    int n_slots;             // bodies (other than the root) that have children: FK transforms kept
+    int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
+    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, total;
+};
+
+__host__ __device__ inline int count_slots(const parc_char_model_t& cm) {
+    unsigned has_child = 0;
+    for (int j = 1; j < cm.num_bodies; ++j) has_child |= 1u << cm.parent[j];
+    has_child &= ~1u;
+    int n = 0;
+    for (int j = 1; j < cm.num_bodies; ++j) n += (has_child >> j) & 1u;
+    return n;
 }
+
+__host__ __device__ inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const ObsLayout& L) {
+    SmemPlan p;
+    const int J = cm.num_bodies, D = cm.dof_size;
+    const RefLayout R = make_ref_layout(J, D, C);
+    p.row_pitch = (L.o_hf + R.width) | 1;
+    p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
+    p.n_pose_threads = TILE * p.n_pose;
+    p.n_slots = count_slots(cm);
+    p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
+    size_t o = 0;
+    p.off_env = o;    o += sizeof(EnvU) * TILE;                          o = (o + 15) & ~size_t(15);
+    p.off_row = o;    o += sizeof(float) * TILE * p.row_pitch;           o = (o + 15) & ~size_t(15);
+    p.off_charq = o;  o += sizeof(float4) * TILE * J;                    o = (o + 15) & ~size_t(15);
+    p.off_xf = o;     o += sizeof(float) * 7 * p.n_slots * p.n_pose_threads;   o = (o + 15) & ~size_t(15);
+    p.off_terms = o;  o += sizeof(float) * TILE * p.term_pitch;          o = (o + 15) & ~size_t(15);
+    p.off_refmap = o; o += 16 * (size_t)R.width;                         o = (o + 15) & ~size_t(15);
+    p.total = o;
+    return p;
+}
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 // rotate_2d_vec (torch_util.py:650-662) + root xy, products rounded separately (bit-exact cells)
 __device__ __forceinline__ void ray_world(float px, float py, float c, float s, float rx, float ry, float& wx, float& wy) {
@@ -59,413 +128,539 @@ __device__ __forceinline__ void ray_world(float px, float py, float c, float s, 
     wy = __fadd_rn(__fadd_rn(__fmul_rn(px, s), __fmul_rn(py, c)), ry);
 }
 
-template <int G>
-__global__ void __launch_bounds__(STEP_THREADS) env_step_kernel(
+// quat_to_tan_norm (torch_util.py:392-404) = [rotate(q, x), rotate(q, z)] with the multiplications by
+// the 0 / 1 components of the unit vectors folded away. Only exact operations are removed
+// (a*0, a*1, a+0), so the result is bit-identical to the general quat_rotate.
+__device__ __forceinline__ void tan_norm_exact(Quat q, float* __restrict__ o) {
+    {   // v = (1,0,0): c0 = (0, qz, -qy), t = (0, 2qz, -2qy)
+        const float ty = __fmul_rn(2.f, q.z), tz = __fmul_rn(2.f, -q.y);
+        const float c1x = __fmaf_rn(q.y, tz, -__fmul_rn(q.z, ty));
+        const float c1y = -__fmul_rn(q.x, tz);
+        const float c1z = __fmul_rn(q.x, ty);
+        o[0] = __fadd_rn(1.f, c1x);
+        o[1] = __fadd_rn(__fmul_rn(q.w, ty), c1y);
+        o[2] = __fadd_rn(__fmul_rn(q.w, tz), c1z);
+    }
+    {   // v = (0,0,1): c0 = (qy, -qx, 0), t = (2qy, -2qx, 0)
+        const float tx = __fmul_rn(2.f, q.y), ty = __fmul_rn(2.f, -q.x);
+        const float c1x = -__fmul_rn(q.z, ty);
+        const float c1y = __fmul_rn(q.z, tx);
+        const float c1z = __fmaf_rn(q.x, ty, -__fmul_rn(q.y, tx));
+        o[3] = __fadd_rn(__fmul_rn(q.w, tx), c1x);
+        o[4] = __fadd_rn(__fmul_rn(q.w, ty), c1y);
+        o[5] = __fadd_rn(1.f, c1z);
+    }
+}
+
+// (x - mn) / d for the nearest-cell index with d, 1/d uniform: q = x * rc; r = fma(-q, d, x);
+// q' = fma(r, rc, q) (Markstein) is the correctly rounded quotient for normal operands when rc is
+// the correctly rounded reciprocal; checked against div.rn by parc_b200_selftest_div.
+__device__ __forceinline__ float div_const(float x, float d, float rc) {
+    const float q = __fmul_rn(x, rc);
+    const float r = __fmaf_rn(-q, d, x);
+    return __fmaf_rn(r, rc, q);
+}
+struct GridParams { float min_x, min_y, dx, dy, rdx, rdy, max_ix, max_iy; };
+__device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float rd, float mx) {
+    float u = rintf(div_const(__fsub_rn(p, mn), d, rd));
+    u = fminf(fmaxf(u, 0.f), mx);
+    return (int)u;
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const unsigned parts, const long long* __restrict__ env_ids,
-    const long long n_rows_host, const int bulk_ok, const int* __restrict__ env_ids32, const int* __restrict__ n_rows_dev) {
-    extern __shared__ __align__(16) float smem[];
-    // row count either from the host or (graph-captured reset path) from the device-side done counter
+    const long long n_rows_host, const int* __restrict__ env_ids32, const int* __restrict__ n_rows_dev) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     const long long n_rows = n_rows_dev ? min((long long)*n_rows_dev, n_rows_host) : n_rows_host;
-    if ((long long)blockIdx.x * TILE >= n_rows) return;
-    constexpr int HALVES = 32 / G;
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const int h = lane / G;          // which pose of the round this lane works on
-    const int sub = lane & (G - 1);  // body owned by this lane
+    const long long row0 = (long long)blockIdx.x * TILE;
+    if (row0 >= n_rows) return;
+    const int tid = threadIdx.x;
     const int J = cm.num_bodies, D = cm.dof_size, C = lib.num_contacts;
     const int S = cfg.enable_tar_obs ? cfg.num_tar_steps : 0;
     const int K = cfg.num_key_bodies, P = cfg.num_ray_points;
     const ObsLayout L = make_layout(J, D, C, cfg);
-    const LaneBody lb = load_lane_body<G>(cm);
-    const int my_key = lb.active ? find_key_slot(cfg, lb.body) : -1;
+    const RefLayout R = make_ref_layout(J, D, C);
+    const SmemPlan plan = make_plan(cm, C, cfg, L);
+    EnvU* s_env = reinterpret_cast<EnvU*>(smem_raw + plan.off_env);
+    float* s_row = reinterpret_cast<float*>(smem_raw + plan.off_row);
+    float4* s_charq = reinterpret_cast<float4*>(smem_raw + plan.off_charq);
+    float* s_xf = reinterpret_cast<float*>(smem_raw + plan.off_xf);
+    float* s_terms = reinterpret_cast<float*>(smem_raw + plan.off_terms);
+    unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
+    const int ROWP = plan.row_pitch;
+    const int NPT = plan.n_pose_threads;
 
-    const long long row = (long long)blockIdx.x * TILE + warp;
-    const bool live = row < n_rows;
-    const long long e = live ? (env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row)) : 0;
-    float* srow = smem + warp * L.obs_dim;
-
+    const bool do_heights = parts & PARC_STEP_HEIGHTS;
     const bool do_obs = parts & PARC_STEP_OBS;
     const bool do_ref = parts & PARC_STEP_REF;
     const bool do_reward = parts & PARC_STEP_REWARD;
     const bool do_done = parts & PARC_STEP_DONE;
+    const bool need_ref_pose = do_ref || do_reward || do_done;
+    const bool need_char_q = do_obs || do_reward;
+    const int tile_rows = (int)min((long long)TILE, n_rows - row0);
 
-    if (live) {
-        // ---- uniform per-env state (broadcast loads) ---------------------------------------
-        const Vec3 c_pos = view_ld_vec3(env.char_root_pos, e);
-        const Quat c_rot = view_ld_quat(env.char_root_rot, e);
-        const Vec3 c_vel = view_ld_vec3(env.char_root_vel, e);
-        const Vec3 c_avel = view_ld_vec3(env.char_root_ang_vel, e);
-        const float eox = __ldg(env.env_offsets + e * 3), eoy = __ldg(env.env_offsets + e * 3 + 1), eoz = __ldg(env.env_offsets + e * 3 + 2);
-
-        // ---- _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----------
-        if (parts & PARC_STEP_HEIGHTS) {
-            const float gx = __fadd_rn(c_pos.x, eox), gy = __fadd_rn(c_pos.y, eoy), gz = __fadd_rn(c_pos.z, eoz);
-            const float heading = calc_heading(c_rot);
-            const float sh = sinf(heading), ch = cosf(heading);
-            for (int p = lane; p < P; p += 32) {
-                const float2 pt = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + p);
-                float wx, wy;
-                ray_world(pt.x, pt.y, ch, sh, gx, gy, wx, wy);
-                const int ix = grid_index(wx, terrain.min_x, terrain.dx, terrain.dim_x);
-                const int iy = grid_index(wy, terrain.min_y, terrain.dy, terrain.dim_y);
-                const float hv = __ldg(terrain.hf + (long long)ix * terrain.dim_y + iy);
-                const float v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
-                if (do_obs) srow[L.o_hf + p] = v;
-                if (env.ray_hfs) env.ray_hfs[e * P + p] = v;
-            }
-        } else if (do_obs) {
-            for (int p = lane; p < P; p += 32) srow[L.o_hf + p] = env.ray_hfs[e * P + p];
-        }
-
-        // ---- _update_time (ig_env.py:391-394) -----------------------------------------------
-        float time;
-        if (parts & PARC_STEP_TIME) {
-            const int ts = env.timestep_buf[e] + 1;
-            time = __fmul_rn(cfg.timestep, (float)ts);
-            __syncwarp();   // every lane has read the old step count before lane 0 replaces it
-            if (lane == 0) { env.timestep_buf[e] = ts; env.time_buf[e] = time; }
-        } else {
-            time = env.time_buf[e];
-        }
-
-        const long long mid = env.motion_ids[e];
-        const long long tid = env.motion_terrain_ids[e];
-        const MotionMeta mm = load_motion_meta(lib.meta, mid);
-        const float t0 = __fadd_rn(time, env.motion_time_offsets[e]);              // dm_env.py:547-552
-        // _move_to_motion_terrain (dm_env.py:554-565): offset = dm_offsets[m, t] - env_offsets[:, 0:2]
-        const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tid) * 2;
-        const float tox = __fsub_rn(__ldg(dmo), eox), toy = __fsub_rn(__ldg(dmo + 1), eoy);
-
-        const Quat hinv = calc_heading_quat_inv(c_rot);   // heading frame of the CHARACTER root
-
-        // per-lane values that outlive the pose loop
-        Quat ref_q = quat_identity(), char_q = quat_identity();
-        Vec3 ref_bpos = make_vec3(0.f, 0.f, 0.f);
-        Vec3 ref_rpos = make_vec3(0.f, 0.f, 0.f);
-        Quat ref_rrot = quat_identity();
-        float ref_contact = 0.f;
-        long long ref_idx0 = 0;
-
-        const int n_poses = S + 2;   // 0 = reference pose, 1..S = target steps, S+1 = simulated character
-        const bool need_poses = do_obs || do_ref || do_reward || do_done;
-        const int n_rounds = need_poses ? (n_poses + HALVES - 1) / HALVES : 0;
-        for (int r = 0; r < n_rounds; ++r) {
-            const int pose = r * HALVES + h;
-            const bool is_ref = pose == 0;
-            const bool is_tar = pose >= 1 && pose <= S;
-            const bool is_char = pose == S + 1;
+    // ================================ phase A ====================================================
+    // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
+    if (need_char_q) {
+        for (int it = tid; it < TILE * (J - 1); it += THREADS) {
+            const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
+            if (el >= tile_rows) continue;
+            const long long row = row0 + el;
+            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
+            const int jt = cm.joint_type[j], di = cm.dof_idx[j];
             Quat q = quat_identity();
-            Vec3 rpos = c_pos;
-            float contact = 0.f;
-            long long idx0 = 0;
-            if (is_ref || is_tar) {
-                // fetch_tar_obs_data (mgdm_dm_util.py:221-244): motion_times + timestep * tar_obs_steps
-                const float t = is_ref ? t0 : __fadd_rn(t0, cfg.tar_dt[pose - 1]);
-                const FrameBlend fb = calc_frame_blend(mm, t);
-                const PoseSample ps = eval_pose_lane(lib, lb, fb, J);
-                q = ps.q;
-                rpos = make_vec3(__fadd_rn(ps.root_pos.x, tox), __fadd_rn(ps.root_pos.y, toy), ps.root_pos.z);
-                contact = ps.contact;
-                idx0 = fb.idx0;
-            } else if (is_char) {
-                if (sub == 0) q = c_rot;
-                else if (lb.active) q = dof_to_rot_lane(lb, [&](int k) { return view_ld(env.char_dof_pos, e, k); });
-            }
-            // forward kinematics of this pose (root rotation lives in the group's lane 0)
-            const Quat rrot = group_bcast<G>(q, 0);
-            Vec3 bpos; Quat brot;
-            fk_lanes<G>(lb, q, rpos, rrot, bpos, brot);
+            if (jt == PARC_JOINT_SPHERICAL)
+                q = exp_map_to_quat(make_vec3(view_ld(env.char_dof_pos, e, di), view_ld(env.char_dof_pos, e, di + 1), view_ld(env.char_dof_pos, e, di + 2)));
+            else if (jt == PARC_JOINT_HINGE)
+                q = axis_angle_to_quat(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), view_ld(env.char_dof_pos, e, di));
+            s_charq[el * J + j] = quat_to_f4(q);
+        }
+    }
+    // A.2 scatter map of the ref_* section: column k -> (base pointer, row stride in bytes)
+    if (do_ref) {
+        for (int k = tid; k < R.width; k += THREADS) {
+            const parc_view3_t* v; int off;
+            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
+            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
+            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
+            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
+            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
+            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
+            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
+            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
+            else { v = &env.ref_contacts; off = k - R.contacts; }
+            long long eoff;
+            if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
+            else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
+            else eoff = off * v->elem_stride;
+            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
+            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
+        }
+    }
+    // A.3 per-env uniforms
+    if (tid < TILE) {
+        EnvU u;
+        const int el = tid;
+        u.live = el < tile_rows;
+        const long long row = row0 + (u.live ? el : 0);
+        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
+        u.e = e;
+        u.c_pos = view_ld_vec3(env.char_root_pos, e);
+        u.c_rot = view_ld_quat(env.char_root_rot, e);
+        u.c_vel = view_ld_vec3(env.char_root_vel, e);
+        u.c_avel = view_ld_vec3(env.char_root_ang_vel, e);
+        u.eo = make_vec3(__ldg(env.env_offsets + e * 3), __ldg(env.env_offsets + e * 3 + 1), __ldg(env.env_offsets + e * 3 + 2));
+        u.g = u.c_pos + u.eo;                                          // ig_parkour_env.py:522
+        const float heading = calc_heading(u.c_rot);
+        u.sh = sinf(heading); u.ch = cosf(heading);
+        u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
+        if (parts & PARC_STEP_TIME) {                                   // _update_time, ig_env.py:391-394
+            const int ts = env.timestep_buf[e] + 1;
+            u.time = __fmul_rn(cfg.timestep, (float)ts);
+            if (u.live) { env.timestep_buf[e] = ts; env.time_buf[e] = u.time; }
+        } else {
+            u.time = env.time_buf[e];
+        }
+        u.mid = env.motion_ids[e];
+        const long long tidx = env.motion_terrain_ids[e];
+        u.mm = load_motion_meta(lib.meta, u.mid);
+        u.t0 = __fadd_rn(u.time, env.motion_time_offsets[e]);          // dm_env.py:547-552
+        const float* dmo = env.dm_motion_offsets + (u.mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
+        u.tox = __fsub_rn(__ldg(dmo), u.eo.x); u.toy = __fsub_rn(__ldg(dmo + 1), u.eo.y);
+        u.vel_rec = lib.vel;
+        u.flags = 0;
+        s_env[el] = u;
+        if (need_char_q) s_charq[el * J] = quat_to_f4(u.c_rot);
+    }
+    __syncthreads();
 
+    // ================================ phase B ====================================================
+    const int pose_warps = (NPT + 31) >> 5;
+    const bool pose_work = do_obs || need_ref_pose;
+    if (tid < pose_warps * 32) {
+        // ---- B.1 one thread per (env, pose); pose-major so that a warp holds few distinct poses ----
+        const int pose = tid / TILE, el = tid - pose * TILE;
+        const bool is_ref = pose == 0, is_char = pose == S + 1, is_tar = pose >= 1 && pose <= S;
+        const bool wanted = (is_ref && need_ref_pose) || (is_tar && do_obs) || (is_char && do_obs);
+        if (pose_work && tid < NPT && wanted && s_env[el].live) {
+            const EnvU& u = s_env[el];
+            float* row = s_row + el * ROWP;
+            float* rsec = row + L.o_hf;                    // ref_* section
+            const float *r0 = nullptr, *r1 = nullptr;
+            float b = 0.f, omb = 1.f;
+            Quat rq = u.c_rot;
+            Vec3 rpos = u.c_pos;
+            if (!is_char) {
+                // MotionLib.calc_motion_frame (motion_lib.py:94-126); fetch_tar_obs_data (mgdm_dm_util.py:221-244)
+                const float t = is_ref ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
+                const FrameBlend fb = calc_frame_blend(u.mm, t);
+                r0 = lib.interp + fb.idx0 * lib.irec;
+                r1 = lib.interp + fb.idx1 * lib.irec;
+                b = fb.blend; omb = __fsub_rn(1.0f, b);
+                rq = slerp(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), b);
+                const float4 p0 = ldg4(r0 + 4 * J), p1 = ldg4(r1 + 4 * J);
+                rpos = make_vec3(__fadd_rn(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x), u.tox),
+                                 __fadd_rn(__fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y), u.toy),
+                                 __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
+                if (is_ref) s_env[el].vel_rec = lib.vel + fb.idx0 * lib.vrec;
+            }
+            // ---- root-level outputs ----
+            float* o_pose = nullptr;        // start of this pose's joint tan-norm block
+            float* o_key = nullptr;         // start of this pose's key-body block
+            Vec3 rp_obs = make_vec3(0.f, 0.f, 0.f);
             if (is_ref) {
-                ref_q = q; ref_bpos = bpos; ref_rpos = rpos; ref_rrot = rrot; ref_contact = contact; ref_idx0 = idx0;
-                if (do_ref) {
-                    // DeepMimicEnv._update_ref_motion (dm_env.py:523-545)
-                    if (sub == 0) {
-                        view_st_vec3(env.ref_root_pos, e, rpos);
-                        view_st_quat(env.ref_root_rot, e, q);
-                    } else if (lb.active) {
-                        float* jr = env.ref_joint_rot.ptr + e * env.ref_joint_rot.row_stride + (sub - 1) * env.ref_joint_rot.mid_stride;
-                        const long long es = env.ref_joint_rot.elem_stride;
-                        jr[0] = q.x; jr[es] = q.y; jr[2 * es] = q.z; jr[3 * es] = q.w;
-                        float dd[3];
-                        const int nd = rot_to_dof_lane(lb, q, dd);
-                        for (int k = 0; k < nd; ++k) view_st(env.ref_dof_pos, e, lb.dof_idx + k, dd[k]);
-                    }
-                    if (lb.active) {
-                        view_st3(env.ref_body_pos, e, sub, 0, bpos.x);
-                        view_st3(env.ref_body_pos, e, sub, 1, bpos.y);
-                        view_st3(env.ref_body_pos, e, sub, 2, bpos.z);
-                    }
-                    if (sub < C && env.ref_contacts.ptr) view_st(env.ref_contacts, e, sub, contact);
-                    const float* v = lib.vel + idx0 * lib.vrec;
-                    for (int k = sub; k < 6 + D; k += G) {
-                        const float x = __ldg(v + k);
-                        if (k < 3) view_st(env.ref_root_vel, e, k, x);
-                        else if (k < 6) view_st(env.ref_root_ang_vel, e, k - 3, x);
-                        else view_st(env.ref_dof_vel, e, k - 6, x);
+                rsec[R.root_pos] = rpos.x; rsec[R.root_pos + 1] = rpos.y; rsec[R.root_pos + 2] = rpos.z;
+                rsec[R.root_rot] = rq.x; rsec[R.root_rot + 1] = rq.y; rsec[R.root_rot + 2] = rq.z; rsec[R.root_rot + 3] = rq.w;
+                rsec[R.body_pos] = rpos.x; rsec[R.body_pos + 1] = rpos.y; rsec[R.body_pos + 2] = rpos.z;
+                // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
+                const float* v = s_env[el].vel_rec;
+                for (int k = 0; k < 6 + D; k += 4) {
+                    const float4 x = ldg4(v + k);
+                    const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int kk = k + c;
+                        if (kk < 3) rsec[R.root_vel + kk] = xs[c];
+                        else if (kk < 6) rsec[R.root_ang_vel + kk - 3] = xs[c];
+                        else if (kk < 6 + D) rsec[R.dof_vel + kk - 6] = xs[c];
                     }
                 }
             } else if (is_tar) {
-                if (do_obs) {
-                    // compute_tar_obs (mgdm_dm_util.py:404-461) for target step `pose - 1`
-                    float* o = srow + L.o_tar + (pose - 1) * L.tar_step_dim;
-                    Vec3 rp_obs = rpos - c_pos;
-                    if (!cfg.global_obs) rp_obs = quat_rotate(hinv, rp_obs);
-                    Quat oq = q;
-                    if (sub == 0) {
-                        o[0] = rp_obs.x; o[1] = rp_obs.y; o[2] = rp_obs.z;
-                        if (!cfg.global_obs) oq = quat_mul(hinv, q);
-                    }
-                    if (lb.active) {
-                        float tn[6];
-                        quat_to_tan_norm(oq, tn);
-                        float* d = o + 3 + 6 * sub;
-#pragma unroll
-                        for (int k = 0; k < 6; ++k) d[k] = tn[k];
-                        if (my_key >= 0) {
-                            Vec3 kp = bpos - rpos;
-                            if (!cfg.global_obs) kp = quat_rotate(hinv, kp) + rp_obs;
-                            for (int k = 0; k < K; ++k)
-                                if (cfg.key_body_ids[k] == lb.body) {
-                                    float* kd = o + 9 + 6 * (J - 1) + 3 * k;
-                                    kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
-                                }
-                        }
-                    }
-                    if (cfg.use_contact_info && sub < C) srow[L.o_tarc + (pose - 1) * C + sub] = contact;
-                }
-            } else if (is_char) {
-                char_q = q;
-                if (do_obs) {
-                    // compute_char_obs (ig_char_env.py:581-625)
-                    float* o = srow + L.root_h;
-                    if (sub == 0) {
-                        if (L.root_h) srow[0] = c_pos.z;
-                        Quat oq = cfg.global_obs ? c_rot : quat_mul(hinv, c_rot);
-                        float tn[6];
-                        quat_to_tan_norm(oq, tn);
-#pragma unroll
-                        for (int k = 0; k < 6; ++k) o[k] = tn[k];
-                        Vec3 v = cfg.global_obs ? c_vel : quat_rotate(hinv, c_vel);
-                        Vec3 w = cfg.global_obs ? c_avel : quat_rotate(hinv, c_avel);
-                        o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
-                    } else if (lb.active) {
-                        float tn[6];
-                        quat_to_tan_norm(q, tn);
-                        float* d = o + 12 + 6 * (sub - 1);
-#pragma unroll
-                        for (int k = 0; k < 6; ++k) d[k] = tn[k];
-                    }
-                    for (int k = sub; k < D; k += G) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, e, k);
-                    if (my_key >= 0) {
-                        Vec3 kp = bpos - c_pos;
-                        if (!cfg.global_obs) kp = quat_rotate(hinv, kp);
-                        for (int k = 0; k < K; ++k)
-                            if (cfg.key_body_ids[k] == lb.body) {
-                                float* kd = o + 12 + 6 * (J - 1) + D + 3 * k;
-                                kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
-                            }
-                    }
-                    if (cfg.use_contact_info && lb.active) {
-                        // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
-                        const float fx = view_ld3(env.char_contact_forces, e, sub, 0), fy = view_ld3(env.char_contact_forces, e, sub, 1),
-                                    fz = view_ld3(env.char_contact_forces, e, sub, 2);
-                        srow[L.o_charc + sub] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
+                // compute_tar_obs (mgdm_dm_util.py:404-461) for target step pose-1
+                float* o = row + L.o_tar + (pose - 1) * L.tar_step_dim;
+                rp_obs = rpos - u.c_pos;
+                Quat oq = rq;
+                if (!cfg.global_obs) { rp_obs = quat_rotate(u.hinv, rp_obs); oq = quat_mul(u.hinv, rq); }
+                o[0] = rp_obs.x; o[1] = rp_obs.y; o[2] = rp_obs.z;
+                tan_norm_exact(oq, o + 3);
+                o_pose = o + 9; o_key = o + 9 + 6 * (J - 1);
+            } else {
+                // compute_char_obs (ig_char_env.py:581-625)
+                float* o = row + L.root_h;
+                if (L.root_h) row[0] = u.c_pos.z;
+                Quat oq = u.c_rot; Vec3 v = u.c_vel, w = u.c_avel;
+                if (!cfg.global_obs) { oq = quat_mul(u.hinv, u.c_rot); v = quat_rotate(u.hinv, u.c_vel); w = quat_rotate(u.hinv, u.c_avel); }
+                tan_norm_exact(oq, o);
+                o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
+                o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
+                for (int k = 0; k < D; ++k) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
+                if (cfg.use_contact_info) {
+                    // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+                    for (int c = 0; c < J; ++c) {
+                        const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
+                                    fz = view_ld3(env.char_contact_forces, u.e, c, 2);
+                        row[L.o_charc + c] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
                     }
                 }
             }
+            // contact labels: lerp of the two records (motion_lib.py:121)
+            if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
+                float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
+                const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
+                for (int c = 0; c < C; c += 4) {
+                    const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
+                    oc[c] = lerp_exact(omb, a.x, b, d.x);
+                    if (c + 1 < C) oc[c + 1] = lerp_exact(omb, a.y, b, d.y);
+                    if (c + 2 < C) oc[c + 2] = lerp_exact(omb, a.z, b, d.z);
+                    if (c + 3 < C) oc[c + 3] = lerp_exact(omb, a.w, b, d.w);
+                }
+            }
+            // ---- joints: slerp + forward kinematics (kin_char_model.py:617-649), parents precede children ----
+            unsigned has_child = 0;
+            for (int j = 1; j < J; ++j) has_child |= 1u << cm.parent[j];
+            bool lrot_ident = true;
+            for (int j = 1; j < J; ++j)
+                lrot_ident = lrot_ident && cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f;
+            float* xf = s_xf + tid;                         // [slot][7][NPT], this thread's column
+            for (int j = 1; j < J; ++j) {
+                Quat q;
+                if (is_char) q = quat_from_f4(s_charq[el * J + j]);
+                else q = slerp(quat_from_f4(ldg4(r0 + 4 * j)), quat_from_f4(ldg4(r1 + 4 * j)), b);
+                const int par = cm.parent[j];
+                Vec3 ppos = rpos; Quat prot = rq;
+                if (par != 0) {
+                    const int ps = __popc(has_child & ((1u << par) - 1u) & ~1u);
+                    const float* x = xf + ps * 7 * NPT;
+                    ppos = make_vec3(x[0], x[NPT], x[2 * NPT]);
+                    prot = make_quat(x[3 * NPT], x[4 * NPT], x[5 * NPT], x[6 * NPT]);
+                }
+                const Vec3 bpos = ppos + quat_rotate(prot, make_vec3(cm.local_trans[j][0], cm.local_trans[j][1], cm.local_trans[j][2]));
+                if ((has_child >> j) & 1u) {
+                    const Quat cq = lrot_ident ? q : quat_mul(make_quat(cm.local_rot[j][0], cm.local_rot[j][1], cm.local_rot[j][2], cm.local_rot[j][3]), q);
+                    const Quat brot = quat_mul(prot, cq);
+                    const int sl = __popc(has_child & ((1u << j) - 1u) & ~1u);
+                    float* x = xf + sl * 7 * NPT;
+                    x[0] = bpos.x; x[NPT] = bpos.y; x[2 * NPT] = bpos.z;
+                    x[3 * NPT] = brot.x; x[4 * NPT] = brot.y; x[5 * NPT] = brot.z; x[6 * NPT] = brot.w;
+                }
+                if (is_ref) {
+                    float* jr = rsec + R.joint_rot + 4 * (j - 1);
+                    jr[0] = q.x; jr[1] = q.y; jr[2] = q.z; jr[3] = q.w;
+                    float* bp = rsec + R.body_pos + 3 * j;
+                    bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
+                } else {
+                    tan_norm_exact(q, o_pose + 6 * (j - 1));
+                    for (int k = 0; k < K; ++k) {
+                        if (cfg.key_body_ids[k] != j) continue;
+                        Vec3 kp = bpos - rpos;
+                        if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
+                        float* kd = o_key + 3 * k;
+                        kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+                    }
+                }
+            }
+            // a key body may also be the root itself
+            if (!is_ref)
+                for (int k = 0; k < K; ++k)
+                    if (cfg.key_body_ids[k] == 0) {
+                        Vec3 kp = make_vec3(0.f, 0.f, 0.f);
+                        if (!cfg.global_obs && is_tar) kp = kp + rp_obs;
+                        float* kd = o_key + 3 * k;
+                        kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+                    }
         }
-
-        // Bring the reference pose (group 0, round 0) and the character pose (group hc) to every lane.
-        constexpr int ref_lane_base = 0;
-        const int char_lane_base = ((S + 1) % HALVES) * G;
-        if (do_reward || do_done) {
-            ref_q = make_quat(__shfl_sync(FULL_MASK, ref_q.x, ref_lane_base + sub), __shfl_sync(FULL_MASK, ref_q.y, ref_lane_base + sub),
-                              __shfl_sync(FULL_MASK, ref_q.z, ref_lane_base + sub), __shfl_sync(FULL_MASK, ref_q.w, ref_lane_base + sub));
-            char_q = make_quat(__shfl_sync(FULL_MASK, char_q.x, char_lane_base + sub), __shfl_sync(FULL_MASK, char_q.y, char_lane_base + sub),
-                               __shfl_sync(FULL_MASK, char_q.z, char_lane_base + sub), __shfl_sync(FULL_MASK, char_q.w, char_lane_base + sub));
-            ref_bpos = make_vec3(__shfl_sync(FULL_MASK, ref_bpos.x, ref_lane_base + sub), __shfl_sync(FULL_MASK, ref_bpos.y, ref_lane_base + sub),
-                                 __shfl_sync(FULL_MASK, ref_bpos.z, ref_lane_base + sub));
-            ref_rpos = make_vec3(__shfl_sync(FULL_MASK, ref_rpos.x, 0), __shfl_sync(FULL_MASK, ref_rpos.y, 0), __shfl_sync(FULL_MASK, ref_rpos.z, 0));
-            ref_rrot = make_quat(__shfl_sync(FULL_MASK, ref_rrot.x, 0), __shfl_sync(FULL_MASK, ref_rrot.y, 0),
-                                 __shfl_sync(FULL_MASK, ref_rrot.z, 0), __shfl_sync(FULL_MASK, ref_rrot.w, 0));
-            ref_contact = __shfl_sync(FULL_MASK, ref_contact, ref_lane_base + sub);
-            ref_idx0 = __shfl_sync(FULL_MASK, ref_idx0, 0);
+    } else if (P > 0 && (do_heights || do_obs)) {
+        // ---- B.2 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
+        const int ht = tid - pose_warps * 32, hn = THREADS - pose_warps * 32;
+        const float rdx = __frcp_rn(terrain.dx), rdy = __frcp_rn(terrain.dy);
+        const float mx = (float)(terrain.dim_x - 1), my = (float)(terrain.dim_y - 1);
+        for (int el = 0; el < tile_rows; ++el) {
+            const EnvU& u = s_env[el];
+            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
+            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
+            if (do_heights) {
+                const float ch = u.ch, sh = u.sh, gx = u.g.x, gy = u.g.y, gz = u.g.z;
+                for (int p = ht; p < P; p += hn) {
+                    const float2 pt = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + p);
+                    float wx, wy;
+                    ray_world(pt.x, pt.y, ch, sh, gx, gy, wx, wy);
+                    const int ix = grid_index_fast(wx, terrain.min_x, terrain.dx, rdx, mx);
+                    const int iy = grid_index_fast(wy, terrain.min_y, terrain.dy, rdy, my);
+                    const float hv = __ldg(terrain.hf + ix * terrain.dim_y + iy);
+                    const float v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
+                    if (orow) orow[p] = v;
+                    if (hrow) hrow[p] = v;
+                }
+            } else {
+                for (int p = ht; p < P; p += hn) orow[p] = hrow[p];
+            }
         }
-        const bool first_group = h == 0;   // per-body terms are summed over one group only
+    }
+    __syncthreads();
 
-        // simulator rigid-body position of the lane's body (reward key bodies + termination)
-        Vec3 sim_bpos = make_vec3(0.f, 0.f, 0.f);
-        Vec3 sim_b0 = make_vec3(0.f, 0.f, 0.f);
-        if (do_reward || do_done) {
-            if (lb.active)
-                sim_bpos = make_vec3(view_ld3(env.char_rigid_body_pos, e, sub, 0), view_ld3(env.char_rigid_body_pos, e, sub, 1),
-                                     view_ld3(env.char_rigid_body_pos, e, sub, 2));
-            sim_b0 = make_vec3(view_ld3(env.char_rigid_body_pos, e, 0, 0), view_ld3(env.char_rigid_body_pos, e, 0, 1),
-                               view_ld3(env.char_rigid_body_pos, e, 0, 2));
+    // ================================ phase C ====================================================
+    // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
+    const int o_pose_t = 0, o_vel_t = J - 1, o_con_t = o_vel_t + D, o_key_t = o_con_t + J;
+    const int TP = plan.term_pitch;
+    if (need_ref_pose) {
+        // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
+        for (int it = tid; it < TILE * (J - 1); it += THREADS) {
+            const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
+            if (el >= tile_rows) continue;
+            float* rsec = s_row + el * ROWP + L.o_hf;
+            const float* jr = rsec + R.joint_rot + 4 * (j - 1);
+            const Quat q = make_quat(jr[0], jr[1], jr[2], jr[3]);
+            if (do_ref) {
+                const int jt = cm.joint_type[j], di = cm.dof_idx[j];
+                if (jt == PARC_JOINT_SPHERICAL) {
+                    const Vec3 ex = quat_to_exp_map(q);
+                    rsec[R.dof_pos + di] = ex.x; rsec[R.dof_pos + di + 1] = ex.y; rsec[R.dof_pos + di + 2] = ex.z;
+                } else if (jt == PARC_JOINT_HINGE) {
+                    Vec3 axis; float angle;
+                    quat_to_axis_angle(q, axis, angle);
+                    const float dd = dot3_seq(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), axis);
+                    rsec[R.dof_pos + di] = (dd < 0.f) ? -angle : angle;
+                }
+            }
+            if (do_reward) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
+                const float a = quat_diff_angle(quat_from_f4(s_charq[el * J + j]), q);
+                s_terms[el * TP + o_pose_t + (j - 1)] = cfg.joint_err_w[j - 1] * a * a;
+            }
+            if (do_done && cfg.enable_early_termination && cfg.pose_termination) {
+                // compute_done pose test (mgdm_dm_util.py:372-384): squared norm summed left to right
+                const EnvU& u = s_env[el];
+                const Vec3 sb = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, j, 0), view_ld3(env.char_rigid_body_pos, u.e, j, 1), view_ld3(env.char_rigid_body_pos, u.e, j, 2));
+                const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, 0, 0), view_ld3(env.char_rigid_body_pos, u.e, 0, 1), view_ld3(env.char_rigid_body_pos, u.e, 0, 2));
+                const float* bp = rsec + R.body_pos;
+                const Vec3 a = sb - s0;
+                const Vec3 bb = make_vec3(bp[3 * j], bp[3 * j + 1], bp[3 * j + 2]) - make_vec3(bp[0], bp[1], bp[2]);
+                const Vec3 d = bb - a;
+                const float td = cfg.pose_termination_dist[j - 1];
+                if (sqnorm3_seq(d) > __fmul_rn(td, td)) atomicOr(&s_env[el].flags, 4);
+            }
         }
+    }
+    if (do_reward) {
+        // dof velocity term (mgdm_dm_util.py:289-291)
+        for (int it = tid; it < TILE * D; it += THREADS) {
+            const int el = it / D, k = it - el * D;
+            if (el >= tile_rows) continue;
+            const EnvU& u = s_env[el];
+            const float dv = s_row[el * ROWP + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
+            s_terms[el * TP + o_vel_t + k] = cfg.dof_err_w[k] * dv * dv;
+        }
+        // key body term (mgdm_dm_util.py:303-323); key positions of the CHARACTER come from the simulator's rigid bodies
+        for (int it = tid; it < TILE * K; it += THREADS) {
+            const int el = it / K, k = it - el * K;
+            if (el >= tile_rows) continue;
+            const EnvU& u = s_env[el];
+            const int body = cfg.key_body_ids[k];
+            const float* rsec = s_row + el * ROWP + L.o_hf;
+            const float* bp = rsec + R.body_pos;
+            const Vec3 ref_rpos = make_vec3(bp[0], bp[1], bp[2]);
+            Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
+                                view_ld3(env.char_rigid_body_pos, u.e, body, 2)) - u.c_pos;
+            Vec3 tkp = make_vec3(bp[3 * body], bp[3 * body + 1], bp[3 * body + 2]) - ref_rpos;
+            if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
+                const Quat rr = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
+                kp = quat_rotate(u.hinv, kp);
+                tkp = quat_rotate(calc_heading_quat_inv(rr), tkp);
+            }
+            const Vec3 d = tkp - kp;
+            s_terms[el * TP + o_key_t + k] = d.x * d.x + d.y * d.y + d.z * d.z;
+        }
+    }
+    if ((do_reward && cfg.use_contact_info) || (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0)) {
+        for (int it = tid; it < TILE * J; it += THREADS) {
+            const int el = it / J, c = it - el * J;
+            if (el >= tile_rows) continue;
+            const EnvU& u = s_env[el];
+            const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
+                        fz = view_ld3(env.char_contact_forces, u.e, c, 2);
+            if (do_reward && cfg.use_contact_info) {
+                // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
+                const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
+                const float rc = s_row[el * ROWP + L.o_hf + R.contacts + c];
+                float cr = -(1.0f - rc) * f;
+                cr += rc * f;
+                s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
+            }
+            if (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0 && !((cfg.fall_contact_body_mask >> c) & 1u)) {
+                // fall test (mgdm_dm_util.py:147-150, 349-362)
+                int fl = 0;
+                if (fabsf(fx) > 0.1f || fabsf(fy) > 0.1f || fabsf(fz) > 0.1f) fl |= 1;
+                const float bx = view_ld3(env.char_rigid_body_pos, u.e, c, 0), by = view_ld3(env.char_rigid_body_pos, u.e, c, 1),
+                            bz = view_ld3(env.char_rigid_body_pos, u.e, c, 2);
+                const int ix = grid_index(__fadd_rn(bx, u.eo.x), terrain.min_x, terrain.dx, terrain.dim_x);
+                const int iy = grid_index(__fadd_rn(by, u.eo.y), terrain.min_y, terrain.dy, terrain.dim_y);
+                const float th = __fadd_rn(__ldg(terrain.hf + (long long)ix * terrain.dim_y + iy), cfg.termination_height);
+                if (bz < th) fl |= 2;
+                if (fl) atomicOr(&s_env[el].flags, fl);
+            }
+        }
+    }
+    __syncthreads();
 
-        // ---- _update_reward (ig_parkour_env.py:984-1044) ------------------------------------
+    // ================================ phase D ====================================================
+    if (tid < tile_rows && (do_reward || do_done)) {
+        const int el = tid;
+        const EnvU& u = s_env[el];
+        const long long e = u.e;
+        const float* rsec = s_row + el * ROWP + L.o_hf;
+        const Vec3 ref_rpos = make_vec3(rsec[R.root_pos], rsec[R.root_pos + 1], rsec[R.root_pos + 2]);
+        const Quat ref_rrot = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
         if (do_reward) {
-            const float* rv = lib.vel + ref_idx0 * lib.vrec;
-            const Vec3 r_vel = make_vec3(__ldg(rv), __ldg(rv + 1), __ldg(rv + 2));
-            const Vec3 r_avel = make_vec3(__ldg(rv + 3), __ldg(rv + 4), __ldg(rv + 5));
-            // compute_deepmimic_reward (mgdm_dm_util.py:269-332)
-            float pose_t = 0.f;
-            if (first_group && lb.active && sub > 0) {
-                const float a = quat_diff_angle(char_q, ref_q);
-                pose_t = cfg.joint_err_w[sub - 1] * a * a;
-            }
-            float vel_t = 0.f;
-            for (int k = lane; k < D; k += 32) {
-                const float dv = __ldg(rv + 6 + k) - view_ld(env.char_dof_vel, e, k);
-                vel_t += cfg.dof_err_w[k] * dv * dv;
-            }
-            Vec3 rpd = ref_rpos - c_pos;
+            // _update_reward (ig_parkour_env.py:984-1044) + compute_deepmimic_reward (mgdm_dm_util.py:269-332)
+            const float* tm = s_terms + el * TP;
+            float pose_t = 0.f, vel_t = 0.f, key_t = 0.f, con_t = 0.f;
+            for (int k = 0; k < J - 1; ++k) pose_t += tm[o_pose_t + k];
+            for (int k = 0; k < D; ++k) vel_t += tm[o_vel_t + k];
+            for (int k = 0; k < K; ++k) key_t += tm[o_key_t + k];
+            Vec3 rpd = ref_rpos - u.c_pos;
             if (!cfg.track_root) { rpd.x = 0.f; rpd.y = 0.f; }
             if (!cfg.track_root_h) rpd.z = 0.f;
             const float root_pos_err = rpd.x * rpd.x + rpd.y * rpd.y + rpd.z * rpd.z;
-            Quat a_rot = c_rot, b_rot = ref_rrot;
-            Vec3 a_vel = c_vel, b_vel = r_vel, a_av = c_avel, b_av = r_avel;
-            Vec3 kp = sim_bpos - c_pos, tkp = ref_bpos - ref_rpos;
+            Quat a_rot = u.c_rot, b_rot = ref_rrot;
+            Vec3 a_vel = u.c_vel, a_av = u.c_avel;
+            Vec3 b_vel = make_vec3(rsec[R.root_vel], rsec[R.root_vel + 1], rsec[R.root_vel + 2]);
+            Vec3 b_av = make_vec3(rsec[R.root_ang_vel], rsec[R.root_ang_vel + 1], rsec[R.root_ang_vel + 2]);
             if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
                 const Quat hr = calc_heading_quat_inv(ref_rrot);
-                a_rot = quat_mul(hinv, c_rot); b_rot = quat_mul(hr, ref_rrot);
-                a_vel = quat_rotate(hinv, c_vel); b_vel = quat_rotate(hr, r_vel);
-                a_av = quat_rotate(hinv, c_avel); b_av = quat_rotate(hr, r_avel);
-                kp = quat_rotate(hinv, kp); tkp = quat_rotate(hr, tkp);
+                a_rot = quat_mul(u.hinv, u.c_rot); b_rot = quat_mul(hr, ref_rrot);
+                a_vel = quat_rotate(u.hinv, a_vel); b_vel = quat_rotate(hr, b_vel);
+                a_av = quat_rotate(u.hinv, a_av); b_av = quat_rotate(hr, b_av);
             }
-            float key_t = 0.f;
-            if (first_group && my_key >= 0) {
-                const Vec3 d = tkp - kp;
-                int mult = 0;
-                for (int k = 0; k < K; ++k) mult += (cfg.key_body_ids[k] == lb.body);
-                key_t = mult * (d.x * d.x + d.y * d.y + d.z * d.z);
+            const float rra = quat_diff_angle(a_rot, b_rot);
+            const float root_rot_err = rra * rra;
+            const Vec3 dv = b_vel - a_vel, dw = b_av - a_av;
+            const float root_vel_err = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
+            const float root_av_err = dw.x * dw.x + dw.y * dw.y + dw.z * dw.z;
+            const float pose_r = expf(-0.25f * pose_t);
+            const float vel_r = expf(-0.01f * vel_t);
+            const float root_pose_r = expf(-5.0f * (root_pos_err + 0.1f * root_rot_err));
+            const float root_vel_r = expf(-1.0f * (root_vel_err + 0.1f * root_av_err));
+            const float key_r = expf(-10.0f * key_t);
+            float total = cfg.pose_w * pose_r + cfg.vel_w * vel_r + cfg.root_pos_w * root_pose_r + cfg.root_vel_w * root_vel_r + cfg.key_pos_w * key_r;
+            float pen = 0.f;
+            if (cfg.use_contact_info) {
+                for (int k = 0; k < J; ++k) con_t += tm[o_con_t + k];
+                pen = con_t / (float)C;
+                total += pen;
             }
-            float con_t = 0.f;
-            if (cfg.use_contact_info && first_group && sub < C) {
-                // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
-                const float fx = view_ld3(env.char_contact_forces, e, sub, 0), fy = view_ld3(env.char_contact_forces, e, sub, 1),
-                            fz = view_ld3(env.char_contact_forces, e, sub, 2);
-                const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
-                float cr = -(1.0f - ref_contact) * f;
-                cr += ref_contact * f;
-                con_t = cfg.contact_weights[sub] * cr;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                pose_t += __shfl_xor_sync(FULL_MASK, pose_t, o);
-                vel_t += __shfl_xor_sync(FULL_MASK, vel_t, o);
-                key_t += __shfl_xor_sync(FULL_MASK, key_t, o);
-                con_t += __shfl_xor_sync(FULL_MASK, con_t, o);
-            }
-            if (lane == 0) {
-                float rra = quat_diff_angle(a_rot, b_rot);
-                const float root_rot_err = rra * rra;
-                const Vec3 dv = b_vel - a_vel, dw = b_av - a_av;
-                const float root_vel_err = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
-                const float root_av_err = dw.x * dw.x + dw.y * dw.y + dw.z * dw.z;
-                const float pose_r = expf(-0.25f * pose_t);
-                const float vel_r = expf(-0.01f * vel_t);
-                const float root_pose_r = expf(-5.0f * (root_pos_err + 0.1f * root_rot_err));
-                const float root_vel_r = expf(-1.0f * (root_vel_err + 0.1f * root_av_err));
-                const float key_r = expf(-10.0f * key_t);
-                float total = cfg.pose_w * pose_r + cfg.vel_w * vel_r + cfg.root_pos_w * root_pose_r + cfg.root_vel_w * root_vel_r + cfg.key_pos_w * key_r;
-                float pen = 0.f;
-                if (cfg.use_contact_info) { pen = con_t / (float)C; total += pen; }
-                env.reward_buf[e] = total;
-                if (env.reward_terms) {
-                    float4* t4 = reinterpret_cast<float4*>(env.reward_terms + e * 8);
-                    t4[0] = make_float4(pose_r, vel_r, root_pose_r, root_vel_r);
-                    t4[1] = make_float4(key_r, pen, total, 0.f);
-                }
+            env.reward_buf[e] = total;
+            if (env.reward_terms) {
+                float4* t4 = reinterpret_cast<float4*>(env.reward_terms + e * 8);
+                t4[0] = make_float4(pose_r, vel_r, root_pose_r, root_vel_r);
+                t4[1] = make_float4(key_r, pen, total, 0.f);
             }
         }
-
-        // ---- _update_done (ig_parkour_env.py:967-982; mgdm_dm_util.py:147-172, 334-402; dm_env.py:628-665)
         if (do_done) {
+            // _update_done (ig_parkour_env.py:967-982; mgdm_dm_util.py:147-172, 334-402; dm_env.py:628-665)
             int done = PARC_DONE_NULL;
-            if (time >= cfg.episode_length) done = PARC_DONE_TIME;
+            if (u.time >= cfg.episode_length) done = PARC_DONE_TIME;
             if (cfg.enable_early_termination) {
                 bool failed = false;
-                if (cfg.num_fall_contact_bodies > 0) {
-                    bool fc = false, fh = false;
-                    if (first_group && lb.active && !((cfg.fall_contact_body_mask >> sub) & 1u)) {
-                        const float fx = view_ld3(env.char_contact_forces, e, sub, 0), fy = view_ld3(env.char_contact_forces, e, sub, 1),
-                                    fz = view_ld3(env.char_contact_forces, e, sub, 2);
-                        fc = fabsf(fx) > 0.1f || fabsf(fy) > 0.1f || fabsf(fz) > 0.1f;
-                        const int ix = grid_index(__fadd_rn(sim_bpos.x, eox), terrain.min_x, terrain.dx, terrain.dim_x);
-                        const int iy = grid_index(__fadd_rn(sim_bpos.y, eoy), terrain.min_y, terrain.dy, terrain.dim_y);
-                        const float th = __fadd_rn(__ldg(terrain.hf + (long long)ix * terrain.dim_y + iy), cfg.termination_height);
-                        fh = sim_bpos.z < th;
-                    }
-                    failed = __any_sync(FULL_MASK, fc) && __any_sync(FULL_MASK, fh);
-                }
+                if (cfg.num_fall_contact_bodies > 0) failed = (u.flags & 1) && (u.flags & 2);
                 if (cfg.pose_termination) {
-                    bool pf = false;
-                    if (first_group && lb.active && sub > 0) {
-                        // (tar_body - tar_root) - (body - root), squared norm summed left to right
-                        const Vec3 a = make_vec3(__fsub_rn(sim_bpos.x, sim_b0.x), __fsub_rn(sim_bpos.y, sim_b0.y), __fsub_rn(sim_bpos.z, sim_b0.z));
-                        const Vec3 b = make_vec3(__fsub_rn(ref_bpos.x, ref_rpos.x), __fsub_rn(ref_bpos.y, ref_rpos.y), __fsub_rn(ref_bpos.z, ref_rpos.z));
-                        const Vec3 d = make_vec3(__fsub_rn(b.x, a.x), __fsub_rn(b.y, a.y), __fsub_rn(b.z, a.z));
-                        const float td = cfg.pose_termination_dist[sub - 1];
-                        pf = sqnorm3_seq(d) > __fmul_rn(td, td);
-                    }
-                    pf = __any_sync(FULL_MASK, pf);
+                    bool pf = (u.flags & 4) != 0;
                     if (cfg.track_root) {
-                        const Vec3 d = make_vec3(__fsub_rn(sim_b0.x, ref_rpos.x), __fsub_rn(sim_b0.y, ref_rpos.y), __fsub_rn(sim_b0.z, ref_rpos.z));
+                        const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, e, 0, 0), view_ld3(env.char_rigid_body_pos, e, 0, 1),
+                                                  view_ld3(env.char_rigid_body_pos, e, 0, 2));
+                        const Vec3 d = s0 - ref_rpos;
                         pf = pf || (sqnorm3_seq(d) > cfg.root_pos_termination_dist);   // host passes fp32(dist*dist)
-                        pf = pf || (fabsf(quat_diff_angle(c_rot, ref_rrot)) > cfg.root_rot_termination_angle);
+                        pf = pf || (fabsf(quat_diff_angle(u.c_rot, ref_rrot)) > cfg.root_rot_termination_angle);
                     }
                     failed = failed || pf;
                 }
-                failed = failed && (time > 1e-5f);
+                failed = failed && (u.time > 1e-5f);
                 if (failed) done = PARC_DONE_FAIL;
             }
             // DeepMimicEnv.update_done tail (dm_env.py:638-665)
-            const bool motion_end = (t0 >= mm.length) && (mm.loop_mode != PARC_LOOP_WRAP);
+            const bool motion_end = (u.t0 >= u.mm.length) && (u.mm.loop_mode != PARC_LOOP_WRAP);
             int code = 0;
             if (done == PARC_DONE_FAIL) code = 1;
             else if (done != PARC_DONE_NULL || motion_end) code = 2;
             if (motion_end) done = PARC_DONE_FAIL;
             if (cfg.never_done) done = PARC_DONE_NULL;
-            if (lane == 0) {
-                env.done_buf[e] = done;
-                if (env.done_code) env.done_code[e] = (unsigned char)code;
-                if (code != 0 && env.done_list) {
-                    const int slot = atomicAdd(env.done_count, 1);
-                    if (slot < env.num_envs) env.done_list[slot] = (int)e;   // a stale (un-zeroed) count must not overrun the list
-                }
+            env.done_buf[e] = done;
+            if (env.done_code) env.done_code[e] = (unsigned char)code;
+            if (code != 0 && env.done_list) {
+                const int slot = atomicAdd(env.done_count, 1);
+                if (slot < env.num_envs) env.done_list[slot] = (int)e;   // a stale (un-zeroed) count must not overrun the list
             }
         }
     }
 
-    // ---- observation rows leave the SM -------------------------------------------------------
-    if (do_obs) {
-        const long long row0 = (long long)blockIdx.x * TILE;
-        const long long rows = min((long long)TILE, n_rows - row0);
-        const long long total = rows * L.obs_dim;
-        if (bulk_ok && ((total & 3) == 0)) {
-            fence_async_smem();
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                float* g = env.obs_buf + row0 * env.obs_row_stride;
-                unsigned bytes = (unsigned)(total * 4);
-                unsigned off = 0;
-                while (off < bytes) {
-                    unsigned chunk = min(bytes - off, 32768u);
-                    bulk_store_s2g(reinterpret_cast<char*>(g) + off, reinterpret_cast<const char*>(smem) + off, chunk);
-                    off += chunk;
-                }
-                bulk_commit_wait_read();
+    // ================================ phase E ====================================================
+    // staged rows -> global: warp w streams env w; consecutive lanes write consecutive columns
+    {
+        const int warp = tid >> 5, lane = tid & 31;
+        for (int el = warp; el < tile_rows; el += THREADS / 32) {
+            const EnvU& u = s_env[el];
+            const float* row = s_row + el * ROWP;
+            if (do_obs) {
+                float* g = env.obs_buf + u.e * env.obs_row_stride;
+                for (int k = lane; k < L.o_hf; k += 32) g[k] = row[k];
             }
-        } else {
-            __syncwarp();
-            if (live) {
-                float* g = env.obs_buf + e * env.obs_row_stride;
-                for (int k = lane; k < L.obs_dim; k += 32) g[k] = srow[k];
+            if (do_ref) {
+                const float* rsec = row + L.o_hf;
+                for (int k = lane; k < R.width; k += 32) {
+                    const unsigned long long base = s_refmap[2 * k];
+                    if (base) *reinterpret_cast<float*>(base + (unsigned long long)u.e * s_refmap[2 * k + 1]) = rsec[k];
+                }
             }
         }
     }
@@ -473,7 +668,24 @@ __global__ void __launch_bounds__(STEP_THREADS) env_step_kernel(
 
 }  // namespace parc
 
+namespace parc {
+__global__ void selftest_div_kernel(const float* __restrict__ x, long long n, float d, float* __restrict__ q_fast, float* __restrict__ q_ieee) {
+    const float rc = __frcp_rn(d);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        q_fast[i] = div_const(x[i], d, rc);
+        q_ieee[i] = __fdiv_rn(x[i], d);
+    }
+}
+}  // namespace parc
+
 using namespace parc;
+
+extern "C" int parc_b200_selftest_div(const float* x, int64_t n, float d, float* q_fast, float* q_ieee, void* stream) {
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(x && q_fast && q_ieee, "selftest_div: NULL pointer");
+    selftest_div_kernel<<<kNumSMs * 8, 256, 0, as_stream(stream)>>>(x, n, d, q_fast, q_ieee);
+    return check_launch("selftest_div");
+}
 
 static int validate_env(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_env_config_t* cfg,
                         const parc_env_buffers_t* env, const char* who) {
@@ -532,8 +744,10 @@ extern "C" int parc_b200_env_step(const parc_char_model_t* m, const parc_motion_
     const ObsLayout L = make_layout(m->num_bodies, m->dof_size, lib->num_contacts, *cfg);
     PARC_REQUIRE(!(parts & PARC_STEP_OBS) || env->obs_row_stride >= L.obs_dim, "env_step: obs_row_stride %lld < obs_dim %d",
                  (long long)env->obs_row_stride, L.obs_dim);
-    const size_t smem = (parts & PARC_STEP_OBS) ? (size_t)TILE * L.obs_dim * sizeof(float) : 0;
-    PARC_REQUIRE(smem <= 227 * 1024, "env_step: observation tile of %zu bytes exceeds shared memory", smem);
+    PARC_REQUIRE((long long)terrain->dim_x * terrain->dim_y < (1ll << 31), "env_step: terrain has more than 2^31 cells");
+    const SmemPlan plan = make_plan(*m, lib->num_contacts, *cfg, L);
+    PARC_REQUIRE(plan.total <= 227 * 1024, "env_step: staging of %zu bytes exceeds shared memory", plan.total);
+    PARC_REQUIRE(plan.n_pose_threads <= STEP_THREADS - 32, "env_step: %d target steps leave no threads for the heightmap", cfg->num_tar_steps);
     return parc::launch_env_step(m, lib, terrain, cfg, env, parts, env_ids, n_rows, nullptr, nullptr, stream);
 }
 
@@ -544,23 +758,16 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
                     const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts, const int64_t* env_ids,
                     long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream) {
     const ObsLayout L = make_layout(m->num_bodies, m->dof_size, lib->num_contacts, *cfg);
-    const size_t smem = (parts & PARC_STEP_OBS) ? (size_t)TILE * L.obs_dim * sizeof(float) : 0;
-    const int bulk_ok = (env_ids == nullptr) && (env_ids32 == nullptr) && (env->obs_row_stride == L.obs_dim) &&
-                        ((reinterpret_cast<uintptr_t>(env->obs_buf) & 15) == 0);
-    const long long blocks = (max_rows + TILE - 1) / TILE;
-    cudaError_t ce;
-    if (m->num_bodies <= 16) {
-        ce = cudaFuncSetAttribute(env_step_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (ce == cudaSuccess)
-            env_step_kernel<16><<<(unsigned)blocks, STEP_THREADS, smem, as_stream(stream)>>>(
-                *m, *lib, *terrain, *cfg, *env, parts, (const long long*)env_ids, max_rows, bulk_ok, env_ids32, n_rows_dev);
-    } else {
-        ce = cudaFuncSetAttribute(env_step_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (ce == cudaSuccess)
-            env_step_kernel<32><<<(unsigned)blocks, STEP_THREADS, smem, as_stream(stream)>>>(
-                *m, *lib, *terrain, *cfg, *env, parts, (const long long*)env_ids, max_rows, bulk_ok, env_ids32, n_rows_dev);
+    const SmemPlan plan = make_plan(*m, lib->num_contacts, *cfg, L);
+    static size_t smem_attr = 0;   // opt-in dynamic shared memory, raised only when a larger plan shows up
+    if (plan.total > smem_attr) {
+        cudaError_t ce = cudaFuncSetAttribute(env_step_kernel<STEP_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
+        if (ce != cudaSuccess) { set_error("env_step: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+        smem_attr = plan.total;
     }
-    if (ce != cudaSuccess) { set_error("env_step: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+    const long long blocks = (max_rows + TILE - 1) / TILE;
+    env_step_kernel<STEP_THREADS><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+        *m, *lib, *terrain, *cfg, *env, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev);
     return check_launch("env_step");
 }
 }  // namespace parc

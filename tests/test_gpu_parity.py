@@ -142,6 +142,23 @@ def test_ray_heights_and_grid_index_bit_exact(model):
     assert torch.equal(terr.get_hf_val_from_points(pts.to(DEV)).cpu(), oterr.height_at(pts))
 
 
+def test_cell_index_division_is_correctly_rounded():
+    """The fused step's divide-by-cell-size (reciprocal + one fma correction) must equal div.rn bit for bit."""
+    from parc_b200 import _lib
+    g = torch.Generator().manual_seed(10)
+    n = 1 << 22
+    for d in (0.4, 0.1, 0.25, 1.0, 0.3):
+        x = (torch.rand(n, generator=g) * 900.0 - 450.0)
+        k = torch.arange(0, 4096, dtype=torch.float32)
+        x[:4096] = (k + 0.5) * torch.tensor(d, dtype=torch.float32)          # exact cell boundaries
+        x[4096:8192] = (k - 2048.0) * torch.tensor(d, dtype=torch.float32)
+        x = x.to(DEV)
+        qf, qi = torch.empty_like(x), torch.empty_like(x)
+        _lib.check(_lib.lib().parc_b200_selftest_div(_lib.ptr(x), n, d, _lib.ptr(qf), _lib.ptr(qi), _lib.stream_ptr(torch.device(DEV))))
+        assert torch.equal(qf, qi), "d=%g: %d quotients differ from div.rn" % (d, int((qf != qi).sum()))
+        assert torch.equal(qi.cpu(), x.cpu() / torch.tensor(d, dtype=torch.float32))
+
+
 # ------------------------------------------------------------------------------------- fused env step
 def _golden_env(model):
     from parc_b200.tracking_env import TrackingEnv, default_env_config
