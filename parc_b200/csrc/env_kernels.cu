@@ -88,7 +88,7 @@ struct SmemPlan {
     int n_pose_threads;      // TILE * n_pose
     int n_slots;             // bodies (other than the root) that have children: FK transforms kept
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
-    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, total;
+    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_counter, total;
 };
 
 __host__ __device__ inline int count_slots(const parc_char_model_t& cm) {
@@ -116,8 +116,44 @@ __host__ __device__ inline SmemPlan make_plan(const parc_char_model_t& cm, int C
     p.off_xf = o;     o += sizeof(float) * 7 * p.n_slots * p.n_pose_threads;   o = (o + 15) & ~size_t(15);
     p.off_terms = o;  o += sizeof(float) * TILE * p.term_pitch;          o = (o + 15) & ~size_t(15);
     p.off_refmap = o; o += 16 * (size_t)R.width;                         o = (o + 15) & ~size_t(15);
+    p.off_counter = o; o += 16;
     p.total = o;
     return p;
+}
+
+// Everything the kernel would otherwise re-derive per thread from the model / config, computed once
+// on the host per launch and passed by value.
+struct StepPlan {
+    ObsLayout L;
+    RefLayout R;
+    SmemPlan S;
+    unsigned has_child;                   // bit j: body j has children (root excluded from slots)
+    unsigned key_mask;                    // bit j: body j is listed in key_body_ids
+    int lrot_ident;                       // every _local_rotation is the identity
+    signed char slot[PARC_MAX_BODIES];    // shared-memory transform slot of body j, -1 if it has no children
+    float rdx, rdy;                       // correctly rounded 1/dx, 1/dy
+    float max_ix, max_iy;                 // dim - 1 as floats
+};
+
+inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const parc_terrain_t& tr) {
+    StepPlan sp;
+    sp.L = make_layout(cm.num_bodies, cm.dof_size, C, cfg);
+    sp.R = make_ref_layout(cm.num_bodies, cm.dof_size, C);
+    sp.S = make_plan(cm, C, cfg, sp.L);
+    sp.has_child = 0;
+    for (int j = 1; j < cm.num_bodies; ++j) sp.has_child |= 1u << cm.parent[j];
+    sp.key_mask = 0;
+    for (int k = 0; k < cfg.num_key_bodies; ++k) sp.key_mask |= 1u << cfg.key_body_ids[k];
+    sp.lrot_ident = 1;
+    int n = 0;
+    for (int j = 0; j < PARC_MAX_BODIES; ++j) sp.slot[j] = -1;
+    for (int j = 1; j < cm.num_bodies; ++j) {
+        if (!(cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f)) sp.lrot_ident = 0;
+        if ((sp.has_child >> j) & 1u) sp.slot[j] = (signed char)n++;
+    }
+    sp.rdx = 1.0f / tr.dx; sp.rdy = 1.0f / tr.dy;    // IEEE single division on the host == RN(1/d)
+    sp.max_ix = (float)(tr.dim_x - 1); sp.max_iy = (float)(tr.dim_y - 1);
+    return sp;
 }
 
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
@@ -168,11 +204,12 @@ __device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float
 }
 
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
+__global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
-    const __grid_constant__ parc_env_buffers_t env, const unsigned parts, const long long* __restrict__ env_ids,
-    const long long n_rows_host, const int* __restrict__ env_ids32, const int* __restrict__ n_rows_dev) {
+    const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
+    const long long* __restrict__ env_ids, const long long n_rows_host, const int* __restrict__ env_ids32,
+    const int* __restrict__ n_rows_dev) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const long long n_rows = n_rows_dev ? min((long long)*n_rows_dev, n_rows_host) : n_rows_host;
     const long long row0 = (long long)blockIdx.x * TILE;
@@ -181,15 +218,16 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
     const int J = cm.num_bodies, D = cm.dof_size, C = lib.num_contacts;
     const int S = cfg.enable_tar_obs ? cfg.num_tar_steps : 0;
     const int K = cfg.num_key_bodies, P = cfg.num_ray_points;
-    const ObsLayout L = make_layout(J, D, C, cfg);
-    const RefLayout R = make_ref_layout(J, D, C);
-    const SmemPlan plan = make_plan(cm, C, cfg, L);
+    const ObsLayout& L = sp.L;
+    const RefLayout& R = sp.R;
+    const SmemPlan& plan = sp.S;
     EnvU* s_env = reinterpret_cast<EnvU*>(smem_raw + plan.off_env);
     float* s_row = reinterpret_cast<float*>(smem_raw + plan.off_row);
     float4* s_charq = reinterpret_cast<float4*>(smem_raw + plan.off_charq);
     float* s_xf = reinterpret_cast<float*>(smem_raw + plan.off_xf);
     float* s_terms = reinterpret_cast<float*>(smem_raw + plan.off_terms);
     unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
+    int* s_chunk = reinterpret_cast<int*>(smem_raw + plan.off_counter);
     const int ROWP = plan.row_pitch;
     const int NPT = plan.n_pose_threads;
 
@@ -240,6 +278,7 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
             s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
         }
     }
+    if (tid == THREADS - 1) *s_chunk = 0;
     // A.3 per-env uniforms
     if (tid < TILE) {
         EnvU u;
@@ -369,11 +408,8 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                 }
             }
             // ---- joints: slerp + forward kinematics (kin_char_model.py:617-649), parents precede children ----
-            unsigned has_child = 0;
-            for (int j = 1; j < J; ++j) has_child |= 1u << cm.parent[j];
-            bool lrot_ident = true;
-            for (int j = 1; j < J; ++j)
-                lrot_ident = lrot_ident && cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f;
+            const unsigned has_child = sp.has_child;
+            const bool lrot_ident = sp.lrot_ident != 0;
             float* xf = s_xf + tid;                         // [slot][7][NPT], this thread's column
             for (int j = 1; j < J; ++j) {
                 Quat q;
@@ -382,8 +418,7 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                 const int par = cm.parent[j];
                 Vec3 ppos = rpos; Quat prot = rq;
                 if (par != 0) {
-                    const int ps = __popc(has_child & ((1u << par) - 1u) & ~1u);
-                    const float* x = xf + ps * 7 * NPT;
+                    const float* x = xf + (int)sp.slot[par] * 7 * NPT;
                     ppos = make_vec3(x[0], x[NPT], x[2 * NPT]);
                     prot = make_quat(x[3 * NPT], x[4 * NPT], x[5 * NPT], x[6 * NPT]);
                 }
@@ -391,8 +426,7 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                 if ((has_child >> j) & 1u) {
                     const Quat cq = lrot_ident ? q : quat_mul(make_quat(cm.local_rot[j][0], cm.local_rot[j][1], cm.local_rot[j][2], cm.local_rot[j][3]), q);
                     const Quat brot = quat_mul(prot, cq);
-                    const int sl = __popc(has_child & ((1u << j) - 1u) & ~1u);
-                    float* x = xf + sl * 7 * NPT;
+                    float* x = xf + (int)sp.slot[j] * 7 * NPT;
                     x[0] = bpos.x; x[NPT] = bpos.y; x[2 * NPT] = bpos.z;
                     x[3 * NPT] = brot.x; x[4 * NPT] = brot.y; x[5 * NPT] = brot.z; x[6 * NPT] = brot.w;
                 }
@@ -403,7 +437,7 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                     bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
                 } else {
                     tan_norm_exact(q, o_pose + 6 * (j - 1));
-                    for (int k = 0; k < K; ++k) {
+                    if ((sp.key_mask >> j) & 1u) for (int k = 0; k < K; ++k) {
                         if (cfg.key_body_ids[k] != j) continue;
                         Vec3 kp = bpos - rpos;
                         if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
@@ -413,7 +447,7 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                 }
             }
             // a key body may also be the root itself
-            if (!is_ref)
+            if (!is_ref && (sp.key_mask & 1u))
                 for (int k = 0; k < K; ++k)
                     if (cfg.key_body_ids[k] == 0) {
                         Vec3 kp = make_vec3(0.f, 0.f, 0.f);
@@ -422,30 +456,41 @@ __global__ void __launch_bounds__(THREADS, 2) env_step_kernel(
                         kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                     }
         }
-    } else if (P > 0 && (do_heights || do_obs)) {
+    }
+    if (P > 0 && (do_heights || do_obs)) {
         // ---- B.2 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
-        const int ht = tid - pose_warps * 32, hn = THREADS - pose_warps * 32;
-        const float rdx = __frcp_rn(terrain.dx), rdy = __frcp_rn(terrain.dy);
-        const float mx = (float)(terrain.dim_x - 1), my = (float)(terrain.dim_y - 1);
-        for (int el = 0; el < tile_rows; ++el) {
+        // Every warp (the pose warps once they are done) claims chunks of HCHUNK sample points from a
+        // block-wide counter, so the two kinds of work balance without a barrier in between.
+        // a chunk is a quarter of one env's sample points (rounded up to whole warps)
+        const int lane = tid & 31;
+        const int chunk_pts = (((P + 3) >> 2) + 31) & ~31;
+        const int n_chunks = tile_rows * 4;
+        const float rdx = sp.rdx, rdy = sp.rdy, mx = sp.max_ix, my = sp.max_iy;
+        for (;;) {
+            int c = 0;
+            if (lane == 0) c = atomicAdd(s_chunk, 1);
+            c = __shfl_sync(FULL_MASK, c, 0);
+            if (c >= n_chunks) break;
+            const int el = c >> 2, p0 = (c & 3) * chunk_pts, p1 = min(P, p0 + chunk_pts);
             const EnvU& u = s_env[el];
             float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
-            if (do_heights) {
-                const float ch = u.ch, sh = u.sh, gx = u.g.x, gy = u.g.y, gz = u.g.z;
-                for (int p = ht; p < P; p += hn) {
+            const float ch = u.ch, sh = u.sh, gx = u.g.x, gy = u.g.y, gz = u.g.z;
+            for (int p = p0 + lane; p < p1; p += 32) {
+                float v;
+                if (do_heights) {
                     const float2 pt = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + p);
                     float wx, wy;
                     ray_world(pt.x, pt.y, ch, sh, gx, gy, wx, wy);
                     const int ix = grid_index_fast(wx, terrain.min_x, terrain.dx, rdx, mx);
                     const int iy = grid_index_fast(wy, terrain.min_y, terrain.dy, rdy, my);
                     const float hv = __ldg(terrain.hf + ix * terrain.dim_y + iy);
-                    const float v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
-                    if (orow) orow[p] = v;
+                    v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
                     if (hrow) hrow[p] = v;
+                } else {
+                    v = hrow[p];
                 }
-            } else {
-                for (int p = ht; p < P; p += hn) orow[p] = hrow[p];
+                if (orow) orow[p] = v;
             }
         }
     }
@@ -757,8 +802,8 @@ namespace parc {
 int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
                     const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts, const int64_t* env_ids,
                     long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream) {
-    const ObsLayout L = make_layout(m->num_bodies, m->dof_size, lib->num_contacts, *cfg);
-    const SmemPlan plan = make_plan(*m, lib->num_contacts, *cfg, L);
+    const StepPlan sp = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
+    const SmemPlan& plan = sp.S;
     static size_t smem_attr = 0;   // opt-in dynamic shared memory, raised only when a larger plan shows up
     if (plan.total > smem_attr) {
         cudaError_t ce = cudaFuncSetAttribute(env_step_kernel<STEP_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
@@ -767,7 +812,7 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
     }
     const long long blocks = (max_rows + TILE - 1) / TILE;
     env_step_kernel<STEP_THREADS><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
-        *m, *lib, *terrain, *cfg, *env, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev);
+        *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev);
     return check_launch("env_step");
 }
 }  // namespace parc

@@ -139,22 +139,35 @@ __device__ __forceinline__ float quat_diff_angle(Quat q0, Quat q1) {
     return angle;
 }
 
+// sin(x) for 0 <= x <= pi/2 (slerp arguments never leave that range): odd Taylor polynomial to
+// x^11, truncation error < 6e-8 absolute, no range reduction and no slow path.
+__device__ __forceinline__ float sin_first_quadrant(float x) {
+    const float x2 = x * x;
+    float p = fmaf(x2, -2.5052108e-8f, 2.7557319e-6f);
+    p = fmaf(p, x2, -1.9841270e-4f);
+    p = fmaf(p, x2, 8.3333338e-3f);
+    p = fmaf(p, x2, -1.6666667e-1f);
+    return fmaf(x * x2, p, x);
+}
+
 // slerp, torch_util.py:474-499. Branches are taken on the SAME fp32 values as the reference
-// (dot product summed left to right, 1 - c*c unfused); the result is not re-normalised and the
-// |sin| < 0.001 fallback is the un-normalised midpoint, exactly as upstream.
+// (dot product summed left to right, 1 - c*c unfused, correctly rounded sqrt); the result is not
+// re-normalised and the |sin| < 0.001 fallback is the un-normalised midpoint, exactly as upstream.
+// The two special cases are tested first (the reference evaluates everything and selects): static
+// joints have c == 1 and would otherwise send sqrt / divide down their zero-operand slow paths.
 __device__ __forceinline__ Quat slerp(Quat q0, Quat q1, float t) {
     float c = dot4_seq(q0, q1);
     if (c < 0.f) q1 = make_quat(-q1.x, -q1.y, -q1.z, -q1.w);
     c = fabsf(c);
-    float half_theta = acosf(c);
-    float s = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(c, c)));
-    float ra = sinf((1.f - t) * half_theta) / s;
-    float rb = sinf(t * half_theta) / s;
-    Quat r = make_quat(ra * q0.x + rb * q1.x, ra * q0.y + rb * q1.y, ra * q0.z + rb * q1.z, ra * q0.w + rb * q1.w);
-    if (fabsf(s) < 0.001f)
-        r = make_quat(0.5f * q0.x + 0.5f * q1.x, 0.5f * q0.y + 0.5f * q1.y, 0.5f * q0.z + 0.5f * q1.z, 0.5f * q0.w + 0.5f * q1.w);
-    if (c >= 1.f) r = q0;
-    return r;
+    if (c >= 1.f) return q0;
+    const float s = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(c, c)));
+    if (s < 0.001f)
+        return make_quat(0.5f * q0.x + 0.5f * q1.x, 0.5f * q0.y + 0.5f * q1.y, 0.5f * q0.z + 0.5f * q1.z, 0.5f * q0.w + 0.5f * q1.w);
+    const float half_theta = acosf(c);
+    const float inv_s = __fdividef(1.0f, s);
+    const float ra = sin_first_quadrant((1.f - t) * half_theta) * inv_s;
+    const float rb = sin_first_quadrant(t * half_theta) * inv_s;
+    return make_quat(ra * q0.x + rb * q1.x, ra * q0.y + rb * q1.y, ra * q0.z + rb * q1.z, ra * q0.w + rb * q1.w);
 }
 
 // calc_heading, torch_util.py:501-510: atan2 of the rotated x axis.
