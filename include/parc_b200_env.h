@@ -225,6 +225,11 @@ int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_mot
 int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n,
                                  int64_t* ids, void* stream);
 
+/* Host-side plan of the fused step's forward kinematics (no GPU needed): the joints 1..J-1 are
+ * split into 4 ancestor-closed lists, one per cooperating thread. entries [4 * PARC_MAX_BODIES]:
+ * joint | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16, -1 past the end of a list. */
+int parc_b200_tree_parts(const parc_char_model_t* h_model, int32_t* entries, int32_t* max_len, int32_t* num_slots);
+
 /* Self-test of the heightmap index arithmetic: the fused step divides by the (uniform) cell size
  * with q = x*rc; r = fma(-q, d, x); q' = fma(r, rc, q), rc = RN(1/d), instead of div.rn. This entry
  * evaluates both on x [n] so that a test can demand bit-identical quotients (the nearest-cell

@@ -194,6 +194,7 @@ def _declare(lib):
                                         P(EnvConfigStruct), P(EnvBuffersStruct), vp, i32, u64, u64, i32, vp],
         "parc_b200_sample_motions_cdf": [vp, i32, vp, i64, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)   # AttributeError here = header/library mismatch: fail loudly

@@ -85,37 +85,29 @@ struct EnvU {
 struct SmemPlan {
     int row_pitch;           // floats per staged row: o_hf + ref width, forced odd
     int n_pose;              // poses per env: S + 2
-    int n_pose_threads;      // TILE * n_pose
-    int n_slots;             // bodies (other than the root) that have children: FK transforms kept
+    int n_slots;             // FK transforms a thread keeps: max over parts of bodies with children inside the part
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
-    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_counter, total;
+    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_tab, off_counter, total;
 };
 
-__host__ __device__ inline int count_slots(const parc_char_model_t& cm) {
-    unsigned has_child = 0;
-    for (int j = 1; j < cm.num_bodies; ++j) has_child |= 1u << cm.parent[j];
-    has_child &= ~1u;
-    int n = 0;
-    for (int j = 1; j < cm.num_bodies; ++j) n += (has_child >> j) & 1u;
-    return n;
-}
+constexpr int NPART = 4;                // threads cooperating on one (env, pose): each walks one part of the tree
 
-__host__ __device__ inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const ObsLayout& L) {
+inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const ObsLayout& L, int n_slots) {
     SmemPlan p;
     const int J = cm.num_bodies, D = cm.dof_size;
     const RefLayout R = make_ref_layout(J, D, C);
     p.row_pitch = (L.o_hf + R.width) | 1;
     p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
-    p.n_pose_threads = TILE * p.n_pose;
-    p.n_slots = count_slots(cm);
+    p.n_slots = n_slots;
     p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
     size_t o = 0;
     p.off_env = o;    o += sizeof(EnvU) * TILE;                          o = (o + 15) & ~size_t(15);
     p.off_row = o;    o += sizeof(float) * TILE * p.row_pitch;           o = (o + 15) & ~size_t(15);
     p.off_charq = o;  o += sizeof(float4) * TILE * J;                    o = (o + 15) & ~size_t(15);
-    p.off_xf = o;     o += sizeof(float) * 7 * p.n_slots * p.n_pose_threads;   o = (o + 15) & ~size_t(15);
+    p.off_xf = o;     o += sizeof(float) * 7 * p.n_slots * STEP_THREADS;       o = (o + 15) & ~size_t(15);
     p.off_terms = o;  o += sizeof(float) * TILE * p.term_pitch;          o = (o + 15) & ~size_t(15);
     p.off_refmap = o; o += 16 * (size_t)R.width;                         o = (o + 15) & ~size_t(15);
+    p.off_tab = o;    o += sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J;   o = (o + 15) & ~size_t(15);
     p.off_counter = o; o += 16;
     p.total = o;
     return p;
@@ -130,27 +122,123 @@ struct StepPlan {
     unsigned has_child;                   // bit j: body j has children (root excluded from slots)
     unsigned key_mask;                    // bit j: body j is listed in key_body_ids
     int lrot_ident;                       // every _local_rotation is the identity
-    signed char slot[PARC_MAX_BODIES];    // shared-memory transform slot of body j, -1 if it has no children
+    int max_part_len;                     // longest joint list of a part
+    // part_entry[p][i]: joint j | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16; -1 past the end.
+    // A part's list is closed under ancestors (shared ancestors are recomputed, only one part owns = outputs them).
+    int part_entry[NPART][PARC_MAX_BODIES];
     float rdx, rdy;                       // correctly rounded 1/dx, 1/dy
     float max_ix, max_iy;                 // dim - 1 as floats
 };
 
+// Splits the joints 1..J-1 into NPART ancestor-closed lists of similar length: start from the
+// subtrees below the root, keep splitting the largest one at its first branching body (the chain
+// above the branch is recomputed by every piece, owned by the first), then pack the pieces into
+// NPART bins, largest first.
+struct TreeUnit { int prefix[PARC_MAX_BODIES]; unsigned char prefix_owned[PARC_MAX_BODIES]; int n_prefix; int top; int size; };
+
+static int subtree_size(const parc_char_model_t& cm, int r) {
+    int n = 1;
+    for (int j = r + 1; j < cm.num_bodies; ++j) {
+        int a = cm.parent[j];
+        while (a > r) a = cm.parent[a];
+        if (a == r) ++n;
+    }
+    return n;
+}
+static bool in_subtree(const parc_char_model_t& cm, int r, int j) {
+    while (j > r) j = cm.parent[j];
+    return j == r;
+}
+
 inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const parc_terrain_t& tr) {
     StepPlan sp;
-    sp.L = make_layout(cm.num_bodies, cm.dof_size, C, cfg);
-    sp.R = make_ref_layout(cm.num_bodies, cm.dof_size, C);
-    sp.S = make_plan(cm, C, cfg, sp.L);
+    const int J = cm.num_bodies;
+    sp.L = make_layout(J, cm.dof_size, C, cfg);
+    sp.R = make_ref_layout(J, cm.dof_size, C);
     sp.has_child = 0;
-    for (int j = 1; j < cm.num_bodies; ++j) sp.has_child |= 1u << cm.parent[j];
+    for (int j = 1; j < J; ++j) sp.has_child |= 1u << cm.parent[j];
     sp.key_mask = 0;
     for (int k = 0; k < cfg.num_key_bodies; ++k) sp.key_mask |= 1u << cfg.key_body_ids[k];
     sp.lrot_ident = 1;
-    int n = 0;
-    for (int j = 0; j < PARC_MAX_BODIES; ++j) sp.slot[j] = -1;
-    for (int j = 1; j < cm.num_bodies; ++j) {
+    for (int j = 1; j < J; ++j)
         if (!(cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f)) sp.lrot_ident = 0;
-        if ((sp.has_child >> j) & 1u) sp.slot[j] = (signed char)n++;
+    // ---- units ----
+    TreeUnit units[2 * PARC_MAX_BODIES];
+    int nu = 0;
+    for (int j = 1; j < J; ++j)
+        if (cm.parent[j] == 0) { TreeUnit u; u.n_prefix = 0; u.top = j; u.size = subtree_size(cm, j); units[nu++] = u; }
+    const int target = (J - 1 + NPART - 1) / NPART;
+    for (int iter = 0; iter < 4 * PARC_MAX_BODIES; ++iter) {
+        int best = -1;
+        for (int a = 0; a < nu; ++a)
+            if (units[a].size > target && (best < 0 || units[a].size > units[best].size)) {
+                // splittable only if some body on the single-child chain below `top` branches
+                int node = units[a].top, nch;
+                for (;;) { nch = 0; int only = -1; for (int j = node + 1; j < J; ++j) if (cm.parent[j] == node) { ++nch; only = j; } if (nch != 1) break; node = only; }
+                if (nch >= 2) best = a;
+            }
+        if (best < 0 || (nu >= NPART && units[best].size <= target + 1) || nu + PARC_MAX_BODIES / 2 > 2 * PARC_MAX_BODIES) break;
+        TreeUnit u = units[best];
+        int node = u.top;
+        for (;;) {
+            u.prefix[u.n_prefix] = node; u.prefix_owned[u.n_prefix] = 1; ++u.n_prefix;
+            int nch = 0, only = -1;
+            for (int j = node + 1; j < J; ++j) if (cm.parent[j] == node) { ++nch; only = j; }
+            if (nch != 1) break;
+            node = only;
+        }
+        units[best] = units[--nu];
+        bool first = true;
+        for (int j = node + 1; j < J; ++j)
+            if (cm.parent[j] == node) {
+                TreeUnit c = u;
+                if (!first) for (int k = 0; k < c.n_prefix; ++k) c.prefix_owned[k] = 0;
+                first = false;
+                c.top = j; c.size = c.n_prefix + subtree_size(cm, j);
+                units[nu++] = c;
+            }
     }
+    // ---- pack into NPART bins, largest unit first ----
+    unsigned bin_has[NPART] = {0, 0, 0, 0}, bin_owned[NPART] = {0, 0, 0, 0};
+    int load[NPART] = {0, 0, 0, 0};
+    bool used[2 * PARC_MAX_BODIES] = {false};
+    for (int n = 0; n < nu; ++n) {
+        int a = -1;
+        for (int k = 0; k < nu; ++k) if (!used[k] && (a < 0 || units[k].size > units[a].size)) a = k;
+        used[a] = true;
+        int b = 0;
+        for (int k = 1; k < NPART; ++k) if (load[k] < load[b]) b = k;
+        const TreeUnit& u = units[a];
+        for (int k = 0; k < u.n_prefix; ++k) { bin_has[b] |= 1u << u.prefix[k]; if (u.prefix_owned[k]) bin_owned[b] |= 1u << u.prefix[k]; }
+        for (int j = u.top; j < J; ++j) if (in_subtree(cm, u.top, j)) { bin_has[b] |= 1u << j; bin_owned[b] |= 1u << j; }
+        load[b] = __builtin_popcount(bin_has[b]);
+    }
+    // a prefix body owned by a unit packed next to another copy must be owned exactly once overall
+    unsigned owned_seen = 0;
+    for (int b = 0; b < NPART; ++b) { bin_owned[b] &= ~owned_seen; owned_seen |= bin_owned[b]; }
+    sp.max_part_len = 0;
+    int max_slots = 1;
+    for (int b = 0; b < NPART; ++b) {
+        int slot_of[PARC_MAX_BODIES];
+        int ns = 0, len = 0;
+        for (int j = 1; j < J; ++j) {
+            slot_of[j] = -1;
+            if (!((bin_has[b] >> j) & 1u)) continue;
+            bool child_in_bin = false;
+            for (int c = j + 1; c < J; ++c) if (cm.parent[c] == j && ((bin_has[b] >> c) & 1u)) child_in_bin = true;
+            if (child_in_bin) slot_of[j] = ns++;
+        }
+        for (int j = 1; j < J; ++j) {
+            if (!((bin_has[b] >> j) & 1u)) continue;
+            const int par = cm.parent[j];
+            const int pslot = par == 0 ? -1 : slot_of[par];
+            sp.part_entry[b][len++] = j | ((int)((bin_owned[b] >> j) & 1u) << 8) | ((slot_of[j] + 1) << 12) | ((pslot + 1) << 16);
+        }
+        for (int k = len; k < PARC_MAX_BODIES; ++k) sp.part_entry[b][k] = -1;
+        if (len > sp.max_part_len) sp.max_part_len = len;
+        if (ns > max_slots) max_slots = ns;
+    }
+    sp.S = make_plan(cm, C, cfg, sp.L, max_slots);
     sp.rdx = 1.0f / tr.dx; sp.rdy = 1.0f / tr.dy;    // IEEE single division on the host == RN(1/d)
     sp.max_ix = (float)(tr.dim_x - 1); sp.max_iy = (float)(tr.dim_y - 1);
     return sp;
@@ -228,8 +316,9 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     float* s_terms = reinterpret_cast<float*>(smem_raw + plan.off_terms);
     unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
     int* s_chunk = reinterpret_cast<int*>(smem_raw + plan.off_counter);
+    int* s_part = reinterpret_cast<int*>(smem_raw + plan.off_tab);
+    float* s_jc = reinterpret_cast<float*>(smem_raw + plan.off_tab + sizeof(int) * NPART * PARC_MAX_BODIES);
     const int ROWP = plan.row_pitch;
-    const int NPT = plan.n_pose_threads;
 
     const bool do_heights = parts & PARC_STEP_HEIGHTS;
     const bool do_obs = parts & PARC_STEP_OBS;
@@ -279,6 +368,11 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         }
     }
     if (tid == THREADS - 1) *s_chunk = 0;
+    for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_part[k] = sp.part_entry[k / PARC_MAX_BODIES][k % PARC_MAX_BODIES];
+    for (int k = tid; k < 8 * J; k += THREADS) {
+        const int j = k >> 3, c = k & 7;
+        s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
+    }
     // A.3 per-env uniforms
     if (tid < TILE) {
         EnvU u;
@@ -317,145 +411,155 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     __syncthreads();
 
     // ================================ phase B ====================================================
-    const int pose_warps = (NPT + 31) >> 5;
+    static_assert(TILE * NPART == 32, "one warp = one pose of the tile's envs x NPART tree parts");
     const bool pose_work = do_obs || need_ref_pose;
-    if (tid < pose_warps * 32) {
-        // ---- B.1 one thread per (env, pose); pose-major so that a warp holds few distinct poses ----
-        const int pose = tid / TILE, el = tid - pose * TILE;
+    // ---- B.1 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
+    //      walks its own ancestor-closed part of the joint tree, so all lanes of a warp run the same code ----
+    for (int pose = tid >> 5; pose_work && pose < plan.n_pose; pose += THREADS / 32) {
+        const int lane = tid & 31, el = lane / NPART, part = lane - el * NPART;
         const bool is_ref = pose == 0, is_char = pose == S + 1, is_tar = pose >= 1 && pose <= S;
         const bool wanted = (is_ref && need_ref_pose) || (is_tar && do_obs) || (is_char && do_obs);
-        if (pose_work && tid < NPT && wanted && s_env[el].live) {
-            const EnvU& u = s_env[el];
-            float* row = s_row + el * ROWP;
-            float* rsec = row + L.o_hf;                    // ref_* section
-            const float *r0 = nullptr, *r1 = nullptr;
-            float b = 0.f, omb = 1.f;
-            Quat rq = u.c_rot;
-            Vec3 rpos = u.c_pos;
-            if (!is_char) {
-                // MotionLib.calc_motion_frame (motion_lib.py:94-126); fetch_tar_obs_data (mgdm_dm_util.py:221-244)
-                const float t = is_ref ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
-                const FrameBlend fb = calc_frame_blend(u.mm, t);
-                r0 = lib.interp + fb.idx0 * lib.irec;
-                r1 = lib.interp + fb.idx1 * lib.irec;
-                b = fb.blend; omb = __fsub_rn(1.0f, b);
-                rq = slerp(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), b);
-                const float4 p0 = ldg4(r0 + 4 * J), p1 = ldg4(r1 + 4 * J);
-                rpos = make_vec3(__fadd_rn(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x), u.tox),
-                                 __fadd_rn(__fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y), u.toy),
-                                 __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
-                if (is_ref) s_env[el].vel_rec = lib.vel + fb.idx0 * lib.vrec;
-            }
-            // ---- root-level outputs ----
-            float* o_pose = nullptr;        // start of this pose's joint tan-norm block
-            float* o_key = nullptr;         // start of this pose's key-body block
-            Vec3 rp_obs = make_vec3(0.f, 0.f, 0.f);
-            if (is_ref) {
+        if (!wanted || !s_env[el].live) continue;
+        const EnvU& u = s_env[el];
+        float* row = s_row + el * ROWP;
+        float* rsec = row + L.o_hf;                    // ref_* section
+        const float *r0 = nullptr, *r1 = nullptr;
+        float b = 0.f, omb = 1.f;
+        Quat rq = u.c_rot;
+        Vec3 rpos = u.c_pos;
+        const float* vrec = nullptr;
+        if (!is_char) {
+            // MotionLib.calc_motion_frame (motion_lib.py:94-126); fetch_tar_obs_data (mgdm_dm_util.py:221-244)
+            const float t = is_ref ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
+            const FrameBlend fb = calc_frame_blend(u.mm, t);
+            r0 = lib.interp + fb.idx0 * lib.irec;
+            r1 = lib.interp + fb.idx1 * lib.irec;
+            b = fb.blend; omb = __fsub_rn(1.0f, b);
+            rq = slerp(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), b);
+            const float4 p0 = ldg4(r0 + 4 * J), p1 = ldg4(r1 + 4 * J);
+            rpos = make_vec3(__fadd_rn(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x), u.tox),
+                             __fadd_rn(__fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y), u.toy),
+                             __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
+            vrec = lib.vel + fb.idx0 * lib.vrec;
+        }
+        // ---- root-level outputs (scalar pieces by part 0, the per-dof / per-body lists strided over the parts) ----
+        float* o_pose = nullptr;        // start of this pose's joint tan-norm block
+        float* o_key = nullptr;         // start of this pose's key-body block
+        Vec3 rp_obs = make_vec3(0.f, 0.f, 0.f);
+        if (is_ref) {
+            if (part == 0) {
                 rsec[R.root_pos] = rpos.x; rsec[R.root_pos + 1] = rpos.y; rsec[R.root_pos + 2] = rpos.z;
                 rsec[R.root_rot] = rq.x; rsec[R.root_rot + 1] = rq.y; rsec[R.root_rot + 2] = rq.z; rsec[R.root_rot + 3] = rq.w;
                 rsec[R.body_pos] = rpos.x; rsec[R.body_pos + 1] = rpos.y; rsec[R.body_pos + 2] = rpos.z;
-                // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
-                const float* v = s_env[el].vel_rec;
-                for (int k = 0; k < 6 + D; k += 4) {
-                    const float4 x = ldg4(v + k);
-                    const float xs[4] = {x.x, x.y, x.z, x.w};
+            }
+            // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
+            for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
+                const float4 x = ldg4(vrec + k);
+                const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const int kk = k + c;
-                        if (kk < 3) rsec[R.root_vel + kk] = xs[c];
-                        else if (kk < 6) rsec[R.root_ang_vel + kk - 3] = xs[c];
-                        else if (kk < 6 + D) rsec[R.dof_vel + kk - 6] = xs[c];
-                    }
+                for (int c = 0; c < 4; ++c) {
+                    const int kk = k + c;
+                    if (kk < 3) rsec[R.root_vel + kk] = xs[c];
+                    else if (kk < 6) rsec[R.root_ang_vel + kk - 3] = xs[c];
+                    else if (kk < 6 + D) rsec[R.dof_vel + kk - 6] = xs[c];
                 }
-            } else if (is_tar) {
-                // compute_tar_obs (mgdm_dm_util.py:404-461) for target step pose-1
-                float* o = row + L.o_tar + (pose - 1) * L.tar_step_dim;
-                rp_obs = rpos - u.c_pos;
-                Quat oq = rq;
-                if (!cfg.global_obs) { rp_obs = quat_rotate(u.hinv, rp_obs); oq = quat_mul(u.hinv, rq); }
+            }
+        } else if (is_tar) {
+            // compute_tar_obs (mgdm_dm_util.py:404-461) for target step pose-1
+            float* o = row + L.o_tar + (pose - 1) * L.tar_step_dim;
+            rp_obs = rpos - u.c_pos;
+            Quat oq = rq;
+            if (!cfg.global_obs) { rp_obs = quat_rotate(u.hinv, rp_obs); oq = quat_mul(u.hinv, rq); }
+            if (part == 0) {
                 o[0] = rp_obs.x; o[1] = rp_obs.y; o[2] = rp_obs.z;
                 tan_norm_exact(oq, o + 3);
-                o_pose = o + 9; o_key = o + 9 + 6 * (J - 1);
-            } else {
-                // compute_char_obs (ig_char_env.py:581-625)
-                float* o = row + L.root_h;
+            }
+            o_pose = o + 9; o_key = o + 9 + 6 * (J - 1);
+        } else {
+            // compute_char_obs (ig_char_env.py:581-625)
+            float* o = row + L.root_h;
+            if (part == 0) {
                 if (L.root_h) row[0] = u.c_pos.z;
                 Quat oq = u.c_rot; Vec3 v = u.c_vel, w = u.c_avel;
                 if (!cfg.global_obs) { oq = quat_mul(u.hinv, u.c_rot); v = quat_rotate(u.hinv, u.c_vel); w = quat_rotate(u.hinv, u.c_avel); }
                 tan_norm_exact(oq, o);
                 o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
-                o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
-                for (int k = 0; k < D; ++k) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
-                if (cfg.use_contact_info) {
-                    // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
-                    for (int c = 0; c < J; ++c) {
-                        const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
-                                    fz = view_ld3(env.char_contact_forces, u.e, c, 2);
-                        row[L.o_charc + c] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
-                    }
+            }
+            o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
+            for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
+            if (cfg.use_contact_info) {
+                // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+                for (int c = part; c < J; c += NPART) {
+                    const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
+                                fz = view_ld3(env.char_contact_forces, u.e, c, 2);
+                    row[L.o_charc + c] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
                 }
             }
-            // contact labels: lerp of the two records (motion_lib.py:121)
-            if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
-                float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
-                const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
-                for (int c = 0; c < C; c += 4) {
-                    const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
-                    oc[c] = lerp_exact(omb, a.x, b, d.x);
-                    if (c + 1 < C) oc[c + 1] = lerp_exact(omb, a.y, b, d.y);
-                    if (c + 2 < C) oc[c + 2] = lerp_exact(omb, a.z, b, d.z);
-                    if (c + 3 < C) oc[c + 3] = lerp_exact(omb, a.w, b, d.w);
-                }
-            }
-            // ---- joints: slerp + forward kinematics (kin_char_model.py:617-649), parents precede children ----
-            const unsigned has_child = sp.has_child;
-            const bool lrot_ident = sp.lrot_ident != 0;
-            float* xf = s_xf + tid;                         // [slot][7][NPT], this thread's column
-            for (int j = 1; j < J; ++j) {
-                Quat q;
-                if (is_char) q = quat_from_f4(s_charq[el * J + j]);
-                else q = slerp(quat_from_f4(ldg4(r0 + 4 * j)), quat_from_f4(ldg4(r1 + 4 * j)), b);
-                const int par = cm.parent[j];
-                Vec3 ppos = rpos; Quat prot = rq;
-                if (par != 0) {
-                    const float* x = xf + (int)sp.slot[par] * 7 * NPT;
-                    ppos = make_vec3(x[0], x[NPT], x[2 * NPT]);
-                    prot = make_quat(x[3 * NPT], x[4 * NPT], x[5 * NPT], x[6 * NPT]);
-                }
-                const Vec3 bpos = ppos + quat_rotate(prot, make_vec3(cm.local_trans[j][0], cm.local_trans[j][1], cm.local_trans[j][2]));
-                if ((has_child >> j) & 1u) {
-                    const Quat cq = lrot_ident ? q : quat_mul(make_quat(cm.local_rot[j][0], cm.local_rot[j][1], cm.local_rot[j][2], cm.local_rot[j][3]), q);
-                    const Quat brot = quat_mul(prot, cq);
-                    float* x = xf + (int)sp.slot[j] * 7 * NPT;
-                    x[0] = bpos.x; x[NPT] = bpos.y; x[2 * NPT] = bpos.z;
-                    x[3 * NPT] = brot.x; x[4 * NPT] = brot.y; x[5 * NPT] = brot.z; x[6 * NPT] = brot.w;
-                }
-                if (is_ref) {
-                    float* jr = rsec + R.joint_rot + 4 * (j - 1);
-                    jr[0] = q.x; jr[1] = q.y; jr[2] = q.z; jr[3] = q.w;
-                    float* bp = rsec + R.body_pos + 3 * j;
-                    bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
-                } else {
-                    tan_norm_exact(q, o_pose + 6 * (j - 1));
-                    if ((sp.key_mask >> j) & 1u) for (int k = 0; k < K; ++k) {
-                        if (cfg.key_body_ids[k] != j) continue;
-                        Vec3 kp = bpos - rpos;
-                        if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
-                        float* kd = o_key + 3 * k;
-                        kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
-                    }
-                }
-            }
-            // a key body may also be the root itself
-            if (!is_ref && (sp.key_mask & 1u))
-                for (int k = 0; k < K; ++k)
-                    if (cfg.key_body_ids[k] == 0) {
-                        Vec3 kp = make_vec3(0.f, 0.f, 0.f);
-                        if (!cfg.global_obs && is_tar) kp = kp + rp_obs;
-                        float* kd = o_key + 3 * k;
-                        kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
-                    }
         }
+        // contact labels: lerp of the two records (motion_lib.py:121)
+        if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
+            float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
+            const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
+            for (int c = 4 * part; c < C; c += 4 * NPART) {
+                const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
+                oc[c] = lerp_exact(omb, a.x, b, d.x);
+                if (c + 1 < C) oc[c + 1] = lerp_exact(omb, a.y, b, d.y);
+                if (c + 2 < C) oc[c + 2] = lerp_exact(omb, a.z, b, d.z);
+                if (c + 3 < C) oc[c + 3] = lerp_exact(omb, a.w, b, d.w);
+            }
+        }
+        // ---- joints of this part: slerp + forward kinematics (kin_char_model.py:617-649) ----
+        const bool lrot_ident = sp.lrot_ident != 0;
+        float* xf = s_xf + tid;                         // [slot][7][THREADS], this thread's column
+        const int* my_part = s_part + part * PARC_MAX_BODIES;
+        for (int i = 0; i < sp.max_part_len; ++i) {
+            const int entry = my_part[i];
+            if (entry < 0) continue;
+            const int j = entry & 0xff, owned = (entry >> 8) & 1, st_slot = ((entry >> 12) & 0xf) - 1, p_slot = ((entry >> 16) & 0xf) - 1;
+            Quat q;
+            if (is_char) q = quat_from_f4(s_charq[el * J + j]);
+            else q = slerp(quat_from_f4(ldg4(r0 + 4 * j)), quat_from_f4(ldg4(r1 + 4 * j)), b);
+            Vec3 ppos = rpos; Quat prot = rq;
+            if (p_slot >= 0) {
+                const float* x = xf + p_slot * 7 * THREADS;
+                ppos = make_vec3(x[0], x[THREADS], x[2 * THREADS]);
+                prot = make_quat(x[3 * THREADS], x[4 * THREADS], x[5 * THREADS], x[6 * THREADS]);
+            }
+            const float* jc = s_jc + 8 * j;
+            const Vec3 bpos = ppos + quat_rotate(prot, make_vec3(jc[0], jc[1], jc[2]));
+            if (st_slot >= 0) {
+                const Quat cq = lrot_ident ? q : quat_mul(make_quat(jc[3], jc[4], jc[5], jc[6]), q);
+                const Quat brot = quat_mul(prot, cq);
+                float* x = xf + st_slot * 7 * THREADS;
+                x[0] = bpos.x; x[THREADS] = bpos.y; x[2 * THREADS] = bpos.z;
+                x[3 * THREADS] = brot.x; x[4 * THREADS] = brot.y; x[5 * THREADS] = brot.z; x[6 * THREADS] = brot.w;
+            }
+            if (!owned) continue;
+            if (is_ref) {
+                float* jr = rsec + R.joint_rot + 4 * (j - 1);
+                jr[0] = q.x; jr[1] = q.y; jr[2] = q.z; jr[3] = q.w;
+                float* bp = rsec + R.body_pos + 3 * j;
+                bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
+            } else {
+                tan_norm_exact(q, o_pose + 6 * (j - 1));
+                if ((sp.key_mask >> j) & 1u) for (int k = 0; k < K; ++k) {
+                    if (cfg.key_body_ids[k] != j) continue;
+                    Vec3 kp = bpos - rpos;
+                    if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
+                    float* kd = o_key + 3 * k;
+                    kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+                }
+            }
+        }
+        // a key body may also be the root itself
+        if (!is_ref && part == 0 && (sp.key_mask & 1u))
+            for (int k = 0; k < K; ++k)
+                if (cfg.key_body_ids[k] == 0) {
+                    Vec3 kp = make_vec3(0.f, 0.f, 0.f);
+                    if (!cfg.global_obs && is_tar) kp = kp + rp_obs;
+                    float* kd = o_key + 3 * k;
+                    kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+                }
     }
     if (P > 0 && (do_heights || do_obs)) {
         // ---- B.2 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
@@ -732,6 +836,20 @@ extern "C" int parc_b200_selftest_div(const float* x, int64_t n, float d, float*
     return check_launch("selftest_div");
 }
 
+extern "C" int parc_b200_tree_parts(const parc_char_model_t* m, int32_t* entries, int32_t* max_len, int32_t* num_slots) {
+    if (!model_ok(m, "tree_parts")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(entries && max_len && num_slots, "tree_parts: NULL output");
+    parc_env_config_t cfg = {};
+    parc_terrain_t tr = {};
+    tr.dx = tr.dy = 1.f; tr.dim_x = tr.dim_y = 1;
+    const StepPlan sp = make_step_plan(*m, 0, cfg, tr);
+    for (int p = 0; p < NPART; ++p)
+        for (int i = 0; i < PARC_MAX_BODIES; ++i) entries[p * PARC_MAX_BODIES + i] = sp.part_entry[p][i];
+    *max_len = sp.max_part_len;
+    *num_slots = sp.S.n_slots;
+    return PARC_OK;
+}
+
 static int validate_env(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_env_config_t* cfg,
                         const parc_env_buffers_t* env, const char* who) {
     if (!model_ok(m, who)) return PARC_ERR_INVALID_ARG;
@@ -790,9 +908,8 @@ extern "C" int parc_b200_env_step(const parc_char_model_t* m, const parc_motion_
     PARC_REQUIRE(!(parts & PARC_STEP_OBS) || env->obs_row_stride >= L.obs_dim, "env_step: obs_row_stride %lld < obs_dim %d",
                  (long long)env->obs_row_stride, L.obs_dim);
     PARC_REQUIRE((long long)terrain->dim_x * terrain->dim_y < (1ll << 31), "env_step: terrain has more than 2^31 cells");
-    const SmemPlan plan = make_plan(*m, lib->num_contacts, *cfg, L);
-    PARC_REQUIRE(plan.total <= 227 * 1024, "env_step: staging of %zu bytes exceeds shared memory", plan.total);
-    PARC_REQUIRE(plan.n_pose_threads <= STEP_THREADS - 32, "env_step: %d target steps leave no threads for the heightmap", cfg->num_tar_steps);
+    const StepPlan sp_check = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
+    PARC_REQUIRE(sp_check.S.total <= 227 * 1024, "env_step: staging of %zu bytes exceeds shared memory", sp_check.S.total);
     return parc::launch_env_step(m, lib, terrain, cfg, env, parts, env_ids, n_rows, nullptr, nullptr, stream);
 }
 
