@@ -569,7 +569,8 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         const int lane = tid & 31;
         const int chunk_pts = (((P + 3) >> 2) + 31) & ~31;
         const int n_chunks = tile_rows * 4;
-        const float rdx = sp.rdx, rdy = sp.rdy, mx = sp.max_ix, my = sp.max_iy;
+        const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
+        const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1;
         for (;;) {
             int c = 0;
             if (lane == 0) c = atomicAdd(s_chunk, 1);
@@ -579,15 +580,24 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
             const EnvU& u = s_env[el];
             float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
-            const float ch = u.ch, sh = u.sh, gx = u.g.x, gy = u.g.y, gz = u.g.z;
+            // packed fp32x2 arithmetic (FMUL2 / FADD2 / FFMA2, sm_100): x and y of a sample point share every
+            // instruction; each lane of a pair is the same IEEE operation as the scalar form, so cells stay bit-exact
+            const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
+            const float gz = u.g.z;
             for (int p = p0 + lane; p < p1; p += 32) {
                 float v;
                 if (do_heights) {
                     const float2 pt = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + p);
-                    float wx, wy;
-                    ray_world(pt.x, pt.y, ch, sh, gx, gy, wx, wy);
-                    const int ix = grid_index_fast(wx, terrain.min_x, terrain.dx, rdx, mx);
-                    const int iy = grid_index_fast(wy, terrain.min_y, terrain.dy, rdy, my);
+                    // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy)
+                    const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt.x, pt.x), cs), __fmul2_rn(make_float2(pt.y, pt.y), nsc)), g2);
+                    // (w - min) / dxdy: Markstein division by the uniform cell size
+                    const float2 x = __fadd2_rn(w, nmn);
+                    float2 q = __fmul2_rn(x, rd2);
+                    const float2 r = __ffma2_rn(q, nd2, x);
+                    q = __ffma2_rn(r, rd2, q);
+                    // round half to even, clamp to the grid (terrain_util.py:139-152)
+                    const int ix = max(0, min(__float2int_rn(q.x), imx));
+                    const int iy = max(0, min(__float2int_rn(q.y), imy));
                     const float hv = __ldg(terrain.hf + ix * terrain.dim_y + iy);
                     v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
                     if (hrow) hrow[p] = v;

@@ -43,6 +43,11 @@ __device__ __forceinline__ float dot4_seq(Quat a, Quat b) {
 }
 __device__ __forceinline__ float sqnorm3_seq(Vec3 a) { return dot3_seq(a, a); }
 
+// Approximate reciprocal / square root (MUFU, ~1 ulp, no slow path) for values that are only held to
+// the 1e-5 tolerance. Index- and flag-critical expressions keep the IEEE forms.
+__device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 // quat_conjugate, torch_util.py:30-32
 __device__ __forceinline__ Quat quat_conj(Quat q) { return make_quat(-q.x, -q.y, -q.z, q.w); }
 
@@ -82,12 +87,12 @@ __device__ __forceinline__ Vec3 quat_rotate(Quat q, Vec3 v) {
 
 // normalize, torch_util.py:10-13: x / max(||x||, 1e-9)
 __device__ __forceinline__ Vec3 normalize3(Vec3 v) {
-    float n = fmaxf(sqrtf(v.x * v.x + v.y * v.y + v.z * v.z), 1e-9f);
-    return make_vec3(v.x / n, v.y / n, v.z / n);
+    const float r = fast_rcp(fmaxf(fast_sqrt(v.x * v.x + v.y * v.y + v.z * v.z), 1e-9f));
+    return make_vec3(v.x * r, v.y * r, v.z * r);
 }
 __device__ __forceinline__ Quat quat_unit(Quat q) {
-    float n = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-9f);
-    return make_quat(q.x / n, q.y / n, q.z / n, q.w / n);
+    const float r = fast_rcp(fmaxf(fast_sqrt(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-9f));
+    return make_quat(q.x * r, q.y * r, q.z * r, q.w * r);
 }
 // quat_normalize, torch_util.py:469-472: unit(pos(q))
 __device__ __forceinline__ Quat quat_normalize(Quat q) { return quat_unit(quat_pos(q)); }
@@ -95,12 +100,12 @@ __device__ __forceinline__ Quat quat_normalize(Quat q) { return quat_unit(quat_p
 // quat_to_axis_angle, torch_util.py:69-91: eps 1e-5 on ||xyz||, safe length 1e-6, default axis z.
 __device__ __forceinline__ void quat_to_axis_angle(Quat q, Vec3& axis, float& angle) {
     q = quat_pos(q);
-    float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
-    float a = 2.0f * atan2f(len, q.w);
-    float safe = fmaxf(len, 1e-6f);
-    bool mask = len > 1e-5f;
+    const float len = fast_sqrt(q.x * q.x + q.y * q.y + q.z * q.z);
+    const float a = 2.0f * atan2f(len, q.w);
+    const float rs = fast_rcp(fmaxf(len, 1e-6f));
+    const bool mask = len > 1e-5f;
     angle = mask ? a : 0.f;
-    axis = mask ? make_vec3(q.x / safe, q.y / safe, q.z / safe) : make_vec3(0.f, 0.f, 1.f);
+    axis = mask ? make_vec3(q.x * rs, q.y * rs, q.z * rs) : make_vec3(0.f, 0.f, 1.f);
 }
 
 // quat_to_exp_map, torch_util.py:371-376
@@ -112,21 +117,48 @@ __device__ __forceinline__ Vec3 quat_to_exp_map(Quat q) {
 
 // normalize_angle, torch_util.py:5-8
 __device__ __forceinline__ float normalize_angle(float x) { return atan2f(sinf(x), cosf(x)); }
+// the same for x >= 0 (a vector norm): atan2(sin x, cos x) is x itself below pi, up to rounding
+__device__ __forceinline__ float normalize_angle_nonneg(float x) { return x < 3.1415925f ? x : normalize_angle(x); }
+
+// sin / cos of a half angle |x| <= pi/2 + eps (the argument of axis_angle_to_quat after
+// normalize_angle): Taylor polynomials, truncation error < 1e-7
+__device__ __forceinline__ float cos_first_quadrant(float x) {
+    const float x2 = x * x;
+    float p = fmaf(x2, 2.0876757e-9f, -2.7557319e-7f);
+    p = fmaf(p, x2, 2.4801587e-5f);
+    p = fmaf(p, x2, -1.3888889e-3f);
+    p = fmaf(p, x2, 4.1666668e-2f);
+    p = fmaf(p, x2, -0.5f);
+    return fmaf(p, x2, 1.0f);
+}
 
 // axis_angle_to_quat, torch_util.py:336-342: normalises the axis AND the resulting quaternion.
 __device__ __forceinline__ Quat axis_angle_to_quat(Vec3 axis, float angle) {
     float s, c;
-    sincosf(angle * 0.5f, &s, &c);
+    const float h = angle * 0.5f;
+    if (fabsf(h) <= 1.5708f) {
+        const float ah = fabsf(h);
+        const float x2 = ah * ah;
+        float p = fmaf(x2, -2.5052108e-8f, 2.7557319e-6f);
+        p = fmaf(p, x2, -1.9841270e-4f);
+        p = fmaf(p, x2, 8.3333338e-3f);
+        p = fmaf(p, x2, -1.6666667e-1f);
+        s = copysignf(fmaf(ah * x2, p, ah), h);
+        c = cos_first_quadrant(ah);
+    } else {
+        sincosf(h, &s, &c);
+    }
     Vec3 n = normalize3(axis);
     return quat_unit(make_quat(n.x * s, n.y * s, n.z * s, c));
 }
 
 // exp_map_to_axis_angle + exp_map_to_quat, torch_util.py:425-450: min_theta 1e-5, default axis z.
 __device__ __forceinline__ Quat exp_map_to_quat(Vec3 e) {
-    float ang = sqrtf(e.x * e.x + e.y * e.y + e.z * e.z);
-    float nang = normalize_angle(ang);
-    bool mask = fabsf(nang) > 1e-5f;
-    Vec3 axis = mask ? make_vec3(e.x / ang, e.y / ang, e.z / ang) : make_vec3(0.f, 0.f, 1.f);
+    const float ang = fast_sqrt(e.x * e.x + e.y * e.y + e.z * e.z);
+    const float nang = normalize_angle_nonneg(ang);
+    const bool mask = fabsf(nang) > 1e-5f;
+    const float ra = fast_rcp(fmaxf(ang, 1e-30f));
+    Vec3 axis = mask ? make_vec3(e.x * ra, e.y * ra, e.z * ra) : make_vec3(0.f, 0.f, 1.f);
     float angle = mask ? nang : 0.f;
     return axis_angle_to_quat(axis, angle);
 }
