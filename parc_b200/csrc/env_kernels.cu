@@ -330,44 +330,6 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     const int tile_rows = (int)min((long long)TILE, n_rows - row0);
 
     // ================================ phase A ====================================================
-    // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
-    if (need_char_q) {
-        for (int it = tid; it < TILE * (J - 1); it += THREADS) {
-            const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
-            if (el >= tile_rows) continue;
-            const long long row = row0 + el;
-            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
-            const int jt = cm.joint_type[j], di = cm.dof_idx[j];
-            Quat q = quat_identity();
-            if (jt == PARC_JOINT_SPHERICAL)
-                q = exp_map_to_quat(make_vec3(view_ld(env.char_dof_pos, e, di), view_ld(env.char_dof_pos, e, di + 1), view_ld(env.char_dof_pos, e, di + 2)));
-            else if (jt == PARC_JOINT_HINGE)
-                q = axis_angle_to_quat(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), view_ld(env.char_dof_pos, e, di));
-            s_charq[el * J + j] = quat_to_f4(q);
-        }
-    }
-    // A.2 scatter map of the ref_* section: column k -> (base pointer, row stride in bytes)
-    if (do_ref) {
-        for (int k = tid; k < R.width; k += THREADS) {
-            const parc_view3_t* v; int off;
-            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
-            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
-            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
-            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
-            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
-            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
-            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
-            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
-            else { v = &env.ref_contacts; off = k - R.contacts; }
-            long long eoff;
-            if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
-            else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
-            else eoff = off * v->elem_stride;
-            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
-            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
-        }
-    }
-    if (tid == THREADS - 1) *s_chunk = 0;
     for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_part[k] = sp.part_entry[k / PARC_MAX_BODIES][k % PARC_MAX_BODIES];
     for (int k = tid; k < 8 * J; k += THREADS) {
         const int j = k >> 3, c = k & 7;
@@ -407,6 +369,63 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         u.flags = 0;
         s_env[el] = u;
         if (need_char_q) s_charq[el * J] = quat_to_f4(u.c_rot);
+    }
+    __syncthreads();
+    // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
+    //      the two adjacent interp records (and the velocity record of the reference pose); the dof -> quaternion
+    //      work below runs while they arrive
+    if (do_obs || need_ref_pose) {
+        for (int it = tid; it < TILE * (S + 1); it += THREADS) {
+            const int el = it / (S + 1), pose = it - el * (S + 1);
+            if (el >= tile_rows) continue;
+            const EnvU& u = s_env[el];
+            const float t = pose == 0 ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
+            const FrameBlend fb = calc_frame_blend(u.mm, t);
+            const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * lib.irec);
+            const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * lib.irec * sizeof(float));
+            for (int off = 0; off < bytes; off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(r0 + off));
+            if (pose == 0) {
+                const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * lib.vrec);
+                for (int off = 0; off < (int)(lib.vrec * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
+            }
+        }
+    }
+    // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
+    if (need_char_q) {
+        for (int it = tid; it < TILE * (J - 1); it += THREADS) {
+            const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
+            if (el >= tile_rows) continue;
+            const long long row = row0 + el;
+            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
+            const int jt = cm.joint_type[j], di = cm.dof_idx[j];
+            Quat q = quat_identity();
+            if (jt == PARC_JOINT_SPHERICAL)
+                q = exp_map_to_quat(make_vec3(view_ld(env.char_dof_pos, e, di), view_ld(env.char_dof_pos, e, di + 1), view_ld(env.char_dof_pos, e, di + 2)));
+            else if (jt == PARC_JOINT_HINGE)
+                q = axis_angle_to_quat(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), view_ld(env.char_dof_pos, e, di));
+            s_charq[el * J + j] = quat_to_f4(q);
+        }
+    }
+    // A.2 scatter map of the ref_* section: column k -> (base pointer, row stride in bytes)
+    if (do_ref) {
+        for (int k = tid; k < R.width; k += THREADS) {
+            const parc_view3_t* v; int off;
+            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
+            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
+            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
+            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
+            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
+            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
+            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
+            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
+            else { v = &env.ref_contacts; off = k - R.contacts; }
+            long long eoff;
+            if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
+            else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
+            else eoff = off * v->elem_stride;
+            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
+            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
+        }
     }
     __syncthreads();
 
@@ -563,20 +582,12 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     }
     if (P > 0 && (do_heights || do_obs)) {
         // ---- B.2 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
-        // Every warp (the pose warps once they are done) claims chunks of HCHUNK sample points from a
-        // block-wide counter, so the two kinds of work balance without a barrier in between.
-        // a chunk is a quarter of one env's sample points (rounded up to whole warps)
+        // warp w samples the points of env w (after its pose work): no cross-warp bookkeeping
         const int lane = tid & 31;
-        const int chunk_pts = (((P + 3) >> 2) + 31) & ~31;
-        const int n_chunks = tile_rows * 4;
         const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
         const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1;
-        for (;;) {
-            int c = 0;
-            if (lane == 0) c = atomicAdd(s_chunk, 1);
-            c = __shfl_sync(FULL_MASK, c, 0);
-            if (c >= n_chunks) break;
-            const int el = c >> 2, p0 = (c & 3) * chunk_pts, p1 = min(P, p0 + chunk_pts);
+        for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
+            const int p0 = 0, p1 = P;
             const EnvU& u = s_env[el];
             float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
