@@ -315,7 +315,6 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     float* s_xf = reinterpret_cast<float*>(smem_raw + plan.off_xf);
     float* s_terms = reinterpret_cast<float*>(smem_raw + plan.off_terms);
     unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
-    int* s_chunk = reinterpret_cast<int*>(smem_raw + plan.off_counter);
     int* s_part = reinterpret_cast<int*>(smem_raw + plan.off_tab);
     float* s_jc = reinterpret_cast<float*>(smem_raw + plan.off_tab + sizeof(int) * NPART * PARC_MAX_BODIES);
     const int ROWP = plan.row_pitch;
@@ -335,10 +334,11 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
-    // A.3 per-env uniforms
-    if (tid < TILE) {
+    // A.3 per-env uniforms: the first lanes of the LAST warp, so that the dependent loads (env id -> motion id -> clip
+    //     meta) overlap the dof -> quaternion work of the leading warps
+    if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
         EnvU u;
-        const int el = tid;
+        const int el = tid - (THREADS - 32);
         u.live = el < tile_rows;
         const long long row = row0 + (u.live ? el : 0);
         const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
@@ -369,26 +369,6 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         u.flags = 0;
         s_env[el] = u;
         if (need_char_q) s_charq[el * J] = quat_to_f4(u.c_rot);
-    }
-    __syncthreads();
-    // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
-    //      the two adjacent interp records (and the velocity record of the reference pose); the dof -> quaternion
-    //      work below runs while they arrive
-    if (do_obs || need_ref_pose) {
-        for (int it = tid; it < TILE * (S + 1); it += THREADS) {
-            const int el = it / (S + 1), pose = it - el * (S + 1);
-            if (el >= tile_rows) continue;
-            const EnvU& u = s_env[el];
-            const float t = pose == 0 ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
-            const FrameBlend fb = calc_frame_blend(u.mm, t);
-            const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * lib.irec);
-            const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * lib.irec * sizeof(float));
-            for (int off = 0; off < bytes; off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(r0 + off));
-            if (pose == 0) {
-                const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * lib.vrec);
-                for (int off = 0; off < (int)(lib.vrec * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
-            }
-        }
     }
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
@@ -429,10 +409,96 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     }
     __syncthreads();
 
+    // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
+    //      the two adjacent interp records (and the velocity record of the reference pose); the dof -> quaternion
+    //      work below runs while they arrive
+    if (do_reward || do_done) {
+        // simulator state read in phase C (rigid body positions, contact forces, dof velocities): 3 rows per env
+        for (int it = tid; it < TILE * 3 * 4; it += THREADS) {
+            const int el = it / 12, w = (it >> 2) % 3, ln = it & 3;
+            if (el >= tile_rows) continue;
+            const parc_view3_t& v = w == 0 ? env.char_rigid_body_pos : (w == 1 ? env.char_contact_forces : env.char_dof_vel);
+            const long long span = (w == 2 ? (long long)D * v.elem_stride : (long long)J * v.mid_stride) * (long long)sizeof(float);
+            if (v.ptr && ln * 128 < span)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(v.ptr + s_env[el].e * v.row_stride) + ln * 128));
+        }
+    }
+    if (do_obs || need_ref_pose) {
+        for (int it = tid; it < TILE * (S + 1); it += THREADS) {
+            const int el = it / (S + 1), pose = it - el * (S + 1);
+            if (el >= tile_rows) continue;
+            const EnvU& u = s_env[el];
+            const float t = pose == 0 ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
+            const FrameBlend fb = calc_frame_blend(u.mm, t);
+            const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * lib.irec);
+            const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * lib.irec * sizeof(float));
+            for (int off = 0; off < bytes; off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(r0 + off));
+            if (pose == 0) {
+                const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * lib.vrec);
+                for (int off = 0; off < (int)(lib.vrec * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
+            }
+        }
+    }
+
     // ================================ phase B ====================================================
     static_assert(TILE * NPART == 32, "one warp = one pose of the tile's envs x NPART tree parts");
     const bool pose_work = do_obs || need_ref_pose;
-    // ---- B.1 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
+    if (P > 0 && (do_heights || do_obs)) {
+        // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
+        // warp w samples the points of env w; runs BEFORE the pose work so that the frame records requested above
+        // arrive meanwhile. Four points per lane and iteration keep four independent gathers in flight.
+        const int lane = tid & 31;
+        const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
+        const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1, dimy = terrain.dim_y;
+        const float lo = cfg.min_obs_h, hi = cfg.max_obs_h;
+        const float2* __restrict__ pts = reinterpret_cast<const float2*>(env.ray_xy_points);
+        for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
+            const EnvU& u = s_env[el];
+            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
+            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
+            if (do_heights) {
+                // packed fp32x2 arithmetic (FMUL2 / FADD2 / FFMA2, sm_100): x and y of a sample point share every
+                // instruction; each half is the same IEEE operation as the scalar form, so cells stay bit-exact
+                const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
+                const float gz = u.g.z;
+                constexpr int U = 4;
+                for (int p = lane; p < P; p += 32 * U) {
+                    float2 pt[U];
+                    int cell[U];
+                    float v[U];
+#pragma unroll
+                    for (int k = 0; k < U; ++k) pt[k] = __ldg(pts + min(p + 32 * k, P - 1));
+#pragma unroll
+                    for (int k = 0; k < U; ++k) {
+                        // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy)
+                        const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt[k].x, pt[k].x), cs), __fmul2_rn(make_float2(pt[k].y, pt[k].y), nsc)), g2);
+                        // (w - min) / dxdy: Markstein division by the uniform cell size
+                        const float2 x = __fadd2_rn(w, nmn);
+                        float2 q = __fmul2_rn(x, rd2);
+                        const float2 r = __ffma2_rn(q, nd2, x);
+                        q = __ffma2_rn(r, rd2, q);
+                        // round half to even, clamp to the grid (terrain_util.py:139-152)
+                        const int ix = max(0, min(__float2int_rn(q.x), imx));
+                        const int iy = max(0, min(__float2int_rn(q.y), imy));
+                        cell[k] = ix * dimy + iy;
+                    }
+#pragma unroll
+                    for (int k = 0; k < U; ++k) v[k] = __ldg(terrain.hf + cell[k]);
+#pragma unroll
+                    for (int k = 0; k < U; ++k) {
+                        const float h = fminf(fmaxf(__fsub_rn(v[k], gz), lo), hi);
+                        if (p + 32 * k < P) {
+                            if (hrow) hrow[p + 32 * k] = h;
+                            if (orow) orow[p + 32 * k] = h;
+                        }
+                    }
+                }
+            } else if (orow) {
+                for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
+            }
+        }
+    }
+    // ---- B.2 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
     //      walks its own ancestor-closed part of the joint tree, so all lanes of a warp run the same code ----
     for (int pose = tid >> 5; pose_work && pose < plan.n_pose; pose += THREADS / 32) {
         const int lane = tid & 31, el = lane / NPART, part = lane - el * NPART;
@@ -580,145 +646,118 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
                     kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                 }
     }
-    if (P > 0 && (do_heights || do_obs)) {
-        // ---- B.2 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
-        // warp w samples the points of env w (after its pose work): no cross-warp bookkeeping
-        const int lane = tid & 31;
-        const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
-        const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1;
-        for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
-            const int p0 = 0, p1 = P;
-            const EnvU& u = s_env[el];
-            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
-            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
-            // packed fp32x2 arithmetic (FMUL2 / FADD2 / FFMA2, sm_100): x and y of a sample point share every
-            // instruction; each lane of a pair is the same IEEE operation as the scalar form, so cells stay bit-exact
-            const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-            const float gz = u.g.z;
-            for (int p = p0 + lane; p < p1; p += 32) {
-                float v;
-                if (do_heights) {
-                    const float2 pt = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + p);
-                    // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy)
-                    const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt.x, pt.x), cs), __fmul2_rn(make_float2(pt.y, pt.y), nsc)), g2);
-                    // (w - min) / dxdy: Markstein division by the uniform cell size
-                    const float2 x = __fadd2_rn(w, nmn);
-                    float2 q = __fmul2_rn(x, rd2);
-                    const float2 r = __ffma2_rn(q, nd2, x);
-                    q = __ffma2_rn(r, rd2, q);
-                    // round half to even, clamp to the grid (terrain_util.py:139-152)
-                    const int ix = max(0, min(__float2int_rn(q.x), imx));
-                    const int iy = max(0, min(__float2int_rn(q.y), imy));
-                    const float hv = __ldg(terrain.hf + ix * terrain.dim_y + iy);
-                    v = fminf(fmaxf(__fsub_rn(hv, gz), cfg.min_obs_h), cfg.max_obs_h);
-                    if (hrow) hrow[p] = v;
-                } else {
-                    v = hrow[p];
-                }
-                if (orow) orow[p] = v;
-            }
-        }
-    }
     __syncthreads();
 
     // ================================ phase C ====================================================
     // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
     const int o_pose_t = 0, o_vel_t = J - 1, o_con_t = o_vel_t + D, o_key_t = o_con_t + J;
     const int TP = plan.term_pitch;
-    if (need_ref_pose) {
-        // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
-        for (int it = tid; it < TILE * (J - 1); it += THREADS) {
-            const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
-            if (el >= tile_rows) continue;
-            float* rsec = s_row + el * ROWP + L.o_hf;
-            const float* jr = rsec + R.joint_rot + 4 * (j - 1);
-            const Quat q = make_quat(jr[0], jr[1], jr[2], jr[3]);
-            if (do_ref) {
-                const int jt = cm.joint_type[j], di = cm.dof_idx[j];
-                if (jt == PARC_JOINT_SPHERICAL) {
-                    const Vec3 ex = quat_to_exp_map(q);
-                    rsec[R.dof_pos + di] = ex.x; rsec[R.dof_pos + di + 1] = ex.y; rsec[R.dof_pos + di + 2] = ex.z;
-                } else if (jt == PARC_JOINT_HINGE) {
-                    Vec3 axis; float angle;
-                    quat_to_axis_angle(q, axis, angle);
-                    const float dd = dot3_seq(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), axis);
-                    rsec[R.dof_pos + di] = (dd < 0.f) ? -angle : angle;
+    {
+        // Four item kinds (joints, contacts, key bodies, dof velocities) cut into warp-sized tasks that are dealt
+        // round-robin to the 8 warps: every warp runs about the same number of (prefetched) global reads.
+        const bool want_c = (do_reward && cfg.use_contact_info) || (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0);
+        const int nt_j = need_ref_pose ? (TILE * (J - 1) + 31) >> 5 : 0;
+        const int nt_c = want_c ? (TILE * J + 31) >> 5 : 0;
+        const int nt_k = do_reward ? (TILE * K + 31) >> 5 : 0;
+        const int nt_d = do_reward ? (TILE * D + 31) >> 5 : 0;
+        const int b_c = nt_j, b_k = b_c + nt_c, b_d = b_k + nt_k, n_task = b_d + nt_d;
+        const int lane = tid & 31;
+        for (int task = tid >> 5; task < n_task; task += THREADS / 32) {
+            if (task < b_c) {
+                // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
+                const int it = task * 32 + lane;
+                if (it >= TILE * (J - 1)) continue;
+                const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
+                if (el >= tile_rows) continue;
+                float* rsec = s_row + el * ROWP + L.o_hf;
+                const float* jr = rsec + R.joint_rot + 4 * (j - 1);
+                const Quat q = make_quat(jr[0], jr[1], jr[2], jr[3]);
+                if (do_ref) {
+                    const int jt = cm.joint_type[j], di = cm.dof_idx[j];
+                    if (jt == PARC_JOINT_SPHERICAL) {
+                        const Vec3 ex = quat_to_exp_map(q);
+                        rsec[R.dof_pos + di] = ex.x; rsec[R.dof_pos + di + 1] = ex.y; rsec[R.dof_pos + di + 2] = ex.z;
+                    } else if (jt == PARC_JOINT_HINGE) {
+                        Vec3 axis; float angle;
+                        quat_to_axis_angle(q, axis, angle);
+                        const float dd = dot3_seq(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), axis);
+                        rsec[R.dof_pos + di] = (dd < 0.f) ? -angle : angle;
+                    }
                 }
-            }
-            if (do_reward) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
-                const float a = quat_diff_angle(quat_from_f4(s_charq[el * J + j]), q);
-                s_terms[el * TP + o_pose_t + (j - 1)] = cfg.joint_err_w[j - 1] * a * a;
-            }
-            if (do_done && cfg.enable_early_termination && cfg.pose_termination) {
-                // compute_done pose test (mgdm_dm_util.py:372-384): squared norm summed left to right
+                if (do_reward) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
+                    const float a = quat_diff_angle(quat_from_f4(s_charq[el * J + j]), q);
+                    s_terms[el * TP + o_pose_t + (j - 1)] = cfg.joint_err_w[j - 1] * a * a;
+                }
+                if (do_done && cfg.enable_early_termination && cfg.pose_termination) {
+                    // compute_done pose test (mgdm_dm_util.py:372-384): squared norm summed left to right
+                    const EnvU& u = s_env[el];
+                    const Vec3 sb = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, j, 0), view_ld3(env.char_rigid_body_pos, u.e, j, 1), view_ld3(env.char_rigid_body_pos, u.e, j, 2));
+                    const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, 0, 0), view_ld3(env.char_rigid_body_pos, u.e, 0, 1), view_ld3(env.char_rigid_body_pos, u.e, 0, 2));
+                    const float* bp = rsec + R.body_pos;
+                    const Vec3 a = sb - s0;
+                    const Vec3 bb = make_vec3(bp[3 * j], bp[3 * j + 1], bp[3 * j + 2]) - make_vec3(bp[0], bp[1], bp[2]);
+                    const Vec3 d = bb - a;
+                    const float td = cfg.pose_termination_dist[j - 1];
+                    if (sqnorm3_seq(d) > __fmul_rn(td, td)) atomicOr(&s_env[el].flags, 4);
+                }
+            } else if (task < b_k) {
+                const int it = (task - b_c) * 32 + lane;
+                if (it >= TILE * J) continue;
+                const int el = it / J, c = it - el * J;
+                if (el >= tile_rows) continue;
                 const EnvU& u = s_env[el];
-                const Vec3 sb = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, j, 0), view_ld3(env.char_rigid_body_pos, u.e, j, 1), view_ld3(env.char_rigid_body_pos, u.e, j, 2));
-                const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, 0, 0), view_ld3(env.char_rigid_body_pos, u.e, 0, 1), view_ld3(env.char_rigid_body_pos, u.e, 0, 2));
+                const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
+                            fz = view_ld3(env.char_contact_forces, u.e, c, 2);
+                if (do_reward && cfg.use_contact_info) {
+                    // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
+                    const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
+                    const float rc = s_row[el * ROWP + L.o_hf + R.contacts + c];
+                    float cr = -(1.0f - rc) * f;
+                    cr += rc * f;
+                    s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
+                }
+                if (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0 && !((cfg.fall_contact_body_mask >> c) & 1u)) {
+                    // fall test (mgdm_dm_util.py:147-150, 349-362)
+                    int fl = 0;
+                    if (fabsf(fx) > 0.1f || fabsf(fy) > 0.1f || fabsf(fz) > 0.1f) fl |= 1;
+                    const float bx = view_ld3(env.char_rigid_body_pos, u.e, c, 0), by = view_ld3(env.char_rigid_body_pos, u.e, c, 1),
+                                bz = view_ld3(env.char_rigid_body_pos, u.e, c, 2);
+                    const int ix = grid_index(__fadd_rn(bx, u.eo.x), terrain.min_x, terrain.dx, terrain.dim_x);
+                    const int iy = grid_index(__fadd_rn(by, u.eo.y), terrain.min_y, terrain.dy, terrain.dim_y);
+                    const float th = __fadd_rn(__ldg(terrain.hf + (long long)ix * terrain.dim_y + iy), cfg.termination_height);
+                    if (bz < th) fl |= 2;
+                    if (fl) atomicOr(&s_env[el].flags, fl);
+                }
+            } else if (task < b_d) {
+                // key body term (mgdm_dm_util.py:303-323); key positions of the CHARACTER come from the simulator's rigid bodies
+                const int it = (task - b_k) * 32 + lane;
+                if (it >= TILE * K) continue;
+                const int el = it / K, k = it - el * K;
+                if (el >= tile_rows) continue;
+                const EnvU& u = s_env[el];
+                const int body = cfg.key_body_ids[k];
+                const float* rsec = s_row + el * ROWP + L.o_hf;
                 const float* bp = rsec + R.body_pos;
-                const Vec3 a = sb - s0;
-                const Vec3 bb = make_vec3(bp[3 * j], bp[3 * j + 1], bp[3 * j + 2]) - make_vec3(bp[0], bp[1], bp[2]);
-                const Vec3 d = bb - a;
-                const float td = cfg.pose_termination_dist[j - 1];
-                if (sqnorm3_seq(d) > __fmul_rn(td, td)) atomicOr(&s_env[el].flags, 4);
-            }
-        }
-    }
-    if (do_reward) {
-        // dof velocity term (mgdm_dm_util.py:289-291)
-        for (int it = tid; it < TILE * D; it += THREADS) {
-            const int el = it / D, k = it - el * D;
-            if (el >= tile_rows) continue;
-            const EnvU& u = s_env[el];
-            const float dv = s_row[el * ROWP + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
-            s_terms[el * TP + o_vel_t + k] = cfg.dof_err_w[k] * dv * dv;
-        }
-        // key body term (mgdm_dm_util.py:303-323); key positions of the CHARACTER come from the simulator's rigid bodies
-        for (int it = tid; it < TILE * K; it += THREADS) {
-            const int el = it / K, k = it - el * K;
-            if (el >= tile_rows) continue;
-            const EnvU& u = s_env[el];
-            const int body = cfg.key_body_ids[k];
-            const float* rsec = s_row + el * ROWP + L.o_hf;
-            const float* bp = rsec + R.body_pos;
-            const Vec3 ref_rpos = make_vec3(bp[0], bp[1], bp[2]);
-            Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
-                                view_ld3(env.char_rigid_body_pos, u.e, body, 2)) - u.c_pos;
-            Vec3 tkp = make_vec3(bp[3 * body], bp[3 * body + 1], bp[3 * body + 2]) - ref_rpos;
-            if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
-                const Quat rr = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
-                kp = quat_rotate(u.hinv, kp);
-                tkp = quat_rotate(calc_heading_quat_inv(rr), tkp);
-            }
-            const Vec3 d = tkp - kp;
-            s_terms[el * TP + o_key_t + k] = d.x * d.x + d.y * d.y + d.z * d.z;
-        }
-    }
-    if ((do_reward && cfg.use_contact_info) || (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0)) {
-        for (int it = tid; it < TILE * J; it += THREADS) {
-            const int el = it / J, c = it - el * J;
-            if (el >= tile_rows) continue;
-            const EnvU& u = s_env[el];
-            const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
-                        fz = view_ld3(env.char_contact_forces, u.e, c, 2);
-            if (do_reward && cfg.use_contact_info) {
-                // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
-                const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
-                const float rc = s_row[el * ROWP + L.o_hf + R.contacts + c];
-                float cr = -(1.0f - rc) * f;
-                cr += rc * f;
-                s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
-            }
-            if (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0 && !((cfg.fall_contact_body_mask >> c) & 1u)) {
-                // fall test (mgdm_dm_util.py:147-150, 349-362)
-                int fl = 0;
-                if (fabsf(fx) > 0.1f || fabsf(fy) > 0.1f || fabsf(fz) > 0.1f) fl |= 1;
-                const float bx = view_ld3(env.char_rigid_body_pos, u.e, c, 0), by = view_ld3(env.char_rigid_body_pos, u.e, c, 1),
-                            bz = view_ld3(env.char_rigid_body_pos, u.e, c, 2);
-                const int ix = grid_index(__fadd_rn(bx, u.eo.x), terrain.min_x, terrain.dx, terrain.dim_x);
-                const int iy = grid_index(__fadd_rn(by, u.eo.y), terrain.min_y, terrain.dy, terrain.dim_y);
-                const float th = __fadd_rn(__ldg(terrain.hf + (long long)ix * terrain.dim_y + iy), cfg.termination_height);
-                if (bz < th) fl |= 2;
-                if (fl) atomicOr(&s_env[el].flags, fl);
+                const Vec3 ref_rpos = make_vec3(bp[0], bp[1], bp[2]);
+                Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
+                                    view_ld3(env.char_rigid_body_pos, u.e, body, 2)) - u.c_pos;
+                Vec3 tkp = make_vec3(bp[3 * body], bp[3 * body + 1], bp[3 * body + 2]) - ref_rpos;
+                if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
+                    const Quat rr = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
+                    kp = quat_rotate(u.hinv, kp);
+                    tkp = quat_rotate(calc_heading_quat_inv(rr), tkp);
+                }
+                const Vec3 d = tkp - kp;
+                s_terms[el * TP + o_key_t + k] = d.x * d.x + d.y * d.y + d.z * d.z;
+            } else {
+                // dof velocity term (mgdm_dm_util.py:289-291)
+                const int it = (task - b_d) * 32 + lane;
+                if (it >= TILE * D) continue;
+                const int el = it / D, k = it - el * D;
+                if (el >= tile_rows) continue;
+                const EnvU& u = s_env[el];
+                const float dv = s_row[el * ROWP + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
+                s_terms[el * TP + o_vel_t + k] = cfg.dof_err_w[k] * dv * dv;
             }
         }
     }
