@@ -289,8 +289,20 @@ def run_gpu_arm(args):
         return float(tt.item())
 
     # ---- device-resident timing: K steps, per-launch events around the dominant kernel ---------------
-    for _ in range(W):
+    def final_stats():
+        # final scalar reward / termination statistics: the only cross-rank exchange of the path
+        st = torch.stack([env._reward_buf.sum().double(), (env._done_buf != 0).sum().double(),
+                          env._motion_id_fail_rates.mean().double()])
+        if distributed:
+            dist.all_reduce(st, op=dist.ReduceOp.SUM)
+        return st
+
+    for _ in range(W - 1):
         env.step()
+    env.post_physics_step()
+    done_per_step = int(env._done_count.item())      # envs that finish (and are reset) in a steady-state step
+    env.reset_done()
+    final_stats()          # warm-up covers the statistics reduction too (first use loads its kernels / NCCL channels)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -301,9 +313,9 @@ def run_gpu_arm(args):
     L = _lib.lib()
     km, lib_cs = env._kin_char_model._cstruct(), env._mlib.cstruct()
     stream = env._stream()
-    done_total = torch.zeros(1, dtype=torch.int64, device=dev)
     barrier()
     t_start.record()
+    host_t0 = time.perf_counter()
     for i in range(K):
         ev[i][0].record()
         _lib.check(L.parc_b200_env_step(km, lib_cs, env._terrain_cs, env._cfg, env._bufs, _lib.STEP_ALL, None, 0, stream))
@@ -312,11 +324,8 @@ def run_gpu_arm(args):
                                              _lib.ptr(env._ema_scratch), stream))
         env._step_count += 1
         env.reset_done()
-    # final scalar reward / termination statistics: the only cross-rank exchange of the path
-    stats = torch.stack([env._reward_buf.sum().double(), (env._done_buf != 0).sum().double(),
-                         env._motion_id_fail_rates.mean().double()])
-    if distributed:
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    host_enqueue_ms = (time.perf_counter() - host_t0) * 1e3 / K
+    stats = final_stats()
     t_end.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -364,12 +373,12 @@ def run_gpu_arm(args):
                 traffic = json.load(f).get("dram_bytes_per_launch")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
-            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": host_enqueue_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "65,536 envs/GPU, 1,000-clip synthetic library of the repo humanoid, 32x32 local heightmap "
                                    "observations (BASELINE configs[1]); step = post-physics pass + fail-rate EMA + RSI reset",
                        "envs_per_gpu": N, "clips": args.motions, "frames": int(env._mlib._frame_root_pos.shape[0]),
-                       "ray_points": int(env._ray_xy_points.shape[0]), "obs_dim": env.get_obs_dim(),
+                       "ray_points": int(env._ray_xy_points.shape[0]), "resets_per_step": done_per_step, "obs_dim": env.get_obs_dim(),
                        "terrain_cells": list(env._terrain.hf.shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,
                        "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (step_bytes / 1e9)},
             "clocks": clocks,
@@ -378,7 +387,7 @@ def run_gpu_arm(args):
                     "note": "H2D of root/dof/rigid-body/contact state from pinned memory, fused step + reset, D2H of reward+done; "
                             "the observation stays on the device for the policy, as in the reference"},
             "gpu_launches": LAUNCHES_PER_STEP * K,
-            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<16>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<256>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": step_bytes, "bytes_per_env": b_env,
                          "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / (ms_total / K)},

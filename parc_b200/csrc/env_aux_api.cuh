@@ -106,7 +106,19 @@ extern "C" int parc_b200_fail_rate_ema(const parc_env_config_t* cfg, const parc_
     PARC_REQUIRE(env->done_count && env->done_list && env->done_code && env->motion_ids && env->motion_id_fail_rates && scratch,
                  "fail_rate_ema: done/fail-rate buffers not set");
     PARC_REQUIRE(cdf == nullptr || env->motion_weights, "fail_rate_ema: motion_weights not set");
-    fail_rate_ema_kernel<<<1, EMA_THREADS, 0, as_stream(stream)>>>(*cfg, *env, num_motions, cdf, scratch);
+    PARC_REQUIRE(env->num_envs < (1ll << 30), "fail_rate_ema: more than 2^30 envs");
+    // shared-memory staging: the two per-motion tables when they fit in 64 KB, then as much bucket as is left of 200 KB
+    const int tables = (size_t)num_motions * 8 <= 64 * 1024;
+    const size_t table_bytes = tables ? (size_t)num_motions * 8 : 0;
+    const long long cap = std::min<long long>(env->num_envs, (long long)((200 * 1024 - table_bytes) / 4));
+    const size_t smem = table_bytes + (size_t)cap * 4;
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaError_t ce = cudaFuncSetAttribute(fail_rate_ema_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
+        if (ce != cudaSuccess) { set_error("fail_rate_ema: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+        smem_set = 200 * 1024;
+    }
+    fail_rate_ema_kernel<<<1, EMA_THREADS, smem, as_stream(stream)>>>(*cfg, *env, num_motions, cdf, scratch, tables, (int)cap);
     return check_launch("fail_rate_ema");
 }
 

@@ -431,47 +431,87 @@ namespace parc {
 // one thread; different motions proceed in parallel. One block:
 //   histogram per motion -> exclusive scan -> bucket scatter -> per-motion sort + apply -> RSI CDF.
 constexpr int EMA_THREADS = 1024;
+constexpr int EMA_ILP = 8;              // done-list entries a thread keeps in flight
 
-__device__ void block_exclusive_scan_int(const int* __restrict__ in, int* __restrict__ out, int M, int* smem_partials) {
-    const int t = threadIdx.x, T = blockDim.x;
-    const int chunk = (M + T - 1) / T;
-    const int b = min(t * chunk, M), e = min(b + chunk, M);
-    int s = 0;
-    for (int k = b; k < e; ++k) s += in[k];
-    smem_partials[t] = s;
+// Block-wide exclusive scan of one value per thread (warp shuffles + one pass over the 32 warp totals).
+template <typename T>
+__device__ __forceinline__ T block_exclusive_scan(T v, T* warp_tot /* [32] smem */, T* total) {
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    T inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const T o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) warp_tot[w] = inc;
     __syncthreads();
-    if (t == 0) {
-        int run = 0;
-        for (int k = 0; k < T; ++k) { const int v = smem_partials[k]; smem_partials[k] = run; run += v; }
+    if (w == 0) {
+        const T x = lane < (int)(blockDim.x >> 5) ? warp_tot[lane] : T(0);
+        T xi = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const T o = __shfl_up_sync(0xffffffffu, xi, d);
+            if (lane >= d) xi += o;
+        }
+        warp_tot[lane] = xi - x;                   // exclusive prefix of the warp totals
+        if (lane == 31 && total) *total = xi;
     }
     __syncthreads();
-    int run = smem_partials[t];
-    for (int k = b; k < e; ++k) { const int v = in[k]; out[k] = run; run += v; }
+    const T r = warp_tot[w] + (inc - v);
     __syncthreads();
+    return r;
 }
 
+// Dynamic shared memory: [hist M | offs M] when `tables_in_smem`, then a bucket of `bucket_cap` entries; the global
+// scratch (2M + N ints) takes whatever does not fit. A bucket entry is env_id << 1 | failed, so that sorting the
+// entries sorts by env id and the apply loop needs no further global reads.
 __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid_constant__ parc_env_config_t cfg,
                                                                     const __grid_constant__ parc_env_buffers_t env, int M,
-                                                                    float* __restrict__ cdf, int* __restrict__ scratch) {
-    __shared__ int partial_i[EMA_THREADS];
-    __shared__ float partial_f[EMA_THREADS];
+                                                                    float* __restrict__ cdf, int* __restrict__ scratch,
+                                                                    int tables_in_smem, int bucket_cap) {
+    extern __shared__ int ema_smem[];
+    __shared__ int warp_i[32];
+    __shared__ float warp_f[32];
     const int t = threadIdx.x, T = blockDim.x;
     const int n = min(*env.done_count, (int)env.num_envs);
-    int* hist = scratch;            // [M]
-    int* offs = scratch + M;        // [M]
-    int* bucket = scratch + 2 * M;  // [n]
+    int* hist = tables_in_smem ? ema_smem : scratch;                 // [M]
+    int* offs = hist + M;                                            // [M]
+    int* bucket = n <= bucket_cap ? ema_smem + (tables_in_smem ? 2 * M : 0) : scratch + 2 * M;   // [n]
     if (n > 0) {
         for (int m = t; m < M; m += T) hist[m] = 0;
         __syncthreads();
-        for (int i = t; i < n; i += T) atomicAdd(&hist[(int)env.motion_ids[env.done_list[i]]], 1);
+        // pass 1: histogram of the finished envs' motions; EMA_ILP independent (done_list -> motion id, code) chains
+        for (int i0 = t; i0 < n; i0 += T * EMA_ILP) {
+            int e[EMA_ILP], m[EMA_ILP];
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k) e[k] = env.done_list[min(i0 + k * T, n - 1)];
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k) m[k] = (int)env.motion_ids[e[k]];
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k)
+                if (i0 + k * T < n) atomicAdd(&hist[m[k]], 1);
+        }
         __syncthreads();
-        block_exclusive_scan_int(hist, offs, M, partial_i);
-        for (int m = t; m < M; m += T) hist[m] = 0;   // reuse as per-motion cursor
+        // exclusive scan over motions -> segment starts; hist becomes the per-motion cursor
+        {
+            const int chunk = (M + T - 1) / T;
+            const int b = min(t * chunk, M), e = min(b + chunk, M);
+            int sum = 0;
+            for (int k = b; k < e; ++k) sum += hist[k];
+            int run = block_exclusive_scan<int>(sum, warp_i, nullptr);
+            for (int k = b; k < e; ++k) { const int v = hist[k]; offs[k] = run; run += v; hist[k] = 0; }
+        }
         __syncthreads();
-        for (int i = t; i < n; i += T) {
-            const int e = env.done_list[i];
-            const int m = (int)env.motion_ids[e];
-            bucket[offs[m] + atomicAdd(&hist[m], 1)] = e;
+        // pass 2: scatter env_id << 1 | failed into the motion's segment
+        for (int i0 = t; i0 < n; i0 += T * EMA_ILP) {
+            int e[EMA_ILP], m[EMA_ILP], c[EMA_ILP];
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k) e[k] = env.done_list[min(i0 + k * T, n - 1)];
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k) { m[k] = (int)env.motion_ids[e[k]]; c[k] = env.done_code[e[k]] == 1; }
+#pragma unroll
+            for (int k = 0; k < EMA_ILP; ++k)
+                if (i0 + k * T < n) bucket[offs[m[k]] + atomicAdd(&hist[m[k]], 1)] = (e[k] << 1) | c[k];
         }
         __syncthreads();
         const float w = cfg.ema_weight;
@@ -488,9 +528,8 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
             }
             float r = env.motion_id_fail_rates[m];
             for (int a = 0; a < cnt; ++a) {
-                const unsigned char code = env.done_code[seg[a]];
                 r = __fmul_rn(r, keep);
-                if (code == 1) r = __fadd_rn(r, w);
+                if (seg[a] & 1) r = __fadd_rn(r, w);
             }
             env.motion_id_fail_rates[m] = r;
         }
@@ -502,14 +541,7 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
         const int b = min(t * chunk, M), e = min(b + chunk, M);
         float s = 0.f;
         for (int k = b; k < e; ++k) s += fmaxf(env.motion_id_fail_rates[k], cfg.min_motion_weight) * env.motion_weights[k];
-        partial_f[t] = s;
-        __syncthreads();
-        if (t == 0) {
-            float run = 0.f;
-            for (int k = 0; k < T; ++k) { const float v = partial_f[k]; partial_f[k] = run; run += v; }
-        }
-        __syncthreads();
-        float run = partial_f[t];
+        float run = block_exclusive_scan<float>(s, warp_f, nullptr);
         for (int k = b; k < e; ++k) {
             run += fmaxf(env.motion_id_fail_rates[k], cfg.min_motion_weight) * env.motion_weights[k];
             cdf[k] = run;
