@@ -87,7 +87,7 @@ struct SmemPlan {
     int n_pose;              // poses per env: S + 2
     int n_slots;             // FK transforms a thread keeps: max over parts of bodies with children inside the part
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
-    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_tab, off_counter, total;
+    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_tab, off_pts, total;
 };
 
 constexpr int NPART = 4;                // threads cooperating on one (env, pose): each walks one part of the tree
@@ -104,11 +104,16 @@ inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_con
     p.off_env = o;    o += sizeof(EnvU) * TILE;                          o = (o + 15) & ~size_t(15);
     p.off_row = o;    o += sizeof(float) * TILE * p.row_pitch;           o = (o + 15) & ~size_t(15);
     p.off_charq = o;  o += sizeof(float4) * TILE * J;                    o = (o + 15) & ~size_t(15);
-    p.off_xf = o;     o += sizeof(float) * 7 * p.n_slots * STEP_THREADS;       o = (o + 15) & ~size_t(15);
-    p.off_terms = o;  o += sizeof(float) * TILE * p.term_pitch;          o = (o + 15) & ~size_t(15);
-    p.off_refmap = o; o += 16 * (size_t)R.width;                         o = (o + 15) & ~size_t(15);
+    // The FK transform columns are only live in phase B; the reward terms (phase C/D) and the ref_* scatter map
+    // (built in phase C, read in phase E) reuse the same bytes.
+    const size_t xf_bytes = sizeof(float) * 7 * p.n_slots * STEP_THREADS;
+    const size_t terms_bytes = (sizeof(float) * TILE * p.term_pitch + 15) & ~size_t(15);
+    p.off_xf = o;
+    p.off_terms = o;
+    p.off_refmap = o + terms_bytes;
+    o += std::max(xf_bytes, terms_bytes + 16 * (size_t)R.width);      o = (o + 15) & ~size_t(15);
     p.off_tab = o;    o += sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J;   o = (o + 15) & ~size_t(15);
-    p.off_counter = o; o += 16;
+    p.off_pts = o;    o += sizeof(float2) * (size_t)cfg.num_ray_points;   // ray_xy_points, shared by the tile's envs
     p.total = o;
     return p;
 }
@@ -219,19 +224,27 @@ inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_en
     sp.max_part_len = 0;
     int max_slots = 1;
     for (int b = 0; b < NPART; ++b) {
-        int slot_of[PARC_MAX_BODIES];
+        // Slots are handed out by liveness: a body's transform is kept only until its last child inside the part has
+        // read it, and a child may take over its parent's slot (the walk reads the parent before storing the child).
+        int slot_of[PARC_MAX_BODIES], kids_left[PARC_MAX_BODIES];
+        bool slot_busy[PARC_MAX_BODIES] = {false};
         int ns = 0, len = 0;
         for (int j = 1; j < J; ++j) {
-            slot_of[j] = -1;
+            slot_of[j] = -1; kids_left[j] = 0;
             if (!((bin_has[b] >> j) & 1u)) continue;
-            bool child_in_bin = false;
-            for (int c = j + 1; c < J; ++c) if (cm.parent[c] == j && ((bin_has[b] >> c) & 1u)) child_in_bin = true;
-            if (child_in_bin) slot_of[j] = ns++;
+            for (int c = j + 1; c < J; ++c) if (cm.parent[c] == j && ((bin_has[b] >> c) & 1u)) ++kids_left[j];
         }
         for (int j = 1; j < J; ++j) {
             if (!((bin_has[b] >> j) & 1u)) continue;
             const int par = cm.parent[j];
             const int pslot = par == 0 ? -1 : slot_of[par];
+            if (par != 0 && --kids_left[par] == 0) slot_busy[pslot] = false;
+            if (kids_left[j] > 0) {
+                int f = 0;
+                while (slot_busy[f]) ++f;
+                slot_busy[f] = true; slot_of[j] = f;
+                if (f + 1 > ns) ns = f + 1;
+            }
             sp.part_entry[b][len++] = j | ((int)((bin_owned[b] >> j) & 1u) << 8) | ((slot_of[j] + 1) << 12) | ((pslot + 1) << 16);
         }
         for (int k = len; k < PARC_MAX_BODIES; ++k) sp.part_entry[b][k] = -1;
@@ -291,8 +304,53 @@ __device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float
     return (int)u;
 }
 
+// One env's heightmap samples by one warp (_refresh_obs_hfs, ig_parkour_env.py:518-533; get_hf_val, terrain_util.py:139-156).
+// Points come from shared memory, four per lane and iteration so that four independent gathers are in flight; the two
+// destination rows are running pointers with immediate offsets. FULL: P is a multiple of 128 (no tail predicates).
+template <bool HAS_H, bool HAS_O, bool FULL>
+__device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const float* __restrict__ hf, int dimy,
+                                               int imx, int imy, float2 cs, float2 nsc, float2 g2, float gz, float2 nmn, float2 rd2,
+                                               float2 nd2, float lo, float hi, float* __restrict__ hrow, float* __restrict__ orow) {
+    constexpr int U = 4;
+    const float2* sp = s_pts + lane;
+    float* ph = hrow + lane;
+    float* po = orow + lane;
+    for (int p = lane; p < P; p += 32 * U, sp += 32 * U, ph += 32 * U, po += 32 * U) {
+        float2 pt[U];
+        int cell[U];
+        float v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) pt[k] = (FULL || p + 32 * k < P) ? sp[32 * k] : make_float2(0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy); packed fp32x2 (FMUL2 / FADD2 / FFMA2, sm_100):
+            // x and y of a sample point share every instruction
+            const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt[k].x, pt[k].x), cs), __fmul2_rn(make_float2(pt[k].y, pt[k].y), nsc)), g2);
+            // (w - min) / dxdy: Markstein division by the uniform cell size
+            const float2 x = __fadd2_rn(w, nmn);
+            float2 q = __fmul2_rn(x, rd2);
+            const float2 r = __ffma2_rn(q, nd2, x);
+            q = __ffma2_rn(r, rd2, q);
+            // round half to even, clamp to the grid (terrain_util.py:139-152)
+            const int ix = max(0, min(__float2int_rn(q.x), imx));
+            const int iy = max(0, min(__float2int_rn(q.y), imy));
+            cell[k] = ix * dimy + iy;
+        }
+#pragma unroll
+        for (int k = 0; k < U; ++k) v[k] = __ldg(hf + cell[k]);
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            const float h = fminf(fmaxf(__fsub_rn(v[k], gz), lo), hi);
+            if (FULL || p + 32 * k < P) {
+                if (HAS_H) ph[32 * k] = h;
+                if (HAS_O) po[32 * k] = h;
+            }
+        }
+    }
+}
+
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
+__global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
@@ -317,6 +375,7 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
     int* s_part = reinterpret_cast<int*>(smem_raw + plan.off_tab);
     float* s_jc = reinterpret_cast<float*>(smem_raw + plan.off_tab + sizeof(int) * NPART * PARC_MAX_BODIES);
+    float2* s_pts = reinterpret_cast<float2*>(smem_raw + plan.off_pts);
     const int ROWP = plan.row_pitch;
 
     const bool do_heights = parts & PARC_STEP_HEIGHTS;
@@ -334,6 +393,8 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
+    if (do_heights)
+        for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
     // A.3 per-env uniforms: the first lanes of the LAST warp, so that the dependent loads (env id -> motion id -> clip
     //     meta) overlap the dof -> quaternion work of the leading warps
     if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
@@ -386,27 +447,6 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
             s_charq[el * J + j] = quat_to_f4(q);
         }
     }
-    // A.2 scatter map of the ref_* section: column k -> (base pointer, row stride in bytes)
-    if (do_ref) {
-        for (int k = tid; k < R.width; k += THREADS) {
-            const parc_view3_t* v; int off;
-            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
-            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
-            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
-            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
-            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
-            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
-            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
-            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
-            else { v = &env.ref_contacts; off = k - R.contacts; }
-            long long eoff;
-            if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
-            else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
-            else eoff = off * v->elem_stride;
-            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
-            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
-        }
-    }
     __syncthreads();
 
     // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
@@ -451,48 +491,23 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
         const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
         const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1, dimy = terrain.dim_y;
         const float lo = cfg.min_obs_h, hi = cfg.max_obs_h;
-        const float2* __restrict__ pts = reinterpret_cast<const float2*>(env.ray_xy_points);
         for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
             const EnvU& u = s_env[el];
             float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
             if (do_heights) {
-                // packed fp32x2 arithmetic (FMUL2 / FADD2 / FFMA2, sm_100): x and y of a sample point share every
-                // instruction; each half is the same IEEE operation as the scalar form, so cells stay bit-exact
                 const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-                const float gz = u.g.z;
-                constexpr int U = 4;
-                for (int p = lane; p < P; p += 32 * U) {
-                    float2 pt[U];
-                    int cell[U];
-                    float v[U];
-#pragma unroll
-                    for (int k = 0; k < U; ++k) pt[k] = __ldg(pts + min(p + 32 * k, P - 1));
-#pragma unroll
-                    for (int k = 0; k < U; ++k) {
-                        // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy)
-                        const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt[k].x, pt[k].x), cs), __fmul2_rn(make_float2(pt[k].y, pt[k].y), nsc)), g2);
-                        // (w - min) / dxdy: Markstein division by the uniform cell size
-                        const float2 x = __fadd2_rn(w, nmn);
-                        float2 q = __fmul2_rn(x, rd2);
-                        const float2 r = __ffma2_rn(q, nd2, x);
-                        q = __ffma2_rn(r, rd2, q);
-                        // round half to even, clamp to the grid (terrain_util.py:139-152)
-                        const int ix = max(0, min(__float2int_rn(q.x), imx));
-                        const int iy = max(0, min(__float2int_rn(q.y), imy));
-                        cell[k] = ix * dimy + iy;
-                    }
-#pragma unroll
-                    for (int k = 0; k < U; ++k) v[k] = __ldg(terrain.hf + cell[k]);
-#pragma unroll
-                    for (int k = 0; k < U; ++k) {
-                        const float h = fminf(fmaxf(__fsub_rn(v[k], gz), lo), hi);
-                        if (p + 32 * k < P) {
-                            if (hrow) hrow[p + 32 * k] = h;
-                            if (orow) orow[p + 32 * k] = h;
-                        }
-                    }
+#define PARC_HEIGHTS(HH, OO, FF) heights_of_env<HH, OO, FF>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow)
+                if ((P & 127) == 0) {
+                    if (hrow && orow) PARC_HEIGHTS(true, true, true);
+                    else if (orow) PARC_HEIGHTS(false, true, true);
+                    else if (hrow) PARC_HEIGHTS(true, false, true);
+                } else {
+                    if (hrow && orow) PARC_HEIGHTS(true, true, false);
+                    else if (orow) PARC_HEIGHTS(false, true, false);
+                    else if (hrow) PARC_HEIGHTS(true, false, false);
                 }
+#undef PARC_HEIGHTS
             } else if (orow) {
                 for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
             }
@@ -652,6 +667,28 @@ __global__ void __launch_bounds__(THREADS, 3) env_step_kernel(
     // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
     const int o_pose_t = 0, o_vel_t = J - 1, o_con_t = o_vel_t + D, o_key_t = o_con_t + J;
     const int TP = plan.term_pitch;
+    // C.0 scatter map of the ref_* section for phase E: column k -> (base pointer, row stride in bytes). Lives in the
+    //     bytes the FK columns used during phase B; phase E starts behind the barrier that ends phase C.
+    if (do_ref) {
+        for (int k = tid; k < R.width; k += THREADS) {
+            const parc_view3_t* v; int off;
+            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
+            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
+            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
+            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
+            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
+            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
+            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
+            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
+            else { v = &env.ref_contacts; off = k - R.contacts; }
+            long long eoff;
+            if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
+            else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
+            else eoff = off * v->elem_stride;
+            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
+            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
+        }
+    }
     {
         // Four item kinds (joints, contacts, key bodies, dof velocities) cut into warp-sized tasks that are dealt
         // round-robin to the 8 warps: every warp runs about the same number of (prefetched) global reads.
