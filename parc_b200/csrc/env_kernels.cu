@@ -306,12 +306,14 @@ __device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float
 
 // One env's heightmap samples by one warp (_refresh_obs_hfs, ig_parkour_env.py:518-533; get_hf_val, terrain_util.py:139-156).
 // Points come from shared memory, four per lane and iteration so that four independent gathers are in flight; the two
-// destination rows are running pointers with immediate offsets. FULL: P is a multiple of 128 (no tail predicates).
-template <bool HAS_H, bool HAS_O, bool FULL>
+// destination rows (either may be absent) are running pointers with immediate offsets. FULL: P is a multiple of 128
+// (no tail predicates).
+template <bool FULL>
 __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const float* __restrict__ hf, int dimy,
                                                int imx, int imy, float2 cs, float2 nsc, float2 g2, float gz, float2 nmn, float2 rd2,
                                                float2 nd2, float lo, float hi, float* __restrict__ hrow, float* __restrict__ orow) {
     constexpr int U = 4;
+    const bool HAS_H = hrow != nullptr, HAS_O = orow != nullptr;   // warp-uniform: predicated stores, one code copy
     const float2* sp = s_pts + lane;
     float* ph = hrow + lane;
     float* po = orow + lane;
@@ -497,17 +499,10 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
             if (do_heights) {
                 const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-#define PARC_HEIGHTS(HH, OO, FF) heights_of_env<HH, OO, FF>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow)
-                if ((P & 127) == 0) {
-                    if (hrow && orow) PARC_HEIGHTS(true, true, true);
-                    else if (orow) PARC_HEIGHTS(false, true, true);
-                    else if (hrow) PARC_HEIGHTS(true, false, true);
-                } else {
-                    if (hrow && orow) PARC_HEIGHTS(true, true, false);
-                    else if (orow) PARC_HEIGHTS(false, true, false);
-                    else if (hrow) PARC_HEIGHTS(true, false, false);
-                }
-#undef PARC_HEIGHTS
+                if ((P & 127) == 0)
+                    heights_of_env<true>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
+                else
+                    heights_of_env<false>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
             } else if (orow) {
                 for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
             }

@@ -1,0 +1,173 @@
+"""CPU-side tests (no GPU, no compute calls): the C-ABI library loads and exports every symbol that
+include/*.h declares, the ctypes structs have the layout of the C structs, the host-side planning
+exposed through the ABI (tree parts, obs layout) is consistent, and the product classes refuse to
+run without CUDA instead of falling back to anything."""
+import ctypes
+import glob
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_functions():
+    names = set()
+    for path in sorted(glob.glob(os.path.join(ROOT, "include", "*.h"))):
+        src = open(path).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)        # comments mention symbols too
+        src = re.sub(r"//[^\n]*", "", src)
+        for m in re.finditer(r"\b(parc_b200_[a-z0-9_]+)\s*\(", src):
+            names.add(m.group(1))
+    return sorted(names)
+
+
+def test_library_exports_every_declared_symbol():
+    from parc_b200 import _lib
+    handle = _lib.lib()                       # builds with nvcc if the .so is missing (cross-compiles on CPU)
+    declared = _header_functions()
+    assert len(declared) >= 25
+    missing = [n for n in declared if not hasattr(handle, n)]
+    assert not missing, "declared in include/*.h but not exported: %s" % missing
+    # and the Python binding table names exactly the header's functions
+    assert sorted(_lib.EXPORTED_SYMBOLS) == declared
+    assert handle.parc_b200_version().decode().startswith("parc_b200")
+
+
+def test_library_is_sm100a_only():
+    from parc_b200 import build
+    out = subprocess.run(["cuobjdump", "-lelf", str(build.LIB)], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+def test_ctypes_struct_sizes_match_the_c_structs(tmp_path):
+    """sizeof() of each struct passed by pointer, compiled from the headers with gcc."""
+    from parc_b200 import _lib
+    prog = tmp_path / "sizes.c"
+    prog.write_text('#include <stdio.h>\n#include "parc_b200.h"\n#include "parc_b200_env.h"\n'
+                    'int main(void){printf("%zu %zu %zu %zu %zu\\n", sizeof(parc_char_model_t), sizeof(parc_motion_lib_t),'
+                    'sizeof(parc_terrain_t), sizeof(parc_env_config_t), sizeof(parc_env_buffers_t));return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(prog), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    mine = [ctypes.sizeof(s) for s in (_lib.CharModelStruct, _lib.MotionLibStruct, _lib.TerrainStruct, _lib.EnvConfigStruct,
+                                       _lib.EnvBuffersStruct)]
+    assert mine == sizes
+
+
+def _tree_parts(model):
+    from parc_b200 import _lib
+    L = _lib.lib()
+    ent = np.full((4, 32), -1, dtype=np.int32)
+    max_len, n_slots = ctypes.c_int32(), ctypes.c_int32()
+    _lib.check(L.parc_b200_tree_parts(model._cstruct(), ent.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), ctypes.byref(max_len),
+                                      ctypes.byref(n_slots)))
+    return ent, max_len.value, n_slots.value
+
+
+def test_tree_parts_partition_the_humanoid():
+    """The fused step walks the joint tree in 4 ancestor-closed parts (one lane each). Every joint is
+    owned by exactly one part, a part contains the ancestors of its joints, and replaying the slot
+    plan never reads a transform that was overwritten."""
+    model = H.product_model("cpu")
+    parents = [int(p) for p in model._parent_indices.tolist()]
+    J = len(parents)
+    ent, max_len, n_slots = _tree_parts(model)
+    owned = []
+    for b in range(4):
+        seen, slot_holds = set(), {}
+        entries = [int(e) for e in ent[b] if e >= 0]
+        assert len(entries) <= max_len
+        for e in entries:
+            j, own, st, ps = e & 0xFF, (e >> 8) & 1, ((e >> 12) & 0xF) - 1, ((e >> 16) & 0xF) - 1
+            assert 1 <= j < J
+            par = parents[j]
+            assert par == 0 or par in seen, "part %d is not ancestor-closed at joint %d" % (b, j)
+            if par == 0:
+                assert ps == -1
+            else:
+                assert 0 <= ps < n_slots and slot_holds.get(ps) == par, "joint %d would read a stale parent transform" % j
+            if st >= 0:
+                assert st < n_slots
+                slot_holds[st] = j
+            seen.add(j)
+            if own:
+                owned.append(j)
+    assert sorted(owned) == list(range(1, J)), "each joint must be produced exactly once"
+    assert max_len <= (J - 1 + 3) // 4 + 2          # balanced within the duplicated chain prefix
+    assert n_slots == 1                              # humanoid: chains only, children take over the parent's slot
+
+
+def test_obs_dim_matches_reference_layout():
+    from parc_b200 import _lib
+    from parc_b200.tracking_env import build_config_struct, default_env_config
+    model = H.product_model("cpu")
+    for P, want in ((441, 1312), (1024, 1895), (0, 871)):
+        cfg = build_config_struct(default_env_config(), model, P)
+        assert _lib.lib().parc_b200_obs_dim(model._cstruct(), cfg) == want
+    ec = default_env_config()
+    ec.update(global_obs=True, global_root_height_obs=True)
+    assert _lib.lib().parc_b200_obs_dim(model._cstruct(), build_config_struct(ec, model, 441)) == 1313
+    ec = default_env_config()
+    ec.update(enable_tar_obs=False, use_contact_info=False)
+    assert _lib.lib().parc_b200_obs_dim(model._cstruct(), build_config_struct(ec, model, 441)) == 136 + 441
+
+
+def test_config_struct_rounding_follows_the_reference():
+    from parc_b200.tracking_env import build_config_struct, default_env_config
+    model = H.product_model("cpu")
+    cfg = build_config_struct(default_env_config(), model, 441)
+    assert np.float32(cfg.root_pos_termination_dist) == np.float32(0.6) * np.float32(0.6) or \
+        abs(cfg.root_pos_termination_dist - 0.36) < 1e-7
+    assert np.float32(cfg.ema_keep) == np.float32(1.0 - 0.01)
+    assert cfg.num_tar_steps == 6 and cfg.num_key_bodies == 4
+    steps = torch.tensor([1, 2, 3, 10, 20, 30], dtype=torch.int32)
+    want = (np.float32(cfg.timestep) * steps).float()
+    assert [np.float32(cfg.tar_dt[i]) for i in range(6)] == [np.float32(x) for x in want.tolist()]
+
+
+def test_product_path_refuses_to_run_without_cuda():
+    from parc_b200 import _lib
+    with pytest.raises(_lib.ParcB200Error):
+        _lib.ptr(torch.zeros(4))
+    model = H.product_model("cpu")
+    if not torch.cuda.is_available():
+        with pytest.raises((_lib.ParcB200Error, AssertionError, RuntimeError)):
+            model.forward_kinematics(torch.zeros(2, 3), torch.tensor([[0., 0, 0, 1]] * 2), torch.zeros(2, 14, 4))
+
+
+def test_null_arguments_are_rejected_with_the_reference_error_type():
+    """Invalid arguments come back as PARC_ERR_INVALID_ARG -> AssertionError (the reference asserts)."""
+    from parc_b200 import _lib
+    L = _lib.lib()
+    model = H.product_model("cpu")
+    rc = L.parc_b200_forward_kinematics(model._cstruct(), None, None, None, 4, None, None, None)
+    assert rc != 0
+    with pytest.raises(AssertionError):
+        _lib.check(rc)
+    assert b"NULL" in L.parc_b200_last_error() or len(L.parc_b200_last_error()) > 0
+    # n == 0 is a no-op, as an empty env_ids tensor is in the reference (dm_env.py:567-570)
+    assert L.parc_b200_forward_kinematics(model._cstruct(), None, None, None, 0, None, None, None) == 0
+
+
+def test_synthetic_library_is_deterministic_and_in_spec():
+    from parc_b200 import synth
+    spec = synth.humanoid_spec()
+    a = synth.make_clips(spec, 5, seed=11, min_frames=60, max_frames=80)
+    b = synth.make_clips(spec, 5, seed=11, min_frames=60, max_frames=80)
+    for x, y in zip(a, b):
+        assert torch.equal(x["root_pos"], y["root_pos"]) and torch.equal(x["joint_rot"], y["joint_rot"])
+        assert 60 <= x["root_pos"].shape[0] <= 80 and x["joint_rot"].shape[1:] == (14, 4)
+        n = x["joint_rot"].norm(dim=-1)
+        assert float((n - 1).abs().max()) < 1e-5
+    hf, min_point, dx, offs = synth.build_terrain_square(a, padding_cells=1)
+    tiles = int(np.ceil(np.sqrt(5)))
+    assert hf.shape[0] == hf.shape[1] and hf.shape[0] % tiles == 0 and offs.shape == (5, 1, 2)
+    assert synth.grid_ray_points().shape == (1024, 2) and synth.cone_ray_points().shape == (441, 2)
