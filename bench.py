@@ -168,7 +168,7 @@ def algorithmic_bytes(env):
     return N * b_env + b_lib, b_env
 
 
-LAUNCHES_PER_STEP = 5   # env_step, fail_rate_ema, env_reset_sampled, env_step(reset rows), done-count clear
+LAUNCHES_PER_STEP = 6   # sim_standin, env_step, fail_rate_ema, env_reset_sampled, env_step(reset rows), done-count clear
 
 
 # ------------------------------------------------------------------------------------------------
@@ -202,9 +202,14 @@ def run_cpu_port(world, num_envs, steps, warmup, threads):
     env.char_dof_pos[:], env.char_dof_vel[:] = sim["dof_pos"], sim["dof_vel"]
     env.char_rigid_body_pos[:], env.char_contact_forces[:] = sim["body_pos"], sim["contact_forces"]
 
+    noise = synth.standin_noise(N, m.J, m.D, seed=5678)
+    resets = []
+
     def one_step(i):
+        synth.apply_standin_torch(env, noise, m.J, m.D)      # the same simulator stand-in as the GPU arm
         env.post_physics_step()
         ids = torch.nonzero(env.done_buf != O.DONE_NULL).flatten()
+        resets.append(int(ids.numel()))
         if ids.numel() > 0:
             d = synth.reset_draws(ids.numel(), lib.num_motions(), 1, lib.lengths, env.sampling_weights(), seed=1000 + i)
             env.reset(ids, *d)
@@ -218,7 +223,8 @@ def run_cpu_port(world, num_envs, steps, warmup, threads):
         one_step(warmup + i)
         times.append(time.perf_counter() - t0)
     total = float(np.sum(times))
-    return {"value": N * steps / total, "median_s": float(np.median(times)), "min_s": float(np.min(times)), "total_s": total}
+    return {"value": N * steps / total, "median_s": float(np.median(times)), "min_s": float(np.min(times)), "total_s": total,
+            "resets_per_step": float(np.mean(resets[warmup:]))}
 
 
 def cpu_baseline_block(world, args, steps, warmup):
@@ -226,8 +232,8 @@ def cpu_baseline_block(world, args, steps, warmup):
     r = run_cpu_port(world, args.cpu_envs, steps, warmup, cores)
     return {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d envs x %d steps (+%d warm-up) of the same %d-clip / 32x32-heightmap workload, torch CPU eager, "
-                      "%d threads; median %.3f s/step, min %.3f s/step" % (args.cpu_envs, steps, warmup, args.motions, cores,
-                                                                          r["median_s"], r["min_s"])}, r
+                      "%d threads; median %.3f s/step, min %.3f s/step; %.1f resets/step"
+                      % (args.cpu_envs, steps, warmup, args.motions, cores, r["median_s"], r["min_s"], r["resets_per_step"])}, r
 
 
 def run_reference_arm(args):
@@ -244,7 +250,8 @@ def run_reference_arm(args):
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps_cpu,
             "warmup": warm_cpu, "ms_per_step": 1e3 * r["total_s"] / steps_cpu, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "65,536-env / 1,000-clip / 32x32-heightmap tracking step; CPU arm runs a %d-env sample per step"
+            "config": {"workload": "65,536-env / 1,000-clip / 32x32-heightmap tracking step (same stand-in + step + reset as the b200 "
+                                   "arm); CPU arm runs a %d-env sample per step"
                                    % args.cpu_envs, "envs_per_step": args.cpu_envs, "clips": args.motions, "ray_points": 1024,
                        "obs_dim": 1895},
             "cpu_baseline": cb,
@@ -275,6 +282,8 @@ def run_gpu_arm(args):
     env = build_gpu_env(world, N, rank * N, n_gpus * N, dev)
     init_gpu_state(env, rank * N)
     step_bytes, b_env = algorithmic_bytes(env)
+    from parc_b200 import synth
+    noise = synth.standin_noise(N, env._J, env._D, seed=5678 + rank * N).to(dev)   # simulator stand-in
 
     def barrier():
         if distributed:
@@ -298,7 +307,9 @@ def run_gpu_arm(args):
         return st
 
     for _ in range(W - 1):
+        env.sim_standin(noise)
         env.step()
+    env.sim_standin(noise)
     env.post_physics_step()
     done_per_step = int(env._done_count.item())      # envs that finish (and are reset) in a steady-state step
     env.reset_done()
@@ -317,6 +328,7 @@ def run_gpu_arm(args):
     t_start.record()
     host_t0 = time.perf_counter()
     for i in range(K):
+        env.sim_standin(noise)                 # "physics": the character follows its reference with a fixed error
         ev[i][0].record()
         _lib.check(L.parc_b200_env_step(km, lib_cs, env._terrain_cs, env._cfg, env._bufs, _lib.STEP_ALL, None, 0, stream))
         ev[i][1].record()
@@ -344,12 +356,13 @@ def run_gpu_arm(args):
     d2h = sum(v.numel() * v.element_size() for v in host_res.values())
     Ke = K
     for _ in range(3):
-        env.upload_sim_state(host_state); env.step(); env.download_results(host_res)
+        env.upload_sim_state(host_state); env.sim_standin(noise); env.step(); env.download_results(host_res)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(Ke):
         env.upload_sim_state(host_state)       # this step's simulator state from pinned host memory
+        env.sim_standin(noise)                 # (its values are then re-centred on the reference: stationary workload)
         env.step()
         env.download_results(host_res)         # reward + done back to the host
         torch.cuda.current_stream(dev).synchronize()   # the caller needs the results before the next physics step
@@ -376,7 +389,8 @@ def run_gpu_arm(args):
             "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": host_enqueue_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "65,536 envs/GPU, 1,000-clip synthetic library of the repo humanoid, 32x32 local heightmap "
-                                   "observations (BASELINE configs[1]); step = post-physics pass + fail-rate EMA + RSI reset",
+                                   "observations (BASELINE configs[1]); step = simulator stand-in (char := ref + fixed noise, FK) + post-physics "
+                                   "pass + fail-rate EMA + device-side RSI reset + obs refresh of the reset envs",
                        "envs_per_gpu": N, "clips": args.motions, "frames": int(env._mlib._frame_root_pos.shape[0]),
                        "ray_points": int(env._ray_xy_points.shape[0]), "resets_per_step": done_per_step, "obs_dim": env.get_obs_dim(),
                        "terrain_cells": list(env._terrain.hf.shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,

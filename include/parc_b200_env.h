@@ -225,6 +225,17 @@ int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_mot
 int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n,
                                  int64_t* ids, void* stream);
 
+/* Benchmark / test utility, NOT a reference function: a stand-in for the physics simulator between two
+ * control steps, so that a device-resident loop sees a stationary workload. For every env it rewrites
+ * the simulated character state as the env's current reference state plus a fixed per-env
+ * perturbation: char_root_pos = ref_root_pos + n[0:3]; char_root_rot = normalize(ref_root_rot (x)
+ * n[3:7]) (n[3:7] a unit quaternion); char_root_vel / ang_vel / dof_pos / dof_vel = ref_* + noise;
+ * char_rigid_body_pos = forward kinematics of that root + dof state + body noise (what the simulator
+ * would report; ref_body_pos is stale for envs that were just reset). noise is [N, 13 + 2 D + 3 J]
+ * row-major in that column order. Contact forces are left as they are. */
+int parc_b200_sim_standin(const parc_char_model_t* h_model, const parc_env_buffers_t* h_env, const float* noise,
+                          void* stream);
+
 /* Host-side plan of the fused step's forward kinematics (no GPU needed): the joints 1..J-1 are
  * split into 4 ancestor-closed lists, one per cooperating thread. entries [4 * PARC_MAX_BODIES]:
  * joint | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16, -1 past the end of a list. */

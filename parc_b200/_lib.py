@@ -193,6 +193,7 @@ def _declare(lib):
         "parc_b200_env_reset_sampled": [P(CharModelStruct), P(MotionLibStruct), P(TerrainStruct),
                                         P(EnvConfigStruct), P(EnvBuffersStruct), vp, i32, u64, u64, i32, vp],
         "parc_b200_sample_motions_cdf": [vp, i32, vp, i64, vp, vp],
+        "parc_b200_sim_standin": [P(CharModelStruct), P(EnvBuffersStruct), vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
     }

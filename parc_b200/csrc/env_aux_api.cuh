@@ -180,3 +180,18 @@ extern "C" int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motion
     sample_cdf_kernel<<<blocks_for(n, 256), 256, 0, as_stream(stream)>>>(cdf, num_motions, u, n, (long long*)ids);
     return check_launch("sample_motions_cdf");
 }
+
+extern "C" int parc_b200_sim_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise, void* stream) {
+    PARC_REQUIRE(m && env && noise, "sim_standin: NULL argument");
+    if (env->num_envs == 0) return PARC_OK;
+    PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_root_vel.ptr && env->char_root_ang_vel.ptr &&
+                     env->char_dof_pos.ptr && env->char_dof_vel.ptr && env->char_rigid_body_pos.ptr && env->ref_root_pos.ptr &&
+                     env->ref_root_rot.ptr && env->ref_root_vel.ptr && env->ref_root_ang_vel.ptr && env->ref_dof_pos.ptr &&
+                     env->ref_dof_vel.ptr && env->ref_body_pos.ptr, "sim_standin: state views not set");
+    PARC_REQUIRE(m->num_bodies <= 32, "sim_standin: more than 32 bodies");
+    const long long groups_per_block = 256 / (m->num_bodies <= 16 ? 16 : 32);
+    const unsigned blocks = (unsigned)std::min<long long>((env->num_envs + groups_per_block - 1) / groups_per_block, kNumSMs * 32);
+    if (m->num_bodies <= 16) sim_standin_kernel<16><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise);
+    else sim_standin_kernel<32><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise);
+    return check_launch("sim_standin");
+}

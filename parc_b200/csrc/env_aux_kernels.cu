@@ -549,6 +549,50 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
     }
 }
 
+// ---- simulator stand-in for benchmarks (see parc_b200_sim_standin) -----------------------------------
+// G lanes per env: the lanes first write the root / dof columns (ref + noise), then run dof_to_rot + forward
+// kinematics on that state, in registers, for the rigid body positions the simulator would report.
+template <int G>
+__global__ void __launch_bounds__(256) sim_standin_kernel(const __grid_constant__ parc_char_model_t cm,
+                                                          const __grid_constant__ parc_env_buffers_t env,
+                                                          const float* __restrict__ noise) {
+    const int J = cm.num_bodies, D = cm.dof_size;
+    const int W = 13 + 2 * D + 3 * J, W1 = 13 + 2 * D;
+    const LaneBody lb = load_lane_body<G>(cm);
+    const long long gpb = blockDim.x / G;
+    const long long gid0 = (long long)blockIdx.x * gpb + threadIdx.x / G;
+    const long long warp_first = gid0 - ((threadIdx.x & 31) / G);
+    for (long long base = warp_first; base < env.num_envs; base += (long long)gridDim.x * gpb) {
+        const long long i = base + ((threadIdx.x & 31) / G);
+        const bool live = i < env.num_envs;
+        const long long e = live ? i : 0;
+        const float* n = noise + e * W;
+        const Vec3 rp = view_ld_vec3(env.ref_root_pos, e) + make_vec3(n[0], n[1], n[2]);
+        const Quat rr = quat_unit(quat_mul(view_ld_quat(env.ref_root_rot, e), make_quat(n[3], n[4], n[5], n[6])));
+        if (live) {
+            // root / dof columns: lane j of the env's group takes columns j, j + G, ...
+            for (int c = threadIdx.x & (G - 1); c < W1; c += G) {
+                if (c < 3) view_st(env.char_root_pos, e, c, c == 0 ? rp.x : (c == 1 ? rp.y : rp.z));
+                else if (c < 7) { if (c == 3) view_st_quat(env.char_root_rot, e, rr); }
+                else if (c < 10) view_st(env.char_root_vel, e, c - 7, view_ld(env.ref_root_vel, e, c - 7) + n[c]);
+                else if (c < 13) view_st(env.char_root_ang_vel, e, c - 10, view_ld(env.ref_root_ang_vel, e, c - 10) + n[c]);
+                else if (c < 13 + D) view_st(env.char_dof_pos, e, c - 13, view_ld(env.ref_dof_pos, e, c - 13) + n[c]);
+                else view_st(env.char_dof_vel, e, c - 13 - D, view_ld(env.ref_dof_vel, e, c - 13 - D) + n[c]);
+            }
+        }
+        Quat q = quat_identity();
+        if (lb.active && lb.body > 0) q = dof_to_rot_lane(lb, [&](int k) { return view_ld(env.ref_dof_pos, e, k) + n[13 + k]; });
+        Vec3 pos; Quat rot;
+        fk_lanes<G>(lb, q, rp, rr, pos, rot);
+        if (live && lb.active) {
+            const float* nb = n + W1 + 3 * lb.body;
+            view_st3(env.char_rigid_body_pos, e, lb.body, 0, pos.x + nb[0]);
+            view_st3(env.char_rigid_body_pos, e, lb.body, 1, pos.y + nb[1]);
+            view_st3(env.char_rigid_body_pos, e, lb.body, 2, pos.z + nb[2]);
+        }
+    }
+}
+
 __global__ void zero_int_kernel(int* p) { *p = 0; }
 
 }  // namespace parc

@@ -214,3 +214,35 @@ def reset_draws(num, num_motions, terrains_per_motion, lengths, weights, seed):
     times = torch.rand(num, generator=g) * lengths.cpu()[mids]
     noise = torch.rand(num, 2, generator=g) * 2.0 - 1.0
     return mids, tids, times, noise
+
+
+def standin_noise(num_envs, J, D, seed=5678, fail_fraction=0.02):
+    """[N, 13 + 2 D + 3 J] perturbation rows for the simulator stand-in (parc_b200_sim_standin and the same
+    arithmetic in torch for the CPU arm): root pos | unit noise quaternion | root vel | root ang vel | dof pos |
+    dof vel | body pos, with the scales of sim_noise. A `fail_fraction` of the envs is pushed 0.8 m off the
+    reference root so that early termination keeps firing at a stationary rate."""
+    nz = sim_noise(num_envs, J, D, seed)
+    q = _exp_to_quat(nz["root_rot_exp"])
+    root_pos = nz["root_pos"].clone()
+    k = int(round(num_envs * fail_fraction))
+    if k > 0:
+        g = torch.Generator().manual_seed(seed + 17)
+        idx = torch.randperm(num_envs, generator=g)[:k]
+        root_pos[idx, 0] += 0.8
+    return torch.cat([root_pos, q, nz["root_vel"], nz["root_ang_vel"], nz["dof_pos"], nz["dof_vel"],
+                      nz["body_pos"].reshape(num_envs, 3 * J)], dim=1).contiguous()
+
+
+def apply_standin_torch(env, noise, J, D):
+    """The stand-in on an oracle TrackingEnv (torch CPU): same formulas as sim_standin_kernel. `env.model` supplies
+    forward_kinematics / dof_to_rot."""
+    n = noise
+    env.char_root_pos[:] = env.ref_root_pos + n[:, 0:3]
+    q = _qmul(env.ref_root_rot, n[:, 3:7])
+    env.char_root_rot[:] = q / q.norm(dim=-1, keepdim=True)
+    env.char_root_vel[:] = env.ref_root_vel + n[:, 7:10]
+    env.char_root_ang_vel[:] = env.ref_root_ang_vel + n[:, 10:13]
+    env.char_dof_pos[:] = env.ref_dof_pos + n[:, 13:13 + D]
+    env.char_dof_vel[:] = env.ref_dof_vel + n[:, 13 + D:13 + 2 * D]
+    body_pos = env.model.forward_kinematics(env.char_root_pos, env.char_root_rot, env.model.dof_to_rot(env.char_dof_pos))[0]
+    env.char_rigid_body_pos[:] = body_pos + n[:, 13 + 2 * D:].reshape(-1, J, 3)

@@ -137,6 +137,35 @@ def build_config_struct(env_config, char_model: KinCharModel, num_ray_points: in
 REWARD_TERM_NAMES = ("pose_r", "vel_r", "root_pos_r", "root_vel_r", "key_pos_r", "contact_penalty", "total_r")
 
 
+def make_buffers_struct(num_envs, *, obs_buf, reward_buf, done_buf, time_buf, timestep_buf, env_offsets, motion_ids,
+                        motion_terrain_ids, motion_time_offsets, dm_motion_offsets, terrains_per_motion=1, reward_terms=None,
+                        actors_need_reset=None, ray_xy_points=None, ray_hfs=None, motion_id_fail_rates=None, motion_weights=None,
+                        done_count=None, done_list=None, done_code=None, **views) -> _lib.EnvBuffersStruct:
+    """parc_env_buffers_t from the tensors the env shell injects into DeepMimicEnv (get_sim_tensor_views /
+    get_data_buffer_views / get_obs_buf_view, mgdm_dm_util.py:37-84). `views` are the simulator and ref_* tensors by the
+    names of include/parc_b200_env.h (char_root_pos, ..., ref_contacts): column slices and stride-2 slices are passed as
+    they are -- the kernels read and write through (ptr, row_stride, mid_stride, elem_stride)."""
+    unknown = set(views) - set(_lib._VIEW_NAMES)
+    assert not unknown, "unknown state views: %s" % sorted(unknown)
+    b = _lib.EnvBuffersStruct()
+    b.num_envs = int(num_envs)
+    for name in _lib._VIEW_NAMES:
+        setattr(b, name, _lib.view3(views.get(name)))
+    p = _lib.ptr
+    b.reward_buf, b.reward_terms, b.done_buf = p(reward_buf), p(reward_terms), p(done_buf)
+    b.time_buf, b.timestep_buf = p(time_buf), p(timestep_buf)
+    b.actors_need_reset = p(actors_need_reset)
+    b.actors_per_env = int(actors_need_reset.shape[1]) if actors_need_reset is not None else 0
+    b.env_offsets, b.ray_xy_points, b.ray_hfs = p(env_offsets), p(ray_xy_points), p(ray_hfs)
+    b.obs_buf, b.obs_row_stride = p(obs_buf), int(obs_buf.stride(0))
+    b.motion_ids, b.motion_terrain_ids = p(motion_ids), p(motion_terrain_ids)
+    b.motion_time_offsets, b.motion_id_fail_rates = p(motion_time_offsets), p(motion_id_fail_rates)
+    b.motion_weights, b.dm_motion_offsets = p(motion_weights), p(dm_motion_offsets)
+    b.terrains_per_motion = int(terrains_per_motion)
+    b.done_count, b.done_list, b.done_code = p(done_count), p(done_list), p(done_code)
+    return b
+
+
 class TrackingEnv:
     """Post-physics half of the tracking env on one GPU. `env_offset_rows` lets a rank of a
     sharded job own envs [first_env, first_env + num_envs) of a larger grid."""
@@ -215,23 +244,13 @@ class TrackingEnv:
 
     # ---------------------------------------------------------------- descriptors
     def _build_buffers_struct(self):
-        b = _lib.EnvBuffersStruct()
-        b.num_envs = self._num_envs
-        v = _lib.view3
-        for name in _lib._VIEW_NAMES:
-            setattr(b, name, v(getattr(self, "_" + name)))
-        p = _lib.ptr
-        b.reward_buf, b.reward_terms, b.done_buf = p(self._reward_buf), p(self._reward_terms), p(self._done_buf)
-        b.time_buf, b.timestep_buf = p(self._time_buf), p(self._timestep_buf)
-        b.actors_need_reset, b.actors_per_env = p(self._actors_need_reset), int(self._actors_need_reset.shape[1])
-        b.env_offsets, b.ray_xy_points, b.ray_hfs = p(self._env_offsets), p(self._ray_xy_points), p(self._ray_hfs)
-        b.obs_buf, b.obs_row_stride = p(self._obs_buf), int(self._obs_buf.stride(0))
-        b.motion_ids, b.motion_terrain_ids = p(self._motion_ids), p(self._motion_terrain_ids)
-        b.motion_time_offsets, b.motion_id_fail_rates = p(self._motion_time_offsets), p(self._motion_id_fail_rates)
-        b.motion_weights, b.dm_motion_offsets = p(self._mlib._motion_weights), p(self._dm_motion_offsets)
-        b.terrains_per_motion = self._terrains_per_motion
-        b.done_count, b.done_list, b.done_code = p(self._done_count), p(self._done_list), p(self._done_code)
-        self._bufs = b
+        names = list(_lib._VIEW_NAMES) + ["reward_buf", "reward_terms", "done_buf", "time_buf", "timestep_buf", "actors_need_reset",
+                                          "env_offsets", "ray_xy_points", "ray_hfs", "obs_buf", "motion_ids", "motion_terrain_ids",
+                                          "motion_time_offsets", "motion_id_fail_rates", "dm_motion_offsets", "done_count",
+                                          "done_list", "done_code"]
+        self._bufs = make_buffers_struct(self._num_envs, motion_weights=self._mlib._motion_weights,
+                                         terrains_per_motion=self._terrains_per_motion,
+                                         **{n: getattr(self, "_" + n) for n in names})
         self._terrain_cs = self._terrain.cstruct()
 
     def _stream(self):
@@ -308,6 +327,12 @@ class TrackingEnv:
             self._kin_char_model._cstruct(), self._mlib.cstruct(), self._terrain_cs, self._cfg, self._bufs,
             _lib.ptr(self._cdf), self._mlib.num_motions(), self._seed, self._step_count, int(self._rand_reset),
             self._stream()))
+
+    def sim_standin(self, noise):
+        """Benchmark utility (not a reference method): stands in for the simulator between two steps --
+        character state := current reference state + a fixed per-env perturbation (synth.standin_noise)."""
+        assert noise.shape == (self._num_envs, 13 + 2 * self._D + 3 * self._J) and noise.dtype == torch.float32
+        _lib.check(_lib.lib().parc_b200_sim_standin(self._kin_char_model._cstruct(), self._bufs, _lib.ptr(noise), self._stream()))
 
     def step(self):
         """One full control step after physics: post_physics_step + reset of the finished envs."""

@@ -399,3 +399,34 @@ def test_full_size_properties_65536_envs():
     assert torch.equal(done.cpu()[sel], oenv.done_buf), "done flags must be bit-exact"
     H.assert_close_world(obs.cpu()[sel], oenv.obs_buf, float(oenv.ref_root_pos.abs().max()), what="obs (65536-env run, 256 sampled rows)")
     assert_close(rew.cpu()[sel], oenv.reward_buf, atol=1e-5, what="reward")
+    # shard invariance: a rank that owns global envs [a, b) -- not aligned to the kernel's 8-env tiles -- computes
+    # bit-identical rows (bench.py --gpus N relies on this; there is no exchange on the data path)
+    a, b = 16384 + 3, 16384 + 3 + 4099
+    shard = H.Scenario.__new__(H.Scenario)
+    shard.__dict__.update(sc.__dict__)
+    shard.N, shard.env_offsets = b - a, sc.env_offsets[a:b]
+    senv = shard.product_env(DEV)
+    for k, v in snap.items():
+        getattr(senv, k).copy_(v[a:b])
+    senv._motion_id_fail_rates.fill_(1.0)
+    senv.post_physics_step()
+    torch.cuda.synchronize()
+    assert torch.equal(senv._obs_buf, obs[a:b]) and torch.equal(senv._reward_buf, rew[a:b]) and torch.equal(senv._done_buf, done[a:b])
+
+
+def test_simulator_standin_matches_torch_formulas():
+    """parc_b200_sim_standin (bench utility) == synth.apply_standin_torch on the oracle env."""
+    sc = H.Scenario(num_envs=333, num_motions=5, ray="cone", seed=4, max_frames=80)
+    oenv = sc.oracle_env()
+    H.randomize_oracle_state(oenv, seed=6)
+    penv = sc.product_env(DEV)
+    H.copy_oracle_state_to_product(oenv, penv)
+    noise = synth.standin_noise(sc.N, 15, 28, seed=9)
+    synth.apply_standin_torch(oenv, noise, 15, 28)
+    penv.sim_standin(noise.to(DEV))
+    torch.cuda.synchronize()
+    W = float(oenv.ref_root_pos.abs().max())
+    for k in ("root_pos", "rigid_body_pos"):
+        H.assert_close_world(getattr(penv, "_char_" + k).cpu(), getattr(oenv, "char_" + k), W, what="standin " + k)
+    for k in ("root_rot", "root_vel", "root_ang_vel", "dof_pos", "dof_vel"):
+        assert_close(getattr(penv, "_char_" + k).cpu(), getattr(oenv, "char_" + k), what="standin " + k)
