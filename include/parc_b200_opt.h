@@ -1,0 +1,83 @@
+/* parc_b200_opt.h -- C ABI of the kinematic motion optimizer's loss.
+ *
+ * Replaces, for the FK + terrain penetration / contact loss of PARC's motion_synthesis optimizer:
+ *   terrain_util.points_hf_sdf                      PARC/util/terrain_util.py:1736-1794
+ *   terrain_util.points_boxes_sdf / geom_util.sdBox PARC/util/terrain_util.py:1678-1705, PARC/util/geom_util.py:124-145
+ *   motion_terrain_contact_loss_localized           PARC/motion_synthesis/motion_opt/motion_optimization.py:426-656
+ *   (and the torch autograd pass the optimizer runs through it, motion_optimization.py:772-797)
+ *
+ * Conventions as in parc_b200.h: device pointers, row-major fp32, quaternions xyzw, `stream` is a
+ * cudaStream_t, return 0 = ok / negative PARC_ERR_*. */
+#ifndef PARC_B200_OPT_H
+#define PARC_B200_OPT_H
+
+#include "parc_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* LossType order of motion_optimization.py:15-25 (first nine members). */
+enum {
+    PARC_LOSS_ROOT_POS = 0,
+    PARC_LOSS_ROOT_ROT = 1,
+    PARC_LOSS_JOINT_ROT = 2,
+    PARC_LOSS_SMOOTHNESS = 3,
+    PARC_LOSS_PENETRATION = 4,
+    PARC_LOSS_CONTACT = 5,
+    PARC_LOSS_SLIDING = 6,
+    PARC_LOSS_BODY_CONSTRAINT = 7, /* always 0: body_constraints=None is the only supported setting */
+    PARC_LOSS_JERK = 8,
+    PARC_NUM_LOSS_TERMS = 9
+};
+
+typedef struct {
+    /* w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
+     * w_body_constraints, w_jerk (indexed by the enum above) */
+    float w[PARC_NUM_LOSS_TERMS];
+    float max_jerk;                                 /* multiplied by (1/30)^3 inside, :621-623 */
+    float base_z;                                   /* -10.0 in the reference (:553, :559) */
+    int32_t num_points;                             /* Np = sum of the per-body sample counts */
+    int32_t point_start[PARC_MAX_BODIES + 1];       /* body b owns points [point_start[b], point_start[b+1]) */
+    int32_t contact_col[PARC_MAX_BODIES];           /* column of `contacts` for body b, or -1 (:575-579) */
+    int32_t num_contact_cols;                       /* trailing dim of `contacts`; sliding needs == num_bodies (:608) */
+} parc_opt_config_t;
+
+/* terrain_util.points_hf_sdf without `radius`: points [B,N,3], hf [B,X,Y], min_box_center [B,2]
+ * -> sd [B,N]. One axis-aligned box per heightfield cell (solid column from base_z up to the cell
+ * height, or, inverted, the air column from the cell height up to -base_z with the result negated),
+ * minimum over all X*Y cells. grad (may be NULL) receives d sd / d point [B,N,3] -- what autograd
+ * would propagate through the argmin cell. */
+int parc_b200_points_hf_sdf(const float* points, int64_t B, int64_t N, const float* hf, int32_t X, int32_t Y,
+                            const float* min_box_center, float dx, float dy, float base_z, int32_t inverted,
+                            float* sd, float* grad, void* stream);
+
+/* Bytes of scratch parc_b200_motion_loss needs for B motions of T frames. */
+int64_t parc_b200_motion_loss_workspace_bytes(const parc_char_model_t* h_model, int64_t B, int64_t T);
+
+/* motion_terrain_contact_loss_localized for B independent motions of T frames each (the reference
+ * takes one motion per call; BASELINE config 4 is 1,024 x 300), value and gradient in one pass:
+ *   tgt_root_pos [B,T,3], tgt_root_rot [B,T,3] (exp map), tgt_joint_dof [B,T,D]      -- the parameters
+ *   src_root_pos [B,T,3], src_root_rot_quat [B,T,4], src_joint_rot [B,T,J-1,4],
+ *   src_body_vels [B,T-1,J,3], src_body_rot_vels [B,T-1,J], contacts [B,T,C]
+ *   terrain: hf [B,X,Y] with hf_motion_stride = X*Y, or one shared [X,Y] with stride 0;
+ *            min_point [B,2] / [2] likewise (min_point_motion_stride 2 or 0)
+ *   body_points [Np,3] in body order (geom_util.get_char_point_samples, geom_util.py:790-872)
+ * Outputs: terms [B,9] unweighted loss terms, loss [B] weighted total; if the g_* pointers are
+ * non-NULL, d loss / d parameter in g_root_pos [B,T,3], g_root_rot [B,T,3], g_joint_dof [B,T,D]
+ * (all three or none). Heightfield windows follow the reference: per frame the cells covering the
+ * frame's body points +- 2 cells, all frames of a motion sharing the largest window (:507-551). */
+int parc_b200_motion_loss(const parc_char_model_t* h_model, const parc_opt_config_t* h_cfg, int64_t B, int64_t T,
+                          const float* tgt_root_pos, const float* tgt_root_rot, const float* tgt_joint_dof,
+                          const float* src_root_pos, const float* src_root_rot_quat, const float* src_joint_rot,
+                          const float* src_body_vels, const float* src_body_rot_vels, const float* contacts,
+                          const float* hf, int64_t hf_motion_stride, int32_t X, int32_t Y,
+                          const float* min_point, int64_t min_point_motion_stride, float dx, float dy,
+                          const float* body_points, void* workspace, int64_t workspace_bytes,
+                          float* terms, float* loss, float* g_root_pos, float* g_root_rot, float* g_joint_dof,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

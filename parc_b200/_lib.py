@@ -151,6 +151,22 @@ class EnvBuffersStruct(C.Structure):
     )
 
 
+PARC_NUM_LOSS_TERMS = 9
+
+
+class OptConfigStruct(C.Structure):
+    """parc_opt_config_t (include/parc_b200_opt.h)."""
+    _fields_ = [
+        ("w", C.c_float * PARC_NUM_LOSS_TERMS),
+        ("max_jerk", C.c_float),
+        ("base_z", C.c_float),
+        ("num_points", C.c_int32),
+        ("point_start", C.c_int32 * (MAX_BODIES + 1)),
+        ("contact_col", C.c_int32 * MAX_BODIES),
+        ("num_contact_cols", C.c_int32),
+    ]
+
+
 class ParcB200Error(RuntimeError):
     pass
 
@@ -194,6 +210,9 @@ def _declare(lib):
                                         P(EnvConfigStruct), P(EnvBuffersStruct), vp, i32, u64, u64, i32, vp],
         "parc_b200_sample_motions_cdf": [vp, i32, vp, i64, vp, vp],
         "parc_b200_sim_standin": [P(CharModelStruct), P(EnvBuffersStruct), vp, vp],
+        "parc_b200_points_hf_sdf": [vp, i64, i64, vp, i32, i32, vp, f32, f32, f32, i32, vp, vp, vp],
+        "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
+                                                                                                 vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
     }
@@ -201,6 +220,9 @@ def _declare(lib):
         fn = getattr(lib, name)   # AttributeError here = header/library mismatch: fail loudly
         fn.restype = C.c_int
         fn.argtypes = argtypes
+    lib.parc_b200_motion_loss_workspace_bytes.restype = i64
+    lib.parc_b200_motion_loss_workspace_bytes.argtypes = [P(CharModelStruct), i64, i64]
+    sigs["parc_b200_motion_loss_workspace_bytes"] = lib.parc_b200_motion_loss_workspace_bytes.argtypes
     return sigs
 
 

@@ -124,3 +124,37 @@ class SubTerrain:
                                                   -3.0e38, 3.0e38, _lib.ptr(out), 1, None,
                                                   _lib.stream_ptr(pts.device)))
         return out.reshape(lead)
+
+
+class _PointsHfSdfFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, hf, min_box_center, dx, dy, base_z, inverted):
+        from . import _lib
+        B, N = points.shape[0], points.shape[1]
+        p = points.detach().to(torch.float32).contiguous()
+        sd = torch.empty(B, N, dtype=torch.float32, device=p.device)
+        grad = torch.empty(B, N, 3, dtype=torch.float32, device=p.device) if ctx.needs_input_grad[0] else None
+        _lib.check(_lib.lib().parc_b200_points_hf_sdf(_lib.ptr(p), B, N, _lib.ptr(hf), hf.shape[1], hf.shape[2], _lib.ptr(min_box_center),
+                                                      dx, dy, base_z, int(bool(inverted)), _lib.ptr(sd), _lib.ptr(grad),
+                                                      _lib.stream_ptr(p.device)))
+        if grad is not None:
+            ctx.save_for_backward(grad)
+        return sd
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return g.unsqueeze(-1) * grad, None, None, None, None, None, None
+
+
+def points_hf_sdf(points, hf, hf_min_box_center, hf_dxdy, base_z=-10.0, inverted=True, radius=None):
+    """terrain_util.points_hf_sdf (PARC/util/terrain_util.py:1736-1794): signed distance of points [B,N,3] to the
+    box-per-cell heightfield hf [B,X,Y] whose (0,0) cell centre is hf_min_box_center [B,2]; differentiable in
+    `points`. `radius` (rounded boxes) is not supported."""
+    assert points.dim() == 3 and hf.dim() == 3 and hf_min_box_center.dim() == 2 and hf_dxdy.dim() == 1
+    if radius is not None:
+        raise NotImplementedError("points_hf_sdf: radius is not supported by the CUDA kernel")
+    dev = points.device
+    hf = hf.to(device=dev, dtype=torch.float32).contiguous()
+    mc = hf_min_box_center.to(device=dev, dtype=torch.float32).contiguous()
+    return _PointsHfSdfFn.apply(points, hf, mc, float(hf_dxdy[0]), float(hf_dxdy[1]), float(base_z), bool(inverted))

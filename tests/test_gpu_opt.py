@@ -1,0 +1,146 @@
+"""GPU parity of the kinematic-optimizer rows: CUDA kernels through the
+C ABI against the golden vectors of the unmodified reference and against the pinned oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import parc_oracle_opt as OO
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+KIN_GEN = dict(w_root_pos=1.0, w_root_rot=10.0, w_joint_rot=1.0, w_smoothness=10.0, w_penetration=1000.0, w_contact=1000.0,
+               w_sliding=10.0, w_body_constraints=1000.0, w_jerk=1000.0, max_jerk=1000.0)
+
+
+def _t(x, dev="cpu"):
+    return torch.as_tensor(np.asarray(x)).to(dev)
+
+
+def _body_points(dev):
+    bp = H.load_npz("ref_body_points.npz")
+    pts, out, o = _t(bp["points"]), [], 0
+    for c in bp["counts"]:
+        out.append(pts[o:o + int(c)].to(dev))
+        o += int(c)
+    return out, bp
+
+
+def test_points_hf_sdf_matches_reference_values_and_oracle_gradient():
+    from parc_b200.terrain import points_hf_sdf
+    d = H.load_npz("ref_hf_sdf.npz")
+    for inverted, key in ((True, "sd_inverted"), (False, "sd_solid")):
+        p = _t(d["points"], DEV).requires_grad_(True)
+        sd = points_hf_sdf(p, _t(d["hf"], DEV), _t(d["min_box_center"], DEV), _t(d["dxdy"]), -10.0, inverted)
+        torch.testing.assert_close(sd.detach().cpu(), _t(d[key]), rtol=1e-5, atol=2e-6)
+        w = torch.linspace(0.5, 1.5, sd.numel(), device=DEV).reshape(sd.shape)
+        (sd * w).sum().backward()
+        po = _t(d["points"]).requires_grad_(True)
+        so = OO.points_hf_sdf(po, _t(d["hf"]), _t(d["min_box_center"]), _t(d["dxdy"]), -10.0, inverted)
+        (so * w.cpu()).sum().backward()
+        torch.testing.assert_close(p.grad.cpu(), po.grad, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("tag", ["full", "nocontact"])
+def test_motion_loss_matches_reference_golden(tag):
+    from parc_b200.motion_optimization import LossType, motion_terrain_contact_loss_localized
+    d = H.load_npz("ref_opt_loss.npz")
+    model = H.product_model(DEV)
+    pts, _ = _body_points(DEV)
+    terrain = H.product_terrain(_t(d["hf"]), d["min_point"], float(d["dxdy"][0]), DEV)
+    p = [_t(d[k], DEV).clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+    w = d[tag + "_weights"]
+    kw = dict(zip(("w_root_pos", "w_root_rot", "w_joint_rot", "w_smoothness", "w_penetration", "w_contact", "w_sliding",
+                   "w_body_constraints", "w_jerk", "max_jerk"), [float(x) for x in w]))
+    loss, losses = motion_terrain_contact_loss_localized(
+        p[0], p[1], p[2], _t(d["src_root_pos"], DEV), _t(d["src_root_rot_quat"], DEV), _t(d["src_joint_rot"], DEV),
+        _t(d["src_body_vels"], DEV), _t(d["src_body_rot_vels"], DEV), _t(d["contacts"], DEV), terrain, pts, model,
+        body_constraints=None, **kw)
+    loss.backward()
+    got = np.array([losses[t] for t in list(LossType)[:9]])
+    np.testing.assert_allclose(got, d[tag + "_terms"], rtol=2e-5, atol=2e-6)
+    np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
+    for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
+        ref = d[tag + k]
+        np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+
+
+def _synthetic_batch(B, T, seed):
+    """B clips of the synthetic generator with their own 32x32 blocky terrains (BASELINE config 4 shape)."""
+    from parc_b200 import synth
+    spec = synth.humanoid_spec()
+    clips = synth.make_clips(spec, B, seed=seed, min_frames=T, max_frames=T, wrap_fraction=0.0)
+    om = H.oracle_model()
+    g = torch.Generator().manual_seed(seed + 1)
+    out = dict(src_root_pos=[], src_root_rot_quat=[], src_joint_rot=[], src_body_vels=[], src_body_rot_vels=[], contacts=[], hf=[],
+               min_point=[], tgt_root_pos=[], tgt_root_rot=[], tgt_joint_dof=[])
+    from oracle import parc_oracle as O
+    for c in clips:
+        rp, rr, jr = c["root_pos"], c["root_rot"], c["joint_rot"]
+        bp, br = om.forward_kinematics(rp, rr, jr)
+        out["src_root_pos"].append(rp); out["src_root_rot_quat"].append(rr); out["src_joint_rot"].append(jr)
+        out["src_body_vels"].append(bp[1:] - bp[:-1]); out["src_body_rot_vels"].append(O.quat_diff_angle(br[1:], br[:-1]))
+        out["contacts"].append(c["contacts"])
+        out["hf"].append(torch.as_tensor(c["hf"], dtype=torch.float32)); out["min_point"].append(torch.as_tensor(c["min_point"], dtype=torch.float32))
+        out["tgt_root_pos"].append(rp + 0.02 * torch.randn(T, 3, generator=g) + torch.tensor([0.0, 0.0, -0.04]))
+        out["tgt_root_rot"].append(O.quat_to_exp_map(rr) + 0.03 * torch.randn(T, 3, generator=g))
+        out["tgt_joint_dof"].append(om.rot_to_dof(jr) + 0.05 * torch.randn(T, 28, generator=g))
+    return {k: torch.stack(v) for k, v in out.items()}, float(clips[0]["dx"])
+
+
+def test_batched_motion_loss_vs_oracle_per_motion():
+    from parc_b200.motion_optimization import motion_loss_batched
+    B, T = 3, 40
+    d, dx = _synthetic_batch(B, T, seed=31)
+    model = H.product_model(DEV)
+    pts, bp = _body_points(DEV)
+    om = H.oracle_model()
+    w = [KIN_GEN[k] for k in ("w_root_pos", "w_root_rot", "w_joint_rot", "w_smoothness", "w_penetration", "w_contact", "w_sliding",
+                              "w_body_constraints", "w_jerk", "max_jerk")]
+    p = [d[k].to(DEV).clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+    dxdy = torch.tensor([dx, dx])
+    loss, terms = motion_loss_batched(p[0], p[1], p[2], *[d[k].to(DEV) for k in ("src_root_pos", "src_root_rot_quat", "src_joint_rot",
+                                                                                 "src_body_vels", "src_body_rot_vels", "contacts")],
+                                      d["hf"].to(DEV), d["min_point"].to(DEV), dxdy, pts, model, **KIN_GEN)
+    loss.sum().backward()
+    for b in range(B):
+        po = [d[k][b].clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+        lo, to = OO.motion_loss(om, _t(bp["points"]), bp["counts"], d["hf"][b], d["min_point"][b], dxdy, po[0], po[1], po[2],
+                                d["src_root_pos"][b], d["src_root_rot_quat"][b], d["src_joint_rot"][b], d["src_body_vels"][b],
+                                d["src_body_rot_vels"][b], d["contacts"][b], w)
+        lo.backward()
+        np.testing.assert_allclose(terms[b].cpu().numpy(), to.numpy(), rtol=3e-5, atol=3e-6)
+        np.testing.assert_allclose(float(loss[b]), float(lo), rtol=3e-5)
+        for g, go in zip(p, po):
+            ref = go.grad.numpy()
+            np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+
+
+def test_config4_size_properties():
+    """1,024 motions x 300 frames: finite, deterministic, and batch-invariant (a motion evaluated alone
+    gives bit-identical terms and gradients to its row in the batch)."""
+    from parc_b200.motion_optimization import motion_loss_batched
+    B, T = 64, 300
+    d, dx = _synthetic_batch(B, T, seed=77)
+    rep = 16                                        # tile the 64 generated motions to 1,024
+    dd = {k: v.repeat(rep, *([1] * (v.dim() - 1))).to(DEV) for k, v in d.items()}
+    model = H.product_model(DEV)
+    pts, _ = _body_points(DEV)
+    dxdy = torch.tensor([dx, dx])
+    names = ("src_root_pos", "src_root_rot_quat", "src_joint_rot", "src_body_vels", "src_body_rot_vels", "contacts")
+
+    def run(sl):
+        p = [dd[k][sl].clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+        loss, terms = motion_loss_batched(p[0], p[1], p[2], *[dd[k][sl] for k in names], dd["hf"][sl], dd["min_point"][sl], dxdy, pts,
+                                          model, **KIN_GEN)
+        loss.sum().backward()
+        return loss.detach(), terms, [x.grad for x in p]
+
+    loss, terms, grads = run(slice(0, B * rep))
+    assert loss.shape == (B * rep,) and bool(torch.isfinite(loss).all()) and all(bool(torch.isfinite(g).all()) for g in grads)
+    assert bool((terms[:, 4] > 0).any()) and bool((terms >= 0).all())
+    loss2, terms2, grads2 = run(slice(0, B * rep))
+    assert torch.equal(loss, loss2) and torch.equal(terms, terms2) and all(torch.equal(a, b) for a, b in zip(grads, grads2))
+    assert torch.equal(terms[:B], terms[B:2 * B])   # tiled copies
+    l1, t1, g1 = run(slice(5, 6))
+    assert torch.equal(t1[0], terms[5]) and torch.equal(l1[0], loss[5]) and all(torch.equal(a[0], b[5]) for a, b in zip(g1, grads))
