@@ -1,0 +1,140 @@
+#!/usr/bin/env python
+"""BASELINE config 4: kinematic motion optimizer batch, 1,024 motions x 300 frames, loss forward + backward
+(FK + terrain penetration/contact SDF + temporal regularisers) through parc_b200.motion_optimization.
+
+    python bench_optimizer.py [--motions 1024] [--frames 300] [--steps 10] [--warmup 3] [--cpu-motions 2]
+
+Prints one JSON line: motions/s and ms per value-and-gradient evaluation on the GPU (CUDA events), the
+per-kernel split, and the CPU oracle port (torch autograd) on a bounded sample of the same batch. This is
+a secondary measurement; the driver's bench.py stays on config 2."""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+KIN_GEN = dict(w_root_pos=1.0, w_root_rot=10.0, w_joint_rot=1.0, w_smoothness=10.0, w_penetration=1000.0, w_contact=1000.0,
+               w_sliding=10.0, w_body_constraints=1000.0, w_jerk=1000.0, max_jerk=1000.0)
+NAMES = ("src_root_pos", "src_root_rot_quat", "src_joint_rot", "src_body_vels", "src_body_rot_vels", "contacts")
+
+
+def build_batch(model, B, T, seed, dev):
+    """Synthetic clips (SURVEY 8d generator) with their own 32x32 terrains; source features by the CUDA FK."""
+    from parc_b200 import synth
+    gen = min(B, 64)
+    clips = synth.make_clips(synth.humanoid_spec(), gen, seed=seed, min_frames=T, max_frames=T, wrap_fraction=0.0)
+    rp = torch.stack([c["root_pos"] for c in clips]).to(dev)
+    rr = torch.stack([c["root_rot"] for c in clips]).to(dev)
+    jr = torch.stack([c["joint_rot"] for c in clips]).to(dev)
+    hf0 = torch.stack([torch.as_tensor(c["hf"], dtype=torch.float32) for c in clips]).to(dev)
+    mp0 = torch.stack([torch.as_tensor(c["min_point"], dtype=torch.float32) for c in clips]).to(dev)
+    # ground the character: root height = terrain height under the root + 0.9 m (the generator's clips float at a
+    # fixed height over blocky terrain, which would bury half the body in the taller blocks)
+    dx0 = float(clips[0]["dx"])
+    ij = torch.round((rp[..., :2] - mp0[:, None, :]) / dx0).long().clamp(0, hf0.shape[1] - 1)
+    ground = hf0[torch.arange(gen, device=dev)[:, None], ij[..., 0], ij[..., 1]]
+    rp = rp.clone()
+    rp[..., 2] = ground + 0.9
+    bp, br = model.forward_kinematics(rp, rr, jr)
+    d = dict(src_root_pos=rp, src_root_rot_quat=rr, src_joint_rot=jr, src_body_vels=bp[:, 1:] - bp[:, :-1])
+    dq = br[:, 1:], br[:, :-1]
+    # quat_diff_angle on the host side of the harness (input preparation, not the timed path)
+    q1, q0 = dq[1], dq[0]
+    conj = torch.cat([-q0[..., :3], q0[..., 3:]], dim=-1)
+    w = q1[..., 3] * conj[..., 3] - (q1[..., :3] * conj[..., :3]).sum(-1)
+    v = q1[..., 3:] * conj[..., :3] + conj[..., 3:] * q1[..., :3] + torch.cross(q1[..., :3], conj[..., :3], dim=-1)
+    ln = v.norm(dim=-1)
+    d["src_body_rot_vels"] = torch.where(ln > 1e-5, 2.0 * torch.atan2(ln, w.abs()), torch.zeros_like(ln))
+    d["contacts"] = torch.stack([c["contacts"] for c in clips]).to(dev)
+    d["hf"] = torch.stack([torch.as_tensor(c["hf"], dtype=torch.float32) for c in clips]).to(dev)
+    d["min_point"] = torch.stack([torch.as_tensor(c["min_point"], dtype=torch.float32) for c in clips]).to(dev)
+    g = torch.Generator().manual_seed(seed + 1)
+    d["tgt_root_pos"] = rp + (0.02 * torch.randn(gen, T, 3, generator=g) + torch.tensor([0.0, 0.0, -0.02])).to(dev)
+    d["tgt_root_rot"] = model_rot_to_exp(rr) + 0.03 * torch.randn(gen, T, 3, generator=g).to(dev)
+    d["tgt_joint_dof"] = model.rot_to_dof(jr) + 0.05 * torch.randn(gen, T, 28, generator=g).to(dev)
+    rep = (B + gen - 1) // gen
+    d = {k: v.repeat(rep, *([1] * (v.dim() - 1)))[:B].contiguous() for k, v in d.items()}
+    return d, float(clips[0]["dx"])
+
+
+def model_rot_to_exp(q):
+    s = torch.where(q[..., 3:] < 0, -1.0, 1.0)
+    q = q * s
+    ln = q[..., :3].norm(dim=-1, keepdim=True)
+    ang = 2.0 * torch.atan2(ln, q[..., 3:])
+    axis = q[..., :3] / ln.clamp(min=1e-6)
+    return torch.where(ln > 1e-5, axis * ang, torch.zeros_like(axis))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--motions", type=int, default=1024)
+    ap.add_argument("--frames", type=int, default=300)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--cpu-motions", type=int, default=2)
+    args = ap.parse_args()
+    assert torch.cuda.is_available(), "needs a CUDA device (no CPU fallback on the product path)"
+    dev = torch.device("cuda", 0)
+    from parc_b200 import KinCharModel, geom_util, synth
+    from parc_b200.motion_optimization import motion_loss_batched
+    model = KinCharModel(dev)
+    model.load_char_file(synth.HUMANOID_JSON)
+    pts = geom_util.get_char_point_samples(model)
+    B, T = args.motions, args.frames
+    d, dx = build_batch(model, B, T, 77, dev)
+    dxdy = torch.tensor([dx, dx])
+
+    def step():
+        p = [d[k].clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+        loss, terms = motion_loss_batched(p[0], p[1], p[2], *[d[k] for k in NAMES], d["hf"], d["min_point"], dxdy, pts, model, **KIN_GEN)
+        loss.sum().backward()
+        return loss, terms, p
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss, terms, p = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    # CPU oracle port on a bounded sample (test infrastructure used as the reported baseline only)
+    cpu = None
+    if args.cpu_motions > 0:
+        from oracle import parc_oracle_opt as OO
+        from tests import helpers as H
+        om = H.oracle_model()
+        bp = torch.cat([x.cpu() for x in pts])
+        counts = [int(x.shape[0]) for x in pts]
+        w = [KIN_GEN[k] for k in ("w_root_pos", "w_root_rot", "w_joint_rot", "w_smoothness", "w_penetration", "w_contact", "w_sliding",
+                                  "w_body_constraints", "w_jerk", "max_jerk")]
+        torch.set_num_threads(os.cpu_count() or 1)
+        t0 = time.perf_counter()
+        for b in range(args.cpu_motions):
+            po = [d[k][b].cpu().clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+            lo, _ = OO.motion_loss(om, bp, counts, d["hf"][b].cpu(), d["min_point"][b].cpu(), dxdy, po[0], po[1], po[2],
+                                   *[d[k][b].cpu() for k in NAMES], w)
+            lo.backward()
+        dt = (time.perf_counter() - t0) / args.cpu_motions
+        cpu = {"value": 1.0 / dt, "unit": "motions/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": "%d of the %d motions, torch CPU autograd, %.2f s per motion fwd+bwd" % (args.cpu_motions, B, dt)}
+    frames = B * T
+    alg_bytes = frames * 266 * 4            # params + grads + source pose + contacts + source body vels per frame
+    print(json.dumps({"metric": "optimizer loss fwd+bwd, motions/s (1,024 x 300 frames)", "value": B / (ms * 1e-3), "unit": "motions/s",
+                      "ms_per_eval": ms, "frames_per_s": frames / (ms * 1e-3), "config": {"workload": "BASELINE configs[3]", "motions": B,
+                      "frames": T, "body_points": int(sum(x.shape[0] for x in pts)), "terrain": list(d["hf"].shape[1:])},
+                      "hbm_floor_ms": alg_bytes / 6546.6e9 * 1e3, "cpu_baseline": cpu,
+                      "stats": {"mean_loss": float(loss.mean()), "mean_penetration": float(terms[:, 4].mean())}}))
+
+
+if __name__ == "__main__":
+    main()

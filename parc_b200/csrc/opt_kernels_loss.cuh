@@ -117,6 +117,43 @@ __global__ void __launch_bounds__(256) opt_pose_kernel(const __grid_constant__ p
     }
 }
 
+// Minimum of the column SDFs over the window's cells for one point. The cell under the point is evaluated first; a
+// cell k columns away is at least (k - 1) * dx from the point, so only cells within floor(bound / min(dx, dy)) + 1
+// of it can still be closer than `bound`. What still needs a scan:
+//   air columns   only while the running minimum is > 0 (<= 0 means "not inside the ground": the penetration term
+//                 is 0 whatever the other cells say);
+//   solid columns only for bodies with a non-zero contact label, and only below `solid_cap` (the body's closest
+//                 distance found so far: a point that cannot beat it does not matter).
+// Within those limits the result equals the reference's minimum over the whole window.
+struct CellScan { float air, solid; int arg_air, arg_solid; };
+template <typename HF>
+__device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float ox, float oy, float dx, float dy, float base_z,
+                                               bool need_air, bool need_solid, float solid_cap, HF height) {
+    const float hx = dx * 0.5f, hy = dy * 0.5f;
+    const int ix0 = max(0, min(__float2int_rn((P.x - ox) / dx), psx - 1)), iy0 = max(0, min(__float2int_rn((P.y - oy) / dy), psy - 1));
+    const int c0 = ix0 * psy + iy0;
+    const CellSd r0 = cell_sd(P.x - (ix0 * dx + ox), P.y - (iy0 * dy + oy), P.z, height(ix0, iy0), hx, hy, base_z);
+    CellScan out;
+    out.air = r0.air; out.solid = r0.solid; out.arg_air = c0; out.arg_solid = c0;
+    const float b_air = (need_air && out.air > 0.f) ? out.air : 0.f;
+    const float b_solid = (need_solid && out.solid > 0.f) ? fminf(out.solid, solid_cap) : 0.f;
+    const float bound = fmaxf(b_air, b_solid);
+    if (!(bound > 0.f)) return out;
+    const int r = (int)fminf(bound / fminf(dx, dy), 1.0e6f) + 1;
+    const int x0 = max(ix0 - r, 0), x1 = min(ix0 + r, psx - 1), y0 = max(iy0 - r, 0), y1 = min(iy0 + r, psy - 1);
+    for (int cx = x0; cx <= x1; ++cx) {
+        const float rx = P.x - (cx * dx + ox);
+        for (int cy = y0; cy <= y1; ++cy) {
+            const int c = cx * psy + cy;
+            const CellSd v = cell_sd(rx, P.y - (cy * dy + oy), P.z, height(cx, cy), hx, hy, base_z);
+            // the lower cell index wins ties, as a scan in index order would
+            if (v.air < out.air || (v.air == out.air && c < out.arg_air)) { out.air = v.air; out.arg_air = c; }
+            if (v.solid < out.solid || (v.solid == out.solid && c < out.arg_solid)) { out.solid = v.solid; out.arg_solid = c; }
+        }
+    }
+    return out;
+}
+
 // ---- 2. penetration + contact against the frame's heightfield window ---------------------------------
 // One block per frame. Thread k < Np owns body sample point k. Shared memory: the window's heights, the
 // per-body closest (distance, point) key, the per-body gradient accumulators.
@@ -126,6 +163,8 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
                                                       OptTerrain ter, OptWs ws, int need_grad) {
     __shared__ float s_h[OPT_MAX_PATCH];
     __shared__ unsigned long long s_key[PARC_MAX_BODIES];
+    __shared__ unsigned s_bub[PARC_MAX_BODIES];     // per body: smallest own-cell solid distance of its points (float bits, >= 0)
+    __shared__ float s_hmax;
     __shared__ float s_g[PARC_MAX_BODIES][8];
     __shared__ float s_red[16];
     extern __shared__ float s_pg[];          // [num_points][7] per-point gradient w.r.t. the body transform (need_grad)
@@ -140,16 +179,26 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
         for (int k = tid; k < cells; k += blockDim.x) { const int cx = k / psy, cy = k - cx * psy; s_h[k] = hf[(sx + cx) * ter.Y + sy + cy]; }
     for (int k = tid; k < J; k += blockDim.x) {
         s_key[k] = ~0ull;
+        s_bub[k] = 0x7f800000u;
 #pragma unroll
         for (int c = 0; c < 8; ++c) s_g[k][c] = 0.f;
     }
     __syncthreads();
+    if (tid < 32) {   // highest cell of the window: a point above it is at least (z - hmax) from every solid column
+        float m = -3.0e38f;
+        for (int k = tid; k < cells; k += 32) { const int cx = k / psy, cy = k - cx * psy; m = fmaxf(m, staged ? s_h[k] : hf[(sx + cx) * ter.Y + sy + cy]); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL_MASK, m, o));
+        if (tid == 0) s_hmax = m;
+    }
     // window origin (:549): min_point + start * dxdy
     const float ox = __fadd_rn(ter.min_point[b * ter.mp_stride], __fmul_rn((float)sx, ter.dx));
     const float oy = __fadd_rn(ter.min_point[b * ter.mp_stride + 1], __fmul_rn((float)sy, ter.dy));
     const float hx = ter.dx * 0.5f, hy = ter.dy * 0.5f, top = -cfg.base_z;
     const bool want_contact = cfg.w[PARC_LOSS_CONTACT] != 0.f;
+    auto height = [&](int cx, int cy) { return staged ? s_h[cx * psy + cy] : hf[(sx + cx) * ter.Y + sy + cy]; };
     float pen_sum = 0.f;
+    // ---- pass 1: penetration (air columns) of every point; own-cell solid distance of the contact bodies' points
     for (int k = tid; k < cfg.num_points; k += blockDim.x) {
         int body = 0;
         while (k >= cfg.point_start[body + 1]) ++body;
@@ -157,38 +206,44 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
         const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
         const Vec3 lp = make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2]);
         const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
-        float best_a = 3.0e38f, best_s = 3.0e38f;
-        int arg_a = 0;
-        for (int cx = 0; cx < psx; ++cx) {
-            const float rx = P.x - (cx * ter.dx + ox);
-            for (int cy = 0; cy < psy; ++cy) {
-                const int c = cx * psy + cy;
-                const float h = staged ? s_h[c] : hf[(sx + cx) * ter.Y + sy + cy];
-                const CellSd r = cell_sd(rx, P.y - (cy * ter.dy + oy), P.z, h, hx, hy, cfg.base_z);
-                if (r.air < best_a) { best_a = r.air; arg_a = c; }
-                best_s = fminf(best_s, r.solid);
-            }
-        }
+        const int col = cfg.contact_col[body];
+        const bool need_solid = want_contact && col >= 0 && contacts[i * cfg.num_contact_cols + col] != 0.f;
+        const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, true, false, 0.f, height);
         // penetration (:553-556): -min(-min_air, 0) = max(min_air, 0)
-        const float pen = fmaxf(best_a, 0.f);
-        pen_sum += pen;
+        pen_sum += fmaxf(sc.air, 0.f);
         Vec3 gP = make_vec3(0.f, 0.f, 0.f);
-        if (need_grad && best_a > 0.f) {
-            const int cx = arg_a / psy, cy = arg_a - cx * psy;
-            const float h = staged ? s_h[arg_a] : hf[(sx + cx) * ter.Y + sy + cy];
+        if (need_grad && sc.air > 0.f) {
+            const int cx = sc.arg_air / psy, cy = sc.arg_air - cx * psy;
+            const float h = height(cx, cy);
             gP = cfg.w[PARC_LOSS_PENETRATION] * cell_sd_grad(P.x - (cx * ter.dx + ox), P.y - (cy * ter.dy + oy), P.z - (h + top) * 0.5f, hx, hy, (top - h) * 0.5f);
         }
-        const int col = cfg.contact_col[body];
-        const float pos_sd = fmaxf(best_s, 0.f);
-        if (want_contact && col >= 0) {
-            // closest point of the body (:570-572): min over its points, first index on ties
-            const unsigned long long key = ((unsigned long long)__float_as_uint(pos_sd) << 32) | (unsigned)(k - cfg.point_start[body]);
-            atomicMin(&s_key[body], key);
-        }
+        if (need_solid) atomicMin(&s_bub[body], __float_as_uint(fmaxf(sc.solid, 0.f)));   // sc.solid here = the cell under the point
         if (need_grad) {
             const Quat gq = rotate_bwd_q(rot, lp, gP);
             float* o = s_pg + k * 7;
             o[0] = gP.x; o[1] = gP.y; o[2] = gP.z; o[3] = gq.x; o[4] = gq.y; o[5] = gq.z; o[6] = gq.w;
+        }
+    }
+    __syncthreads();
+    // ---- pass 2: closest point of each contact body (:570-572): min over its points of the solid-column distance,
+    //      first index on ties. A point is scanned only if it can still beat the body's best own-cell distance.
+    if (want_contact) {
+        const float hmax = s_hmax;
+        for (int k = tid; k < cfg.num_points; k += blockDim.x) {
+            int body = 0;
+            while (k >= cfg.point_start[body + 1]) ++body;
+            const int col = cfg.contact_col[body];
+            if (col < 0 || contacts[i * cfg.num_contact_cols + col] == 0.f) continue;
+            const float* bp = ws.body_pos + (i * J + body) * 3;
+            const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
+            const Vec3 P = quat_rotate(rot, make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2])) + make_vec3(bp[0], bp[1], bp[2]);
+            const float cap = __uint_as_float(s_bub[body]);
+            // above every column by more than the body's best (1e-4 m of slack: the column distance is computed as
+            // |z - centre| - half height, which rounds differently from z - top)
+            if (P.z - hmax > cap + 1e-4f) continue;
+            const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, cap, height);
+            const unsigned long long key = ((unsigned long long)__float_as_uint(fmaxf(sc.solid, 0.f)) << 32) | (unsigned)(k - cfg.point_start[body]);
+            atomicMin(&s_key[body], key);
         }
     }
     __syncthreads();
@@ -217,13 +272,7 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
                 const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
                 const Vec3 lp = make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2]);
                 const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
-                float best_s = 3.0e38f; int arg_s = 0;
-                for (int c = 0; c < cells; ++c) {
-                    const int cx = c / psy, cy = c - cx * psy;
-                    const float h = staged ? s_h[c] : hf[(sx + cx) * ter.Y + sy + cy];
-                    const CellSd r = cell_sd(P.x - (cx * ter.dx + ox), P.y - (cy * ter.dy + oy), P.z, h, hx, hy, cfg.base_z);
-                    if (r.solid < best_s) { best_s = r.solid; arg_s = c; }
-                }
+                const int arg_s = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, d * 1.00001f + 1e-6f, height).arg_solid;
                 const int cx = arg_s / psy, cy = arg_s - cx * psy;
                 const float h = staged ? s_h[arg_s] : hf[(sx + cx) * ter.Y + sy + cy];
                 const Vec3 g = (cfg.w[PARC_LOSS_CONTACT] * cw) *
