@@ -123,12 +123,13 @@ __global__ void __launch_bounds__(256) opt_pose_kernel(const __grid_constant__ p
 //   air columns   only while the running minimum is > 0 (<= 0 means "not inside the ground": the penetration term
 //                 is 0 whatever the other cells say);
 //   solid columns only for bodies with a non-zero contact label, and only below `solid_cap` (the body's closest
-//                 distance found so far: a point that cannot beat it does not matter).
+//                 distance found so far: a point that cannot beat it does not matter); `solid_zlb` = how far the
+//                 point is above the highest column top of the window (0 if it is not).
 // Within those limits the result equals the reference's minimum over the whole window.
 struct CellScan { float air, solid; int arg_air, arg_solid; };
 template <typename HF>
 __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float ox, float oy, float dx, float dy, float base_z,
-                                               bool need_air, bool need_solid, float solid_cap, HF height) {
+                                               bool need_air, bool need_solid, float solid_cap, float solid_zlb, HF height) {
     const float hx = dx * 0.5f, hy = dy * 0.5f;
     const int ix0 = max(0, min(__float2int_rn((P.x - ox) / dx), psx - 1)), iy0 = max(0, min(__float2int_rn((P.y - oy) / dy), psy - 1));
     const int c0 = ix0 * psy + iy0;
@@ -137,9 +138,11 @@ __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float o
     out.air = r0.air; out.solid = r0.solid; out.arg_air = c0; out.arg_solid = c0;
     const float b_air = (need_air && out.air > 0.f) ? out.air : 0.f;
     const float b_solid = (need_solid && out.solid > 0.f) ? fminf(out.solid, solid_cap) : 0.f;
-    const float bound = fmaxf(b_air, b_solid);
-    if (!(bound > 0.f)) return out;
-    const int r = (int)fminf(bound / fminf(dx, dy), 1.0e6f) + 1;
+    if (!(fmaxf(b_air, b_solid) > 0.f)) return out;
+    // a point that is at least solid_zlb above every column top is, k columns away, at least
+    // sqrt(((k - 1) dx)^2 + zlb^2) from a column: over flat ground only the neighbouring cells remain
+    const float b_solid_xy = sqrtf(fmaxf(b_solid * b_solid - solid_zlb * solid_zlb, 0.f));
+    const int r = (int)fminf(fmaxf(b_air, b_solid_xy) / fminf(dx, dy), 1.0e6f) + 1;
     const int x0 = max(ix0 - r, 0), x1 = min(ix0 + r, psx - 1), y0 = max(iy0 - r, 0), y1 = min(iy0 + r, psy - 1);
     for (int cx = x0; cx <= x1; ++cx) {
         const float rx = P.x - (cx * dx + ox);
@@ -165,6 +168,10 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
     __shared__ unsigned long long s_key[PARC_MAX_BODIES];
     __shared__ unsigned s_bub[PARC_MAX_BODIES];     // per body: smallest own-cell solid distance of its points (float bits, >= 0)
     __shared__ float s_hmax;
+    __shared__ float s_bpos[PARC_MAX_BODIES][3];     // the frame's body transforms and contact labels, fetched once
+    __shared__ float4 s_brot[PARC_MAX_BODIES];
+    __shared__ float s_cw[PARC_MAX_BODIES];
+    __shared__ unsigned char s_pbody[1184];         // body of each sample point (num_points <= 1170, checked by the caller)
     __shared__ float s_g[PARC_MAX_BODIES][8];
     __shared__ float s_red[16];
     extern __shared__ float s_pg[];          // [num_points][7] per-point gradient w.r.t. the body transform (need_grad)
@@ -177,6 +184,14 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
     const float* hf = ter.hf + b * ter.hf_stride;
     if (staged)
         for (int k = tid; k < cells; k += blockDim.x) { const int cx = k / psy, cy = k - cx * psy; s_h[k] = hf[(sx + cx) * ter.Y + sy + cy]; }
+    for (int k = tid; k < J; k += blockDim.x)
+        for (int q = cfg.point_start[k]; q < cfg.point_start[k + 1]; ++q) s_pbody[q] = (unsigned char)k;
+    for (int k = tid; k < J * 3; k += blockDim.x) s_bpos[k / 3][k % 3] = ws.body_pos[i * J * 3 + k];
+    for (int k = tid; k < J; k += blockDim.x) {
+        s_brot[k] = reinterpret_cast<const float4*>(ws.body_rot)[i * J + k];
+        const int col = cfg.contact_col[k];
+        s_cw[k] = (cfg.w[PARC_LOSS_CONTACT] != 0.f && col >= 0) ? contacts[i * cfg.num_contact_cols + col] : 0.f;
+    }
     for (int k = tid; k < J; k += blockDim.x) {
         s_key[k] = ~0ull;
         s_bub[k] = 0x7f800000u;
@@ -200,15 +215,13 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
     float pen_sum = 0.f;
     // ---- pass 1: penetration (air columns) of every point; own-cell solid distance of the contact bodies' points
     for (int k = tid; k < cfg.num_points; k += blockDim.x) {
-        int body = 0;
-        while (k >= cfg.point_start[body + 1]) ++body;
-        const float* bp = ws.body_pos + (i * J + body) * 3;
-        const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
-        const Vec3 lp = make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2]);
+        const int body = s_pbody[k];
+        const float* bp = s_bpos[body];
+        const Quat rot = quat_from_f4(s_brot[body]);
+        const Vec3 lp = make_vec3(__ldg(body_points + k * 3), __ldg(body_points + k * 3 + 1), __ldg(body_points + k * 3 + 2));
         const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
-        const int col = cfg.contact_col[body];
-        const bool need_solid = want_contact && col >= 0 && contacts[i * cfg.num_contact_cols + col] != 0.f;
-        const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, true, false, 0.f, height);
+        const bool need_solid = s_cw[body] != 0.f;
+        const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, true, false, 0.f, 0.f, height);
         // penetration (:553-556): -min(-min_air, 0) = max(min_air, 0)
         pen_sum += fmaxf(sc.air, 0.f);
         Vec3 gP = make_vec3(0.f, 0.f, 0.f);
@@ -230,18 +243,16 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
     if (want_contact) {
         const float hmax = s_hmax;
         for (int k = tid; k < cfg.num_points; k += blockDim.x) {
-            int body = 0;
-            while (k >= cfg.point_start[body + 1]) ++body;
-            const int col = cfg.contact_col[body];
-            if (col < 0 || contacts[i * cfg.num_contact_cols + col] == 0.f) continue;
-            const float* bp = ws.body_pos + (i * J + body) * 3;
-            const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
-            const Vec3 P = quat_rotate(rot, make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2])) + make_vec3(bp[0], bp[1], bp[2]);
+            const int body = s_pbody[k];
+            if (s_cw[body] == 0.f) continue;
+            const float* bp = s_bpos[body];
+            const Vec3 P = quat_rotate(quat_from_f4(s_brot[body]), make_vec3(__ldg(body_points + k * 3), __ldg(body_points + k * 3 + 1), __ldg(body_points + k * 3 + 2))) +
+                           make_vec3(bp[0], bp[1], bp[2]);
             const float cap = __uint_as_float(s_bub[body]);
             // above every column by more than the body's best (1e-4 m of slack: the column distance is computed as
             // |z - centre| - half height, which rounds differently from z - top)
             if (P.z - hmax > cap + 1e-4f) continue;
-            const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, cap, height);
+            const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, cap, fmaxf(P.z - hmax - 1e-4f, 0.f), height);
             const unsigned long long key = ((unsigned long long)__float_as_uint(fmaxf(sc.solid, 0.f)) << 32) | (unsigned)(k - cfg.point_start[body]);
             atomicMin(&s_key[body], key);
         }
@@ -260,19 +271,20 @@ __global__ void __launch_bounds__(320) opt_sdf_kernel(const __grid_constant__ pa
     // contact term and its gradient: the closest point of each contact body
     float con_sum = 0.f;
     if (want_contact) {
-        for (int body = tid; body < J; body += blockDim.x) {
-            const int col = cfg.contact_col[body];
-            if (col < 0 || s_key[body] == ~0ull) continue;
+        // one body per warp (lane 0), so that the bodies' gradient scans run side by side
+        for (int body = tid >> 5; body < J; body += blockDim.x >> 5) {
+            if (tid & 31) continue;
+            if (s_cw[body] == 0.f || s_key[body] == ~0ull) continue;
             const float d = __uint_as_float((unsigned)(s_key[body] >> 32));
-            const float cw = contacts[i * cfg.num_contact_cols + col];
+            const float cw = s_cw[body];
             con_sum += d * cw;
             if (need_grad && d > 0.f && cw != 0.f) {
                 const int k = cfg.point_start[body] + (int)(s_key[body] & 0xffffffffu);
-                const float* bp = ws.body_pos + (i * J + body) * 3;
-                const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + body]);
-                const Vec3 lp = make_vec3(body_points[k * 3], body_points[k * 3 + 1], body_points[k * 3 + 2]);
+                const float* bp = s_bpos[body];
+                const Quat rot = quat_from_f4(s_brot[body]);
+                const Vec3 lp = make_vec3(__ldg(body_points + k * 3), __ldg(body_points + k * 3 + 1), __ldg(body_points + k * 3 + 2));
                 const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
-                const int arg_s = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, d * 1.00001f + 1e-6f, height).arg_solid;
+                const int arg_s = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, d * 1.00001f + 1e-6f, fmaxf(P.z - s_hmax - 1e-4f, 0.f), height).arg_solid;
                 const int cx = arg_s / psy, cy = arg_s - cx * psy;
                 const float h = staged ? s_h[arg_s] : hf[(sx + cx) * ter.Y + sy + cy];
                 const Vec3 g = (cfg.w[PARC_LOSS_CONTACT] * cw) *
