@@ -178,14 +178,16 @@ int parc_b200_compute_contact_reward(const float* tar_contacts, const float* con
                                      float* out, void* stream);
 
 /* compute_done (mgdm_dm_util.py:334-402); termination_heights [n,J] precomputed by the caller as
- * in RefCharEnv.update_done (:147-172), contact_body_ids i64 [n_cb]. */
+ * in RefCharEnv.update_done (:147-172), contact_body_ids i64 [n_cb], pose_termination_dist [J-1].
+ * root_pos_termination_dist is the python float (a double): it is squared in double and the product
+ * rounded to fp32 for the comparison, as TorchScript does. */
 int parc_b200_compute_done(const int32_t* done_buf_in, const float* time, float ep_len,
                            const float* root_rot, const float* body_pos, const float* tar_root_rot,
                            const float* tar_body_pos, const float* contact_force,
                            const int64_t* contact_body_ids, int32_t n_cb,
                            const float* termination_heights, int32_t pose_termination,
                            const float* pose_termination_dist, int32_t enable_early_termination,
-                           int32_t track_root, float root_pos_termination_dist,
+                           int32_t track_root, double root_pos_termination_dist,
                            float root_rot_termination_angle, int32_t num_bodies, int64_t n,
                            int32_t* done_out, void* stream);
 

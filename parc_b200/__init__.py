@@ -10,6 +10,7 @@ from .kin_char_model import KinCharModel, Joint, JointType, Geom, GeomType   # n
 from .motion_lib import MotionLib, LoopMode                                   # noqa: F401
 from .terrain import SubTerrain                                               # noqa: F401
 from .file_io import MotionFrames, load_ms_file, save_ms_file                 # noqa: F401
+from . import dm_util                                                         # noqa: F401
 
 __all__ = ["KinCharModel", "Joint", "JointType", "Geom", "GeomType", "MotionLib", "LoopMode", "SubTerrain",
-           "MotionFrames", "load_ms_file", "save_ms_file"]
+           "MotionFrames", "load_ms_file", "save_ms_file", "dm_util"]

@@ -176,7 +176,7 @@ _lib = None
 
 
 def _declare(lib):
-    vp, i64, i32, f32, u32, u64 = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_uint32, C.c_uint64
+    vp, i64, i32, f32, u32, u64, f64 = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_uint32, C.c_uint64, C.c_double
     P = C.POINTER
     lib.parc_b200_version.restype = C.c_char_p
     lib.parc_b200_version.argtypes = []
@@ -201,7 +201,7 @@ def _declare(lib):
         "parc_b200_compute_tar_obs": [P(CharModelStruct)] + [vp] * 6 + [i32, i32, i32, i32, i64, vp, vp],
         "parc_b200_compute_deepmimic_reward": [P(CharModelStruct)] + [vp] * 16 + [i32, i32, i32, i64, vp, vp],
         "parc_b200_compute_contact_reward": [vp, vp, vp, i32, i64, vp, vp],
-        "parc_b200_compute_done": [vp, vp, f32, vp, vp, vp, vp, vp, vp, i32, vp, i32, vp, i32, i32, f32, f32,
+        "parc_b200_compute_done": [vp, vp, f32, vp, vp, vp, vp, vp, vp, i32, vp, i32, vp, i32, i32, f64, f32,
                                    i32, i64, vp, vp],
         "parc_b200_fail_rate_ema": [P(EnvConfigStruct), P(EnvBuffersStruct), i32, vp, vp, vp],
         "parc_b200_env_reset": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),

@@ -81,7 +81,7 @@ extern "C" int parc_b200_compute_done(const int32_t* done_buf_in, const float* t
                                       const float* body_pos, const float* tar_root_rot, const float* tar_body_pos,
                                       const float* contact_force, const int64_t* contact_body_ids, int32_t n_cb,
                                       const float* termination_heights, int32_t pose_termination, const float* pose_termination_dist,
-                                      int32_t enable_early_termination, int32_t track_root, float root_pos_termination_dist,
+                                      int32_t enable_early_termination, int32_t track_root, double root_pos_termination_dist,
                                       float root_rot_termination_angle, int32_t num_bodies, int64_t n, int32_t* done_out, void* stream) {
     (void)done_buf_in;   // the reference only uses it for shape/dtype (torch.full_like)
     if (n == 0) return PARC_OK;
@@ -92,10 +92,12 @@ extern "C" int parc_b200_compute_done(const int32_t* done_buf_in, const float* t
         PARC_REQUIRE(!pose_termination || (body_pos && tar_body_pos && pose_termination_dist), "compute_done: pose termination inputs missing");
         PARC_REQUIRE(!(pose_termination && track_root) || (root_rot && tar_root_rot), "compute_done: root rotations missing");
     }
+    // the reference squares the python float in double and compares the fp32 tensor with the rounded product
+    const float root_pos_dist_sq = (float)(root_pos_termination_dist * root_pos_termination_dist);
     compute_done_kernel<<<blocks_for(n, 8), 256, 0, as_stream(stream)>>>(time, ep_len, root_rot, body_pos, tar_root_rot, tar_body_pos, contact_force,
                                                                          (const long long*)contact_body_ids, n_cb, termination_heights,
                                                                          pose_termination, pose_termination_dist, enable_early_termination,
-                                                                         track_root, root_pos_termination_dist, root_rot_termination_angle,
+                                                                         track_root, root_pos_dist_sq, root_rot_termination_angle,
                                                                          num_bodies, n, done_out);
     return check_launch("compute_done");
 }
