@@ -191,6 +191,19 @@ int parc_b200_compute_done(const int32_t* done_buf_in, const float* time, float 
                            float root_rot_termination_angle, int32_t num_bodies, int64_t n,
                            int32_t* done_out, void* stream);
 
+/* compute_tracking_error (mgdm_dm_util.py:520-553) -> [n,7] = root pos L2, |root rot angle|, mean body
+ * pos L2 (root-relative), mean |body rot angle|, mean |dof vel diff|, mean |root vel diff|, mean |root
+ * ang vel diff|. body_rot / body_pos are the FK outputs of both characters, as the caller
+ * (ig_parkour_env.py:1066-1095) computes them. */
+int parc_b200_compute_tracking_error(const float* root_pos, const float* root_rot, const float* body_rot,
+                                     const float* body_pos, const float* tar_root_pos,
+                                     const float* tar_root_rot, const float* tar_body_rot,
+                                     const float* tar_body_pos, const float* root_vel,
+                                     const float* root_ang_vel, const float* dof_vel,
+                                     const float* tar_root_vel, const float* tar_root_ang_vel,
+                                     const float* tar_dof_vel, int32_t num_bodies, int32_t dof_size,
+                                     int64_t n, float* out, void* stream);
+
 /* Fail-rate EMA of DeepMimicEnv.update_done (dm_env.py:648-660): for every finished env IN
  * ASCENDING ENV-ID ORDER per motion, rate <- rate*(1-w) + w (FAIL) or rate*(1-w) (otherwise).
  * Consumes done_list/done_code written by parc_b200_env_step; also refreshes the RSI sampling CDF

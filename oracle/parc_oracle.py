@@ -523,6 +523,20 @@ def compute_done(time, ep_len, root_rot, body_pos, tar_root_rot, tar_body_pos, c
     return done
 
 
+def compute_tracking_error(root_pos, root_rot, body_rot, body_pos, tar_root_pos, tar_root_rot, tar_body_rot, tar_body_pos, root_vel,
+                           root_ang_vel, dof_vel, tar_root_vel, tar_root_ang_vel, tar_dof_vel):
+    """mgdm_dm_util.py:520-553 -> [n,7]"""
+    pose_err = torch.mean(torch.abs(quat_diff_angle(body_rot, tar_body_rot)), dim=-1)
+    root_pos_l2 = torch.linalg.vector_norm(tar_root_pos - root_pos, dim=-1)
+    d = (tar_body_pos - tar_root_pos.unsqueeze(-2)) - (body_pos - root_pos.unsqueeze(-2))
+    body_pos_err = torch.mean(torch.linalg.vector_norm(d, dim=-1), dim=-1)
+    root_rot_err = torch.abs(quat_diff_angle(root_rot, tar_root_rot))
+    dof_vel_err = torch.mean(torch.abs(tar_dof_vel - dof_vel), dim=-1)
+    root_vel_err = torch.mean(torch.abs(tar_root_vel - root_vel), dim=-1)
+    root_ang_vel_err = torch.mean(torch.abs(tar_root_ang_vel - root_ang_vel), dim=-1)
+    return torch.stack([root_pos_l2, root_rot_err, body_pos_err, pose_err, dof_vel_err, root_vel_err, root_ang_vel_err], dim=-1)
+
+
 # ------------------------------------------------------------------------------------------------
 # device-RSI restatement: Philox4x32-10 + inverse-CDF (our own sampler; validated bit-exact)
 # ------------------------------------------------------------------------------------------------

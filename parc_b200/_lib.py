@@ -203,6 +203,7 @@ def _declare(lib):
         "parc_b200_compute_contact_reward": [vp, vp, vp, i32, i64, vp, vp],
         "parc_b200_compute_done": [vp, vp, f32, vp, vp, vp, vp, vp, vp, i32, vp, i32, vp, i32, i32, f64, f32,
                                    i32, i64, vp, vp],
+        "parc_b200_compute_tracking_error": [vp] * 14 + [i32, i32, i64, vp, vp],
         "parc_b200_fail_rate_ema": [P(EnvConfigStruct), P(EnvBuffersStruct), i32, vp, vp, vp],
         "parc_b200_env_reset": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),
                                 vp, i64, vp, vp, vp, vp, vp, vp, vp],

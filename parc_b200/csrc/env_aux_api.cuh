@@ -102,6 +102,25 @@ extern "C" int parc_b200_compute_done(const int32_t* done_buf_in, const float* t
     return check_launch("compute_done");
 }
 
+extern "C" int parc_b200_compute_tracking_error(const float* root_pos, const float* root_rot, const float* body_rot, const float* body_pos,
+                                                const float* tar_root_pos, const float* tar_root_rot, const float* tar_body_rot,
+                                                const float* tar_body_pos, const float* root_vel, const float* root_ang_vel,
+                                                const float* dof_vel, const float* tar_root_vel, const float* tar_root_ang_vel,
+                                                const float* tar_dof_vel, int32_t num_bodies, int32_t dof_size, int64_t n, float* out,
+                                                void* stream) {
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(num_bodies >= 1 && num_bodies <= PARC_MAX_BODIES && dof_size >= 0 && dof_size <= PARC_MAX_DOFS,
+                 "compute_tracking_error: sizes out of range");
+    PARC_REQUIRE(root_pos && root_rot && body_rot && body_pos && tar_root_pos && tar_root_rot && tar_body_rot && tar_body_pos && root_vel &&
+                     root_ang_vel && tar_root_vel && tar_root_ang_vel && out && (dof_size == 0 || (dof_vel && tar_dof_vel)),
+                 "compute_tracking_error: NULL pointer");
+    tracking_error_kernel<<<blocks_for(n, 8), 256, 0, as_stream(stream)>>>(num_bodies, dof_size, root_pos, root_rot, body_rot, body_pos,
+                                                                           tar_root_pos, tar_root_rot, tar_body_rot, tar_body_pos, root_vel,
+                                                                           root_ang_vel, dof_vel, tar_root_vel, tar_root_ang_vel,
+                                                                           tar_dof_vel, n, out);
+    return check_launch("compute_tracking_error");
+}
+
 extern "C" int parc_b200_fail_rate_ema(const parc_env_config_t* cfg, const parc_env_buffers_t* env, int32_t num_motions, float* cdf,
                                        int32_t* scratch, void* stream) {
     PARC_REQUIRE(cfg && env && num_motions > 0, "fail_rate_ema: bad arguments");

@@ -230,6 +230,59 @@ __global__ void contact_reward_kernel(const float* __restrict__ tar, const float
     }
 }
 
+// ---- compute_tracking_error (mgdm_dm_util.py:520-553): one warp per env, lanes over bodies / dofs -----
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(256) tracking_error_kernel(
+    int J, int D, const float* __restrict__ root_pos, const float* __restrict__ root_rot, const float* __restrict__ body_rot,
+    const float* __restrict__ body_pos, const float* __restrict__ tar_root_pos, const float* __restrict__ tar_root_rot,
+    const float* __restrict__ tar_body_rot, const float* __restrict__ tar_body_pos, const float* __restrict__ root_vel,
+    const float* __restrict__ root_ang_vel, const float* __restrict__ dof_vel, const float* __restrict__ tar_root_vel,
+    const float* __restrict__ tar_root_ang_vel, const float* __restrict__ tar_dof_vel, long long n, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long wpb = blockDim.x / 32;
+    for (long long i = (long long)blockIdx.x * wpb + threadIdx.x / 32; i < n; i += (long long)gridDim.x * wpb) {
+        const Vec3 rp = make_vec3(root_pos[i * 3], root_pos[i * 3 + 1], root_pos[i * 3 + 2]);
+        const Vec3 trp = make_vec3(tar_root_pos[i * 3], tar_root_pos[i * 3 + 1], tar_root_pos[i * 3 + 2]);
+        float pose = 0.f, bpos = 0.f, dv = 0.f;
+        for (int b = lane; b < J; b += 32) {
+            const Quat q = quat_from_f4(__ldg(reinterpret_cast<const float4*>(body_rot) + i * J + b));
+            const Quat tq = quat_from_f4(__ldg(reinterpret_cast<const float4*>(tar_body_rot) + i * J + b));
+            pose += fabsf(quat_diff_angle(q, tq));
+            const float* p = body_pos + (i * J + b) * 3;
+            const float* tp = tar_body_pos + (i * J + b) * 3;
+            const Vec3 d = (make_vec3(tp[0], tp[1], tp[2]) - trp) - (make_vec3(p[0], p[1], p[2]) - rp);
+            bpos += sqrtf(sqnorm3_seq(d));
+        }
+        for (int d = lane; d < D; d += 32) dv += fabsf(__fsub_rn(tar_dof_vel[i * D + d], dof_vel[i * D + d]));
+        pose = warp_sum(pose);
+        bpos = warp_sum(bpos);
+        dv = warp_sum(dv);
+        if (lane == 0) {
+            float* o = out + i * 7;
+            o[0] = sqrtf(sqnorm3_seq(trp - rp));
+            const Quat a = quat_from_f4(__ldg(reinterpret_cast<const float4*>(root_rot) + i));
+            const Quat b = quat_from_f4(__ldg(reinterpret_cast<const float4*>(tar_root_rot) + i));
+            o[1] = fabsf(quat_diff_angle(a, b));
+            o[2] = bpos / (float)J;
+            o[3] = pose / (float)J;
+            o[4] = D > 0 ? dv / (float)D : nanf("");     // torch.mean over an empty dim is NaN
+            float rv = 0.f, rav = 0.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                rv += fabsf(__fsub_rn(tar_root_vel[i * 3 + k], root_vel[i * 3 + k]));
+                rav += fabsf(__fsub_rn(tar_root_ang_vel[i * 3 + k], root_ang_vel[i * 3 + k]));
+            }
+            o[5] = rv / 3.0f;
+            o[6] = rav / 3.0f;
+        }
+    }
+}
+
 // ---- compute_done (mgdm_dm_util.py:334-402): one warp per env, lanes over bodies ---------------------
 __global__ void __launch_bounds__(256) compute_done_kernel(const float* __restrict__ time, float ep_len, const float* __restrict__ root_rot,
                                                            const float* __restrict__ body_pos, const float* __restrict__ tar_root_rot,

@@ -6,6 +6,7 @@ include/parc_b200_env.h. Same names, argument order and meaning as the reference
   compute_deepmimic_reward    mgdm_dm_util.py:269-332
   compute_contact_reward      mgdm_dm_util.py:497-518
   compute_done                mgdm_dm_util.py:334-402
+  compute_tracking_error      mgdm_dm_util.py:520-553
   calc_heading                PARC/util/torch_util.py:501-510
 
 The reference functions are independent of the character (they take tensors only); the kernels need
@@ -117,4 +118,18 @@ def compute_done(done_buf, time, ep_len: float, root_rot, body_pos, char_root_po
         _lib.ptr(ids), 0 if ids is None else int(ids.numel()), _lib.ptr(th), int(bool(pose_termination)), _lib.ptr(ptd),
         int(bool(enable_early_termination)), int(bool(track_root)), float(root_pos_termination_dist),
         float(root_rot_termination_angle), J, n, _lib.ptr(out), _lib.stream_ptr(out.device)))
+    return out
+
+
+def compute_tracking_error(root_pos, root_rot, body_rot, body_pos, tar_root_pos, tar_root_rot, tar_body_rot, tar_body_pos, root_vel,
+                           root_ang_vel, dof_vel, tar_root_vel, tar_root_ang_vel, tar_dof_vel):
+    """-> [n,7]: root pos L2, |root rot angle|, mean root-relative body pos L2, mean |body rot angle|, mean |dof vel diff|,
+    mean |root vel diff|, mean |root ang vel diff|"""
+    n, J, D = root_pos.shape[0], body_rot.shape[-2], dof_vel.shape[-1]
+    out = torch.empty(n, 7, dtype=torch.float32, device=root_pos.device)
+    if n == 0:
+        return out
+    a = [_c(x) for x in (root_pos, root_rot, body_rot, body_pos, tar_root_pos, tar_root_rot, tar_body_rot, tar_body_pos, root_vel,
+                         root_ang_vel, dof_vel, tar_root_vel, tar_root_ang_vel, tar_dof_vel)]
+    _lib.check(_lib.lib().parc_b200_compute_tracking_error(*[_lib.ptr(x) for x in a], J, D, n, _lib.ptr(out), _lib.stream_ptr(out.device)))
     return out

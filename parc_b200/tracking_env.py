@@ -276,6 +276,19 @@ class TrackingEnv:
         """dict of [N] views named like IGParkourEnv._info["rewards"] (ig_parkour_env.py:1015-1044)."""
         return {n: self._reward_terms[:, i] for i, n in enumerate(REWARD_TERM_NAMES)}
 
+    def compute_tracking_error(self):
+        """IGParkourEnv._update_info with report_tracking_error (ig_parkour_env.py:1066-1095): FK of the
+        simulated and of the reference character, then compute_tracking_error -> [N,7] (what the
+        reference stores in info["tracking_error"])."""
+        from . import dm_util
+        m = self._kin_char_model
+        char_body_pos, char_body_rot = m.forward_kinematics(self._char_root_pos, self._char_root_rot, m.dof_to_rot(self._char_dof_pos))
+        ref_body_pos, ref_body_rot = m.forward_kinematics(self._ref_root_pos, self._ref_root_rot, self._ref_joint_rot)
+        return dm_util.compute_tracking_error(
+            self._char_root_pos, self._char_root_rot, char_body_rot, char_body_pos, self._ref_root_pos, self._ref_root_rot, ref_body_rot,
+            ref_body_pos, self._char_root_vel, self._char_root_ang_vel, self._char_dof_vel, self._ref_root_vel, self._ref_root_ang_vel,
+            self._ref_dof_vel)
+
     def sim_state_tensors(self):
         """The tensors an external integrator (or a host upload) writes every step."""
         return {"root_state": self._root_state, "dof_state": self._dof_state,

@@ -184,3 +184,37 @@ def test_operators_vs_reference_golden_step():
     pen = dm_util.compute_contact_reward(cu("out_ref_contacts"), cu("in_char_contact_forces"),
                                          torch.tensor(cfg["contact_weights"], dtype=torch.float32, device=DEV))
     assert_close(pen.mean(dim=-1), g["contact_penalty"], atol=2e-6, what="contact penalty vs golden")
+
+
+def test_compute_tracking_error_vs_oracle():
+    g = torch.Generator().manual_seed(11)
+    n = 1000
+    a, b = _state(12, n), _state(13, n)
+    for k in a:
+        b[k] = a[k] + 0.1 * b[k]
+    b["root_rot"] = b["root_rot"] / b["root_rot"].norm(dim=-1, keepdim=True)
+    body_rot, tar_body_rot = _quats(g, n, J), _quats(g, n, J)
+    body_pos = a["root_pos"].unsqueeze(1) + torch.randn(n, J, 3, generator=g) * 0.4
+    tar_body_pos = b["root_pos"].unsqueeze(1) + (body_pos - a["root_pos"].unsqueeze(1)) + torch.randn(n, J, 3, generator=g) * 0.1
+    args = [a["root_pos"], a["root_rot"], body_rot, body_pos, b["root_pos"], b["root_rot"], tar_body_rot, tar_body_pos, a["root_vel"],
+            a["root_ang_vel"], a["dof_vel"], b["root_vel"], b["root_ang_vel"], b["dof_vel"]]
+    want = O.compute_tracking_error(*args)
+    got = dm_util.compute_tracking_error(*_cu(*args))
+    assert got.shape == (n, 7)
+    assert_close(got, want, atol=2e-6, what="tracking error")
+
+
+def test_tracking_error_vs_reference_golden():
+    """a19: the env-level call (dof_to_rot + two FK passes + the error kernel) on the recorded step."""
+    from tests.test_gpu_parity import _golden_env
+    model = H.product_model(DEV)
+    env, g = _golden_env(model)
+    ge = load_npz("ref_tracking_error.npz")
+    cu = lambda k: t(g[k]).to(DEV)
+    for k in ("root_pos", "root_rot", "root_vel", "root_ang_vel", "dof_pos", "dof_vel"):
+        getattr(env, "_char_" + k).copy_(cu("in_char_" + k))
+    for k in ("root_pos", "root_rot", "root_vel", "root_ang_vel", "joint_rot", "dof_vel"):
+        getattr(env, "_ref_" + k).copy_(cu("out_ref_" + k))
+    got = env.compute_tracking_error()
+    W = float(np.abs(g["out_ref_root_pos"]).max())
+    H.assert_close_world(got, ge["tracking_error"], W, what="tracking error vs golden")

@@ -146,3 +146,17 @@ def test_observation_tape_shipped_with_reference():
     assert inside.float().mean() > 0.8
     frac_ok = ((got - want).abs() <= 1e-5).float().mean().item()
     assert frac_ok > 0.999, "heightmap columns inside the stored slice: %.4f reproduce" % frac_ok
+
+
+def test_tracking_error_matches_reference():
+    """a19: oracle compute_tracking_error on the FK outputs the reference recorded (ref_tracking_error.npz)."""
+    g, ge = load_npz("ref_env_step.npz"), load_npz("ref_tracking_error.npz")
+    m = oracle_model()
+    cbp, cbr = m.forward_kinematics(t(g["in_char_root_pos"]), t(g["in_char_root_rot"]), m.dof_to_rot(t(g["in_char_dof_pos"])))
+    rbp, rbr = m.forward_kinematics(t(g["out_ref_root_pos"]), t(g["out_ref_root_rot"]), t(g["out_ref_joint_rot"]))
+    assert_close(cbp, ge["char_body_pos"], atol=2e-6, what="char body pos")
+    assert_close(rbr, ge["ref_body_rot"], atol=2e-6, what="ref body rot")
+    err = O.compute_tracking_error(t(g["in_char_root_pos"]), t(g["in_char_root_rot"]), cbr, cbp, t(g["out_ref_root_pos"]),
+                                   t(g["out_ref_root_rot"]), rbr, rbp, t(g["in_char_root_vel"]), t(g["in_char_root_ang_vel"]),
+                                   t(g["in_char_dof_vel"]), t(g["out_ref_root_vel"]), t(g["out_ref_root_ang_vel"]), t(g["out_ref_dof_vel"]))
+    assert_close(err, ge["tracking_error"], atol=2e-6, what="tracking error")
