@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--motions", type=int, default=NUM_MOTIONS)
     ap.add_argument("--cpu-envs", type=int, default=CPU_SAMPLE_ENVS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunks", type=int, default=8, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
     return ap.parse_args()
 
 
@@ -168,7 +169,7 @@ def algorithmic_bytes(env):
     return N * b_env + b_lib, b_env
 
 
-LAUNCHES_PER_STEP = 6   # sim_standin, env_step, fail_rate_ema, env_reset_sampled, env_step(reset rows), done-count clear
+LAUNCHES_PER_STEP = 6   # device-resident loop: sim_standin, env_step, fail_rate_ema, env_reset_sampled, env_step(reset rows), done-count clear
 
 
 # ------------------------------------------------------------------------------------------------
@@ -355,20 +356,34 @@ def run_gpu_arm(args):
     h2d = sum(v.numel() * v.element_size() for v in host_state.values())
     d2h = sum(v.numel() * v.element_size() for v in host_res.values())
     Ke = K
-    for _ in range(3):
-        env.upload_sim_state(host_state); env.sim_standin(noise); env.step(); env.download_results(host_res)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(Ke):
-        env.upload_sim_state(host_state)       # this step's simulator state from pinned host memory
+
+    def time_e2e(one_step):
+        for _ in range(3):
+            one_step()
+            torch.cuda.current_stream(dev).synchronize()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(Ke):
+            one_step()
+            torch.cuda.current_stream(dev).synchronize()   # the caller needs the results before the next physics step
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    def e2e_serial():
+        env.upload_sim_state(host_state)       # this step's simulator state from pinned host memory, all of it first
         env.sim_standin(noise)                 # (its values are then re-centred on the reference: stationary workload)
-        env.step()
+        env.post_physics_step()
         env.download_results(host_res)         # reward + done back to the host
-        torch.cuda.current_stream(dev).synchronize()   # the caller needs the results before the next physics step
-    e1.record()
-    barrier()
-    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+        env.reset_done()
+
+    def e2e_chunked():
+        # the public host-buffer call: parc_b200_env_step_host uploads range c+1 while range c is stepped
+        env.step_host(host_state, host_res, num_chunks=args.chunks, standin_noise=noise)
+
+    e2e_serial_ms = time_e2e(e2e_serial)
+    e2e_ms = time_e2e(e2e_chunked)
     e2e_value = n_gpus * N * Ke / (e2e_ms * 1e-3)
 
     # ---- CPU baseline (rank 0, N=1 only) ------------------------------------------------------------
@@ -397,9 +412,10 @@ def run_gpu_arm(args):
                        "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (step_bytes / 1e9)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms / Ke,
-                    "note": "H2D of root/dof/rigid-body/contact state from pinned memory, fused step + reset, D2H of reward+done; "
-                            "the observation stays on the device for the policy, as in the reference"},
+                    "ms_per_step": e2e_ms / Ke, "chunks": args.chunks, "ms_per_step_unpipelined": e2e_serial_ms / Ke,
+                    "note": "TrackingEnv.step_host -> parc_b200_env_step_host: every step uploads root/dof/rigid-body/contact state from "
+                            "pinned host memory in row ranges (range c+1 in flight while range c is stepped), fail-rate EMA, D2H of "
+                            "reward+done, RSI reset, host sync; the observation stays on the device for the policy, as in the reference"},
             "gpu_launches": LAUNCHES_PER_STEP * K,
             "roofline": {"bound": "hbm", "kernel": "env_step_kernel<256>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,

@@ -133,6 +133,27 @@ int parc_b200_env_step(const parc_char_model_t* h_model, const parc_motion_lib_t
                        const parc_env_buffers_t* h_env, uint32_t parts, const int64_t* env_ids,
                        int64_t n_sub, void* stream);
 
+/* One [N, row_bytes] array of simulator state that lives in (pinned) HOST memory and its device twin. */
+typedef struct parc_host_rows_t {
+    void* dst_device;        /* device array the env views (char_root_pos, ...) point into */
+    const void* src_host;    /* the same rows in host memory; pinned, or the copy is not asynchronous */
+    int64_t row_bytes;       /* bytes per env */
+} parc_host_rows_t;
+
+/* parc_b200_env_step for a simulator whose state tensors live on the HOST (the CPU pipeline of
+ * IGEnv._post_physics_step, ig_env.py:368-377, where _refresh_sim_tensors hands over host arrays):
+ * the N envs are cut into num_chunks row ranges (multiples of 8 envs); the rows of range c are
+ * uploaded on an internal copy stream while the step kernel of range c-1 runs on `stream`, so the
+ * PCIe transfer hides behind the computation instead of preceding it. Results are those of
+ * parc_b200_env_step over all envs (each env depends on its own rows only). The caller zeroes
+ * done_count first, as for parc_b200_env_step. standin_noise (NULL in production) applies the
+ * benchmark stand-in of parc_b200_sim_standin to each range after its upload. */
+int parc_b200_env_step_host(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                            const parc_terrain_t* h_terrain, const parc_env_config_t* h_cfg,
+                            const parc_env_buffers_t* h_env, uint32_t parts,
+                            const parc_host_rows_t* uploads, int32_t num_uploads, int32_t num_chunks,
+                            const float* standin_noise, void* stream);
+
 /* DeepMimicEnv.compute_tar_obs (dm_env.py:594-626) + fetch_tar_obs_data (mgdm_dm_util.py:221-244):
  * -> tar_root_pos [n,S,3], tar_root_rot [n,S,4], tar_joint_rot [n,S,J-1,4], tar_key_pos [n,S,K,3],
  * tar_contacts [n,S,C]; env_ids may be NULL (all envs, n = N). */

@@ -49,6 +49,10 @@ class MotionLibStruct(C.Structure):
     ]
 
 
+class HostRowsStruct(C.Structure):
+    _fields_ = [("dst_device", C.c_void_p), ("src_host", C.c_void_p), ("row_bytes", C.c_int64)]
+
+
 class TerrainStruct(C.Structure):
     _fields_ = [
         ("hf", C.c_void_p),
@@ -195,6 +199,8 @@ def _declare(lib):
         "parc_b200_obs_dim": [P(CharModelStruct), P(EnvConfigStruct)],
         "parc_b200_env_step": [P(CharModelStruct), P(MotionLibStruct), P(TerrainStruct), P(EnvConfigStruct),
                                P(EnvBuffersStruct), u32, vp, i64, vp],
+        "parc_b200_env_step_host": [P(CharModelStruct), P(MotionLibStruct), P(TerrainStruct), P(EnvConfigStruct),
+                                    P(EnvBuffersStruct), u32, P(HostRowsStruct), i32, i32, vp, vp],
         "parc_b200_compute_tar_obs_data": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct),
                                            P(EnvBuffersStruct), vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_compute_char_obs": [P(CharModelStruct)] + [vp] * 7 + [i32, i32, i32, i64, vp, vp],

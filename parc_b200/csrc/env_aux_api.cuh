@@ -202,17 +202,93 @@ extern "C" int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motion
     return check_launch("sample_motions_cdf");
 }
 
-extern "C" int parc_b200_sim_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise, void* stream) {
+namespace parc {
+int launch_sim_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise, long long first_env,
+                       long long n_rows, void* stream) {
+    const long long groups_per_block = 256 / (m->num_bodies <= 16 ? 16 : 32);
+    const unsigned blocks = (unsigned)std::min<long long>((n_rows + groups_per_block - 1) / groups_per_block, kNumSMs * 32);
+    if (m->num_bodies <= 16) sim_standin_kernel<16><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
+    else sim_standin_kernel<32><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
+    return check_launch("sim_standin");
+}
+}  // namespace parc
+
+static int validate_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise) {
     PARC_REQUIRE(m && env && noise, "sim_standin: NULL argument");
-    if (env->num_envs == 0) return PARC_OK;
     PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_root_vel.ptr && env->char_root_ang_vel.ptr &&
                      env->char_dof_pos.ptr && env->char_dof_vel.ptr && env->char_rigid_body_pos.ptr && env->ref_root_pos.ptr &&
                      env->ref_root_rot.ptr && env->ref_root_vel.ptr && env->ref_root_ang_vel.ptr && env->ref_dof_pos.ptr &&
                      env->ref_dof_vel.ptr && env->ref_body_pos.ptr, "sim_standin: state views not set");
     PARC_REQUIRE(m->num_bodies <= 32, "sim_standin: more than 32 bodies");
-    const long long groups_per_block = 256 / (m->num_bodies <= 16 ? 16 : 32);
-    const unsigned blocks = (unsigned)std::min<long long>((env->num_envs + groups_per_block - 1) / groups_per_block, kNumSMs * 32);
-    if (m->num_bodies <= 16) sim_standin_kernel<16><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise);
-    else sim_standin_kernel<32><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise);
-    return check_launch("sim_standin");
+    return PARC_OK;
+}
+
+extern "C" int parc_b200_sim_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise, void* stream) {
+    const int rc = validate_standin(m, env, noise);
+    if (rc) return rc;
+    if (env->num_envs == 0) return PARC_OK;
+    return parc::launch_sim_standin(m, env, noise, 0, env->num_envs, stream);
+}
+
+// ---- parc_b200_env_step_host: the fused step fed from HOST simulator state ------------------------
+namespace parc {
+constexpr int kMaxHostChunks = 64;
+struct HostPipe {            // one per device: the upload stream and the per-chunk "rows have arrived" events
+    cudaStream_t copy = nullptr;
+    cudaEvent_t arrived[kMaxHostChunks] = {};
+    cudaEvent_t free_to_overwrite = nullptr;
+};
+static HostPipe* host_pipe() {
+    static HostPipe pipes[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    HostPipe& p = pipes[dev];
+    if (p.copy == nullptr) {
+        if (cudaStreamCreateWithFlags(&p.copy, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (int c = 0; c < kMaxHostChunks; ++c)
+            if (cudaEventCreateWithFlags(&p.arrived[c], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&p.free_to_overwrite, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+    return &p;
+}
+}  // namespace parc
+
+extern "C" int parc_b200_env_step_host(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
+                                       const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts,
+                                       const parc_host_rows_t* uploads, int32_t num_uploads, int32_t num_chunks,
+                                       const float* standin_noise, void* stream) {
+    PARC_REQUIRE(env != nullptr, "env_step_host: NULL buffers");
+    const long long N = env->num_envs;
+    if (N == 0 || parts == 0) return PARC_OK;
+    int rc = validate_env_step(m, lib, terrain, cfg, env, parts);
+    if (rc) return rc;
+    PARC_REQUIRE(num_uploads >= 0 && (num_uploads == 0 || uploads), "env_step_host: NULL upload list");
+    PARC_REQUIRE(num_chunks >= 1 && num_chunks <= kMaxHostChunks, "env_step_host: num_chunks %d outside [1, %d]", num_chunks, kMaxHostChunks);
+    for (int k = 0; k < num_uploads; ++k)
+        PARC_REQUIRE(uploads[k].dst_device && uploads[k].src_host && uploads[k].row_bytes > 0, "env_step_host: upload %d is incomplete", k);
+    if (standin_noise) { rc = validate_standin(m, env, standin_noise); if (rc) return rc; }
+    HostPipe* pipe = host_pipe();
+    if (pipe == nullptr) { set_error("env_step_host: cannot create the upload stream"); return PARC_ERR_CUDA; }
+    cudaStream_t cs = as_stream(stream);
+    // the previous step's kernels (enqueued on `stream`) must be done reading the state before it is overwritten
+    cudaEventRecord(pipe->free_to_overwrite, cs);
+    cudaStreamWaitEvent(pipe->copy, pipe->free_to_overwrite, 0);
+    // chunk boundaries on multiples of 8 envs (the step kernel's tile)
+    const long long tiles = (N + 7) / 8;
+    for (int c = 0; c < num_chunks; ++c) {
+        const long long a = std::min(N, tiles * c / num_chunks * 8), b = std::min(N, tiles * (c + 1) / num_chunks * 8);
+        if (b <= a) continue;
+        for (int k = 0; k < num_uploads; ++k) {
+            const long long rb = uploads[k].row_bytes;
+            cudaError_t ce = cudaMemcpyAsync(static_cast<char*>(uploads[k].dst_device) + a * rb, static_cast<const char*>(uploads[k].src_host) + a * rb,
+                                             (size_t)((b - a) * rb), cudaMemcpyHostToDevice, pipe->copy);
+            if (ce != cudaSuccess) { set_error("env_step_host: upload %d: %s", k, cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+        }
+        cudaEventRecord(pipe->arrived[c], pipe->copy);
+        cudaStreamWaitEvent(cs, pipe->arrived[c], 0);
+        if (standin_noise) { rc = launch_sim_standin(m, env, standin_noise, a, b - a, stream); if (rc) return rc; }
+        rc = launch_env_step(m, lib, terrain, cfg, env, parts, nullptr, b - a, nullptr, nullptr, stream, a);
+        if (rc) return rc;
+    }
+    return PARC_OK;
 }

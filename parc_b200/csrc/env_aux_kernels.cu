@@ -608,17 +608,18 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
 template <int G>
 __global__ void __launch_bounds__(256) sim_standin_kernel(const __grid_constant__ parc_char_model_t cm,
                                                           const __grid_constant__ parc_env_buffers_t env,
-                                                          const float* __restrict__ noise) {
+                                                          const float* __restrict__ noise, const long long first_env,
+                                                          const long long n_rows) {
     const int J = cm.num_bodies, D = cm.dof_size;
     const int W = 13 + 2 * D + 3 * J, W1 = 13 + 2 * D;
     const LaneBody lb = load_lane_body<G>(cm);
     const long long gpb = blockDim.x / G;
     const long long gid0 = (long long)blockIdx.x * gpb + threadIdx.x / G;
     const long long warp_first = gid0 - ((threadIdx.x & 31) / G);
-    for (long long base = warp_first; base < env.num_envs; base += (long long)gridDim.x * gpb) {
+    for (long long base = warp_first; base < n_rows; base += (long long)gridDim.x * gpb) {
         const long long i = base + ((threadIdx.x & 31) / G);
-        const bool live = i < env.num_envs;
-        const long long e = live ? i : 0;
+        const bool live = i < n_rows;
+        const long long e = first_env + (live ? i : 0);
         const float* n = noise + e * W;
         const Vec3 rp = view_ld_vec3(env.ref_root_pos, e) + make_vec3(n[0], n[1], n[2]);
         const Quat rr = quat_unit(quat_mul(view_ld_quat(env.ref_root_rot, e), make_quat(n[3], n[4], n[5], n[6])));

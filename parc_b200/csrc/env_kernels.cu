@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
     const long long* __restrict__ env_ids, const long long n_rows_host, const int* __restrict__ env_ids32,
-    const int* __restrict__ n_rows_dev) {
+    const int* __restrict__ n_rows_dev, const long long first_env) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const long long n_rows = n_rows_dev ? min((long long)*n_rows_dev, n_rows_host) : n_rows_host;
     const long long row0 = (long long)blockIdx.x * TILE;
@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
         const int el = tid - (THREADS - 32);
         u.live = el < tile_rows;
         const long long row = row0 + (u.live ? el : 0);
-        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
+        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
         u.e = e;
         u.c_pos = view_ld_vec3(env.char_root_pos, e);
         u.c_rot = view_ld_quat(env.char_root_rot, e);
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
             if (el >= tile_rows) continue;
             const long long row = row0 + el;
-            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row);
+            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
             const int jt = cm.joint_type[j], di = cm.dof_idx[j];
             Quat q = quat_identity();
             if (jt == PARC_JOINT_SPHERICAL)
@@ -966,14 +966,12 @@ extern "C" int parc_b200_obs_dim(const parc_char_model_t* m, const parc_env_conf
     return make_layout(m->num_bodies, m->dof_size, m->num_bodies, *cfg).obs_dim;
 }
 
-extern "C" int parc_b200_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
-                                  const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts,
-                                  const int64_t* env_ids, int64_t n_sub, void* stream) {
+namespace parc {
+// Argument checks shared by parc_b200_env_step and parc_b200_env_step_host.
+int validate_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
+                      const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts) {
     int rc = validate_env(m, lib, cfg, env, "env_step");
     if (rc) return rc;
-    const long long n_rows = env_ids ? n_sub : env->num_envs;
-    PARC_REQUIRE(n_rows >= 0, "env_step: negative row count");
-    if (n_rows == 0 || parts == 0) return PARC_OK;
     PARC_REQUIRE(terrain && terrain->hf && terrain->dim_x > 0 && terrain->dim_y > 0, "env_step: empty terrain");
     PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_root_vel.ptr && env->char_root_ang_vel.ptr &&
                      env->char_dof_pos.ptr && env->char_dof_vel.ptr,
@@ -1002,6 +1000,20 @@ extern "C" int parc_b200_env_step(const parc_char_model_t* m, const parc_motion_
     PARC_REQUIRE((long long)terrain->dim_x * terrain->dim_y < (1ll << 31), "env_step: terrain has more than 2^31 cells");
     const StepPlan sp_check = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
     PARC_REQUIRE(sp_check.S.total <= 227 * 1024, "env_step: staging of %zu bytes exceeds shared memory", sp_check.S.total);
+    return PARC_OK;
+}
+}  // namespace parc
+
+extern "C" int parc_b200_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
+                                  const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts,
+                                  const int64_t* env_ids, int64_t n_sub, void* stream) {
+    int rc = validate_env(m, lib, cfg, env, "env_step");
+    if (rc) return rc;
+    const long long n_rows = env_ids ? n_sub : env->num_envs;
+    PARC_REQUIRE(n_rows >= 0, "env_step: negative row count");
+    if (n_rows == 0 || parts == 0) return PARC_OK;
+    rc = parc::validate_env_step(m, lib, terrain, cfg, env, parts);
+    if (rc) return rc;
     return parc::launch_env_step(m, lib, terrain, cfg, env, parts, env_ids, n_rows, nullptr, nullptr, stream);
 }
 
@@ -1010,7 +1022,7 @@ namespace parc {
 // (done_list/done_count of the previous kernels, grid sized for max_rows), or are simply 0..N-1.
 int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
                     const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts, const int64_t* env_ids,
-                    long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream) {
+                    long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream, long long first_env) {
     const StepPlan sp = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
     const SmemPlan& plan = sp.S;
     static size_t smem_attr = 0;   // opt-in dynamic shared memory, raised only when a larger plan shows up
@@ -1021,7 +1033,7 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
     }
     const long long blocks = (max_rows + TILE - 1) / TILE;
     env_step_kernel<STEP_THREADS><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
-        *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev);
+        *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
     return check_launch("env_step");
 }
 }  // namespace parc

@@ -13,7 +13,10 @@ int check_launch(const char* what);
 
 int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
                     const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts, const int64_t* env_ids,
-                    long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream);
+                    long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream, long long first_env = 0);
+
+int validate_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
+                      const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts);
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

@@ -412,6 +412,37 @@ class TrackingEnv:
         for k, v in self.sim_state_tensors().items():
             v.copy_(host_state[k], non_blocking=True)
 
+    def post_physics_step_host(self, host_state, num_chunks=8, standin_noise=None, parts=_lib.STEP_ALL, update_fail_rates=True):
+        """post_physics_step for simulator state that lives in pinned HOST memory (make_host_state):
+        parc_b200_env_step_host uploads the envs in `num_chunks` row ranges on a copy stream and runs
+        the fused step on each range as soon as its rows have arrived, so the PCIe transfer overlaps
+        the computation. Results equal upload_sim_state + post_physics_step."""
+        sim = self.sim_state_tensors()
+        rows = (_lib.HostRowsStruct * len(sim))()
+        for i, (k, v) in enumerate(sim.items()):
+            h = host_state[k]
+            assert h.shape == v.shape and h.dtype == v.dtype and h.is_contiguous() and v.is_contiguous() and not h.is_cuda
+            assert h.is_pinned(), "host state must be pinned (make_host_state) for the upload to overlap"
+            rows[i].dst_device, rows[i].src_host = v.data_ptr(), h.data_ptr()
+            rows[i].row_bytes = v[0].numel() * v.element_size()
+        L = _lib.lib()
+        if parts & _lib.STEP_DONE:
+            self._done_count.zero_()
+        _lib.check(L.parc_b200_env_step_host(self._kin_char_model._cstruct(), self._mlib.cstruct(), self._terrain_cs, self._cfg,
+                                             self._bufs, parts, rows, len(sim), int(num_chunks), _lib.ptr(standin_noise), self._stream()))
+        if (parts & _lib.STEP_DONE) and update_fail_rates:
+            _lib.check(L.parc_b200_fail_rate_ema(self._cfg, self._bufs, self._mlib.num_motions(), _lib.ptr(self._cdf),
+                                                 _lib.ptr(self._ema_scratch), self._stream()))
+        self._step_count += 1
+
+    def step_host(self, host_state, host_results, num_chunks=8, standin_noise=None):
+        """One full control step from host buffers to host buffers: chunked upload + fused step, fail-rate
+        EMA, device-side RSI reset, reward/done back to the host (asynchronous: synchronise the current
+        stream before reading host_results)."""
+        self.post_physics_step_host(host_state, num_chunks=num_chunks, standin_noise=standin_noise)
+        self.download_results(host_results)     # the rollout reads reward/done of THIS step; the reset follows
+        self.reset_done()
+
     def make_host_results(self):
         return {"reward": torch.empty(self._num_envs, dtype=torch.float32, pin_memory=True),
                 "done": torch.empty(self._num_envs, dtype=torch.int32, pin_memory=True)}

@@ -430,3 +430,46 @@ def test_simulator_standin_matches_torch_formulas():
         H.assert_close_world(getattr(penv, "_char_" + k).cpu(), getattr(oenv, "char_" + k), W, what="standin " + k)
     for k in ("root_rot", "root_vel", "root_ang_vel", "dof_pos", "dof_vel"):
         assert_close(getattr(penv, "_char_" + k).cpu(), getattr(oenv, "char_" + k), what="standin " + k)
+
+
+@pytest.mark.parametrize("num_chunks,use_standin", [(1, False), (5, False), (8, True), (64, False)])
+def test_host_fed_step_equals_upload_then_step(num_chunks, use_standin):
+    """parc_b200_env_step_host (chunked upload overlapped with the step) == upload_sim_state + post_physics_step,
+    bit for bit, including the done list, for an env count that is not a multiple of the chunk / tile size."""
+    sc = H.Scenario(num_envs=1003, num_motions=6, ray="grid", seed=11, wrap_fraction=0.2, max_frames=90)
+    oenv = sc.oracle_env()
+    H.randomize_oracle_state(oenv, seed=12)
+    a, b = sc.product_env(DEV), sc.product_env(DEV)
+    H.copy_oracle_state_to_product(oenv, a)
+    H.copy_oracle_state_to_product(oenv, b)
+    noise = synth.standin_noise(sc.N, 15, 28, seed=9).to(DEV) if use_standin else None
+    host = a.make_host_state()
+    for k, v in a.sim_state_tensors().items():
+        host[k].copy_(v)
+    torch.cuda.synchronize()
+    # the device copies of `b` start out as garbage: everything must come from the host buffers
+    for v in b.sim_state_tensors().values():
+        v.fill_(float("nan"))
+    if use_standin:
+        a.post_physics_step(parts=2, update_fail_rates=False)     # the stand-in reads ref_*: same ref state on both
+        b.post_physics_step_host(host, num_chunks=1, parts=2, update_fail_rates=False)
+        a.sim_standin(noise)
+    a.post_physics_step()
+    b.post_physics_step_host(host, num_chunks=num_chunks, standin_noise=noise)
+    torch.cuda.synchronize()
+    for name in ("_obs_buf", "_reward_buf", "_done_buf", "_time_buf", "_timestep_buf", "_ref_body_pos", "_ref_dof_pos", "_done_code",
+                 "_motion_id_fail_rates", "_char_rigid_body_pos"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    na, nb = int(a._done_count.item()), int(b._done_count.item())
+    assert na == nb and na > 0
+    assert torch.equal(torch.sort(a._done_list[:na]).values, torch.sort(b._done_list[:nb]).values)
+    # and through the host-to-host call: reward / done of the step are read BEFORE the reset clears them
+    res = b.make_host_results()
+    c = sc.product_env(DEV)
+    H.copy_oracle_state_to_product(oenv, c)
+    if use_standin:
+        c.post_physics_step(parts=2, update_fail_rates=False)
+    c.step_host(host, res, num_chunks=num_chunks, standin_noise=noise)
+    torch.cuda.synchronize()
+    assert torch.equal(res["reward"], a._reward_buf.cpu()) and torch.equal(res["done"], a._done_buf.cpu())
+    assert int((res["done"] != 0).sum()) > 0 and int(c._done_buf.abs().sum()) == 0
