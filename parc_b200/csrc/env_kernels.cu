@@ -20,6 +20,19 @@
 #include "parc_common.cuh"
 #include "parc_lanes.cuh"
 
+// The kernel is instruction-fetch bound (ncu: stall_no_inst is the largest stall class; the SASS is ~110 KB against a
+// 32 KB L1.5 instruction cache), so loops that run a handful of iterations per block are kept rolled: nvcc's default
+// 4x unrolling of them cost 5 % of the launch time.
+#define PARC_COLD_LOOP _Pragma("unroll 1")
+#define PARC_COLD_LOOP2 _Pragma("unroll 1")
+#define PARC_COLD_LOOP3 _Pragma("unroll 1")
+#ifndef PARC_EXP_MINB
+#define PARC_EXP_MINB 4
+#endif
+#ifndef PARC_EXP_HU
+#define PARC_EXP_HU 2
+#endif
+
 namespace parc {
 
 constexpr int TILE = 8;                 // envs per block (== warps per block)
@@ -312,7 +325,7 @@ template <bool FULL>
 __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const float* __restrict__ hf, int dimy,
                                                int imx, int imy, float2 cs, float2 nsc, float2 g2, float gz, float2 nmn, float2 rd2,
                                                float2 nd2, float lo, float hi, float* __restrict__ hrow, float* __restrict__ orow) {
-    constexpr int U = 4;
+    constexpr int U = PARC_EXP_HU;
     const bool HAS_H = hrow != nullptr, HAS_O = orow != nullptr;   // warp-uniform: predicated stores, one code copy
     const float2* sp = s_pts + lane;
     float* ph = hrow + lane;
@@ -352,7 +365,7 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
 }
 
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
+__global__ void __launch_bounds__(THREADS, PARC_EXP_MINB) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
@@ -390,12 +403,15 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     const int tile_rows = (int)min((long long)TILE, n_rows - row0);
 
     // ================================ phase A ====================================================
+    PARC_COLD_LOOP
     for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_part[k] = sp.part_entry[k / PARC_MAX_BODIES][k % PARC_MAX_BODIES];
+    PARC_COLD_LOOP
     for (int k = tid; k < 8 * J; k += THREADS) {
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
     if (do_heights)
+        PARC_COLD_LOOP
         for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
     // A.3 per-env uniforms: the first lanes of the LAST warp, so that the dependent loads (env id -> motion id -> clip
     //     meta) overlap the dof -> quaternion work of the leading warps
@@ -435,6 +451,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     }
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
+        PARC_COLD_LOOP
         for (int it = tid; it < TILE * (J - 1); it += THREADS) {
             const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
             if (el >= tile_rows) continue;
@@ -456,6 +473,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     //      work below runs while they arrive
     if (do_reward || do_done) {
         // simulator state read in phase C (rigid body positions, contact forces, dof velocities): 3 rows per env
+        PARC_COLD_LOOP
         for (int it = tid; it < TILE * 3 * 4; it += THREADS) {
             const int el = it / 12, w = (it >> 2) % 3, ln = it & 3;
             if (el >= tile_rows) continue;
@@ -466,6 +484,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
         }
     }
     if (do_obs || need_ref_pose) {
+        PARC_COLD_LOOP
         for (int it = tid; it < TILE * (S + 1); it += THREADS) {
             const int el = it / (S + 1), pose = it - el * (S + 1);
             if (el >= tile_rows) continue;
@@ -474,9 +493,11 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             const FrameBlend fb = calc_frame_blend(u.mm, t);
             const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * lib.irec);
             const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * lib.irec * sizeof(float));
+            PARC_COLD_LOOP
             for (int off = 0; off < bytes; off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(r0 + off));
             if (pose == 0) {
                 const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * lib.vrec);
+                PARC_COLD_LOOP
                 for (int off = 0; off < (int)(lib.vrec * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
             }
         }
@@ -499,7 +520,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
             if (do_heights) {
                 const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-                if ((P & 127) == 0)
+                if (P % (32 * PARC_EXP_HU) == 0)
                     heights_of_env<true>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
                 else
                     heights_of_env<false>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
@@ -548,6 +569,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
                 rsec[R.body_pos] = rpos.x; rsec[R.body_pos + 1] = rpos.y; rsec[R.body_pos + 2] = rpos.z;
             }
             // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
+            PARC_COLD_LOOP2
             for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
                 const float4 x = ldg4(vrec + k);
                 const float xs[4] = {x.x, x.y, x.z, x.w};
@@ -581,9 +603,11 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
                 o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
             }
             o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
+            PARC_COLD_LOOP2
             for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
             if (cfg.use_contact_info) {
                 // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+                PARC_COLD_LOOP2
                 for (int c = part; c < J; c += NPART) {
                     const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
                                 fz = view_ld3(env.char_contact_forces, u.e, c, 2);
@@ -595,6 +619,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
         if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
             float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
             const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
+            PARC_COLD_LOOP2
             for (int c = 4 * part; c < C; c += 4 * NPART) {
                 const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
                 oc[c] = lerp_exact(omb, a.x, b, d.x);
@@ -607,6 +632,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
         const bool lrot_ident = sp.lrot_ident != 0;
         float* xf = s_xf + tid;                         // [slot][7][THREADS], this thread's column
         const int* my_part = s_part + part * PARC_MAX_BODIES;
+        PARC_COLD_LOOP3
         for (int i = 0; i < sp.max_part_len; ++i) {
             const int entry = my_part[i];
             if (entry < 0) continue;
@@ -637,7 +663,9 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
                 bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
             } else {
                 tan_norm_exact(q, o_pose + 6 * (j - 1));
-                if ((sp.key_mask >> j) & 1u) for (int k = 0; k < K; ++k) {
+                if ((sp.key_mask >> j) & 1u)
+                PARC_COLD_LOOP2
+                for (int k = 0; k < K; ++k) {
                     if (cfg.key_body_ids[k] != j) continue;
                     Vec3 kp = bpos - rpos;
                     if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
@@ -665,6 +693,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
     // C.0 scatter map of the ref_* section for phase E: column k -> (base pointer, row stride in bytes). Lives in the
     //     bytes the FK columns used during phase B; phase E starts behind the barrier that ends phase C.
     if (do_ref) {
+        PARC_COLD_LOOP
         for (int k = tid; k < R.width; k += THREADS) {
             const parc_view3_t* v; int off;
             if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
@@ -694,6 +723,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
         const int nt_d = do_reward ? (TILE * D + 31) >> 5 : 0;
         const int b_c = nt_j, b_k = b_c + nt_c, b_d = b_k + nt_k, n_task = b_d + nt_d;
         const int lane = tid & 31;
+        PARC_COLD_LOOP3
         for (int task = tid >> 5; task < n_task; task += THREADS / 32) {
             if (task < b_c) {
                 // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
@@ -807,7 +837,9 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             // _update_reward (ig_parkour_env.py:984-1044) + compute_deepmimic_reward (mgdm_dm_util.py:269-332)
             const float* tm = s_terms + el * TP;
             float pose_t = 0.f, vel_t = 0.f, key_t = 0.f, con_t = 0.f;
+#pragma unroll 4
             for (int k = 0; k < J - 1; ++k) pose_t += tm[o_pose_t + k];
+#pragma unroll 4
             for (int k = 0; k < D; ++k) vel_t += tm[o_vel_t + k];
             for (int k = 0; k < K; ++k) key_t += tm[o_key_t + k];
             Vec3 rpd = ref_rpos - u.c_pos;
@@ -837,6 +869,7 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             float total = cfg.pose_w * pose_r + cfg.vel_w * vel_r + cfg.root_pos_w * root_pose_r + cfg.root_vel_w * root_vel_r + cfg.key_pos_w * key_r;
             float pen = 0.f;
             if (cfg.use_contact_info) {
+#pragma unroll 4
                 for (int k = 0; k < J; ++k) con_t += tm[o_con_t + k];
                 pen = con_t / (float)C;
                 total += pen;
@@ -894,10 +927,12 @@ __global__ void __launch_bounds__(THREADS, 4) env_step_kernel(
             const float* row = s_row + el * ROWP;
             if (do_obs) {
                 float* g = env.obs_buf + u.e * env.obs_row_stride;
+#pragma unroll 4
                 for (int k = lane; k < L.o_hf; k += 32) g[k] = row[k];
             }
             if (do_ref) {
                 const float* rsec = row + L.o_hf;
+#pragma unroll 2
                 for (int k = lane; k < R.width; k += 32) {
                     const unsigned long long base = s_refmap[2 * k];
                     if (base) *reinterpret_cast<float*>(base + (unsigned long long)u.e * s_refmap[2 * k + 1]) = rsec[k];
