@@ -417,7 +417,7 @@ def run_gpu_arm(args):
                             "pinned host memory in row ranges (range c+1 in flight while range c is stepped), fail-rate EMA, D2H of "
                             "reward+done, RSI reset, host sync; the observation stays on the device for the policy, as in the reference"},
             "gpu_launches": LAUNCHES_PER_STEP * K,
-            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<256>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<512>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": step_bytes, "bytes_per_env": b_env,
                          "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / (ms_total / K)},

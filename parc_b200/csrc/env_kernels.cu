@@ -3,7 +3,7 @@
 // i.e. IGEnv._post_physics_step (PARC/motion_tracker/envs/ig_env.py:368-377) minus PhysX, in ONE
 // launch that reads every input once and writes every output once.
 //
-// Work decomposition (a block owns TILE = 8 consecutive envs, 256 threads):
+// Work decomposition (a block owns TILE = 16 consecutive envs, 512 threads = two groups of 8 envs x 8 warps):
 //   A  per-env uniforms (heading, time, clip meta) by 8 lanes; character dof -> quaternion by
 //      one thread per (env, joint)
 //   B  warps 0..1: one thread per (env, pose) -- pose 0 = reference, 1..S = target steps,
@@ -35,8 +35,11 @@
 
 namespace parc {
 
-constexpr int TILE = 8;                 // envs per block (== warps per block)
-constexpr int STEP_THREADS = 256;
+#ifndef PARC_EXP_TILE
+#define PARC_EXP_TILE 16
+#endif
+constexpr int TILE = PARC_EXP_TILE;      // envs per block (== warps per block)
+constexpr int STEP_THREADS = 32 * TILE;
 
 // Column layout of one observation row (IGParkourEnv._compute_obs, ig_parkour_env.py:842-965;
 // compute_char_obs ig_char_env.py:581-625; compute_tar_obs mgdm_dm_util.py:404-461).
@@ -365,7 +368,7 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
 }
 
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, PARC_EXP_MINB) env_step_kernel(
+__global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
@@ -504,7 +507,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB) env_step_kernel(
     }
 
     // ================================ phase B ====================================================
-    static_assert(TILE * NPART == 32, "one warp = one pose of the tile's envs x NPART tree parts");
+    static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART tree parts");
     const bool pose_work = do_obs || need_ref_pose;
     if (P > 0 && (do_heights || do_obs)) {
         // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
@@ -531,8 +534,8 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB) env_step_kernel(
     }
     // ---- B.2 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
     //      walks its own ancestor-closed part of the joint tree, so all lanes of a warp run the same code ----
-    for (int pose = tid >> 5; pose_work && pose < plan.n_pose; pose += THREADS / 32) {
-        const int lane = tid & 31, el = lane / NPART, part = lane - el * NPART;
+    for (int pose = (tid >> 5) & 7; pose_work && pose < plan.n_pose; pose += 8) {
+        const int lane = tid & 31, el = (tid >> 8) * 8 + lane / NPART, part = lane & (NPART - 1);
         const bool is_ref = pose == 0, is_char = pose == S + 1, is_tar = pose >= 1 && pose <= S;
         const bool wanted = (is_ref && need_ref_pose) || (is_tar && do_obs) || (is_char && do_obs);
         if (!wanted || !s_env[el].live) continue;
