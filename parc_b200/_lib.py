@@ -49,6 +49,12 @@ class MotionLibStruct(C.Structure):
     ]
 
 
+class SamplerConfigStruct(C.Structure):     # parc_sampler_config_t, include/parc_b200_sampler.h
+    _fields_ = [("seq_len", C.c_int32), ("ref_frame_idx", C.c_int32), ("relative_z_style", C.c_int32), ("grid_dim_x", C.c_int32),
+                ("grid_dim_y", C.c_int32), ("center_ix", C.c_int32), ("center_iy", C.c_int32), ("min_h", C.c_float),
+                ("max_h", C.c_float), ("future_pos_noise_scale", C.c_float)]
+
+
 class HostRowsStruct(C.Structure):
     _fields_ = [("dst_device", C.c_void_p), ("src_host", C.c_void_p), ("row_bytes", C.c_int64)]
 
@@ -221,6 +227,7 @@ def _declare(lib):
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_mdm_sample_motion_data": [P(CharModelStruct), P(MotionLibStruct), vp, P(SamplerConfigStruct), vp, vp, i64] + [vp] * 14,
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
     }
     for name, argtypes in sigs.items():
