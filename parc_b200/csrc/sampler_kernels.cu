@@ -1,6 +1,6 @@
 // MDM dataset sampler: MDMHeightfieldContactMotionSampler.sample_motion_data
 // (PARC/motion_generator/mdm_heightfield_contact_motion_sampler.py:197-302) in two launches.
-//   mdm_canon_hf_kernel   block per sample: the reference frame's root pose (canonical frame), its heading,
+//   mdm_canon_hf_kernel   warp per sample: the reference frame's root pose (canonical frame), its heading,
 //                         the local heightmap looked up in the motion's own terrain, the target info
 //   mdm_frames_kernel<G>  G lanes per (sample, frame): frame evaluation, canonicalisation, forward kinematics
 // Both reuse the lane building blocks of the tracking path (parc_lanes.cuh). HBM-bound: per sample the output is
@@ -27,17 +27,20 @@ __device__ __forceinline__ void root_pose_at(const parc_motion_lib_t& lib, int J
                     __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
 }
 
-__global__ void __launch_bounds__(128) mdm_canon_hf_kernel(
+// One WARP per sample: lane 0 evaluates the canonical frame (and the target info) and broadcasts the five numbers the
+// height lookups need; the 32 lanes then stride over the gx*gy grid points (coalesced stores into hfs[i]).
+__global__ void __launch_bounds__(256) mdm_canon_hf_kernel(
     const __grid_constant__ parc_motion_lib_t lib, const __grid_constant__ parc_sampler_config_t cfg, const int J,
     const parc_terrain_t* __restrict__ terrains, const long long* __restrict__ motion_ids, const float* __restrict__ start_times,
     const long long n, const float* __restrict__ motion_times, const float* __restrict__ grid_xy,
     const float* __restrict__ future_times, const float* __restrict__ future_noise, float* __restrict__ hfs,
     float* __restrict__ future_pos, float* __restrict__ future_rot, float* __restrict__ canon) {
-    __shared__ float s_c[16];
-    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+    const int lane = threadIdx.x & 31;
+    const long long wpb = blockDim.x / 32;
+    for (long long i = (long long)blockIdx.x * wpb + threadIdx.x / 32; i < n; i += (long long)gridDim.x * wpb) {
         const long long mid = __ldg(motion_ids + i);
-        __syncthreads();                      // s_c of the previous sample has been consumed
-        if (threadIdx.x == 0) {
+        float rx = 0.f, ry = 0.f, rz = 0.f, sh = 0.f, ch = 1.f;
+        if (lane == 0) {
             // canon_root_pos / canon_root_rot = frame ref_frame_idx of the sample (:222-224); times are start + _motion_times (:168)
             Vec3 cp; Quat cq;
             root_pose_at(lib, J, mid, __fadd_rn(__ldg(start_times + i), __ldg(motion_times + cfg.ref_frame_idx)), cp, cq);
@@ -46,7 +49,7 @@ __global__ void __launch_bounds__(128) mdm_canon_hf_kernel(
             float* c = canon + i * CANON_W;
             c[0] = cp.x; c[1] = cp.y; c[2] = cp.z; c[3] = cq.x; c[4] = cq.y; c[5] = cq.z; c[6] = cq.w;
             c[7] = hinv.x; c[8] = hinv.y; c[9] = hinv.z; c[10] = hinv.w;
-            s_c[0] = cp.x; s_c[1] = cp.y; s_c[2] = cp.z; s_c[3] = sinf(heading); s_c[4] = cosf(heading);
+            rx = cp.x; ry = cp.y; rz = cp.z; sh = sinf(heading); ch = cosf(heading);
             if (future_times) {
                 // _sample_target_info (:146-160): root pose at the future time, noise, canonical frame
                 Vec3 fp; Quat fq;
@@ -61,12 +64,12 @@ __global__ void __launch_bounds__(128) mdm_canon_hf_kernel(
                 reinterpret_cast<float4*>(future_rot)[i] = quat_to_f4(fq);
             }
         }
-        __syncthreads();
-        if (hfs == nullptr) { if (threadIdx.x == 0) canon[i * CANON_W + 11] = 0.f; continue; }
+        if (hfs == nullptr) { if (lane == 0) canon[i * CANON_W + 11] = 0.f; continue; }
+        rx = __shfl_sync(FULL_MASK, rx, 0); ry = __shfl_sync(FULL_MASK, ry, 0); rz = __shfl_sync(FULL_MASK, rz, 0);
+        sh = __shfl_sync(FULL_MASK, sh, 0); ch = __shfl_sync(FULL_MASK, ch, 0);
         // get_hfs_from_data (:366-401): the generic grid rotated by the heading, moved to the root, looked up in the
         // MOTION'S OWN terrain (get_hfs_from_data_helper :336-339, SubTerrain.get_grid_index terrain_util.py:143-152)
         const parc_terrain_t tr = terrains[mid];
-        const float rx = s_c[0], ry = s_c[1], rz = s_c[2], sh = s_c[3], ch = s_c[4];
         auto height_at = [&](int p) {
             const float2 pt = __ldg(reinterpret_cast<const float2*>(grid_xy) + p);
             const float wx = __fadd_rn(__fsub_rn(__fmul_rn(pt.x, ch), __fmul_rn(pt.y, sh)), rx);   // rotate_2d_vec, torch_util.py:650-662
@@ -76,10 +79,11 @@ __global__ void __launch_bounds__(128) mdm_canon_hf_kernel(
         };
         const float center_h = height_at(cfg.center_ix * cfg.grid_dim_y + cfg.center_iy);          // :378
         const float base = cfg.relative_z_style == PARC_RELATIVE_TO_ROOT_FLOOR ? center_h : rz;     // :379-388
-        if (threadIdx.x == 0) canon[i * CANON_W + 11] = center_h;
+        if (lane == 0) canon[i * CANON_W + 11] = center_h;
         const int P = cfg.grid_dim_x * cfg.grid_dim_y;
-        for (int p = threadIdx.x; p < P; p += blockDim.x)
-            hfs[i * P + p] = fminf(fmaxf(__fsub_rn(height_at(p), base), cfg.min_h), cfg.max_h);    // clamp :228
+        float* o = hfs + i * P;
+#pragma unroll 4
+        for (int p = lane; p < P; p += 32) o[p] = fminf(fmaxf(__fsub_rn(height_at(p), base), cfg.min_h), cfg.max_h);   // clamp :228
     }
 }
 
@@ -155,7 +159,7 @@ extern "C" int parc_b200_mdm_sample_motion_data(const parc_char_model_t* m, cons
     }
     if (future_times) PARC_REQUIRE(future_pos && future_rot, "mdm_sample_motion_data: target info needs future_pos / future_rot");
     PARC_REQUIRE(m->num_bodies <= 32, "mdm_sample_motion_data: more than 32 bodies");
-    mdm_canon_hf_kernel<<<(unsigned)std::min<long long>(n, kNumSMs * 16), 128, 0, as_stream(stream)>>>(
+    mdm_canon_hf_kernel<<<(unsigned)std::min<long long>((n + 7) / 8, kNumSMs * 32), 256, 0, as_stream(stream)>>>(
         *lib, *cfg, m->num_bodies, terrains, (const long long*)motion_ids, start_times, n, motion_times, grid_xy, future_times,
         future_noise, hfs, future_pos, future_rot, canon);
     int rc = check_launch("mdm_canon_hf");
