@@ -77,6 +77,23 @@ int parc_b200_motion_loss(const parc_char_model_t* h_model, const parc_opt_confi
                           float* terms, float* loss, float* g_root_pos, float* g_root_rot, float* g_joint_dof,
                           void* stream);
 
+/* mdm_path.compute_motion_loss (PARC/motion_synthesis/procgen/mdm_path.py:31-127): the
+ * forward-only penetration / contact score that ranks a batch of generated motions, against ONE terrain taken whole
+ * (no per-frame window). Inputs are the forward-kinematics outputs of the batch (KinCharModel.forward_kinematics, :76):
+ *   body_pos [B,T,J,3], body_rot [B,T,J,4], contacts [B,T,C] (column h_cfg->contact_col[b] labels body b; upstream
+ *   uses column b for every body, :109), hf [X,Y], min_point [2], body_points [Np,3] in body order.
+ * h_cfg supplies point_start / contact_col / num_points / num_contact_cols and base_z (upstream: min(hf) - 10, :78);
+ * its weights are ignored in favour of w_pen / w_contact. Outputs (any may be NULL): pen_loss [B] = w_pen * sum over
+ * frames and points of max(air-column sdf, 0); contact_loss [B] = w_contact * sum over frames and bodies of the
+ * body's closest solid-column distance (>= 0) times its contact label; total_loss = their sum. */
+int64_t parc_b200_path_motion_loss_workspace_bytes(int64_t B, int64_t T);
+int parc_b200_path_motion_loss(const parc_char_model_t* h_model, const parc_opt_config_t* h_cfg, int64_t B, int64_t T,
+                               const float* body_pos, const float* body_rot, const float* contacts,
+                               const float* hf, int32_t X, int32_t Y, const float* min_point, float dx, float dy,
+                               const float* body_points, float w_pen, float w_contact,
+                               void* workspace, int64_t workspace_bytes,
+                               float* pen_loss, float* contact_loss, float* total_loss, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -131,3 +131,31 @@ def icosahedron(radius):
     v = torch.tensor([(-1, p, 0), (1, p, 0), (-1, -p, 0), (1, -p, 0), (0, -1, p), (0, 1, p), (0, -1, -p), (0, 1, -p),
                       (p, 0, -1), (p, 0, 1), (-p, 0, -1), (-p, 0, 1)], dtype=torch.float64)
     return (v / v.norm(dim=-1, keepdim=True) * radius).float()
+
+
+def compute_motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, root_pos, root_rot, joint_rot, contacts, w_contact,
+                        w_pen):
+    """mdm_path.compute_motion_loss (PARC/motion_synthesis/procgen/mdm_path.py:31-127):
+    forward-only penetration + contact terms of a batch of generated motions [B,T,...] against ONE whole terrain.
+    Per body (:83-113): penetration = w_pen * sum over frames and points of max(air-column sdf, 0); contact = w_contact *
+    sum over frames of (closest solid-column distance of the body's points, clamped at 0) * contact label.
+    Returns (total [B], contact [B], pen [B]). Pinned by tests/golden/ref_path_loss.npz."""
+    B, T = root_pos.shape[0], root_pos.shape[1]
+    body_pos, body_rot = model.forward_kinematics(root_pos, root_rot, joint_rot)
+    base_z = float(hf.min()) - 10.0                                                         # :78, :97
+    hfb = hf.unsqueeze(0).expand(B, -1, -1)
+    mpb = min_point.unsqueeze(0).expand(B, -1)
+    pen = torch.zeros(B)
+    con = torch.zeros(B)
+    start = 0
+    for b, cnt in enumerate(body_point_counts):
+        cnt = int(cnt)
+        pts = body_points[start:start + cnt]
+        start += cnt
+        world = O.quat_rotate(body_rot[..., b, :].unsqueeze(-2).expand(-1, -1, cnt, -1), pts.expand(B, T, cnt, 3)) + body_pos[..., b, :].unsqueeze(-2)
+        flat = world.reshape(B, T * cnt, 3)
+        neg = torch.clamp(points_hf_sdf(flat, hfb, mpb, dxdy, base_z, True), max=0.0)        # :92-99
+        pen = pen + torch.sum(-neg, dim=-1) * w_pen
+        pos = torch.clamp(points_hf_sdf(flat, hfb, mpb, dxdy, base_z, False), min=0.0).view(B, T, cnt)   # :101-108
+        con = con + torch.sum(pos.min(dim=-1)[0] * contacts[..., b], dim=-1) * w_contact     # :109-113
+    return con + pen, con, pen

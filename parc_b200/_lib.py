@@ -227,6 +227,8 @@ def _declare(lib):
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_path_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64, vp, vp, vp, vp, i32, i32, vp, f32, f32, vp,
+                                       f32, f32, vp, i64, vp, vp, vp, vp],
         "parc_b200_mdm_sample_motion_data": [P(CharModelStruct), P(MotionLibStruct), vp, P(SamplerConfigStruct), vp, vp, i64] + [vp] * 14,
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
     }
@@ -234,6 +236,9 @@ def _declare(lib):
         fn = getattr(lib, name)   # AttributeError here = header/library mismatch: fail loudly
         fn.restype = C.c_int
         fn.argtypes = argtypes
+    lib.parc_b200_path_motion_loss_workspace_bytes.restype = i64
+    lib.parc_b200_path_motion_loss_workspace_bytes.argtypes = [i64, i64]
+    sigs["parc_b200_path_motion_loss_workspace_bytes"] = lib.parc_b200_path_motion_loss_workspace_bytes.argtypes
     lib.parc_b200_motion_loss_workspace_bytes.restype = i64
     lib.parc_b200_motion_loss_workspace_bytes.argtypes = [P(CharModelStruct), i64, i64]
     sigs["parc_b200_motion_loss_workspace_bytes"] = lib.parc_b200_motion_loss_workspace_bytes.argtypes

@@ -271,3 +271,81 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
     opt_reduce_kernel<<<(unsigned)B, 256, 0, st>>>(*cfg, T, ws, terms, loss);
     return check_launch("motion_loss (reduce)");
 }
+
+// ---- mdm_path.compute_motion_loss: forward-only penetration / contact against a whole terrain ----
+namespace parc {
+// every frame's window is the whole grid: first cell (0,0), size (X,Y); the per-frame terms start at zero
+__global__ void path_loss_window_kernel(long long n, long long B, int X, int Y, OptWs ws) {
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n * OPT_FT; k += (long long)gridDim.x * blockDim.x) {
+        ws.frame_terms[k] = 0.f;
+        if (k < n * 2) ws.gmin[k] = 0;
+        if (k < B * 2) ws.patch[k] = (k & 1) ? Y : X;
+    }
+}
+// one block per motion: frames in order, fp64 accumulation (the reference sums per body over frames x points in fp32;
+// the order does not carry below the 1e-5 tolerance)
+__global__ void __launch_bounds__(128) path_loss_reduce_kernel(long long T, float w_pen, float w_contact, OptWs ws, float* __restrict__ pen,
+                                                               float* __restrict__ con, float* __restrict__ total) {
+    __shared__ double s_p[128], s_c[128];
+    const long long b = blockIdx.x;
+    double p = 0.0, c = 0.0;
+    for (long long t = threadIdx.x; t < T; t += blockDim.x) {
+        p += ws.frame_terms[(b * T + t) * OPT_FT + PARC_LOSS_PENETRATION];
+        c += ws.frame_terms[(b * T + t) * OPT_FT + PARC_LOSS_CONTACT];
+    }
+    s_p[threadIdx.x] = p; s_c[threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { s_p[threadIdx.x] += s_p[threadIdx.x + o]; s_c[threadIdx.x] += s_c[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const float pl = (float)s_p[0] * w_pen, cl = (float)s_c[0] * w_contact;
+        if (pen) pen[b] = pl;
+        if (con) con[b] = cl;
+        if (total) total[b] = cl + pl;                                                     // mdm_path.py:115
+    }
+}
+}  // namespace parc
+
+extern "C" int64_t parc_b200_path_motion_loss_workspace_bytes(int64_t B, int64_t T) {
+    if (B < 0 || T < 0) return 0;
+    return (int64_t)sizeof(float) * ((B * T) * (OPT_FT + 2) + B * 2 + 64);
+}
+
+extern "C" int parc_b200_path_motion_loss(const parc_char_model_t* m, const parc_opt_config_t* cfg, int64_t B, int64_t T,
+                                          const float* body_pos, const float* body_rot, const float* contacts, const float* hf, int32_t X,
+                                          int32_t Y, const float* min_point, float dx, float dy, const float* body_points,
+                                          float w_pen, float w_contact, void* workspace, int64_t workspace_bytes, float* pen_loss,
+                                          float* contact_loss, float* total_loss, void* stream) {
+    if (!model_ok(m, "path_motion_loss")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(cfg != nullptr, "path_motion_loss: NULL config");
+    PARC_REQUIRE(B >= 0 && T >= 0, "path_motion_loss: negative batch / frame count");
+    if (B == 0) return PARC_OK;
+    PARC_REQUIRE(T > 0, "path_motion_loss: motions without frames");
+    PARC_REQUIRE(body_pos && body_rot && contacts && hf && min_point && body_points, "path_motion_loss: NULL input");
+    PARC_REQUIRE(X > 0 && Y > 0 && dx > 0.f && dy > 0.f, "path_motion_loss: empty terrain");
+    PARC_REQUIRE(cfg->num_points > 0 && cfg->num_points <= 1184, "path_motion_loss: %d body sample points (1..1184 supported)", cfg->num_points);
+    PARC_REQUIRE(workspace && workspace_bytes >= parc_b200_path_motion_loss_workspace_bytes(B, T), "path_motion_loss: workspace too small");
+    PARC_REQUIRE(pen_loss || contact_loss || total_loss, "path_motion_loss: no output requested");
+    const long long n = B * T;
+    OptWs ws = {};
+    float* p = reinterpret_cast<float*>(workspace);
+    ws.frame_terms = p; p += n * OPT_FT;
+    ws.gmin = reinterpret_cast<int*>(p); p += n * 2;
+    ws.patch = reinterpret_cast<int*>(p);
+    ws.body_pos = const_cast<float*>(body_pos);       // read-only in the forward pass
+    ws.body_rot = const_cast<float*>(body_rot);
+    parc_opt_config_t c = *cfg;
+    c.w[PARC_LOSS_PENETRATION] = w_pen;
+    c.w[PARC_LOSS_CONTACT] = w_contact;
+    OptTerrain ter = {hf, 0, X, Y, min_point, 0, dx, dy};    // one terrain shared by the batch (mdm_path.py:94-96)
+    cudaStream_t st = as_stream(stream);
+    path_loss_window_kernel<<<(unsigned)std::min<long long>((n * OPT_FT + 255) / 256, (long long)kNumSMs * 8), 256, 0, st>>>(n, B, X, Y, ws);
+    int rc = check_launch("path_motion_loss (window)");
+    if (rc) return rc;
+    opt_sdf_kernel<<<(unsigned)n, 320, 0, st>>>(*m, c, T, contacts, body_points, ter, ws, 0);
+    if ((rc = check_launch("path_motion_loss (sdf)"))) return rc;
+    path_loss_reduce_kernel<<<(unsigned)B, 128, 0, st>>>(T, w_pen, w_contact, ws, pen_loss, contact_loss, total_loss);
+    return check_launch("path_motion_loss (reduce)");
+}

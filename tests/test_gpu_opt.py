@@ -144,3 +144,51 @@ def test_config4_size_properties():
     assert torch.equal(terms[:B], terms[B:2 * B])   # tiled copies
     l1, t1, g1 = run(slice(5, 6))
     assert torch.equal(t1[0], terms[5]) and torch.equal(l1[0], loss[5]) and all(torch.equal(a[0], b[5]) for a, b in zip(g1, grads))
+
+
+@pytest.mark.parametrize("tag", ["teaser", "civ"])
+def test_path_motion_loss_matches_reference_golden(tag):
+    """parc_b200.mdm_path.compute_motion_loss against the reference's outputs; `civ` has a 50x50 terrain
+    (2,500 cells: the kernel reads it from global memory instead of staging it)."""
+    from parc_b200 import geom_util, mdm_path
+    from parc_b200.file_io import MotionFrames
+    d = H.load_npz("ref_path_loss.npz")
+    model = H.product_model(DEV)
+    pts = geom_util.get_char_point_samples(model)
+    g = lambda k: torch.as_tensor(d[tag + "_" + k]).to(DEV)
+    terrain = H.product_terrain(torch.as_tensor(d[tag + "_hf"]), d[tag + "_min_point"], float(d[tag + "_dxdy"][0]), DEV)
+    frames = MotionFrames(root_pos=g("root_pos"), root_rot=g("root_rot"), joint_rot=g("joint_rot"), contacts=g("contacts"))
+    out = mdm_path.compute_motion_loss(frames, None, terrain, model, pts, w_contact=0.1, w_pen=0.1, w_path=0.0, verbose=False)
+    torch.cuda.synchronize()
+    for k in ("pen_loss", "contact_loss", "total_loss"):
+        np.testing.assert_allclose(out[k].cpu().numpy(), d[tag + "_" + k], rtol=2e-5, atol=3e-6, err_msg=tag + " " + k)
+
+
+def test_path_motion_loss_matches_oracle_on_synthetic_batch():
+    """32 x 45 frames (the generation loop's batch, mdm_path.py:25) of synthetic clips on one blocky terrain."""
+    from oracle import parc_oracle_opt as OO
+    from parc_b200 import geom_util, mdm_path, synth
+    from parc_b200.file_io import MotionFrames
+    model = H.product_model(DEV)
+    pts = geom_util.get_char_point_samples(model)
+    B, T = 32, 45
+    clips = synth.make_clips(synth.humanoid_spec(), 1, seed=5, min_frames=B * T, max_frames=B * T, wrap_fraction=0.0)
+    c = clips[0]
+    hf = torch.as_tensor(c["hf"], dtype=torch.float32)
+    rp = c["root_pos"].reshape(B, T, 3).clone()
+    ij = torch.round((rp[..., :2] - torch.as_tensor(c["min_point"])) / float(c["dx"])).long()
+    ij[..., 0].clamp_(0, hf.shape[0] - 1); ij[..., 1].clamp_(0, hf.shape[1] - 1)
+    rp[..., 2] = hf[ij[..., 0], ij[..., 1]] + 0.85 + 0.1 * torch.randn(B, 1, generator=torch.Generator().manual_seed(1))
+    rr, jr, con = c["root_rot"].reshape(B, T, 4), c["joint_rot"].reshape(B, T, 14, 4), c["contacts"].reshape(B, T, 15)
+    terrain = H.product_terrain(hf, c["min_point"], float(c["dx"]), DEV)
+    out = mdm_path.compute_motion_loss(MotionFrames(root_pos=rp.to(DEV), root_rot=rr.to(DEV), joint_rot=jr.to(DEV), contacts=con.to(DEV)),
+                                       None, terrain, model, pts, w_contact=0.1, w_pen=0.1)
+    torch.cuda.synchronize()
+    om = H.oracle_model()
+    counts = [int(p.shape[0]) for p in pts]
+    total, oc, op = OO.compute_motion_loss(om, torch.cat([p.cpu() for p in pts]), counts, hf, torch.as_tensor(c["min_point"], dtype=torch.float32),
+                                           torch.tensor([float(c["dx"])] * 2), rp, rr, jr, con, 0.1, 0.1)
+    assert float(op.max()) > 0 and float(oc.max()) > 0
+    np.testing.assert_allclose(out["pen_loss"].cpu().numpy(), op.numpy(), rtol=3e-5, atol=1e-5)
+    np.testing.assert_allclose(out["contact_loss"].cpu().numpy(), oc.numpy(), rtol=3e-5, atol=1e-5)
+    np.testing.assert_allclose(out["total_loss"].cpu().numpy(), total.numpy(), rtol=3e-5, atol=1e-5)

@@ -33,3 +33,17 @@ def test_motion_loss_and_gradients_match_reference():
         for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
             ref = d[tag + k]
             np.testing.assert_allclose(g.grad.numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+
+
+def test_path_motion_loss_matches_reference():
+    """mdm_path.compute_motion_loss against tests/golden/ref_path_loss.npz."""
+    d = H.load_npz("ref_path_loss.npz")
+    bp = H.load_npz("ref_body_points.npz")
+    model = H.oracle_model()
+    for tag in ("teaser", "civ"):
+        total, con, pen = OO.compute_motion_loss(model, _t(bp["points"]), bp["counts"], _t(d[tag + "_hf"]), _t(d[tag + "_min_point"]),
+                                                 _t(d[tag + "_dxdy"]), _t(d[tag + "_root_pos"]), _t(d[tag + "_root_rot"]),
+                                                 _t(d[tag + "_joint_rot"]), _t(d[tag + "_contacts"]), 0.1, 0.1)
+        np.testing.assert_allclose(pen.numpy(), d[tag + "_pen_loss"], rtol=2e-5, atol=2e-6)
+        np.testing.assert_allclose(con.numpy(), d[tag + "_contact_loss"], rtol=2e-5, atol=2e-6)
+        np.testing.assert_allclose(total.numpy(), d[tag + "_total_loss"], rtol=2e-5, atol=2e-6)
