@@ -133,6 +133,16 @@ int parc_b200_frame_velocities(const parc_char_model_t* h_model, const float* ro
                                float dt, float* root_vel, float* root_ang_vel, float* dof_vel,
                                void* stream);
 
+/* The same for ALL clips of a library in one launch (the per-file loop of MotionLib._load_motion_file,
+ * motion_lib.py:285-372): the frames of the clips are concatenated
+ * (total_frames rows); clip c owns rows [clip_start[c], clip_start[c] + clip_frames[c]) and has its own
+ * fps / dt (= 1/fps as the host computed it). Bit-identical to one parc_b200_frame_velocities per clip. */
+int parc_b200_library_velocities(const parc_char_model_t* h_model, const float* root_pos, const float* root_rot,
+                                 const float* joint_rot, int64_t total_frames, int32_t num_clips,
+                                 const int64_t* clip_start, const int64_t* clip_frames, const float* clip_fps,
+                                 const float* clip_dt, float* root_vel, float* root_ang_vel, float* dof_vel,
+                                 void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * MotionLib
  * ---------------------------------------------------------------------------------------- */

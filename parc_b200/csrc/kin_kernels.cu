@@ -180,21 +180,33 @@ __global__ void __launch_bounds__(256) rot_to_dof_kernel(const __grid_constant__
 // motion_lib.py:318-327: root_vel = fps*(p[t+1]-p[t]); root_ang_vel = fps*exp_map(q[t+1] (x) conj(q[t]));
 // kin_char_model.py:661-690: drot = normalize(conj(q0) (x) q1); spherical: exp_map(drot)/dt;
 // hinge: dot(axis, exp_map(drot)/dt). Last frame copies the one before.
+// One group of G lanes per frame. With clip tables (num_clips > 0) the frames of ALL clips of a library are done in one
+// launch: the group finds its clip by binary search over the exclusive frame offsets and uses that clip's fps / dt and
+// last-frame rule; without them the nf frames are one clip.
 template <int G>
 __global__ void __launch_bounds__(256) frame_vel_kernel(const __grid_constant__ parc_char_model_t cm,
                                                         const float* __restrict__ root_pos,
                                                         const float* __restrict__ root_rot,
                                                         const float* __restrict__ joint_rot, long long nf,
-                                                        float fps, float dt, float* __restrict__ root_vel,
+                                                        float fps1, float dt1, int num_clips, const long long* __restrict__ clip_start,
+                                                        const long long* __restrict__ clip_frames, const float* __restrict__ clip_fps,
+                                                        const float* __restrict__ clip_dt, float* __restrict__ root_vel,
                                                         float* __restrict__ root_ang_vel,
                                                         float* __restrict__ dof_vel) {
     const LaneBody lb = load_lane_body<G>(cm);
     const int J = cm.num_bodies, D = cm.dof_size;
     const long long gpb = blockDim.x / G;
     for (long long t = (long long)blockIdx.x * gpb + threadIdx.x / G; t < nf; t += (long long)gridDim.x * gpb) {
-        // frame t of the output reads the pair (s, s+1) with s = min(t, nf-2)
-        const long long s = (t < nf - 1) ? t : nf - 2;
-        if (nf < 2) {
+        long long first = 0, count = nf;
+        float fps = fps1, dt = dt1;
+        if (num_clips > 0) {
+            int lo = 0, hi = num_clips - 1;          // last clip whose first frame is <= t
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (__ldg(clip_start + mid) <= t) lo = mid; else hi = mid - 1; }
+            first = __ldg(clip_start + lo); count = __ldg(clip_frames + lo); fps = __ldg(clip_fps + lo); dt = __ldg(clip_dt + lo);
+        }
+        // frame t of the output reads the pair (s, s+1) with s = min(t, last-1) inside its clip
+        const long long s = (t < first + count - 1) ? t : first + count - 2;
+        if (count < 2) {
             if (lb.body == 0) for (int k = 0; k < 3; ++k) { root_vel[t * 3 + k] = 0.f; root_ang_vel[t * 3 + k] = 0.f; }
             if (lb.active && lb.body > 0) for (int k = 0; k < joint_dof_dim(lb.jtype); ++k) dof_vel[t * D + lb.dof_idx + k] = 0.f;
             continue;
@@ -288,8 +300,26 @@ extern "C" int parc_b200_frame_velocities(const parc_char_model_t* m, const floa
     if (nf == 0) return PARC_OK;
     PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel, "frame_velocities: NULL pointer");
     if (m->num_bodies <= 16)
-        frame_vel_kernel<16><<<grid_for(nf, 16), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, nf, fps, dt, root_vel, root_ang_vel, dof_vel);
+        frame_vel_kernel<16><<<grid_for(nf, 16), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, nf, fps, dt, 0, nullptr, nullptr, nullptr, nullptr, root_vel, root_ang_vel, dof_vel);
     else
-        frame_vel_kernel<32><<<grid_for(nf, 8), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, nf, fps, dt, root_vel, root_ang_vel, dof_vel);
+        frame_vel_kernel<32><<<grid_for(nf, 8), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, nf, fps, dt, 0, nullptr, nullptr, nullptr, nullptr, root_vel, root_ang_vel, dof_vel);
     return check_launch("frame_velocities");
+}
+
+extern "C" int parc_b200_library_velocities(const parc_char_model_t* m, const float* root_pos, const float* root_rot,
+                                            const float* joint_rot, int64_t total_frames, int32_t num_clips,
+                                            const int64_t* clip_start, const int64_t* clip_frames, const float* clip_fps,
+                                            const float* clip_dt, float* root_vel, float* root_ang_vel, float* dof_vel, void* stream) {
+    if (!model_ok(m, "library_velocities")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(total_frames >= 0 && num_clips >= 0, "library_velocities: negative size");
+    if (total_frames == 0) return PARC_OK;
+    PARC_REQUIRE(num_clips > 0 && clip_start && clip_frames && clip_fps && clip_dt, "library_velocities: clip tables missing");
+    PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel && (joint_rot || m->num_bodies == 1), "library_velocities: NULL pointer");
+    const long long* cs = reinterpret_cast<const long long*>(clip_start);
+    const long long* cf = reinterpret_cast<const long long*>(clip_frames);
+    if (m->num_bodies <= 16)
+        frame_vel_kernel<16><<<grid_for(total_frames, 16), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, total_frames, 0.f, 0.f, num_clips, cs, cf, clip_fps, clip_dt, root_vel, root_ang_vel, dof_vel);
+    else
+        frame_vel_kernel<32><<<grid_for(total_frames, 8), 256, 0, as_stream(stream)>>>(*m, root_pos, root_rot, joint_rot, total_frames, 0.f, 0.f, num_clips, cs, cf, clip_fps, clip_dt, root_vel, root_ang_vel, dof_vel);
+    return check_launch("library_velocities");
 }

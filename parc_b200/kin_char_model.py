@@ -496,6 +496,26 @@ class KinCharModel:
             _lib.ptr(root_vel), _lib.ptr(root_ang_vel), _lib.ptr(dof_vel), _lib.stream_ptr(rp.device)))
         return root_vel, root_ang_vel, dof_vel
 
+    def library_velocities(self, root_pos, root_rot, joint_rot, clip_start, clip_frames, clip_fps, clip_dt):
+        """frame_velocities for every clip of a concatenated library [F,...] in ONE launch (clip c owns rows
+        [clip_start[c], clip_start[c] + clip_frames[c]) and has fps clip_fps[c], dt clip_dt[c]); bit-identical to
+        the per-clip calls (the per-file loop of motion_lib.py:285-372)."""
+        F = root_pos.shape[0]
+        dev = root_pos.device
+        rp, rr, jr = root_pos.contiguous().float(), root_rot.contiguous().float(), joint_rot.contiguous().float()
+        cs = clip_start.to(device=dev, dtype=torch.int64).contiguous()
+        cf = clip_frames.to(device=dev, dtype=torch.int64).contiguous()
+        fps = clip_fps.to(device=dev, dtype=torch.float32).contiguous()
+        dt = clip_dt.to(device=dev, dtype=torch.float32).contiguous()
+        assert cs.shape == cf.shape == fps.shape == dt.shape and int(cf.sum()) == F
+        root_vel = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        root_ang_vel = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        dof_vel = torch.zeros((F, self._dof_size), dtype=torch.float32, device=dev)
+        _lib.check(_lib.lib().parc_b200_library_velocities(
+            self._cstruct(), _lib.ptr(rp), _lib.ptr(rr), _lib.ptr(jr), F, int(cs.shape[0]), _lib.ptr(cs), _lib.ptr(cf), _lib.ptr(fps),
+            _lib.ptr(dt), _lib.ptr(root_vel), _lib.ptr(root_ang_vel), _lib.ptr(dof_vel), _lib.stream_ptr(dev)))
+        return root_vel, root_ang_vel, dof_vel
+
     def compute_frame_dof_vel(self, joint_rot, dt):
         """[T,J-1,4] -> [T,D] (reference :651-659); only the single-clip shape is kernel-backed."""
         assert joint_rot.dim() == 3, "compute_frame_dof_vel: expected [T, J-1, 4]"

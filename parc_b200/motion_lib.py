@@ -117,34 +117,36 @@ class MotionLib:
         M = len(clips)
         assert M > 0
         J = kcm.get_num_joints()
-        fps_l, dt_l, nf_l, len_l, loop_l, delta_l = [], [], [], [], [], []
-        rp_l, rr_l, rv_l, rav_l, jr_l, dv_l, c_l, terrains = [], [], [], [], [], [], [], []
+        fps_l, dt_l, nf_l, len_l, loop_l = [], [], [], [], []
+        rp_l, rr_l, jr_l, c_l, terrains = [], [], [], [], []
         for c in clips:
-            root_pos = c["root_pos"].to(device=dev, dtype=torch.float32)
-            root_rot = c["root_rot"].to(device=dev, dtype=torch.float32)
-            joint_rot = c["joint_rot"].to(device=dev, dtype=torch.float32)
+            root_pos, root_rot, joint_rot = c["root_pos"], c["root_rot"], c["joint_rot"]
             nf = root_pos.shape[0]
             assert nf == root_rot.shape[0] == joint_rot.shape[0]
             fps = c["fps"]
             lm = c["loop_mode"]
             lm = lm.value if isinstance(lm, LoopMode) else (LoopMode[lm].value if isinstance(lm, str) else int(lm))
-            dt = 1.0 / fps
-            delta = root_pos[-1] - root_pos[0]                       # motion_lib.py:315-316
-            delta[..., -1] = 0.0
-            # finite-difference velocities (motion_lib.py:318-327), one launch per clip
-            root_vel, root_ang_vel, dof_vel = kcm.frame_velocities(root_pos, root_rot, joint_rot, fps, dt)
-            fps_l.append(fps); dt_l.append(dt); nf_l.append(nf)
+            fps_l.append(fps); dt_l.append(1.0 / fps); nf_l.append(nf)
             len_l.append(1.0 / fps * (nf - 1))                       # motion_lib.py:313
-            loop_l.append(lm); delta_l.append(delta)
-            rp_l.append(root_pos); rr_l.append(root_rot); rv_l.append(root_vel); rav_l.append(root_ang_vel)
-            jr_l.append(joint_rot); dv_l.append(dof_vel)
+            loop_l.append(lm)
+            rp_l.append(root_pos); rr_l.append(root_rot); jr_l.append(joint_rot)
             if self._contact_info:
                 con = c.get("contacts")
-                if con is None:
-                    con = torch.zeros((nf, J), dtype=torch.float32, device=dev)
-                c_l.append(con.to(device=dev, dtype=torch.float32))
+                c_l.append(con if con is not None else torch.zeros((nf, J), dtype=torch.float32))
             terrains.append(c.get("terrain"))
+        f32 = torch.float32
+        # one concatenation + one upload per tensor kind instead of one per clip
+        frames = dict(root_pos=torch.cat([x.to(dtype=f32) for x in rp_l], dim=0).to(dev),
+                      root_rot=torch.cat([x.to(dtype=f32) for x in rr_l], dim=0).to(dev),
+                      joint_rot=torch.cat([x.to(dtype=f32) for x in jr_l], dim=0).to(dev),
+                      contacts=torch.cat([x.to(dtype=f32) for x in c_l], dim=0).to(dev) if self._contact_info else None)
+        self._build_from_concatenated(frames, nf_l, fps_l, dt_l, len_l, loop_l, weights, names, terrains)
 
+    def _build_from_concatenated(self, frames, nf_l, fps_l, dt_l, len_l, loop_l, weights, names, terrains, hf_mask_inds=None):
+        """Library tensors from the clips' frames already concatenated on the device: per-clip tables, the first/last
+        frame deltas, and the finite-difference velocities of ALL clips in one launch (motion_lib.py:313-327)."""
+        dev = self._device
+        M = len(nf_l)
         if weights is None:
             weights = [1.0] * M
         self._motion_weights = torch.tensor(weights, dtype=torch.float32, device=dev)
@@ -154,17 +156,20 @@ class MotionLib:
         self._motion_num_frames = torch.tensor(nf_l, dtype=torch.long, device=dev)
         self._motion_lengths = torch.tensor(len_l, dtype=torch.float32, device=dev)
         self._motion_loop_modes = torch.tensor(loop_l, dtype=torch.int, device=dev)
-        self._motion_root_pos_delta = torch.stack(delta_l, dim=0)
-        self._frame_root_pos = torch.cat(rp_l, dim=0)
-        self._frame_root_rot = torch.cat(rr_l, dim=0)
-        self._frame_root_vel = torch.cat(rv_l, dim=0)
-        self._frame_root_ang_vel = torch.cat(rav_l, dim=0)
-        self._frame_joint_rot = torch.cat(jr_l, dim=0)
-        self._frame_dof_vel = torch.cat(dv_l, dim=0)
-        self._frame_contacts = torch.cat(c_l, dim=0) if self._contact_info else None
+        self._frame_root_pos = frames["root_pos"]
+        self._frame_root_rot = frames["root_rot"]
+        self._frame_joint_rot = frames["joint_rot"]
+        self._frame_contacts = frames["contacts"] if self._contact_info else None
+        start = torch.cumsum(self._motion_num_frames, 0) - self._motion_num_frames
+        delta = self._frame_root_pos[start + self._motion_num_frames - 1] - self._frame_root_pos[start]   # motion_lib.py:315-316
+        delta[..., -1] = 0.0
+        self._motion_root_pos_delta = delta
+        self._frame_root_vel, self._frame_root_ang_vel, self._frame_dof_vel = self._kin_char_model.library_velocities(
+            self._frame_root_pos, self._frame_root_rot, self._frame_joint_rot, start, self._motion_num_frames, self._motion_fps,
+            self._motion_dt)
         self._terrains = terrains
         self._motion_names = names if names is not None else ["motion_%d" % i for i in range(M)]
-        self._hf_mask_inds = [None] * M
+        self._hf_mask_inds = hf_mask_inds if hf_mask_inds is not None else [None] * M
         self._finish()
 
     def _finish(self):
@@ -254,6 +259,133 @@ class MotionLib:
         self._motion_names = [""]
         self._hf_mask_inds = [None]
         self._finish()
+
+    # ------------------------------------------------------------------ packed on-disk library
+    PACK_MAGIC = b"PARCPACK1\n"
+
+    def save_packed(self, path):
+        """One flat file for the whole library instead of one pickle per clip (the reference's loader walks a yaml of
+        .pkl files, motion_lib.py:255-372): magic | u64 header length | JSON header | 64-byte-aligned raw arrays. It holds
+        the SOURCE data only (poses, contacts, per-clip tables, terrains, hf_mask_inds); velocities and the device
+        records are rebuilt by `from_packed` in two launches."""
+        import json
+        import numpy as np
+        arrays = {}
+
+        def put(name, t):
+            arrays[name] = np.ascontiguousarray(t.detach().cpu().numpy() if torch.is_tensor(t) else np.asarray(t))
+
+        put("root_pos", self._frame_root_pos); put("root_rot", self._frame_root_rot); put("joint_rot", self._frame_joint_rot)
+        if self._frame_contacts is not None:
+            put("contacts", self._frame_contacts)
+        put("num_frames", self._motion_num_frames); put("loop_modes", self._motion_loop_modes)
+        put("fps", self._motion_fps.double()); put("weights", self._motion_weights)
+        M = self.num_motions()
+        has_t = np.array([t is not None for t in self._terrains] + [False] * (M - len(self._terrains)), dtype=np.uint8)
+        put("has_terrain", has_t)
+        ts = [t for t in self._terrains if t is not None]
+        if ts:
+            put("terrain_dims", torch.stack([torch.tensor(t.hf.shape, dtype=torch.int64) for t in ts]))
+            put("terrain_min_point", torch.stack([t.min_point.float().cpu() for t in ts]))
+            put("terrain_dxdy", torch.stack([t.dxdy.float().cpu() for t in ts]))
+            put("terrain_hf", torch.cat([t.hf.float().cpu().reshape(-1) for t in ts]))
+            put("terrain_hf_maxmin", torch.cat([t.hf_maxmin.float().cpu().reshape(-1) for t in ts]))
+        masks = list(self._hf_mask_inds) + [None] * (M - len(self._hf_mask_inds))
+        put("has_mask_inds", np.array([m is not None for m in masks], dtype=np.uint8))
+        flat, offs = [], [0]
+        for m in masks:
+            if m is None:
+                continue
+            for fr in m:                                     # one [k,2] index list per frame of the clip
+                fr = torch.as_tensor(fr, dtype=torch.int64).reshape(-1, 2).cpu()
+                flat.append(fr); offs.append(offs[-1] + fr.shape[0])
+        if flat:
+            put("mask_inds", torch.cat(flat, dim=0)); put("mask_offsets", np.asarray(offs, dtype=np.int64))
+        header = {"version": 1, "contact_info": bool(self._contact_info), "names": list(self._motion_names), "arrays": {}}
+        off = 0
+        for k, a in arrays.items():
+            off = (off + 63) & ~63
+            header["arrays"][k] = {"dtype": str(a.dtype), "shape": list(a.shape), "offset": off}
+            off += a.nbytes
+        hb = json.dumps(header).encode()
+        with open(path, "wb") as f:
+            f.write(self.PACK_MAGIC); f.write(len(hb).to_bytes(8, "little")); f.write(hb)
+            base = f.tell()
+            base_al = (base + 63) & ~63
+            f.write(b"\0" * (base_al - base))
+            for k, a in arrays.items():
+                f.seek(base_al + header["arrays"][k]["offset"])
+                f.write(a.tobytes())
+        return path
+
+    @classmethod
+    def from_packed(cls, path, char_model, device, contact_info=None):
+        """Loads a `save_packed` file: one read, one upload per array, velocities of all clips in one launch, records in
+        one more. Equal, tensor for tensor, to the library the file was saved from."""
+        import json
+        import numpy as np
+        raw = np.fromfile(path, dtype=np.uint8)
+        magic = cls.PACK_MAGIC
+        if raw[:len(magic)].tobytes() != magic:
+            raise ValueError("%s is not a packed parc_b200 motion library" % path)
+        hl = int.from_bytes(raw[len(magic):len(magic) + 8].tobytes(), "little")
+        header = json.loads(raw[len(magic) + 8:len(magic) + 8 + hl].tobytes().decode())
+        base = (len(magic) + 8 + hl + 63) & ~63
+
+        def get(name):
+            if name not in header["arrays"]:
+                return None
+            d = header["arrays"][name]
+            n = int(np.prod(d["shape"])) if d["shape"] else 1
+            a = np.frombuffer(raw, dtype=np.dtype(d["dtype"]), count=n, offset=base + d["offset"]).reshape(d["shape"])
+            return torch.from_numpy(a.copy())
+
+        ci = header["contact_info"] if contact_info is None else contact_info
+        inst = cls(char_model, device, contact_info=ci)
+        dev = inst._device
+        nf = get("num_frames")
+        M = int(nf.shape[0])
+        fps = [float(x) for x in get("fps")]
+        fps = [int(x) if float(x).is_integer() else x for x in fps]
+        frames = dict(root_pos=get("root_pos").to(dev), root_rot=get("root_rot").to(dev), joint_rot=get("joint_rot").to(dev),
+                      contacts=None)
+        if ci:
+            con = get("contacts")
+            frames["contacts"] = (con if con is not None else torch.zeros(frames["root_pos"].shape[0], char_model.get_num_joints())).to(dev)
+        terrains = [None] * M
+        has_t = get("has_terrain")
+        if has_t is not None and bool(has_t.any()):
+            dims, mp, dd = get("terrain_dims"), get("terrain_min_point"), get("terrain_dxdy")
+            hf_all, mm_all = get("terrain_hf").to(dev), get("terrain_hf_maxmin").to(dev)
+            o, k = 0, 0
+            for m in range(M):
+                if not has_t[m]:
+                    continue
+                X, Y = int(dims[k, 0]), int(dims[k, 1])
+                t = SubTerrain(x_dim=X, y_dim=Y, dx=float(dd[k, 0]), dy=float(dd[k, 1]), min_x=float(mp[k, 0]), min_y=float(mp[k, 1]),
+                               device=dev)
+                t.min_point, t.dxdy = mp[k].to(dev), dd[k].to(dev)
+                t.hf = hf_all[o:o + X * Y].reshape(X, Y).clone()
+                t.hf_maxmin = mm_all[2 * o:2 * (o + X * Y)].reshape(X, Y, 2).clone()
+                terrains[m] = t
+                o += X * Y; k += 1
+        masks = [None] * M
+        has_m = get("has_mask_inds")
+        if has_m is not None and bool(has_m.any()):
+            inds, offs = get("mask_inds").to(dev), get("mask_offsets")
+            f0 = 0
+            for m in range(M):
+                if not has_m[m]:
+                    continue
+                n_m = int(nf[m])
+                masks[m] = [inds[int(offs[f0 + t]):int(offs[f0 + t + 1])] for t in range(n_m)]
+                f0 += n_m
+        nf_l = [int(x) for x in nf]
+        inst._build_from_concatenated(frames, nf_l, fps, [1.0 / f for f in fps], [1.0 / f * (n - 1) for f, n in zip(fps, nf_l)],
+                                      [int(x) for x in get("loop_modes")], [float(x) for x in get("weights")], header["names"], terrains,
+                                      hf_mask_inds=masks)
+        inst._motion_weights = get("weights").to(dev)      # already normalised: keep the saved bits
+        return inst
 
     # ------------------------------------------------------------------ device records
     def repack(self):
