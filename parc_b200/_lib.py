@@ -227,6 +227,8 @@ def _declare(lib):
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_hf_mask_inds": [P(CharModelStruct), P(TerrainStruct), vp, vp, i64, vp, vp, i32, vp, vp, vp, vp, vp],
+        "parc_b200_hf_extra_vals": [P(TerrainStruct), vp, vp, f32, f32, f32, f32, vp, vp],
         "parc_b200_library_velocities": [P(CharModelStruct), vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp],
         "parc_b200_path_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64, vp, vp, vp, vp, i32, i32, vp, f32, f32, vp,
                                        f32, f32, vp, i64, vp, vp, vp, vp],

@@ -158,3 +158,71 @@ def points_hf_sdf(points, hf, hf_min_box_center, hf_dxdy, base_z=-10.0, inverted
     hf = hf.to(device=dev, dtype=torch.float32).contiguous()
     mc = hf_min_box_center.to(device=dev, dtype=torch.float32).contiguous()
     return _PointsHfSdfFn.apply(points, hf, mc, float(hf_dxdy[0]), float(hf_dxdy[1]), float(base_z), bool(inverted))
+
+
+# ---- motion-aware terrain post-processing -----------------------------------------
+def _mask_pass(motion_frames, terrain: SubTerrain, char_model, char_body_points):
+    """FK + parc_b200_hf_mask_inds: -> (inds [T,Np,2] i64, counts [T] i32, min_body_heights [X,Y], mask [X,Y] u8)"""
+    root_pos, root_rot, joint_rot = motion_frames.root_pos, motion_frames.root_rot, motion_frames.joint_rot
+    assert root_pos.dim() == 2 and root_rot.dim() == 2 and joint_rot.dim() == 3, "one motion: [T,3], [T,4], [T,J-1,4]"
+    dev, f32 = terrain.hf.device, torch.float32
+    body_pos, body_rot = char_model.forward_kinematics(root_pos.to(dev), root_rot.to(dev), joint_rot.to(dev))      # :1865
+    body_pos, body_rot = body_pos.contiguous().float(), body_rot.contiguous().float()
+    T, J = int(root_pos.shape[0]), char_model.get_num_joints()
+    assert len(char_body_points) == J
+    pts = torch.cat([p.to(device=dev, dtype=f32) for p in char_body_points], dim=0).contiguous()
+    starts = [0]
+    for p in char_body_points:
+        starts.append(starts[-1] + int(p.shape[0]))
+    Np = starts[-1]
+    point_start = torch.tensor(starts, dtype=torch.int32, device=dev)
+    X, Y = terrain.hf.shape
+    inds = torch.empty((T, Np, 2), dtype=torch.int64, device=dev)
+    counts = torch.empty((T,), dtype=torch.int32, device=dev)
+    mins = torch.empty((X, Y), dtype=f32, device=dev)
+    mask = torch.empty((X, Y), dtype=torch.uint8, device=dev)
+    p = _lib.ptr
+    _lib.check(_lib.lib().parc_b200_hf_mask_inds(char_model._cstruct(), terrain.cstruct(), p(body_pos), p(body_rot), T, p(pts), p(point_start),
+                                                 Np, p(inds), p(counts), p(mins), p(mask), _lib.stream_ptr(dev)))
+    return inds, counts, mins, mask
+
+
+def compute_hf_mask_inds(motion_frames, terrain: SubTerrain, char_model, char_body_points):
+    """terrain_util.compute_hf_mask_inds (PARC/util/terrain_util.py:1851-1897): for each frame the unique grid cells
+    under the character's body sample points (sorted as torch.unique(dim=0) sorts them), and the lowest sample height
+    seen over every cell. One launch with a block per frame instead of the frames x bodies x points Python loop; the
+    only host synchronisation is the read of the per-frame counts that cuts the list."""
+    terrain.hf_mask[...] = False                                                                                   # :1869
+    inds, counts, mins, _ = _mask_pass(motion_frames, terrain, char_model, char_body_points)
+    counts = counts.cpu().tolist()
+    return [inds[t, :c] for t, c in enumerate(counts)], mins
+
+
+def compute_hf_mask_from_inds(terrain: SubTerrain, mask_grid_inds):
+    """:1899-1906"""
+    hf_mask = torch.zeros_like(terrain.hf_mask)
+    if len(mask_grid_inds) > 0:
+        allc = torch.cat([x.reshape(-1, 2) for x in mask_grid_inds], dim=0)
+        hf_mask[allc[:, 0], allc[:, 1]] = True
+    return hf_mask
+
+
+def compute_hf_mask(motion_frames, terrain: SubTerrain, char_model, char_body_points):
+    """:1908-1915 -- the union comes straight out of the kernel"""
+    return _mask_pass(motion_frames, terrain, char_model, char_body_points)[3].bool()
+
+
+def compute_hf_extra_vals(motion_frames, terrain: SubTerrain, char_model, char_body_points, z_buf=3.0, jump_buf=0.8):
+    """:1918-1947 -> (mask_grid_inds, copy of the terrain whose hf_maxmin tells the augmenter how far each cell may move)"""
+    ret_terrain = terrain.torch_copy()
+    ret_terrain.hf_mask[...] = False
+    inds, counts, mins, mask = _mask_pass(motion_frames, ret_terrain, char_model, char_body_points)
+    max_h = torch.max(motion_frames.root_pos[:, 2]).item()
+    min_h = torch.min(ret_terrain.hf).item()
+    mm = torch.empty_like(ret_terrain.hf_maxmin)
+    p = _lib.ptr
+    _lib.check(_lib.lib().parc_b200_hf_extra_vals(ret_terrain.cstruct(), p(mask), p(mins), float(max_h), float(min_h), float(z_buf),
+                                                  float(jump_buf), p(mm), _lib.stream_ptr(mm.device)))
+    ret_terrain.hf_maxmin = mm
+    counts = counts.cpu().tolist()
+    return [inds[t, :c] for t, c in enumerate(counts)], ret_terrain
