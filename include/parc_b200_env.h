@@ -261,6 +261,34 @@ int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_mot
 int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motions, const float* u, int64_t n,
                                  int64_t* ids, void* stream);
 
+/* ---- recording path (stage 4 `record`) ---------------------------------------------
+ * IGParkourEnv.write_agent_states (PARC/motion_tracker/envs/ig_parkour/ig_parkour_env.py:759-796) appends, per control
+ * step and per env in a host loop, the character state [root_pos | exp_map(root_rot) | dof_pos] and the contact flags
+ * (_get_char_state, :664-687; the reference character instead when record_ref), optionally the observation row, and
+ * stops an env at its first FAIL. Here the tape lives in HBM and one launch does a step for all envs. */
+typedef struct parc_record_tape_t {
+    float* frames;            /* [N, max_frames, 6 + D] */
+    float* contacts;          /* [N, max_frames, C] */
+    float* obs;               /* [N, max_frames, obs_dim] or NULL (record_obs False, :1157-1163) */
+    int32_t* cursor;          /* [N] frames recorded so far */
+    uint8_t* writing;         /* [N] _writing_env_state (:1177) */
+    uint8_t* success;         /* [N] _env_success_state (:1178) */
+    int32_t* saved_list;      /* [N] envs the reference would hand to save_agent_states_to_file in THIS step (unordered) */
+    int32_t* saved_count;     /* [1] zeroed by the call */
+    int32_t* still_recording; /* [1] set to 1 iff some env was writing at this step = the _write_agent_states_flag the loop leaves (:762-767) */
+    int32_t* overflow;        /* [1] set to 1 if an env ran past max_frames (its later frames are dropped) */
+    int32_t max_frames;
+    int32_t obs_dim;
+} parc_record_tape_t;
+
+/* One write_agent_states step. An env that is writing gets its row appended; if done_buf == FAIL it stops, and it
+ * counts as a success unless (!bypass_record_fail and motion_time < motion_length - 2 * timestep, compared in double
+ * like the Python floats, :786-789), motion_time = time_buf + motion_time_offsets (dm_env.py:547-552). */
+int parc_b200_record_agent_states(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
+                                  const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
+                                  const parc_record_tape_t* h_tape, int32_t record_ref, int32_t bypass_record_fail,
+                                  double timestep, void* stream);
+
 /* Benchmark / test utility, NOT a reference function: a stand-in for the physics simulator between two
  * control steps, so that a device-resident loop sees a stationary workload. For every env it rewrites
  * the simulated character state as the env's current reference state plus a fixed per-env

@@ -55,6 +55,12 @@ class SamplerConfigStruct(C.Structure):     # parc_sampler_config_t, include/par
                 ("max_h", C.c_float), ("future_pos_noise_scale", C.c_float)]
 
 
+class RecordTapeStruct(C.Structure):         # parc_record_tape_t, include/parc_b200_env.h
+    _fields_ = [("frames", C.c_void_p), ("contacts", C.c_void_p), ("obs", C.c_void_p), ("cursor", C.c_void_p), ("writing", C.c_void_p),
+                ("success", C.c_void_p), ("saved_list", C.c_void_p), ("saved_count", C.c_void_p), ("still_recording", C.c_void_p),
+                ("overflow", C.c_void_p), ("max_frames", C.c_int32), ("obs_dim", C.c_int32)]
+
+
 class HostRowsStruct(C.Structure):
     _fields_ = [("dst_device", C.c_void_p), ("src_host", C.c_void_p), ("row_bytes", C.c_int64)]
 
@@ -227,6 +233,8 @@ def _declare(lib):
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_record_agent_states": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),
+                                          P(RecordTapeStruct), i32, i32, f64, vp],
         "parc_b200_hf_mask_inds": [P(CharModelStruct), P(TerrainStruct), vp, vp, i64, vp, vp, i32, vp, vp, vp, vp, vp],
         "parc_b200_hf_extra_vals": [P(TerrainStruct), vp, vp, f32, f32, f32, f32, vp, vp],
         "parc_b200_library_velocities": [P(CharModelStruct), vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp],

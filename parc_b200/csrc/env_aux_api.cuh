@@ -292,3 +292,84 @@ extern "C" int parc_b200_env_step_host(const parc_char_model_t* m, const parc_mo
     }
     return PARC_OK;
 }
+
+// ---- recording path: IGParkourEnv.write_agent_states (ig_parkour_env.py:759-796) ---------------------------------
+namespace parc {
+__global__ void __launch_bounds__(256) record_agent_states_kernel(const int J, const int D, const int C, const __grid_constant__ parc_motion_lib_t lib,
+                                                                  const __grid_constant__ parc_env_config_t cfg, const __grid_constant__ parc_env_buffers_t env,
+                                                                  const __grid_constant__ parc_record_tape_t tape, const int record_ref,
+                                                                  const int bypass, const double timestep) {
+    // one warp per env; lanes stride over the row's columns
+    const int lane = threadIdx.x & 31;
+    const long long wpb = blockDim.x / 32;
+    const int W = 6 + D;
+    for (long long e = (long long)blockIdx.x * wpb + threadIdx.x / 32; e < env.num_envs; e += (long long)gridDim.x * wpb) {
+        if (!tape.writing[e]) continue;                                              // :764-765 (warp-uniform)
+        if (lane == 0) *tape.still_recording = 1;                                    // :766
+        const int cur = tape.cursor[e];
+        const bool room = cur < tape.max_frames;
+        if (room) {
+            float* fr = tape.frames + ((long long)e * tape.max_frames + cur) * W;
+            float* co = tape.contacts + ((long long)e * tape.max_frames + cur) * C;
+            const parc_view3_t& vp = record_ref ? env.ref_root_pos : env.char_root_pos;
+            const parc_view3_t& vr = record_ref ? env.ref_root_rot : env.char_root_rot;
+            const parc_view3_t& vd = record_ref ? env.ref_dof_pos : env.char_dof_pos;
+            if (lane < 3) fr[lane] = view_ld(vp, e, lane);
+            if (lane == 3) {
+                const Vec3 em = quat_to_exp_map(view_ld_quat(vr, e));                // _get_char_state, :664-676
+                fr[3] = em.x; fr[4] = em.y; fr[5] = em.z;
+            }
+            for (int k = lane; k < D; k += 32) fr[6 + k] = view_ld(vd, e, k);
+            for (int c = lane; c < C; c += 32) {
+                float v;
+                if (record_ref) v = view_ld(env.ref_contacts, e, c);
+                else {
+                    const float fx = view_ld3(env.char_contact_forces, e, c, 0), fy = view_ld3(env.char_contact_forces, e, c, 1),
+                                fz = view_ld3(env.char_contact_forces, e, c, 2);
+                    v = sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps ? 1.f : 0.f;   // :674-676
+                }
+                co[c] = v;
+            }
+            if (tape.obs) {
+                const float* src = env.obs_buf + e * env.obs_row_stride;
+                float* dst = tape.obs + ((long long)e * tape.max_frames + cur) * tape.obs_dim;
+                for (int k = lane; k < tape.obs_dim; k += 32) dst[k] = src[k];       // :773-774
+            }
+        }
+        if (lane == 0) {
+            if (room) tape.cursor[e] = cur + 1; else *tape.overflow = 1;
+            if (env.done_buf[e] == PARC_DONE_FAIL) {                                 // :776-794
+                tape.writing[e] = 0;
+                const MotionMeta mm = load_motion_meta(lib.meta, env.motion_ids[e]);
+                const float mt = __fadd_rn(env.time_buf[e], env.motion_time_offsets[e]);
+                const bool failed_early = !bypass && ((double)mt < (double)mm.length - timestep * 2.0);
+                if (!failed_early) {
+                    tape.success[e] = 1;
+                    tape.saved_list[atomicAdd(tape.saved_count, 1)] = (int)e;
+                }
+            }
+        }
+    }
+}
+}  // namespace parc
+
+extern "C" int parc_b200_record_agent_states(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_env_config_t* cfg,
+                                             const parc_env_buffers_t* env, const parc_record_tape_t* tape, int32_t record_ref,
+                                             int32_t bypass_record_fail, double timestep, void* stream) {
+    if (!model_ok(m, "record_agent_states")) return PARC_ERR_INVALID_ARG;
+    PARC_REQUIRE(lib && lib->meta && cfg && env && tape, "record_agent_states: NULL argument");
+    PARC_REQUIRE(tape->frames && tape->contacts && tape->cursor && tape->writing && tape->success && tape->saved_list && tape->saved_count &&
+                     tape->still_recording && tape->overflow && tape->max_frames > 0, "record_agent_states: incomplete tape");
+    PARC_REQUIRE(env->done_buf && env->time_buf && env->motion_time_offsets && env->motion_ids, "record_agent_states: env buffers not set");
+    if (record_ref) PARC_REQUIRE(env->ref_root_pos.ptr && env->ref_root_rot.ptr && env->ref_dof_pos.ptr && env->ref_contacts.ptr, "record_agent_states: ref_* views not set");
+    else PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_dof_pos.ptr && env->char_contact_forces.ptr, "record_agent_states: simulator views not set");
+    if (tape->obs) PARC_REQUIRE(env->obs_buf && tape->obs_dim > 0 && tape->obs_dim <= env->obs_row_stride, "record_agent_states: observation tape without a matching obs_buf");
+    cudaStream_t st = as_stream(stream);
+    zero_int_kernel<<<1, 1, 0, st>>>(tape->saved_count);
+    zero_int_kernel<<<1, 1, 0, st>>>(tape->still_recording);
+    if (env->num_envs == 0) return check_launch("record_agent_states (clear)");
+    const int C = record_ref ? lib->num_contacts : m->num_bodies;
+    const unsigned blocks = (unsigned)std::min<long long>((env->num_envs + 7) / 8, kNumSMs * 16);
+    record_agent_states_kernel<<<blocks, 256, 0, st>>>(m->num_bodies, m->dof_size, C, *lib, *cfg, *env, *tape, record_ref, bypass_record_fail, timestep);
+    return check_launch("record_agent_states");
+}

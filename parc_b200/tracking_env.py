@@ -403,6 +403,61 @@ class TrackingEnv:
             _lib.check(L.parc_b200_env_step(km, self._mlib.cstruct(), self._terrain_cs, self._cfg, self._bufs,
                                             _lib.STEP_HEIGHTS | _lib.STEP_OBS, p(env_ids), n, self._stream()))
 
+    # ---------------------------------------------------------------- recording path (stage 4)
+    def build_agent_states_dict(self, name_suffix="", record_obs=False, max_frames=None, record_ref=False, bypass_record_fail=False):
+        """IGParkourEnv.build_agent_states_dict (ig_parkour_env.py:1153-1182): start recording every env. The reference
+        keeps per-env Python lists of per-step tensors; here the tape is [N, max_frames, ...] in HBM (max_frames defaults
+        to one episode + 2 frames) and write_agent_states is one launch."""
+        N, dev = self._num_envs, self._device
+        if max_frames is None:
+            max_frames = int(round(self._cfg.episode_length / self._cfg.timestep)) + 2
+        C = self._mlib.cstruct().num_contacts if record_ref else self._J
+        z = lambda *s, dt=torch.float32: torch.zeros(s, dtype=dt, device=dev)
+        self._tape = dict(frames=z(N, max_frames, 6 + self._D), contacts=z(N, max_frames, C),
+                          obs=z(N, max_frames, self._obs_dim) if record_obs else None, cursor=z(N, dt=torch.int32),
+                          writing=torch.ones(N, dtype=torch.uint8, device=dev), success=z(N, dt=torch.uint8),
+                          saved_list=z(N, dt=torch.int32), saved_count=z(1, dt=torch.int32),
+                          still_recording=torch.ones(1, dtype=torch.int32, device=dev), overflow=z(1, dt=torch.int32))
+        t = _lib.RecordTapeStruct()
+        for k in ("frames", "contacts", "obs", "cursor", "writing", "success", "saved_list", "saved_count", "still_recording", "overflow"):
+            setattr(t, k, _lib.ptr(self._tape[k]))
+        t.max_frames, t.obs_dim = int(max_frames), int(self._obs_dim if record_obs else 0)
+        self._tape_cs = t
+        self._record_obs, self._record_ref, self._bypass_record_fail = bool(record_obs), bool(record_ref), bool(bypass_record_fail)
+        self._save_motion_name_suffix = name_suffix
+
+    def write_agent_states(self):
+        """IGParkourEnv.write_agent_states (:759-796) for all envs in one launch; call it after post_physics_step and
+        before the reset, as the reference does (:696). Nothing is copied to the host."""
+        _lib.check(_lib.lib().parc_b200_record_agent_states(
+            self._kin_char_model._cstruct(), self._mlib.cstruct(), self._cfg, self._bufs, self._tape_cs, int(self._record_ref),
+            int(self._bypass_record_fail), 1.0 / float(self._env_config["control_freq"]) if "control_freq" in self._env_config
+            else float(self._cfg.timestep), self._stream()))
+
+    def is_writing_agent_states(self):
+        """:742-743 -- reads the device flag (synchronises)."""
+        return bool(self._tape["still_recording"].item())
+
+    def get_env_success_states(self):
+        return self._tape["success"].bool()
+
+    def envs_finished_this_step(self):
+        """Env ids the reference would pass to save_agent_states_to_file in the last write_agent_states call, ascending."""
+        n = int(self._tape["saved_count"].item())
+        return torch.sort(self._tape["saved_list"][:n]).values
+
+    def get_agent_motion(self, env_id):
+        """The recorded dict of one env as save_agent_states_to_file builds it (:698-735) before the terrain slice:
+        frames [T, 6+D] with global xy (:707-708), contacts [T, C], optionally obs [T, obs_dim]."""
+        T = int(self._tape["cursor"][env_id].item())
+        frames = self._tape["frames"][env_id, :T].clone()
+        frames[:, 0:2] += self._env_offsets[env_id, 0:2]                      # _get_global_xy_pos, :1184-1188
+        out = {"fps": int(round(1.0 / self._cfg.timestep)), "loop_mode": "CLAMP", "frames": frames,
+               "contacts": self._tape["contacts"][env_id, :T].clone()}
+        if self._record_obs:
+            out["obs"] = self._tape["obs"][env_id, :T].clone()
+        return out
+
     # ---------------------------------------------------------------- host <-> device (e2e path)
     def make_host_state(self):
         """Pinned host staging buffers with the layout of sim_state_tensors()."""

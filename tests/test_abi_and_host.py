@@ -52,14 +52,14 @@ def test_ctypes_struct_sizes_match_the_c_structs(tmp_path):
     from parc_b200 import _lib
     prog = tmp_path / "sizes.c"
     prog.write_text('#include <stdio.h>\n#include "parc_b200.h"\n#include "parc_b200_env.h"\n#include "parc_b200_sampler.h"\n'
-                    'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(parc_char_model_t), sizeof(parc_motion_lib_t),'
+                    'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu ", sizeof(parc_char_model_t), sizeof(parc_motion_lib_t),'
                     'sizeof(parc_terrain_t), sizeof(parc_env_config_t), sizeof(parc_env_buffers_t), sizeof(parc_host_rows_t),'
-                    'sizeof(parc_sampler_config_t));return 0;}\n')
+                    'sizeof(parc_sampler_config_t));printf("%zu\\n", sizeof(parc_record_tape_t));return 0;}\n')
     exe = tmp_path / "sizes"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(prog), "-o", str(exe)], check=True)
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     mine = [ctypes.sizeof(s) for s in (_lib.CharModelStruct, _lib.MotionLibStruct, _lib.TerrainStruct, _lib.EnvConfigStruct,
-                                       _lib.EnvBuffersStruct, _lib.HostRowsStruct, _lib.SamplerConfigStruct)]
+                                       _lib.EnvBuffersStruct, _lib.HostRowsStruct, _lib.SamplerConfigStruct, _lib.RecordTapeStruct)]
     assert mine == sizes
 
 
