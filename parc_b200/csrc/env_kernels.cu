@@ -32,6 +32,12 @@
 #ifndef PARC_EXP_HU
 #define PARC_EXP_HU 2
 #endif
+#ifndef PARC_SPLIT_A
+#define PARC_SPLIT_A 1      // 1: phase A uniforms as two dependent-load chains in two warps
+#endif
+#ifndef PARC_VEC_ROWS
+#define PARC_VEC_ROWS 1      // 1: staged rows are shifted to the 16-byte phase of their obs_buf row, copy-out in 128-bit pieces
+#endif
 
 namespace parc {
 
@@ -94,12 +100,13 @@ struct EnvU {
     float time, t0, tox, toy;
     MotionMeta mm;
     int live;
+    int row_shift;           // floats the staged row is shifted by (16-byte phase of the env's obs_buf row)
     int flags;               // phase C: bit0 fall contact, bit1 fall height, bit2 pose failure
 };
 
 // Shared-memory plan (dynamic): sized on the host by step_smem_bytes().
 struct SmemPlan {
-    int row_pitch;           // floats per staged row: o_hf + ref width, forced odd
+    int row_pitch;           // floats per staged row: o_hf + ref width (+ up to 3 floats of alignment shift), = 4 mod 32
     int n_pose;              // poses per env: S + 2
     int n_slots;             // FK transforms a thread keeps: max over parts of bodies with children inside the part
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
@@ -112,7 +119,15 @@ inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_con
     SmemPlan p;
     const int J = cm.num_bodies, D = cm.dof_size;
     const RefLayout R = make_ref_layout(J, D, C);
+#if PARC_VEC_ROWS
+    // A row starts at a multiple of 4 floats plus the env's shift (0..3), so that column k of the staged row and of the
+    // obs_buf row have the same 16-byte phase. Pitch = 4 (mod 32): the 8 envs a warp touches at one column land in
+    // banks 4 el + shift -- all different.
+    p.row_pitch = (L.o_hf + R.width + 3 + 3) & ~3;
+    while ((p.row_pitch & 31) != 4) p.row_pitch += 4;
+#else
     p.row_pitch = (L.o_hf + R.width) | 1;
+#endif
     p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
     p.n_slots = n_slots;
     p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
@@ -418,6 +433,60 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
     // A.3 per-env uniforms: the first lanes of the LAST warp, so that the dependent loads (env id -> motion id -> clip
     //     meta) overlap the dof -> quaternion work of the leading warps
+#if PARC_SPLIT_A
+    // two chains in two otherwise idle warps: root state -> heading -> sin/cos/h^-1 (last warp), and time -> motion id ->
+    // clip meta -> terrain offset (the warp before it); each writes its own fields of s_env[el]
+    if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
+        const int el = tid - (THREADS - 32);
+        EnvU& u = s_env[el];
+        const int live = el < tile_rows;
+        const long long row = row0 + (live ? el : 0);
+        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
+        u.live = live;
+        u.e = e;
+        const Vec3 c_pos = view_ld_vec3(env.char_root_pos, e);
+        const Quat c_rot = view_ld_quat(env.char_root_rot, e);
+        u.c_pos = c_pos; u.c_rot = c_rot;
+        u.c_vel = view_ld_vec3(env.char_root_vel, e);
+        u.c_avel = view_ld_vec3(env.char_root_ang_vel, e);
+        const Vec3 eo = make_vec3(__ldg(env.env_offsets + e * 3), __ldg(env.env_offsets + e * 3 + 1), __ldg(env.env_offsets + e * 3 + 2));
+        u.eo = eo;
+        u.g = c_pos + eo;                                              // ig_parkour_env.py:522
+        const float heading = calc_heading(c_rot);
+        u.sh = sinf(heading); u.ch = cosf(heading);
+        u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
+        u.vel_rec = lib.vel;
+        u.flags = 0;
+#if PARC_VEC_ROWS
+        u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
+#else
+        u.row_shift = 0;
+#endif
+        if (need_char_q) s_charq[el * J] = quat_to_f4(c_rot);
+    } else if (tid >= THREADS - 64 && tid < THREADS - 64 + TILE) {
+        const int el = tid - (THREADS - 64);
+        EnvU& u = s_env[el];
+        const int live = el < tile_rows;
+        const long long row = row0 + (live ? el : 0);
+        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
+        float time;
+        if (parts & PARC_STEP_TIME) {                                   // _update_time, ig_env.py:391-394
+            const int ts = env.timestep_buf[e] + 1;
+            time = __fmul_rn(cfg.timestep, (float)ts);
+            if (live) { env.timestep_buf[e] = ts; env.time_buf[e] = time; }
+        } else {
+            time = env.time_buf[e];
+        }
+        u.time = time;
+        const long long mid = env.motion_ids[e];
+        u.mid = mid;
+        const long long tidx = env.motion_terrain_ids[e];
+        u.mm = load_motion_meta(lib.meta, mid);
+        u.t0 = __fadd_rn(time, env.motion_time_offsets[e]);            // dm_env.py:547-552
+        const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
+        u.tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3)); u.toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
+    }
+#else
     if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
         EnvU u;
         const int el = tid - (THREADS - 32);
@@ -449,9 +518,15 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         u.tox = __fsub_rn(__ldg(dmo), u.eo.x); u.toy = __fsub_rn(__ldg(dmo + 1), u.eo.y);
         u.vel_rec = lib.vel;
         u.flags = 0;
+#if PARC_VEC_ROWS
+        u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
+#else
+        u.row_shift = 0;
+#endif
         s_env[el] = u;
         if (need_char_q) s_charq[el * J] = quat_to_f4(u.c_rot);
     }
+#endif
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
         PARC_COLD_LOOP
@@ -540,7 +615,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         const bool wanted = (is_ref && need_ref_pose) || (is_tar && do_obs) || (is_char && do_obs);
         if (!wanted || !s_env[el].live) continue;
         const EnvU& u = s_env[el];
-        float* row = s_row + el * ROWP;
+        float* row = s_row + el * ROWP + u.row_shift;
         float* rsec = row + L.o_hf;                    // ref_* section
         const float *r0 = nullptr, *r1 = nullptr;
         float b = 0.f, omb = 1.f;
@@ -734,7 +809,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 if (it >= TILE * (J - 1)) continue;
                 const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
                 if (el >= tile_rows) continue;
-                float* rsec = s_row + el * ROWP + L.o_hf;
+                float* rsec = s_row + el * ROWP + s_env[el].row_shift + L.o_hf;
                 const float* jr = rsec + R.joint_rot + 4 * (j - 1);
                 const Quat q = make_quat(jr[0], jr[1], jr[2], jr[3]);
                 if (do_ref) {
@@ -776,7 +851,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 if (do_reward && cfg.use_contact_info) {
                     // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
                     const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
-                    const float rc = s_row[el * ROWP + L.o_hf + R.contacts + c];
+                    const float rc = s_row[el * ROWP + u.row_shift + L.o_hf + R.contacts + c];
                     float cr = -(1.0f - rc) * f;
                     cr += rc * f;
                     s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
@@ -801,7 +876,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 if (el >= tile_rows) continue;
                 const EnvU& u = s_env[el];
                 const int body = cfg.key_body_ids[k];
-                const float* rsec = s_row + el * ROWP + L.o_hf;
+                const float* rsec = s_row + el * ROWP + u.row_shift + L.o_hf;
                 const float* bp = rsec + R.body_pos;
                 const Vec3 ref_rpos = make_vec3(bp[0], bp[1], bp[2]);
                 Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
@@ -821,7 +896,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 const int el = it / D, k = it - el * D;
                 if (el >= tile_rows) continue;
                 const EnvU& u = s_env[el];
-                const float dv = s_row[el * ROWP + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
+                const float dv = s_row[el * ROWP + u.row_shift + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
                 s_terms[el * TP + o_vel_t + k] = cfg.dof_err_w[k] * dv * dv;
             }
         }
@@ -833,7 +908,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         const int el = tid;
         const EnvU& u = s_env[el];
         const long long e = u.e;
-        const float* rsec = s_row + el * ROWP + L.o_hf;
+        const float* rsec = s_row + el * ROWP + u.row_shift + L.o_hf;
         const Vec3 ref_rpos = make_vec3(rsec[R.root_pos], rsec[R.root_pos + 1], rsec[R.root_pos + 2]);
         const Quat ref_rrot = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
         if (do_reward) {
@@ -927,11 +1002,22 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         const int warp = tid >> 5, lane = tid & 31;
         for (int el = warp; el < tile_rows; el += THREADS / 32) {
             const EnvU& u = s_env[el];
-            const float* row = s_row + el * ROWP;
+            const float* row = s_row + el * ROWP + u.row_shift;
             if (do_obs) {
                 float* g = env.obs_buf + u.e * env.obs_row_stride;
+#if PARC_VEC_ROWS
+                // column k is 16-byte aligned in both the staged row and the obs_buf row when (row_shift + k) % 4 == 0
+                const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
+                if (lane < head) g[lane] = row[lane];
+                const float4* r4 = reinterpret_cast<const float4*>(row + head);
+                float4* g4 = reinterpret_cast<float4*>(g + head);
+#pragma unroll 2
+                for (int k = lane; k < nvec; k += 32) g4[k] = r4[k];
+                if (t0 + lane < n) g[t0 + lane] = row[t0 + lane];
+#else
 #pragma unroll 4
                 for (int k = lane; k < L.o_hf; k += 32) g[k] = row[k];
+#endif
             }
             if (do_ref) {
                 const float* rsec = row + L.o_hf;
