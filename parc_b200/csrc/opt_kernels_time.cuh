@@ -254,7 +254,7 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
     if (rc) return rc;
     const size_t pg_bytes = need_grad ? sizeof(float) * 7 * (size_t)cfg->num_points : 0;
     PARC_REQUIRE(pg_bytes <= 32 * 1024, "motion_loss: more than 1,170 body sample points");
-    opt_sdf_kernel<<<(unsigned)n, 320, pg_bytes, st>>>(*m, *cfg, T, contacts, body_points, ter, ws, need_grad ? 1 : 0);
+    opt_sdf_kernel<<<(unsigned)n, OPT_SDF_THREADS, pg_bytes, st>>>(*m, *cfg, T, contacts, body_points, ter, ws, need_grad ? 1 : 0);
     if ((rc = check_launch("motion_loss (sdf)"))) return rc;
     PARC_OPT_G(opt_temporal_kernel, *m, *cfg, n, T, src_body_vels, src_body_rot_vels, contacts, ws, need_grad ? 1 : 0);
     if ((rc = check_launch("motion_loss (temporal)"))) return rc;
@@ -344,7 +344,7 @@ extern "C" int parc_b200_path_motion_loss(const parc_char_model_t* m, const parc
     path_loss_window_kernel<<<(unsigned)std::min<long long>((n * OPT_FT + 255) / 256, (long long)kNumSMs * 8), 256, 0, st>>>(n, B, X, Y, ws);
     int rc = check_launch("path_motion_loss (window)");
     if (rc) return rc;
-    opt_sdf_kernel<<<(unsigned)n, 320, 0, st>>>(*m, c, T, contacts, body_points, ter, ws, 0);
+    opt_sdf_kernel<<<(unsigned)n, OPT_SDF_THREADS, 0, st>>>(*m, c, T, contacts, body_points, ter, ws, 0);
     if ((rc = check_launch("path_motion_loss (sdf)"))) return rc;
     path_loss_reduce_kernel<<<(unsigned)B, 128, 0, st>>>(T, w_pen, w_contact, ws, pen_loss, contact_loss, total_loss);
     return check_launch("path_motion_loss (reduce)");
