@@ -275,9 +275,8 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS) opt_sdf_kernel(const __grid_c
     // contact term and its gradient: the closest point of each contact body
     float con_sum = 0.f;
     if (want_contact) {
-        // one body per warp (lane 0), so that the bodies' gradient scans run side by side
-        for (int body = tid >> 5; body < J; body += blockDim.x >> 5) {
-            if (tid & 31) continue;
+        // one thread per body: the bodies' gradient scans run side by side in the lanes of one warp
+        for (int body = tid; body < J; body += blockDim.x) {
             if (s_cw[body] == 0.f || s_key[body] == ~0ull) continue;
             const float d = __uint_as_float((unsigned)(s_key[body] >> 32));
             const float cw = s_cw[body];
