@@ -229,6 +229,7 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
     const int J = m->num_bodies;
     PARC_REQUIRE(J >= 1 && J <= PARC_MAX_BODIES, "motion_loss: bad body count");
     PARC_REQUIRE(cfg->num_points > 0 && cfg->point_start[0] == 0 && cfg->point_start[J] == cfg->num_points, "motion_loss: bad point table");
+    PARC_REQUIRE(cfg->num_points <= 1184, "motion_loss: %d body sample points (at most 1,184 supported)", cfg->num_points);
     PARC_REQUIRE(X > 0 && Y > 0 && dx > 0.f && dy > 0.f, "motion_loss: bad terrain");
     const bool need_grad = g_root_pos || g_root_rot || g_joint_dof;
     PARC_REQUIRE(!need_grad || (g_root_pos && g_root_rot && g_joint_dof), "motion_loss: pass all three gradient outputs or none");
