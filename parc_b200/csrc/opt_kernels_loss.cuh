@@ -165,7 +165,10 @@ constexpr int OPT_MAX_PATCH = 1024;
 #define PARC_OPT_SDF_THREADS 96
 #endif
 constexpr int OPT_SDF_THREADS = PARC_OPT_SDF_THREADS;   // threads of the block that owns a frame; each takes ceil(Np / threads) sample points
-__global__ void __launch_bounds__(OPT_SDF_THREADS) opt_sdf_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
+#ifndef PARC_OPT_SDF_MINB
+#define PARC_OPT_SDF_MINB 12
+#endif
+__global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
                                                       long long T, const float* __restrict__ contacts, const float* __restrict__ body_points,
                                                       OptTerrain ter, OptWs ws, int need_grad) {
     __shared__ float s_h[OPT_MAX_PATCH];
