@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--motions", type=int, default=NUM_MOTIONS)
     ap.add_argument("--cpu-envs", type=int, default=CPU_SAMPLE_ENVS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--chunks", type=int, default=8, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
+    ap.add_argument("--chunks", type=int, default=6, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
     return ap.parse_args()
 
 

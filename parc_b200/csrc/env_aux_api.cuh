@@ -273,10 +273,16 @@ extern "C" int parc_b200_env_step_host(const parc_char_model_t* m, const parc_mo
     // the previous step's kernels (enqueued on `stream`) must be done reading the state before it is overwritten
     cudaEventRecord(pipe->free_to_overwrite, cs);
     cudaStreamWaitEvent(pipe->copy, pipe->free_to_overwrite, 0);
-    // chunk boundaries on multiples of 8 envs (the step kernel's tile)
-    const long long tiles = (N + 7) / 8;
+    // Range boundaries on multiples of 16 envs (the step kernel's tile). The ranges shrink geometrically (x 0.8): what is
+    // left after the last upload has landed is the step of the LAST range only, so that one should be small, while a
+    // larger first range costs nothing (its step overlaps the following uploads, and the step is faster per env than PCIe).
+    const long long tiles = (N + 15) / 16;
+    double cum[kMaxHostChunks + 1];
+    cum[0] = 0.0;
+    for (int c = 0; c < num_chunks; ++c) cum[c + 1] = cum[c] + pow(0.8, (double)c);
     for (int c = 0; c < num_chunks; ++c) {
-        const long long a = std::min(N, tiles * c / num_chunks * 8), b = std::min(N, tiles * (c + 1) / num_chunks * 8);
+        const long long a = std::min(N, (long long)(tiles * (cum[c] / cum[num_chunks])) * 16);
+        const long long b = c + 1 == num_chunks ? N : std::min(N, (long long)(tiles * (cum[c + 1] / cum[num_chunks])) * 16);
         if (b <= a) continue;
         for (int k = 0; k < num_uploads; ++k) {
             const long long rb = uploads[k].row_bytes;

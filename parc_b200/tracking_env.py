@@ -467,7 +467,7 @@ class TrackingEnv:
         for k, v in self.sim_state_tensors().items():
             v.copy_(host_state[k], non_blocking=True)
 
-    def post_physics_step_host(self, host_state, num_chunks=8, standin_noise=None, parts=_lib.STEP_ALL, update_fail_rates=True):
+    def post_physics_step_host(self, host_state, num_chunks=6, standin_noise=None, parts=_lib.STEP_ALL, update_fail_rates=True):
         """post_physics_step for simulator state that lives in pinned HOST memory (make_host_state):
         parc_b200_env_step_host uploads the envs in `num_chunks` row ranges on a copy stream and runs
         the fused step on each range as soon as its rows have arrived, so the PCIe transfer overlaps
@@ -490,7 +490,7 @@ class TrackingEnv:
                                                  _lib.ptr(self._ema_scratch), self._stream()))
         self._step_count += 1
 
-    def step_host(self, host_state, host_results, num_chunks=8, standin_noise=None):
+    def step_host(self, host_state, host_results, num_chunks=6, standin_noise=None):
         """One full control step from host buffers to host buffers: chunked upload + fused step, fail-rate
         EMA, device-side RSI reset, reward/done back to the host (asynchronous: synchronise the current
         stream before reading host_results)."""
