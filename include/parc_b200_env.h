@@ -305,6 +305,13 @@ int parc_b200_sim_standin(const parc_char_model_t* h_model, const parc_env_buffe
  * joint | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16, -1 past the end of a list. */
 int parc_b200_tree_parts(const parc_char_model_t* h_model, int32_t* entries, int32_t* max_len, int32_t* num_slots);
 
+/* Self-test: the packed fp32x2 cell computation of the fused step against the scalar, separately rounded one
+ * (rotate_2d_vec + SubTerrain.get_grid_index) for n sample points [n,2] under one heading (c = cos, s = sin) and
+ * root xy (gx, gy): both cell ids (ix * dim_y + iy) are returned and must be equal everywhere. */
+int parc_b200_selftest_cells(const float* pts_xy, int64_t n, float c, float s, float gx, float gy, float min_x,
+                             float min_y, float dx, float dy, int32_t dim_x, int32_t dim_y,
+                             int32_t* cell_packed, int32_t* cell_scalar, void* stream);
+
 /* Self-test of the heightmap index arithmetic: the fused step divides by the (uniform) cell size
  * with q = x*rc; r = fma(-q, d, x); q' = fma(r, rc, q), rc = RN(1/d), instead of div.rn. This entry
  * evaluates both on x [n] so that a test can demand bit-identical quotients (the nearest-cell

@@ -233,6 +233,7 @@ def _declare(lib):
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
+        "parc_b200_selftest_cells": [vp, i64, f32, f32, f32, f32, f32, f32, f32, f32, i32, i32, vp, vp, vp],
         "parc_b200_record_agent_states": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),
                                           P(RecordTapeStruct), i32, i32, f64, vp],
         "parc_b200_hf_mask_inds": [P(CharModelStruct), P(TerrainStruct), vp, vp, i64, vp, vp, i32, vp, vp, vp, vp, vp],

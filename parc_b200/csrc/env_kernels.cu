@@ -335,6 +335,27 @@ __device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float
     return (int)u;
 }
 
+// Grid cell of one ray sample point: rotate_2d_vec + root xy, (px c - py s + gx, px s + py c + gy), then
+// clamp(round_half_even((w - min) / dxdy), 0, dim - 1) (terrain_util.py:139-152). The sums and the Markstein division
+// (div_const) are packed fp32x2 (FADD2 / FMUL2 / FFMA2, sm_100): x and y of the point share those instructions.
+// Every product and sum must be rounded on its own, as torch's separate mul / sub / add are. ptxas (CUDA 12.9)
+// contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 despite the .rn (seen in the SASS; an FFMA2 with a -0 addend is
+// folded back and contracted too), so the four products are scalar mul.rn -- which it does leave alone -- and only
+// the sums and the division are packed. parc_b200_selftest_cells checks the result against the scalar path on the GPU.
+__device__ __forceinline__ int packed_cell(float2 pt, float2 cs, float2 nsc, float2 g2, float2 nmn, float2 rd2, float2 nd2, int imx, int imy,
+                                           int dimy) {
+    const float2 a = make_float2(__fmul_rn(pt.x, cs.x), __fmul_rn(pt.x, cs.y));
+    const float2 b = make_float2(__fmul_rn(pt.y, nsc.x), __fmul_rn(pt.y, nsc.y));
+    const float2 w = __fadd2_rn(__fadd2_rn(a, b), g2);
+    const float2 x = __fadd2_rn(w, nmn);
+    float2 q = __fmul2_rn(x, rd2);
+    const float2 r = __ffma2_rn(q, nd2, x);
+    q = __ffma2_rn(r, rd2, q);
+    const int ix = max(0, min(__float2int_rn(q.x), imx));
+    const int iy = max(0, min(__float2int_rn(q.y), imy));
+    return ix * dimy + iy;
+}
+
 // One env's heightmap samples by one warp (_refresh_obs_hfs, ig_parkour_env.py:518-533; get_hf_val, terrain_util.py:139-156).
 // Points come from shared memory, four per lane and iteration so that four independent gathers are in flight; the two
 // destination rows (either may be absent) are running pointers with immediate offsets. FULL: P is a multiple of 128
@@ -356,18 +377,7 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
         for (int k = 0; k < U; ++k) pt[k] = (FULL || p + 32 * k < P) ? sp[32 * k] : make_float2(0.f, 0.f);
 #pragma unroll
         for (int k = 0; k < U; ++k) {
-            // rotate_2d_vec + root xy: (px c - py s + gx, px s + py c + gy); packed fp32x2 (FMUL2 / FADD2 / FFMA2, sm_100):
-            // x and y of a sample point share every instruction
-            const float2 w = __fadd2_rn(__fadd2_rn(__fmul2_rn(make_float2(pt[k].x, pt[k].x), cs), __fmul2_rn(make_float2(pt[k].y, pt[k].y), nsc)), g2);
-            // (w - min) / dxdy: Markstein division by the uniform cell size
-            const float2 x = __fadd2_rn(w, nmn);
-            float2 q = __fmul2_rn(x, rd2);
-            const float2 r = __ffma2_rn(q, nd2, x);
-            q = __ffma2_rn(r, rd2, q);
-            // round half to even, clamp to the grid (terrain_util.py:139-152)
-            const int ix = max(0, min(__float2int_rn(q.x), imx));
-            const int iy = max(0, min(__float2int_rn(q.y), imy));
-            cell[k] = ix * dimy + iy;
+            cell[k] = packed_cell(pt[k], cs, nsc, g2, nmn, rd2, nd2, imx, imy, dimy);
         }
 #pragma unroll
         for (int k = 0; k < U; ++k) v[k] = __ldg(hf + cell[k]);
@@ -1044,6 +1054,31 @@ __global__ void selftest_div_kernel(const float* __restrict__ x, long long n, fl
 }  // namespace parc
 
 using namespace parc;
+
+namespace parc {
+// packed_cell against the scalar, separately rounded ray_world + grid_index for n points of one (heading, root) pair
+__global__ void selftest_cells_kernel(const float2* __restrict__ pts, long long n, float c, float s, float gx, float gy, float mnx, float mny,
+                                      float dx, float dy, int dimx, int dimy, int* __restrict__ cell_packed, int* __restrict__ cell_scalar) {
+    const float2 cs = make_float2(c, s), nsc = make_float2(-s, c), g2 = make_float2(gx, gy), nmn = make_float2(-mnx, -mny);
+    const float2 rd2 = make_float2(__frcp_rn(dx), __frcp_rn(dy)), nd2 = make_float2(-dx, -dy);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float2 pt = pts[i];
+        cell_packed[i] = packed_cell(pt, cs, nsc, g2, nmn, rd2, nd2, dimx - 1, dimy - 1, dimy);
+        float wx, wy;
+        ray_world(pt.x, pt.y, c, s, gx, gy, wx, wy);
+        cell_scalar[i] = grid_index(wx, mnx, dx, dimx) * dimy + grid_index(wy, mny, dy, dimy);
+    }
+}
+}  // namespace parc
+
+extern "C" int parc_b200_selftest_cells(const float* pts_xy, int64_t n, float c, float s, float gx, float gy, float min_x, float min_y,
+                                        float dx, float dy, int32_t dim_x, int32_t dim_y, int32_t* cell_packed, int32_t* cell_scalar, void* stream) {
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(pts_xy && cell_packed && cell_scalar && dim_x > 0 && dim_y > 0, "selftest_cells: bad arguments");
+    selftest_cells_kernel<<<kNumSMs * 8, 256, 0, as_stream(stream)>>>(reinterpret_cast<const float2*>(pts_xy), n, c, s, gx, gy, min_x, min_y, dx, dy,
+                                                                     dim_x, dim_y, cell_packed, cell_scalar);
+    return check_launch("selftest_cells");
+}
 
 extern "C" int parc_b200_selftest_div(const float* x, int64_t n, float d, float* q_fast, float* q_ieee, void* stream) {
     if (n == 0) return PARC_OK;

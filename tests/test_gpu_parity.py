@@ -159,6 +159,35 @@ def test_cell_index_division_is_correctly_rounded():
         assert torch.equal(qi.cpu(), x.cpu() / torch.tensor(d, dtype=torch.float32))
 
 
+def test_packed_cell_arithmetic_equals_the_separately_rounded_one():
+    """The fused step computes the grid cell of a ray sample point with packed fp32x2 instructions; every product and sum
+    must still be rounded on its own (torch's mul / sub / add), or points next to a cell boundary land in the wrong
+    cell. ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2, which this test guards against; 16 M points per
+    setting, a third of them placed within a few ulps of a cell boundary."""
+    from parc_b200 import _lib
+    g = torch.Generator().manual_seed(12)
+    n = 1 << 24
+    dev = torch.device(DEV)
+    for dx, dim, heading in ((0.4, 1088, 0.7), (0.4, 1088, -2.4), (0.25, 64, 1.3), (0.1, 500, 3.0)):
+        c, s = float(torch.cos(torch.tensor(heading))), float(torch.sin(torch.tensor(heading)))
+        mn = -0.5 * dx * dim
+        gx, gy = float(torch.rand(1, generator=g)) * 100.0 - 50.0, float(torch.rand(1, generator=g)) * 100.0 - 50.0
+        pts = torch.rand(n, 2, generator=g) * 8.0 - 4.0
+        # world points on cell boundaries, pulled back into the local frame (rounding puts them a few ulps off either way)
+        k = n // 3
+        bx = (torch.randint(0, dim, (k,), generator=g).float() + 0.5) * dx + mn
+        by = (torch.randint(0, dim, (k,), generator=g).float() + 0.5) * dx + mn
+        lx, ly = bx - gx, by - gy
+        pts[:k, 0] = lx * c + ly * s
+        pts[:k, 1] = -lx * s + ly * c
+        pts = pts.to(dev).contiguous()
+        a = torch.empty(n, dtype=torch.int32, device=dev)
+        b = torch.empty(n, dtype=torch.int32, device=dev)
+        _lib.check(_lib.lib().parc_b200_selftest_cells(_lib.ptr(pts), n, c, s, gx, gy, mn, mn, dx, dx, dim, dim, _lib.ptr(a), _lib.ptr(b),
+                                                       _lib.stream_ptr(dev)))
+        assert torch.equal(a, b), "dx=%g: %d of %d cells differ" % (dx, int((a != b).sum()), n)
+
+
 # ------------------------------------------------------------------------------------- fused env step
 def _golden_env(model):
     from parc_b200.tracking_env import TrackingEnv, default_env_config
