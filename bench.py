@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--motions", type=int, default=NUM_MOTIONS)
     ap.add_argument("--cpu-envs", type=int, default=CPU_SAMPLE_ENVS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fail-fraction", type=float, default=0.02,
+                    help="share of the envs the simulator stand-in pushes off their reference every step (they terminate and are "
+                         "reset): 0.02 is the stationary BASELINE configs[1] workload, 0.1 with --envs 262144 is configs[4] (reset-heavy)")
     ap.add_argument("--chunks", type=int, default=6, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
     return ap.parse_args()
 
@@ -176,7 +179,7 @@ LAUNCHES_PER_STEP = 6   # device-resident loop: sim_standin, env_step, fail_rate
 # CPU leg: the oracle port (oracle/parc_oracle.py) on the host cores -- checker code used as the
 # reported baseline only, never on the product path
 # ------------------------------------------------------------------------------------------------
-def run_cpu_port(world, num_envs, steps, warmup, threads):
+def run_cpu_port(world, num_envs, steps, warmup, threads, fail_fraction=0.02):
     from oracle import parc_oracle as O
     from parc_b200 import synth
     from parc_b200.tracking_env import default_env_config
@@ -203,7 +206,7 @@ def run_cpu_port(world, num_envs, steps, warmup, threads):
     env.char_dof_pos[:], env.char_dof_vel[:] = sim["dof_pos"], sim["dof_vel"]
     env.char_rigid_body_pos[:], env.char_contact_forces[:] = sim["body_pos"], sim["contact_forces"]
 
-    noise = synth.standin_noise(N, m.J, m.D, seed=5678)
+    noise = synth.standin_noise(N, m.J, m.D, seed=5678, fail_fraction=fail_fraction)
     resets = []
 
     def one_step(i):
@@ -230,7 +233,7 @@ def run_cpu_port(world, num_envs, steps, warmup, threads):
 
 def cpu_baseline_block(world, args, steps, warmup):
     cores = os.cpu_count() or 1
-    r = run_cpu_port(world, args.cpu_envs, steps, warmup, cores)
+    r = run_cpu_port(world, args.cpu_envs, steps, warmup, cores, args.fail_fraction)
     return {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d envs x %d steps (+%d warm-up) of the same %d-clip / 32x32-heightmap workload, torch CPU eager, "
                       "%d threads; median %.3f s/step, min %.3f s/step; %.1f resets/step"
@@ -284,7 +287,7 @@ def run_gpu_arm(args):
     init_gpu_state(env, rank * N)
     step_bytes, b_env = algorithmic_bytes(env)
     from parc_b200 import synth
-    noise = synth.standin_noise(N, env._J, env._D, seed=5678 + rank * N).to(dev)   # simulator stand-in
+    noise = synth.standin_noise(N, env._J, env._D, seed=5678 + rank * N, fail_fraction=args.fail_fraction).to(dev)   # simulator stand-in
 
     def barrier():
         if distributed:
@@ -407,7 +410,8 @@ def run_gpu_arm(args):
                                    "observations (BASELINE configs[1]); step = simulator stand-in (char := ref + fixed noise, FK) + post-physics "
                                    "pass + fail-rate EMA + device-side RSI reset + obs refresh of the reset envs",
                        "envs_per_gpu": N, "clips": args.motions, "frames": int(env._mlib._frame_root_pos.shape[0]),
-                       "ray_points": int(env._ray_xy_points.shape[0]), "resets_per_step": done_per_step, "obs_dim": env.get_obs_dim(),
+                       "ray_points": int(env._ray_xy_points.shape[0]), "resets_per_step": done_per_step,
+                       "standin_fail_fraction": args.fail_fraction, "obs_dim": env.get_obs_dim(),
                        "terrain_cells": list(env._terrain.hf.shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,
                        "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (step_bytes / 1e9)},
             "clocks": clocks,
