@@ -32,6 +32,9 @@
 #ifndef PARC_EXP_HU
 #define PARC_EXP_HU 2
 #endif
+#ifndef PARC_HEIGHTS_LATE
+#define PARC_HEIGHTS_LATE 1   // 1: height samples after phases C/D (nothing waits for them at a barrier; they cover phase D)
+#endif
 #ifndef PARC_SPLIT_A
 #define PARC_SPLIT_A 1      // 1: phase A uniforms as two dependent-load chains in two warps
 #endif
@@ -594,6 +597,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
     // ================================ phase B ====================================================
     static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART tree parts");
     const bool pose_work = do_obs || need_ref_pose;
+#if !PARC_HEIGHTS_LATE
     if (P > 0 && (do_heights || do_obs)) {
         // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
         // warp w samples the points of env w; runs BEFORE the pose work so that the frame records requested above
@@ -617,6 +621,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
             }
         }
     }
+#endif
     // ---- B.2 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
     //      walks its own ancestor-closed part of the joint tree, so all lanes of a warp run the same code ----
     for (int pose = (tid >> 5) & 7; pose_work && pose < plan.n_pose; pose += 8) {
@@ -1006,6 +1011,33 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         }
     }
 
+#if PARC_HEIGHTS_LATE
+    // heights after the reward / termination phases: nothing waits for them at a barrier, and they fill the issue slots
+    // while the 16 lanes of phase D run their serial sums
+    if (P > 0 && (do_heights || do_obs)) {
+        // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) ----
+        // warp w samples the points of env w; runs BEFORE the pose work so that the frame records requested above
+        // arrive meanwhile. Four points per lane and iteration keep four independent gathers in flight.
+        const int lane = tid & 31;
+        const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
+        const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1, dimy = terrain.dim_y;
+        const float lo = cfg.min_obs_h, hi = cfg.max_obs_h;
+        for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
+            const EnvU& u = s_env[el];
+            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
+            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
+            if (do_heights) {
+                const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
+                if (P % (32 * PARC_EXP_HU) == 0)
+                    heights_of_env<true>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
+                else
+                    heights_of_env<false>(s_pts, P, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
+            } else if (orow) {
+                for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
+            }
+        }
+    }
+#endif
     // ================================ phase E ====================================================
     // staged rows -> global: warp w streams env w; consecutive lanes write consecutive columns
     {
