@@ -32,9 +32,6 @@
 #ifndef PARC_EXP_HU
 #define PARC_EXP_HU 2
 #endif
-#ifndef PARC_HEIGHTS_SPLIT
-#define PARC_HEIGHTS_SPLIT 0
-#endif
 #ifndef PARC_HEIGHTS_LATE
 #define PARC_HEIGHTS_LATE 1   // 1: height samples after phases C/D (nothing waits for them at a barrier; they cover phase D)
 #endif
@@ -436,10 +433,6 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
     const bool need_char_q = do_obs || do_reward;
     const int tile_rows = (int)min((long long)TILE, n_rows - row0);
 
-#if PARC_HEIGHTS_LATE && PARC_HEIGHTS_SPLIT
-    __shared__ unsigned long long s_mbar;
-    if (tid == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_mbar)), "r"(THREADS) : "memory");
-#endif
     // ================================ phase A ====================================================
     PARC_COLD_LOOP
     for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_part[k] = sp.part_entry[k / PARC_MAX_BODIES][k % PARC_MAX_BODIES];
@@ -605,7 +598,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
     static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART tree parts");
     const bool pose_work = do_obs || need_ref_pose;
     // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) for the sample points [p0, p1):
-    //      warp w samples the points of env w. Where this runs is a scheduling choice (PARC_HEIGHTS_LATE / _SPLIT): the
+    //      warp w samples the points of env w. Where this runs is a scheduling choice (PARC_HEIGHTS_LATE): the
     //      samples depend only on the phase A uniforms and write straight to global memory.
     auto sample_heights = [&](const int p0, const int p1) {
         if (!(P > 0 && (do_heights || do_obs)) || p1 <= p0) return;
@@ -628,11 +621,6 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
             }
         }
     };
-#if PARC_HEIGHTS_SPLIT
-    const int P_gap = (P / 2) & ~(32 * PARC_EXP_HU - 1);     // sampled between the end of a warp's pose work and phase C
-#else
-    const int P_gap = 0;
-#endif
 #if !PARC_HEIGHTS_LATE
     sample_heights(0, P);
 #endif
@@ -791,21 +779,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                     kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                 }
     }
-#if PARC_HEIGHTS_LATE && PARC_HEIGHTS_SPLIT
-    {
-        // split-phase barrier: a warp that has finished its pose announces it, samples the first half of its env's heights
-        // while the slower poses finish, and only then waits for the rows of all poses
-        const unsigned mb = (unsigned)__cvta_generic_to_shared(&s_mbar);
-        unsigned long long token;
-        asm volatile("mbarrier.arrive.shared::cta.b64 %0, [%1];" : "=l"(token) : "r"(mb) : "memory");
-        sample_heights(0, P_gap);
-        unsigned done = 0;
-        while (!done)
-            asm volatile("{ .reg .pred p; mbarrier.try_wait.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mb), "l"(token) : "memory");
-    }
-#else
     __syncthreads();
-#endif
 
     // ================================ phase C ====================================================
     // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
@@ -1042,7 +1016,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
 #if PARC_HEIGHTS_LATE
     // heights after the reward / termination phases: nothing waits for them at a barrier, and they fill the issue slots
     // while the 16 lanes of phase D run their serial sums
-    sample_heights(P_gap, P);
+    sample_heights(0, P);
 #endif
     // ================================ phase E ====================================================
     // staged rows -> global: warp w streams env w; consecutive lanes write consecutive columns
