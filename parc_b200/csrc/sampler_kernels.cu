@@ -88,7 +88,13 @@ __global__ void __launch_bounds__(256) mdm_canon_hf_kernel(
 }
 
 template <int G>
-__global__ void __launch_bounds__(256) mdm_frames_kernel(
+#ifndef PARC_MDM_THREADS
+#define PARC_MDM_THREADS 128
+#endif
+#ifndef PARC_MDM_MINB
+#define PARC_MDM_MINB 8
+#endif
+__global__ void __launch_bounds__(PARC_MDM_THREADS, PARC_MDM_MINB) mdm_frames_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_sampler_config_t cfg, const long long* __restrict__ motion_ids, const float* __restrict__ start_times,
     const long long n, const float* __restrict__ motion_times, const float* __restrict__ canon, const int floor_shift,
@@ -166,15 +172,15 @@ extern "C" int parc_b200_mdm_sample_motion_data(const parc_char_model_t* m, cons
     if (rc) return rc;
     if (root_pos || root_rot || joint_pos || joint_rot || contacts) {
         const int G = m->num_bodies <= 16 ? 16 : 32;
-        const long long groups = n * cfg->seq_len, gpb = 256 / G;
+        const long long groups = n * cfg->seq_len, gpb = PARC_MDM_THREADS / G;
         const unsigned blocks = (unsigned)std::min<long long>((groups + gpb - 1) / gpb, kNumSMs * 32);
         const int floor_shift = hfs != nullptr && cfg->relative_z_style == PARC_RELATIVE_TO_ROOT_FLOOR;
         if (G == 16)
-            mdm_frames_kernel<16><<<blocks, 256, 0, as_stream(stream)>>>(*m, *lib, *cfg, (const long long*)motion_ids, start_times, n,
+            mdm_frames_kernel<16><<<blocks, PARC_MDM_THREADS, 0, as_stream(stream)>>>(*m, *lib, *cfg, (const long long*)motion_ids, start_times, n,
                                                                         motion_times, canon, floor_shift, root_pos, root_rot, joint_pos,
                                                                         joint_rot, contacts);
         else
-            mdm_frames_kernel<32><<<blocks, 256, 0, as_stream(stream)>>>(*m, *lib, *cfg, (const long long*)motion_ids, start_times, n,
+            mdm_frames_kernel<32><<<blocks, PARC_MDM_THREADS, 0, as_stream(stream)>>>(*m, *lib, *cfg, (const long long*)motion_ids, start_times, n,
                                                                         motion_times, canon, floor_shift, root_pos, root_rot, joint_pos,
                                                                         joint_rot, contacts);
         rc = check_launch("mdm_frames");
