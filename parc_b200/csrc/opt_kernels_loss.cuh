@@ -1,6 +1,10 @@
 // Included by opt_kernels.cu: the motion-loss kernels and the C ABI of include/parc_b200_opt.h.
 #pragma once
 
+#ifndef PARC_OPT_LANES_MINB
+#define PARC_OPT_LANES_MINB 4
+#endif
+
 namespace parc {
 
 constexpr int OPT_FT = 12;   // per-frame scratch terms: the 9 LossType slots (+3 spare)
@@ -43,7 +47,7 @@ struct OptTerrain {
 
 // ---- 1. poses, regulariser terms, FK, heightfield window ---------------------------------------------
 template <int G>
-__global__ void __launch_bounds__(256) opt_pose_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
+__global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_pose_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
                                                        long long n, long long T, const float* __restrict__ tgt_root_pos,
                                                        const float* __restrict__ tgt_root_rot, const float* __restrict__ tgt_joint_dof,
                                                        const float* __restrict__ src_root_pos, const float* __restrict__ src_root_rot,

@@ -7,7 +7,7 @@ namespace parc {
 // Lane = body j of frame t. The lane owns velocity index t (t <= T-2) and jerk index t (t <= T-4) for the
 // VALUES, and gathers every contribution to d loss / d body_pos[t,j], d loss / d body_rot[t,j].
 template <int G>
-__global__ void __launch_bounds__(256) opt_temporal_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
+__global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
                                                            long long n, long long T, const float* __restrict__ src_body_vels,
                                                            const float* __restrict__ src_body_rot_vels, const float* __restrict__ contacts,
                                                            OptWs ws, int need_grad) {
