@@ -205,10 +205,10 @@ extern "C" int parc_b200_sample_motions_cdf(const float* cdf, int32_t num_motion
 namespace parc {
 int launch_sim_standin(const parc_char_model_t* m, const parc_env_buffers_t* env, const float* noise, long long first_env,
                        long long n_rows, void* stream) {
-    const long long groups_per_block = 256 / (m->num_bodies <= 16 ? 16 : 32);
+    const long long groups_per_block = PARC_STANDIN_THREADS / (m->num_bodies <= 16 ? 16 : 32);
     const unsigned blocks = (unsigned)std::min<long long>((n_rows + groups_per_block - 1) / groups_per_block, kNumSMs * 32);
-    if (m->num_bodies <= 16) sim_standin_kernel<16><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
-    else sim_standin_kernel<32><<<blocks, 256, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
+    if (m->num_bodies <= 16) sim_standin_kernel<16><<<blocks, PARC_STANDIN_THREADS, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
+    else sim_standin_kernel<32><<<blocks, PARC_STANDIN_THREADS, 0, as_stream(stream)>>>(*m, *env, noise, first_env, n_rows);
     return check_launch("sim_standin");
 }
 }  // namespace parc

@@ -605,8 +605,14 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
 // ---- simulator stand-in for benchmarks (see parc_b200_sim_standin) -----------------------------------
 // G lanes per env: the lanes first write the root / dof columns (ref + noise), then run dof_to_rot + forward
 // kinematics on that state, in registers, for the rigid body positions the simulator would report.
+#ifndef PARC_STANDIN_THREADS
+#define PARC_STANDIN_THREADS 128
+#endif
+#ifndef PARC_STANDIN_MINB
+#define PARC_STANDIN_MINB 12
+#endif
 template <int G>
-__global__ void __launch_bounds__(256) sim_standin_kernel(const __grid_constant__ parc_char_model_t cm,
+__global__ void __launch_bounds__(PARC_STANDIN_THREADS, PARC_STANDIN_MINB) sim_standin_kernel(const __grid_constant__ parc_char_model_t cm,
                                                           const __grid_constant__ parc_env_buffers_t env,
                                                           const float* __restrict__ noise, const long long first_env,
                                                           const long long n_rows) {
