@@ -24,13 +24,12 @@
 // 32 KB L1.5 instruction cache), so loops that run a handful of iterations per block are kept rolled: nvcc's default
 // 4x unrolling of them cost 5 % of the launch time.
 #define PARC_COLD_LOOP _Pragma("unroll 1")
-#define PARC_COLD_LOOP2 _Pragma("unroll 1")
-#define PARC_COLD_LOOP3 _Pragma("unroll 1")
-#ifndef PARC_EXP_MINB
-#define PARC_EXP_MINB 4
+// Tuning constants, each set by an A/B measurement on a B200:
+#ifndef PARC_STEP_BLOCKS_PER_SM_AT_TILE8
+#define PARC_STEP_BLOCKS_PER_SM_AT_TILE8 4   // launch bound: 4 blocks per SM at 8 envs per block = 2 at 16 (64 registers)
 #endif
-#ifndef PARC_EXP_HU
-#define PARC_EXP_HU 2
+#ifndef PARC_HEIGHT_GATHERS
+#define PARC_HEIGHT_GATHERS 2                 // independent heightfield gathers per lane and loop iteration
 #endif
 #ifndef PARC_HEIGHTS_LATE
 #define PARC_HEIGHTS_LATE 1   // 1: height samples after phases C/D (nothing waits for them at a barrier; they cover phase D)
@@ -44,10 +43,10 @@
 
 namespace parc {
 
-#ifndef PARC_EXP_TILE
-#define PARC_EXP_TILE 16
+#ifndef PARC_STEP_TILE
+#define PARC_STEP_TILE 16                      // envs per block; a multiple of 8
 #endif
-constexpr int TILE = PARC_EXP_TILE;      // envs per block (== warps per block)
+constexpr int TILE = PARC_STEP_TILE;      // envs per block (== warps per block)
 constexpr int STEP_THREADS = 32 * TILE;
 
 // Column layout of one observation row (IGParkourEnv._compute_obs, ig_parkour_env.py:842-965;
@@ -367,7 +366,7 @@ template <bool FULL>
 __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const float* __restrict__ hf, int dimy,
                                                int imx, int imy, float2 cs, float2 nsc, float2 g2, float gz, float2 nmn, float2 rd2,
                                                float2 nd2, float lo, float hi, float* __restrict__ hrow, float* __restrict__ orow) {
-    constexpr int U = PARC_EXP_HU;
+    constexpr int U = PARC_HEIGHT_GATHERS;
     const bool HAS_H = hrow != nullptr, HAS_O = orow != nullptr;   // warp-uniform: predicated stores, one code copy
     const float2* sp = s_pts + lane;
     float* ph = hrow + lane;
@@ -396,7 +395,7 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
 }
 
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) env_step_kernel(
+__global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 / PARC_STEP_TILE) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
@@ -612,7 +611,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
             float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P + p0 : nullptr;
             if (do_heights) {
                 const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-                if (cnt % (32 * PARC_EXP_HU) == 0)
+                if (cnt % (32 * PARC_HEIGHT_GATHERS) == 0)
                     heights_of_env<true>(s_pts + p0, cnt, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
                 else
                     heights_of_env<false>(s_pts + p0, cnt, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
@@ -664,7 +663,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 rsec[R.body_pos] = rpos.x; rsec[R.body_pos + 1] = rpos.y; rsec[R.body_pos + 2] = rpos.z;
             }
             // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
-            PARC_COLD_LOOP2
+            PARC_COLD_LOOP
             for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
                 const float4 x = ldg4(vrec + k);
                 const float xs[4] = {x.x, x.y, x.z, x.w};
@@ -698,11 +697,11 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
                 o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
             }
             o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
-            PARC_COLD_LOOP2
+            PARC_COLD_LOOP
             for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
             if (cfg.use_contact_info) {
                 // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
-                PARC_COLD_LOOP2
+                PARC_COLD_LOOP
                 for (int c = part; c < J; c += NPART) {
                     const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
                                 fz = view_ld3(env.char_contact_forces, u.e, c, 2);
@@ -714,7 +713,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
             float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
             const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
-            PARC_COLD_LOOP2
+            PARC_COLD_LOOP
             for (int c = 4 * part; c < C; c += 4 * NPART) {
                 const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
                 oc[c] = lerp_exact(omb, a.x, b, d.x);
@@ -727,7 +726,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         const bool lrot_ident = sp.lrot_ident != 0;
         float* xf = s_xf + tid;                         // [slot][7][THREADS], this thread's column
         const int* my_part = s_part + part * PARC_MAX_BODIES;
-        PARC_COLD_LOOP3
+        PARC_COLD_LOOP
         for (int i = 0; i < sp.max_part_len; ++i) {
             const int entry = my_part[i];
             if (entry < 0) continue;
@@ -759,7 +758,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
             } else {
                 tan_norm_exact(q, o_pose + 6 * (j - 1));
                 if ((sp.key_mask >> j) & 1u)
-                PARC_COLD_LOOP2
+                PARC_COLD_LOOP
                 for (int k = 0; k < K; ++k) {
                     if (cfg.key_body_ids[k] != j) continue;
                     Vec3 kp = bpos - rpos;
@@ -818,7 +817,7 @@ __global__ void __launch_bounds__(THREADS, PARC_EXP_MINB * 8 / PARC_EXP_TILE) en
         const int nt_d = do_reward ? (TILE * D + 31) >> 5 : 0;
         const int b_c = nt_j, b_k = b_c + nt_c, b_d = b_k + nt_k, n_task = b_d + nt_d;
         const int lane = tid & 31;
-        PARC_COLD_LOOP3
+        PARC_COLD_LOOP
         for (int task = tid >> 5; task < n_task; task += THREADS / 32) {
             if (task < b_c) {
                 // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
