@@ -59,7 +59,11 @@ typedef struct {
  * (PARC/anim/motion_lib.py:374-396) repacked into two 16-byte-aligned frame records so that one
  * pose evaluation reads two ADJACENT records of one array.
  *   interp record (irec floats): quats[J][4] (root rotation first, then the J-1 joints) |
- *                                root_pos[3] | pad | contacts[C] | pad to a multiple of 4
+ *                                root_pos[3] | pad | contacts[C] | pad to even | pair[J][2] | pad to a multiple of 4
+ *                                pair[j] = the blend-independent half of slerp (PARC/util/torch_util.py:474-499) between
+ *                                quaternion j of this frame and of the clip's next frame (of this frame itself on the last
+ *                                one): (acos|c|, sign(c) / sqrt(1 - c^2)), or (-1, w) for the reference's two special cases
+ *                                (|c| >= 1: w = 0, result q0; sin < 0.001: w = +-0.5, the un-normalised midpoint)
  *   vel record (vrec floats):    root_vel[3] | root_ang_vel[3] | dof_vel[D] | pad to multiple of 4
  *   meta record (8 x 4 bytes):   int32 start_idx | int32 num_frames | float length |
  *                                int32 loop_mode | float root_pos_delta[3] | pad */

@@ -56,6 +56,10 @@ typedef struct {
     float ema_keep;                              /* fp32(1.0 - ema_weight) evaluated in double like the Python expression, dm_env.py:654 */
     float min_motion_weight;                     /* dm_env.py:26 */
     float rand_root_pos_offset_scale;            /* mgdm_dm_util.py:174 */
+    /* ray_xy_points as a lattice (geom_util.get_xy_grid_points, PARC/util/geom_util.py:212-224: meshgrid(xs, ys, 'ij')):
+     * point i * ray_grid_ny + j == (xs[i], ys[j]) bit for bit. 0 x 0 = not a lattice (e.g. get_xy_points_cone, :251-272).
+     * Fill with parc_b200_ray_points_lattice; a lattice lets the step share the rotated xs / ys products per row / column. */
+    int32_t ray_grid_nx, ray_grid_ny;
 } parc_env_config_t;
 
 /* All per-env buffers the reference injects through RefCharEnv.get_sim_tensor_views /
@@ -300,10 +304,20 @@ int parc_b200_record_agent_states(const parc_char_model_t* h_model, const parc_m
 int parc_b200_sim_standin(const parc_char_model_t* h_model, const parc_env_buffers_t* h_env, const float* noise,
                           void* stream);
 
-/* Host-side plan of the fused step's forward kinematics (no GPU needed): the joints 1..J-1 are
- * split into 4 ancestor-closed lists, one per cooperating thread. entries [4 * PARC_MAX_BODIES]:
- * joint | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16, -1 past the end of a list. */
-int parc_b200_tree_parts(const parc_char_model_t* h_model, int32_t* entries, int32_t* max_len, int32_t* num_slots);
+/* Host-side plan of the fused step's forward kinematics (no GPU needed): a schedule of the joints 1..J-1 on the 4
+ * lanes that share one (env, pose). entries [4 * PARC_MAX_BODIES]: entries[lane * PARC_MAX_BODIES + it] = what the lane
+ * evaluates in iteration it (-1 = idle): joint | key-slot mask << 8 | parent-from-slot << 16 | read slot << 17 |
+ * publish << 22 | write slot << 23 | has-children << 28. A joint runs in a later iteration than its parent; without the
+ * from-slot bit the parent is what the same lane evaluated in the previous iteration (or the root, if it has not
+ * evaluated anything yet). max_len = iterations, num_slots = shared transform slots per lane group, root_slot = the slot
+ * the root transform is published to before the first iteration (-1: no entry reads the root from a slot). */
+int parc_b200_tree_parts(const parc_char_model_t* h_model, int32_t* entries, int32_t* max_len, int32_t* num_slots,
+                         int32_t* root_slot);
+
+/* Host-side test (no GPU): are the num_points HOST points h_pts_xy [P,2] the lattice meshgrid(xs, ys, 'ij') of
+ * geom_util.get_xy_grid_points (PARC/util/geom_util.py:212-224), i.e. point i * ny + j == (xs[i], ys[j]) exactly?
+ * nx, ny receive the lattice dims, or 0, 0. The values belong in parc_env_config_t.ray_grid_nx / ray_grid_ny. */
+int parc_b200_ray_points_lattice(const float* h_pts_xy, int32_t num_points, int32_t* nx, int32_t* ny);
 
 /* Self-test: the packed fp32x2 cell computation of the fused step against the scalar, separately rounded one
  * (rotate_2d_vec + SubTerrain.get_grid_index) for n sample points [n,2] under one heading (c = cos, s = sin) and

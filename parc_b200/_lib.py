@@ -125,6 +125,8 @@ class EnvConfigStruct(C.Structure):
         ("ema_keep", C.c_float),
         ("min_motion_weight", C.c_float),
         ("rand_root_pos_offset_scale", C.c_float),
+        ("ray_grid_nx", C.c_int32),
+        ("ray_grid_ny", C.c_int32),
     ]
 
 
@@ -242,7 +244,8 @@ def _declare(lib):
         "parc_b200_path_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64, vp, vp, vp, vp, i32, i32, vp, f32, f32, vp,
                                        f32, f32, vp, i64, vp, vp, vp, vp],
         "parc_b200_mdm_sample_motion_data": [P(CharModelStruct), P(MotionLibStruct), vp, P(SamplerConfigStruct), vp, vp, i64] + [vp] * 14,
-        "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32)],
+        "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32), P(i32)],
+        "parc_b200_ray_points_lattice": [P(f32), i32, P(i32), P(i32)],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)   # AttributeError here = header/library mismatch: fail loudly
@@ -281,6 +284,15 @@ def check(rc: int):
     if rc == PARC_ERR_UNSUPPORTED:
         raise NotImplementedError(msg)
     raise ParcB200Error(msg)
+
+
+def ray_points_lattice(ray_xy_points):
+    """(nx, ny) if the [P,2] points are meshgrid(xs, ys, 'ij') bit for bit (geom_util.get_xy_grid_points), else (0, 0)."""
+    import numpy as np
+    pts = np.ascontiguousarray(ray_xy_points.detach().cpu().numpy(), dtype=np.float32).reshape(-1, 2)
+    nx, ny = C.c_int32(), C.c_int32()
+    check(lib().parc_b200_ray_points_lattice(pts.ctypes.data_as(C.POINTER(C.c_float)), int(pts.shape[0]), C.byref(nx), C.byref(ny)))
+    return nx.value, ny.value
 
 
 def stream_ptr(device=None) -> int:

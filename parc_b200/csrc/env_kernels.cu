@@ -1,44 +1,37 @@
 // Fused post-physics step of the DeepMimic-style tracking env:
-//   heights -> time -> reference motion -> observation -> reward -> termination
+//   time -> reference motion -> observation -> reward -> termination -> heights
 // i.e. IGEnv._post_physics_step (PARC/motion_tracker/envs/ig_env.py:368-377) minus PhysX, in ONE
 // launch that reads every input once and writes every output once.
 //
-// Work decomposition (a block owns TILE = 16 consecutive envs, 512 threads = two groups of 8 envs x 8 warps):
-//   A  per-env uniforms (heading, time, clip meta) by 8 lanes; character dof -> quaternion by
-//      one thread per (env, joint)
-//   B  warps 0..1: one thread per (env, pose) -- pose 0 = reference, 1..S = target steps,
-//      S+1 = simulated character -- walks the joint list once: slerp of the two frame records,
-//      forward kinematics against the parent transform kept in shared memory, observation
-//      features straight into the staged row;   warps 2..7 meanwhile: heightmap samples, one
-//      thread per sample point, written straight into the observation rows (coalesced)
-//   C  one thread per (env, joint | dof | body | key body): rot_to_dof, reward / termination terms
-//   D  8 lanes: ordered sums, exponentials, reward, done flag, done-list append
-//   E  all threads: staged rows (observation minus heights, ref_* buffers) -> global, coalesced
-// The v1 kernel (one warp per env, level-by-level FK with warp shuffles) executed 9.8k warp
-// instructions per env and sat at 10 % of the HBM roofline, issue-bound with 22 % of the lanes
-// doing FK work; this layout keeps every lane on its own pose and needs ~2k.
+// Work decomposition (a block owns TILE = 16 consecutive rows, 512 threads = two groups of 8 envs x 8 warps):
+//   A  per-env uniforms (root state, heading, time, clip meta) as two dependent-load chains in the last two warps;
+//      character dof -> quaternion, one thread per (env, joint); plan tables and ray lattice into shared memory
+//   B  warp w evaluates pose (w mod 8) -- 0 = reference, 1..S = target steps, S+1 = simulated character -- for 8 of the
+//      tile's envs; the NPART = 4 lanes of an (env, pose) follow a host-made schedule of the joint tree: every joint is
+//      evaluated once, a lane hands its transform to its next joint in registers, and a transform that another lane (or
+//      a later iteration) needs goes through a shared slot of the 4-lane group. Slerp uses the pair constants packed
+//      with the library (parc_math.cuh: slerp_pair / slerp_pre). Outputs go to the staged observation row or to the
+//      tile's ref_* block in shared memory
+//   C  reward / termination terms, flattened over the tile into warp-sized tasks
+//   D  16 lanes: ordered sums, exponentials, reward, done flag, done-list append -- while
+//   H  all warps sample the heightmaps (straight to global memory); rows are handed out by a shared counter
+//   E  copy-out: cp.async.bulk (TMA) of each staged observation row and of the ref_* blocks, issued right after phase C
+//      so that the copies run under D / H; plain stores for partial tiles, row subsets and strided ref views
 #include "parc_common.cuh"
 #include "parc_lanes.cuh"
 
-// The kernel is instruction-fetch bound (ncu: stall_no_inst is the largest stall class; the SASS is ~110 KB against a
-// 32 KB L1.5 instruction cache), so loops that run a handful of iterations per block are kept rolled: nvcc's default
-// 4x unrolling of them cost 5 % of the launch time.
+// The kernel is instruction-issue / instruction-fetch bound, so loops that run a handful of iterations per block are kept
+// rolled: nvcc's default 4x unrolling of them only adds code.
 #define PARC_COLD_LOOP _Pragma("unroll 1")
 // Tuning constants, each set by an A/B measurement on a B200:
-#ifndef PARC_STEP_BLOCKS_PER_SM_AT_TILE8
-#define PARC_STEP_BLOCKS_PER_SM_AT_TILE8 4   // launch bound: 4 blocks per SM at 8 envs per block = 2 at 16 (64 registers)
-#endif
 #ifndef PARC_HEIGHT_GATHERS
-#define PARC_HEIGHT_GATHERS 2                 // independent heightfield gathers per lane and loop iteration
+#define PARC_HEIGHT_GATHERS 2                 // general ray sets: independent heightfield gathers per lane and loop iteration
 #endif
-#ifndef PARC_HEIGHTS_LATE
-#define PARC_HEIGHTS_LATE 1   // 1: height samples after phases C/D (nothing waits for them at a barrier; they cover phase D)
+#ifndef PARC_LATTICE_ROWS
+#define PARC_LATTICE_ROWS 4                   // lattice ray sets: lattice rows (= independent gathers) per lane and loop iteration
 #endif
-#ifndef PARC_SPLIT_A
-#define PARC_SPLIT_A 1      // 1: phase A uniforms as two dependent-load chains in two warps
-#endif
-#ifndef PARC_VEC_ROWS
-#define PARC_VEC_ROWS 1      // 1: staged rows are shifted to the 16-byte phase of their obs_buf row, copy-out in 128-bit pieces
+#ifndef PARC_BULK_ROWS
+#define PARC_BULK_ROWS 1                      // 1: staged rows / ref blocks leave through cp.async.bulk where alignment allows
 #endif
 
 namespace parc {
@@ -48,6 +41,9 @@ namespace parc {
 #endif
 constexpr int TILE = PARC_STEP_TILE;      // envs per block (== warps per block)
 constexpr int STEP_THREADS = 32 * TILE;
+constexpr int NPART = 4;                  // lanes cooperating on one (env, pose)
+constexpr int NGROUP = STEP_THREADS / NPART;
+constexpr int LATTICE_NY = 32;            // lattice ray sets take the shared-product height path when they have 32 columns
 
 // Column layout of one observation row (IGParkourEnv._compute_obs, ig_parkour_env.py:842-965;
 // compute_char_obs ig_char_env.py:581-625; compute_tar_obs mgdm_dm_util.py:404-461).
@@ -73,8 +69,10 @@ __host__ __device__ inline ObsLayout make_layout(int J, int D, int C, const parc
     return L;
 }
 
-// Reference-motion outputs staged behind the observation columns of a row (DeepMimicEnv.
-// _update_ref_motion, dm_env.py:523-545): offsets relative to the start of the section.
+// Reference-motion outputs (DeepMimicEnv._update_ref_motion, dm_env.py:523-545). The tile's ref_* values are staged
+// TENSOR-MAJOR: field f of width w_f occupies floats [off_f * TILE, (off_f + w_f) * TILE) as [TILE][w_f] -- which is
+// exactly the memory image of rows e0 .. e0 + TILE - 1 of a contiguous [N, w_f] tensor, so a full tile leaves with one
+// bulk copy per tensor.
 struct RefLayout {
     int root_pos, root_rot, root_vel, root_ang_vel, body_pos, joint_rot, dof_pos, dof_vel, contacts, width;
 };
@@ -88,12 +86,12 @@ __host__ __device__ inline RefLayout make_ref_layout(int J, int D, int C) {
     R.width = R.contacts + C;
     return R;
 }
+constexpr int NREF = 9;   // ref_* tensors
 
 // Per-env uniforms computed once (phase A) and read by every later phase.
 struct EnvU {
     long long e;             // env index of this row
     long long mid;           // motion id
-    const float* vel_rec;    // velocity record of the reference pose's frame idx0 (set by phase B)
     Vec3 c_pos; Quat c_rot; Vec3 c_vel; Vec3 c_avel;
     Quat hinv;               // inverse heading rotation of the CHARACTER root
     Vec3 eo;                 // env offset
@@ -106,50 +104,21 @@ struct EnvU {
     int flags;               // phase C: bit0 fall contact, bit1 fall height, bit2 pose failure
 };
 
-// Shared-memory plan (dynamic): sized on the host by step_smem_bytes().
+// Shared-memory plan (dynamic): sized on the host.
 struct SmemPlan {
-    int row_pitch;           // floats per staged row: o_hf + ref width (+ up to 3 floats of alignment shift), = 4 mod 32
+    int row_pitch;           // floats per staged row: o_hf (+ up to 3 floats of alignment shift), = 4 mod 32
     int n_pose;              // poses per env: S + 2
-    int n_slots;             // FK transforms a thread keeps: max over parts of bodies with children inside the part
+    int n_gslots;            // transforms a 4-lane group keeps in shared memory
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
-    size_t off_env, off_row, off_charq, off_xf, off_terms, off_refmap, off_tab, off_pts, total;
+    size_t off_env, off_row, off_ref, off_charq, off_gx, off_terms, off_refmap, off_tab, off_pts, off_lat, off_ctr, total;
 };
 
-constexpr int NPART = 4;                // threads cooperating on one (env, pose): each walks one part of the tree
-
-inline SmemPlan make_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const ObsLayout& L, int n_slots) {
-    SmemPlan p;
-    const int J = cm.num_bodies, D = cm.dof_size;
-    const RefLayout R = make_ref_layout(J, D, C);
-#if PARC_VEC_ROWS
-    // A row starts at a multiple of 4 floats plus the env's shift (0..3), so that column k of the staged row and of the
-    // obs_buf row have the same 16-byte phase. Pitch = 4 (mod 32): the 8 envs a warp touches at one column land in
-    // banks 4 el + shift -- all different.
-    p.row_pitch = (L.o_hf + R.width + 3 + 3) & ~3;
-    while ((p.row_pitch & 31) != 4) p.row_pitch += 4;
-#else
-    p.row_pitch = (L.o_hf + R.width) | 1;
-#endif
-    p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
-    p.n_slots = n_slots;
-    p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
-    size_t o = 0;
-    p.off_env = o;    o += sizeof(EnvU) * TILE;                          o = (o + 15) & ~size_t(15);
-    p.off_row = o;    o += sizeof(float) * TILE * p.row_pitch;           o = (o + 15) & ~size_t(15);
-    p.off_charq = o;  o += sizeof(float4) * TILE * J;                    o = (o + 15) & ~size_t(15);
-    // The FK transform columns are only live in phase B; the reward terms (phase C/D) and the ref_* scatter map
-    // (built in phase C, read in phase E) reuse the same bytes.
-    const size_t xf_bytes = sizeof(float) * 7 * p.n_slots * STEP_THREADS;
-    const size_t terms_bytes = (sizeof(float) * TILE * p.term_pitch + 15) & ~size_t(15);
-    p.off_xf = o;
-    p.off_terms = o;
-    p.off_refmap = o + terms_bytes;
-    o += std::max(xf_bytes, terms_bytes + 16 * (size_t)R.width);      o = (o + 15) & ~size_t(15);
-    p.off_tab = o;    o += sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J;   o = (o + 15) & ~size_t(15);
-    p.off_pts = o;    o += sizeof(float2) * (size_t)cfg.num_ray_points;   // ray_xy_points, shared by the tile's envs
-    p.total = o;
-    return p;
-}
+// One entry of the joint schedule: what lane `part` of an (env, pose) group does in iteration `it`.
+//   bits 0-7 joint | 8-15 mask of key-body slots that are this joint | 16 parent transform comes from a group slot (else:
+//   from this lane's registers = its previous joint, or the root) | 17-21 slot to read | 22 publish to a slot |
+//   23-27 slot to write | 28 body has children (its rotation is needed);   -1 = idle
+constexpr int SCHED_FROM_SLOT = 1 << 16, SCHED_RSLOT_SHIFT = 17, SCHED_PUBLISH = 1 << 22, SCHED_WSLOT_SHIFT = 23, SCHED_NEEDS_ROT = 1 << 28;
+constexpr int SCHED_MAX_SLOTS = 32;
 
 // Everything the kernel would otherwise re-derive per thread from the model / config, computed once
 // on the host per launch and passed by value.
@@ -157,140 +126,181 @@ struct StepPlan {
     ObsLayout L;
     RefLayout R;
     SmemPlan S;
-    unsigned has_child;                   // bit j: body j has children (root excluded from slots)
     unsigned key_mask;                    // bit j: body j is listed in key_body_ids
     int lrot_ident;                       // every _local_rotation is the identity
-    int max_part_len;                     // longest joint list of a part
-    // part_entry[p][i]: joint j | owned << 8 | (store slot + 1) << 12 | (parent slot + 1) << 16; -1 past the end.
-    // A part's list is closed under ancestors (shared ancestors are recomputed, only one part owns = outputs them).
-    int part_entry[NPART][PARC_MAX_BODIES];
+    int n_iter;                           // iterations of the joint schedule
+    int root_slot;                        // >= 0: the root transform is published to this group slot before the joint loop
+    int sched[PARC_MAX_BODIES * NPART];   // [it][part]
     float rdx, rdy;                       // correctly rounded 1/dx, 1/dy
-    float max_ix, max_iy;                 // dim - 1 as floats
+    int lat_nx, lat_ny;                   // > 0: ray_xy_points is the lattice xs[i] x ys[j], point i * ny + j (cfg.ray_grid_*)
+    int ref_fast;                         // every ref_* view is a contiguous, 16-byte aligned [N, w] tensor
 };
 
-// Splits the joints 1..J-1 into NPART ancestor-closed lists of similar length: start from the
-// subtrees below the root, keep splitting the largest one at its first branching body (the chain
-// above the branch is recomputed by every piece, owned by the first), then pack the pieces into
-// NPART bins, largest first.
-struct TreeUnit { int prefix[PARC_MAX_BODIES]; unsigned char prefix_owned[PARC_MAX_BODIES]; int n_prefix; int top; int size; };
-
-static int subtree_size(const parc_char_model_t& cm, int r) {
-    int n = 1;
-    for (int j = r + 1; j < cm.num_bodies; ++j) {
-        int a = cm.parent[j];
-        while (a > r) a = cm.parent[a];
-        if (a == r) ++n;
-    }
-    return n;
-}
-static bool in_subtree(const parc_char_model_t& cm, int r, int j) {
-    while (j > r) j = cm.parent[j];
-    return j == r;
-}
-
-inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const parc_terrain_t& tr) {
-    StepPlan sp;
+// List scheduling of the joints 1..J-1 on NPART lanes. A joint may run once its parent ran in an EARLIER iteration
+// (transforms change hands between iterations). A lane first continues below the joint it has just finished (the parent
+// is then in its registers); free lanes take the ready joint with the longest chain below it. A parent that is not
+// "the same lane, previous iteration" is read from a group slot; slots are reused once their last reader is done.
+inline void plan_schedule(const parc_char_model_t& cm, const parc_env_config_t& cfg, StepPlan& sp) {
     const int J = cm.num_bodies;
-    sp.L = make_layout(J, cm.dof_size, C, cfg);
-    sp.R = make_ref_layout(J, cm.dof_size, C);
-    sp.has_child = 0;
-    for (int j = 1; j < J; ++j) sp.has_child |= 1u << cm.parent[j];
+    int height[PARC_MAX_BODIES], iter_of[PARC_MAX_BODIES], lane_of[PARC_MAX_BODIES], nkids[PARC_MAX_BODIES];
+    for (int j = 0; j < J; ++j) { height[j] = 1; iter_of[j] = -1; lane_of[j] = -1; nkids[j] = 0; }
+    for (int j = J - 1; j >= 1; --j) {
+        const int p = cm.parent[j];
+        if (height[j] + 1 > height[p]) height[p] = height[j] + 1;
+        ++nkids[p];
+    }
+    iter_of[0] = -1;   // the root is available before iteration 0
+    int prev[NPART];
+    for (int p = 0; p < NPART; ++p) prev[p] = -1;
+    for (int k = 0; k < PARC_MAX_BODIES * NPART; ++k) sp.sched[k] = -1;
+    int remaining = J - 1, it = 0;
+    int joint_at[PARC_MAX_BODIES][NPART];
+    while (remaining > 0) {
+        int chosen[NPART];
+        for (int p = 0; p < NPART; ++p) {
+            chosen[p] = -1;
+            if (prev[p] < 0) continue;
+            for (int c = prev[p] + 1; c < J; ++c)
+                if (cm.parent[c] == prev[p] && iter_of[c] < 0 && (chosen[p] < 0 || height[c] > height[chosen[p]])) chosen[p] = c;
+            if (chosen[p] >= 0) iter_of[chosen[p]] = it;
+        }
+        for (int p = 0; p < NPART; ++p) {
+            if (chosen[p] >= 0) continue;
+            int best = -1;
+            for (int c = 1; c < J; ++c) {
+                if (iter_of[c] >= 0) continue;
+                const int par = cm.parent[c];
+                const bool ready = par == 0 || (iter_of[par] >= 0 && iter_of[par] < it);
+                if (ready && (best < 0 || height[c] > height[best])) best = c;
+            }
+            if (best >= 0) { chosen[p] = best; iter_of[best] = it; }
+        }
+        for (int p = 0; p < NPART; ++p) {
+            joint_at[it][p] = chosen[p];
+            if (chosen[p] >= 0) { lane_of[chosen[p]] = p; --remaining; }
+            prev[p] = chosen[p];
+        }
+        ++it;
+    }
+    sp.n_iter = it;
+    // which parents go through a slot, and until when they are needed
+    int last_reader[PARC_MAX_BODIES];
+    bool from_slot[PARC_MAX_BODIES];
+    for (int j = 0; j < J; ++j) { last_reader[j] = -1; from_slot[j] = false; }
+    for (int c = 1; c < J; ++c) {
+        const int par = cm.parent[c];
+        bool in_regs;
+        if (par == 0) {
+            // root: in registers as long as the lane has not evaluated any joint yet
+            in_regs = true;
+            for (int t = 0; t < iter_of[c]; ++t) if (joint_at[t][lane_of[c]] >= 0) in_regs = false;
+        } else {
+            in_regs = lane_of[par] == lane_of[c] && iter_of[par] == iter_of[c] - 1;
+        }
+        from_slot[c] = !in_regs;
+        if (!in_regs && iter_of[c] > last_reader[par]) last_reader[par] = iter_of[c];
+    }
+    // interval colouring: body j occupies a slot over [iter_of[j], last_reader[j]] (the root from -1)
+    int slot_of[PARC_MAX_BODIES], slot_free_at[SCHED_MAX_SLOTS], ns = 0;
+    for (int s = 0; s < SCHED_MAX_SLOTS; ++s) slot_free_at[s] = -2;
+    for (int j = 0; j < J; ++j) slot_of[j] = -1;
+    for (int t = -1; t < it; ++t)
+        for (int j = 0; j < J; ++j) {
+            if (last_reader[j] < 0 || iter_of[j] != t) continue;
+            int s = 0;
+            while (slot_free_at[s] >= t) ++s;               // free once the last reader's iteration is over; J <= 32 bodies never need more than 32 slots
+            slot_of[j] = s; slot_free_at[s] = last_reader[j];
+            if (s + 1 > ns) ns = s + 1;
+        }
+    sp.root_slot = slot_of[0];
+    for (int t = 0; t < it; ++t)
+        for (int p = 0; p < NPART; ++p) {
+            const int j = joint_at[t][p];
+            if (j < 0) continue;
+            int e = j;
+            for (int k = 0; k < cfg.num_key_bodies; ++k) if (cfg.key_body_ids[k] == j) e |= 1 << (8 + k);
+            if (from_slot[j]) e |= SCHED_FROM_SLOT | (slot_of[cm.parent[j]] << SCHED_RSLOT_SHIFT);
+            if (slot_of[j] >= 0) e |= SCHED_PUBLISH | (slot_of[j] << SCHED_WSLOT_SHIFT);
+            if (nkids[j] > 0) e |= SCHED_NEEDS_ROT;
+            sp.sched[t * NPART + p] = e;
+        }
+    sp.S.n_gslots = ns > 0 ? ns : 1;
+}
+
+inline void make_smem_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, StepPlan& sp) {
+    SmemPlan& p = sp.S;
+    const int J = cm.num_bodies, D = cm.dof_size;
+    const ObsLayout& L = sp.L;
+    const RefLayout& R = sp.R;
+    // A row starts at a multiple of 4 floats plus the env's shift (0..3), so that column k of the staged row and of the
+    // obs_buf row have the same 16-byte phase. Pitch = 4 (mod 32): the 8 envs a warp touches at one column land in
+    // banks 4 el + shift -- all different.
+    p.row_pitch = (L.o_hf + 3 + 3) & ~3;
+    while ((p.row_pitch & 31) != 4) p.row_pitch += 4;
+    p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
+    p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { const size_t at = o; o = (o + bytes + 15) & ~size_t(15); return at; };
+    p.off_env = take(sizeof(EnvU) * TILE);
+    p.off_row = take(sizeof(float) * TILE * p.row_pitch);
+    p.off_ref = take(sizeof(float) * TILE * R.width);
+    p.off_charq = take(sizeof(float4) * TILE * J);
+    // The group slots are only live in phase B; the reward terms (phase C/D) and the ref_* scatter map (built in phase C,
+    // read in phase E) reuse the same bytes.
+    const size_t gx_bytes = sizeof(float) * 7 * p.n_gslots * NGROUP;
+    const size_t terms_bytes = (sizeof(float) * TILE * p.term_pitch + 15) & ~size_t(15);
+    p.off_gx = p.off_terms = o;
+    p.off_refmap = o + terms_bytes;
+    take(std::max(gx_bytes, terms_bytes + 16 * (size_t)R.width));
+    p.off_tab = take(sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J);
+    if (sp.lat_nx > 0) {
+        p.off_pts = take(sizeof(float) * (sp.lat_nx + sp.lat_ny));            // lattice axes xs | ys
+        p.off_lat = take(sizeof(float2) * TILE * sp.lat_nx);                   // per env and lattice row: (x c, x s)
+    } else {
+        p.off_pts = take(sizeof(float2) * (size_t)cfg.num_ray_points);        // ray_xy_points, shared by the tile's envs
+        p.off_lat = o;
+    }
+    p.off_ctr = take(16);
+    p.total = o;
+}
+
+static bool view_is_rows(const parc_view3_t& v, int a, int b) {
+    // [N, a, b] (b = 0: [N, a]) row-major without gaps, base 16-byte aligned
+    if (!v.ptr || (reinterpret_cast<uintptr_t>(v.ptr) & 15)) return false;
+    if (b == 0) return v.row_stride == a && v.elem_stride == 1;
+    return v.row_stride == (long long)a * b && v.mid_stride == b && v.elem_stride == 1;
+}
+
+inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, const parc_terrain_t& tr,
+                               const parc_env_buffers_t* env = nullptr) {
+    StepPlan sp;
+    const int J = cm.num_bodies, D = cm.dof_size;
+    sp.L = make_layout(J, D, C, cfg);
+    sp.R = make_ref_layout(J, D, C);
     sp.key_mask = 0;
     for (int k = 0; k < cfg.num_key_bodies; ++k) sp.key_mask |= 1u << cfg.key_body_ids[k];
     sp.lrot_ident = 1;
     for (int j = 1; j < J; ++j)
         if (!(cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f)) sp.lrot_ident = 0;
-    // ---- units ----
-    TreeUnit units[2 * PARC_MAX_BODIES];
-    int nu = 0;
-    for (int j = 1; j < J; ++j)
-        if (cm.parent[j] == 0) { TreeUnit u; u.n_prefix = 0; u.top = j; u.size = subtree_size(cm, j); units[nu++] = u; }
-    const int target = (J - 1 + NPART - 1) / NPART;
-    for (int iter = 0; iter < 4 * PARC_MAX_BODIES; ++iter) {
-        int best = -1;
-        for (int a = 0; a < nu; ++a)
-            if (units[a].size > target && (best < 0 || units[a].size > units[best].size)) {
-                // splittable only if some body on the single-child chain below `top` branches
-                int node = units[a].top, nch;
-                for (;;) { nch = 0; int only = -1; for (int j = node + 1; j < J; ++j) if (cm.parent[j] == node) { ++nch; only = j; } if (nch != 1) break; node = only; }
-                if (nch >= 2) best = a;
-            }
-        if (best < 0 || (nu >= NPART && units[best].size <= target + 1) || nu + PARC_MAX_BODIES / 2 > 2 * PARC_MAX_BODIES) break;
-        TreeUnit u = units[best];
-        int node = u.top;
-        for (;;) {
-            u.prefix[u.n_prefix] = node; u.prefix_owned[u.n_prefix] = 1; ++u.n_prefix;
-            int nch = 0, only = -1;
-            for (int j = node + 1; j < J; ++j) if (cm.parent[j] == node) { ++nch; only = j; }
-            if (nch != 1) break;
-            node = only;
-        }
-        units[best] = units[--nu];
-        bool first = true;
-        for (int j = node + 1; j < J; ++j)
-            if (cm.parent[j] == node) {
-                TreeUnit c = u;
-                if (!first) for (int k = 0; k < c.n_prefix; ++k) c.prefix_owned[k] = 0;
-                first = false;
-                c.top = j; c.size = c.n_prefix + subtree_size(cm, j);
-                units[nu++] = c;
-            }
-    }
-    // ---- pack into NPART bins, largest unit first ----
-    unsigned bin_has[NPART] = {0, 0, 0, 0}, bin_owned[NPART] = {0, 0, 0, 0};
-    int load[NPART] = {0, 0, 0, 0};
-    bool used[2 * PARC_MAX_BODIES] = {false};
-    for (int n = 0; n < nu; ++n) {
-        int a = -1;
-        for (int k = 0; k < nu; ++k) if (!used[k] && (a < 0 || units[k].size > units[a].size)) a = k;
-        used[a] = true;
-        int b = 0;
-        for (int k = 1; k < NPART; ++k) if (load[k] < load[b]) b = k;
-        const TreeUnit& u = units[a];
-        for (int k = 0; k < u.n_prefix; ++k) { bin_has[b] |= 1u << u.prefix[k]; if (u.prefix_owned[k]) bin_owned[b] |= 1u << u.prefix[k]; }
-        for (int j = u.top; j < J; ++j) if (in_subtree(cm, u.top, j)) { bin_has[b] |= 1u << j; bin_owned[b] |= 1u << j; }
-        load[b] = __builtin_popcount(bin_has[b]);
-    }
-    // a prefix body owned by a unit packed next to another copy must be owned exactly once overall
-    unsigned owned_seen = 0;
-    for (int b = 0; b < NPART; ++b) { bin_owned[b] &= ~owned_seen; owned_seen |= bin_owned[b]; }
-    sp.max_part_len = 0;
-    int max_slots = 1;
-    for (int b = 0; b < NPART; ++b) {
-        // Slots are handed out by liveness: a body's transform is kept only until its last child inside the part has
-        // read it, and a child may take over its parent's slot (the walk reads the parent before storing the child).
-        int slot_of[PARC_MAX_BODIES], kids_left[PARC_MAX_BODIES];
-        bool slot_busy[PARC_MAX_BODIES] = {false};
-        int ns = 0, len = 0;
-        for (int j = 1; j < J; ++j) {
-            slot_of[j] = -1; kids_left[j] = 0;
-            if (!((bin_has[b] >> j) & 1u)) continue;
-            for (int c = j + 1; c < J; ++c) if (cm.parent[c] == j && ((bin_has[b] >> c) & 1u)) ++kids_left[j];
-        }
-        for (int j = 1; j < J; ++j) {
-            if (!((bin_has[b] >> j) & 1u)) continue;
-            const int par = cm.parent[j];
-            const int pslot = par == 0 ? -1 : slot_of[par];
-            if (par != 0 && --kids_left[par] == 0) slot_busy[pslot] = false;
-            if (kids_left[j] > 0) {
-                int f = 0;
-                while (slot_busy[f]) ++f;
-                slot_busy[f] = true; slot_of[j] = f;
-                if (f + 1 > ns) ns = f + 1;
-            }
-            sp.part_entry[b][len++] = j | ((int)((bin_owned[b] >> j) & 1u) << 8) | ((slot_of[j] + 1) << 12) | ((pslot + 1) << 16);
-        }
-        for (int k = len; k < PARC_MAX_BODIES; ++k) sp.part_entry[b][k] = -1;
-        if (len > sp.max_part_len) sp.max_part_len = len;
-        if (ns > max_slots) max_slots = ns;
-    }
-    sp.S = make_plan(cm, C, cfg, sp.L, max_slots);
+    plan_schedule(cm, cfg, sp);
+    // the lattice sampler gives lane l the lattice column l (32 columns) and walks PARC_LATTICE_ROWS rows per iteration
+    const bool lat = cfg.ray_grid_nx > 0 && cfg.ray_grid_ny > 0 && cfg.ray_grid_nx * cfg.ray_grid_ny == cfg.num_ray_points &&
+                     cfg.ray_grid_ny == LATTICE_NY && cfg.ray_grid_nx % PARC_LATTICE_ROWS == 0;
+    sp.lat_nx = lat ? cfg.ray_grid_nx : 0;
+    sp.lat_ny = lat ? cfg.ray_grid_ny : 0;
+    make_smem_plan(cm, C, cfg, sp);
     sp.rdx = 1.0f / tr.dx; sp.rdy = 1.0f / tr.dy;    // IEEE single division on the host == RN(1/d)
-    sp.max_ix = (float)(tr.dim_x - 1); sp.max_iy = (float)(tr.dim_y - 1);
+    sp.ref_fast = 0;
+    if (env)
+        sp.ref_fast = view_is_rows(env->ref_root_pos, 3, 0) && view_is_rows(env->ref_root_rot, 4, 0) && view_is_rows(env->ref_root_vel, 3, 0) &&
+                      view_is_rows(env->ref_root_ang_vel, 3, 0) && view_is_rows(env->ref_body_pos, J, 3) &&
+                      (J == 1 || view_is_rows(env->ref_joint_rot, J - 1, 4)) && (D == 0 || (view_is_rows(env->ref_dof_pos, D, 0) &&
+                      view_is_rows(env->ref_dof_vel, D, 0))) && (C == 0 || view_is_rows(env->ref_contacts, C, 0));
     return sp;
 }
 
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float2 ldg2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
 // rotate_2d_vec (torch_util.py:650-662) + root xy, products rounded separately (bit-exact cells)
 __device__ __forceinline__ void ray_world(float px, float py, float c, float s, float rx, float ry, float& wx, float& wy) {
@@ -330,24 +340,17 @@ __device__ __forceinline__ float div_const(float x, float d, float rc) {
     const float r = __fmaf_rn(-q, d, x);
     return __fmaf_rn(r, rc, q);
 }
-struct GridParams { float min_x, min_y, dx, dy, rdx, rdy, max_ix, max_iy; };
-__device__ __forceinline__ int grid_index_fast(float p, float mn, float d, float rd, float mx) {
-    float u = rintf(div_const(__fsub_rn(p, mn), d, rd));
-    u = fminf(fmaxf(u, 0.f), mx);
-    return (int)u;
-}
 
 // Grid cell of one ray sample point: rotate_2d_vec + root xy, (px c - py s + gx, px s + py c + gy), then
-// clamp(round_half_even((w - min) / dxdy), 0, dim - 1) (terrain_util.py:139-152). The sums and the Markstein division
-// (div_const) are packed fp32x2 (FADD2 / FMUL2 / FFMA2, sm_100): x and y of the point share those instructions.
-// Every product and sum must be rounded on its own, as torch's separate mul / sub / add are. ptxas (CUDA 12.9)
-// contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 despite the .rn (seen in the SASS; an FFMA2 with a -0 addend is
-// folded back and contracted too), so the four products are scalar mul.rn -- which it does leave alone -- and only
-// the sums and the division are packed. parc_b200_selftest_cells checks the result against the scalar path on the GPU.
-__device__ __forceinline__ int packed_cell(float2 pt, float2 cs, float2 nsc, float2 g2, float2 nmn, float2 rd2, float2 nd2, int imx, int imy,
-                                           int dimy) {
-    const float2 a = make_float2(__fmul_rn(pt.x, cs.x), __fmul_rn(pt.x, cs.y));
-    const float2 b = make_float2(__fmul_rn(pt.y, nsc.x), __fmul_rn(pt.y, nsc.y));
+// clamp(round_half_even((w - min) / dxdy), 0, dim - 1) (terrain_util.py:139-152). The caller supplies the four products
+// a = (px c, px s) and b = (-py s, py c), each a scalar mul.rn (for a lattice of sample points they are shared by a
+// whole lattice row / column). The sums and the Markstein division (div_const) are packed fp32x2 (FADD2 / FMUL2 / FFMA2,
+// sm_100): x and y of the point share those instructions. Every product and sum must be rounded on its own, as torch's
+// separate mul / sub / add are. ptxas (CUDA 12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 despite the .rn
+// (seen in the SASS; an FFMA2 with a -0 addend is folded back and contracted too), so the products stay scalar -- which
+// it does leave alone -- and only the sums and the division are packed. parc_b200_selftest_cells checks the result
+// against the scalar path on the GPU.
+__device__ __forceinline__ int packed_cell_ab(float2 a, float2 b, float2 g2, float2 nmn, float2 rd2, float2 nd2, int imx, int imy, int dimy) {
     const float2 w = __fadd2_rn(__fadd2_rn(a, b), g2);
     const float2 x = __fadd2_rn(w, nmn);
     float2 q = __fmul2_rn(x, rd2);
@@ -357,15 +360,26 @@ __device__ __forceinline__ int packed_cell(float2 pt, float2 cs, float2 nsc, flo
     const int iy = max(0, min(__float2int_rn(q.y), imy));
     return ix * dimy + iy;
 }
+__device__ __forceinline__ int packed_cell(float2 pt, float2 cs, float2 nsc, float2 g2, float2 nmn, float2 rd2, float2 nd2, int imx, int imy,
+                                           int dimy) {
+    const float2 a = make_float2(__fmul_rn(pt.x, cs.x), __fmul_rn(pt.x, cs.y));
+    const float2 b = make_float2(__fmul_rn(pt.y, nsc.x), __fmul_rn(pt.y, nsc.y));
+    return packed_cell_ab(a, b, g2, nmn, rd2, nd2, imx, imy, dimy);
+}
 
-// One env's heightmap samples by one warp (_refresh_obs_hfs, ig_parkour_env.py:518-533; get_hf_val, terrain_util.py:139-156).
-// Points come from shared memory, four per lane and iteration so that four independent gathers are in flight; the two
-// destination rows (either may be absent) are running pointers with immediate offsets. FULL: P is a multiple of 128
-// (no tail predicates).
+struct HeightArgs {
+    const float* hf;
+    int dimy, imx, imy;
+    float2 g2, nmn, rd2, nd2;
+    float gz, lo, hi;
+};
+
+// One env's heightmap samples by one warp, general ray set (_refresh_obs_hfs, ig_parkour_env.py:518-533; get_hf_val,
+// terrain_util.py:139-156). Points come from shared memory, PARC_HEIGHT_GATHERS per lane and iteration; the two
+// destination rows (either may be absent) are running pointers with immediate offsets. FULL: no tail predicates.
 template <bool FULL>
-__device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const float* __restrict__ hf, int dimy,
-                                               int imx, int imy, float2 cs, float2 nsc, float2 g2, float gz, float2 nmn, float2 rd2,
-                                               float2 nd2, float lo, float hi, float* __restrict__ hrow, float* __restrict__ orow) {
+__device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts, int P, int lane, const HeightArgs& h, float2 cs, float2 nsc,
+                                               float* __restrict__ hrow, float* __restrict__ orow) {
     constexpr int U = PARC_HEIGHT_GATHERS;
     const bool HAS_H = hrow != nullptr, HAS_O = orow != nullptr;   // warp-uniform: predicated stores, one code copy
     const float2* sp = s_pts + lane;
@@ -378,24 +392,62 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
 #pragma unroll
         for (int k = 0; k < U; ++k) pt[k] = (FULL || p + 32 * k < P) ? sp[32 * k] : make_float2(0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < U; ++k) {
-            cell[k] = packed_cell(pt[k], cs, nsc, g2, nmn, rd2, nd2, imx, imy, dimy);
-        }
+        for (int k = 0; k < U; ++k) cell[k] = packed_cell(pt[k], cs, nsc, h.g2, h.nmn, h.rd2, h.nd2, h.imx, h.imy, h.dimy);
 #pragma unroll
-        for (int k = 0; k < U; ++k) v[k] = __ldg(hf + cell[k]);
+        for (int k = 0; k < U; ++k) v[k] = __ldg(h.hf + cell[k]);
 #pragma unroll
         for (int k = 0; k < U; ++k) {
-            const float h = fminf(fmaxf(__fsub_rn(v[k], gz), lo), hi);
+            const float x = fminf(fmaxf(__fsub_rn(v[k], h.gz), h.lo), h.hi);
             if (FULL || p + 32 * k < P) {
-                if (HAS_H) ph[32 * k] = h;
-                if (HAS_O) po[32 * k] = h;
+                if (HAS_H) ph[32 * k] = x;
+                if (HAS_O) po[32 * k] = x;
             }
         }
     }
 }
 
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 / PARC_STEP_TILE) env_step_kernel(
+// The same for a lattice ray set xs[i] x ys[j] (point i * 32 + j) with 32 columns: lane l owns lattice column l; its two
+// products with ys[l] are formed once per env, the two with xs[i] come from the env's table s_a (phase A), so a sample
+// costs three packed adds, the packed division and the gather. A warp store covers one lattice row = 128 contiguous bytes;
+// the U rows of an iteration are immediate offsets from one running pointer.
+template <bool HAS_H, bool HAS_O>
+__device__ __forceinline__ void heights_of_env_lattice(const float2* __restrict__ s_a, float y, int nx, int lane, const HeightArgs& h, float c,
+                                                       float s, float* __restrict__ hrow, float* __restrict__ orow) {
+    constexpr int U = PARC_LATTICE_ROWS;
+    const float2 b = make_float2(__fmul_rn(y, -s), __fmul_rn(y, c));
+    float* ph = HAS_H ? hrow + lane : nullptr;
+    float* po = HAS_O ? orow + lane : nullptr;
+    const float2* a = s_a;
+    PARC_COLD_LOOP
+    for (int i = 0; i < nx; i += U, a += U) {
+        int cell[U];
+        float v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) cell[k] = packed_cell_ab(a[k], b, h.g2, h.nmn, h.rd2, h.nd2, h.imx, h.imy, h.dimy);
+#pragma unroll
+        for (int k = 0; k < U; ++k) v[k] = __ldg(h.hf + cell[k]);
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            const float x = fminf(fmaxf(__fsub_rn(v[k], h.gz), h.lo), h.hi);
+            if (HAS_H) ph[k * LATTICE_NY] = x;
+            if (HAS_O) po[k * LATTICE_NY] = x;
+        }
+        if (HAS_H) ph += U * LATTICE_NY;
+        if (HAS_O) po += U * LATTICE_NY;
+    }
+}
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+// shared -> global bulk copy (TMA, no tensor map): both addresses 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <int THREADS, bool LATTICE>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
@@ -414,13 +466,17 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
     const SmemPlan& plan = sp.S;
     EnvU* s_env = reinterpret_cast<EnvU*>(smem_raw + plan.off_env);
     float* s_row = reinterpret_cast<float*>(smem_raw + plan.off_row);
+    float* s_ref = reinterpret_cast<float*>(smem_raw + plan.off_ref);
     float4* s_charq = reinterpret_cast<float4*>(smem_raw + plan.off_charq);
-    float* s_xf = reinterpret_cast<float*>(smem_raw + plan.off_xf);
+    float* s_gx = reinterpret_cast<float*>(smem_raw + plan.off_gx);
     float* s_terms = reinterpret_cast<float*>(smem_raw + plan.off_terms);
-    unsigned long long* s_refmap = reinterpret_cast<unsigned long long*>(smem_raw + plan.off_refmap);
-    int* s_part = reinterpret_cast<int*>(smem_raw + plan.off_tab);
+    uint4* s_refmap = reinterpret_cast<uint4*>(smem_raw + plan.off_refmap);
+    int* s_sched = reinterpret_cast<int*>(smem_raw + plan.off_tab);
     float* s_jc = reinterpret_cast<float*>(smem_raw + plan.off_tab + sizeof(int) * NPART * PARC_MAX_BODIES);
-    float2* s_pts = reinterpret_cast<float2*>(smem_raw + plan.off_pts);
+    float2* s_pts = reinterpret_cast<float2*>(smem_raw + plan.off_pts);     // general ray set
+    float* s_axes = reinterpret_cast<float*>(smem_raw + plan.off_pts);      // lattice: xs[nx] | ys[ny]
+    float2* s_lat = reinterpret_cast<float2*>(smem_raw + plan.off_lat);     // lattice: [TILE][nx] (x c, x s)
+    int* s_ctr = reinterpret_cast<int*>(smem_raw + plan.off_ctr);
     const int ROWP = plan.row_pitch;
 
     const bool do_heights = parts & PARC_STEP_HEIGHTS;
@@ -431,23 +487,33 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
     const bool need_ref_pose = do_ref || do_reward || do_done;
     const bool need_char_q = do_obs || do_reward;
     const int tile_rows = (int)min((long long)TILE, n_rows - row0);
+    // the tile's ref_* block of field f (see RefLayout): [TILE][w] floats
+    auto refp = [&](int field_off, int w, int el) -> float* { return s_ref + field_off * TILE + el * w; };
 
     // ================================ phase A ====================================================
     PARC_COLD_LOOP
-    for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_part[k] = sp.part_entry[k / PARC_MAX_BODIES][k % PARC_MAX_BODIES];
+    for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_sched[k] = sp.sched[k];
     PARC_COLD_LOOP
     for (int k = tid; k < 8 * J; k += THREADS) {
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
-    if (do_heights)
-        PARC_COLD_LOOP
-        for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
-    // A.3 per-env uniforms: the first lanes of the LAST warp, so that the dependent loads (env id -> motion id -> clip
-    //     meta) overlap the dof -> quaternion work of the leading warps
-#if PARC_SPLIT_A
-    // two chains in two otherwise idle warps: root state -> heading -> sin/cos/h^-1 (last warp), and time -> motion id ->
-    // clip meta -> terrain offset (the warp before it); each writes its own fields of s_env[el]
+    if (tid == 0) *s_ctr = 0;
+    if (do_heights) {
+        if (LATTICE) {
+            // xs[i] = x of point i * ny, ys[j] = y of point j
+            PARC_COLD_LOOP
+            for (int k = tid; k < sp.lat_nx + sp.lat_ny; k += THREADS)
+                s_axes[k] = k < sp.lat_nx ? __ldg(env.ray_xy_points + 2 * (long long)k * sp.lat_ny) : __ldg(env.ray_xy_points + 2 * (k - sp.lat_nx) + 1);
+        } else {
+            PARC_COLD_LOOP
+            for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
+        }
+    }
+    // A.3 per-env uniforms as two chains in two otherwise idle warps: root state -> heading -> sin/cos/h^-1 (last warp), and
+    //     time -> motion id -> clip meta -> terrain offset (the warp before it); each writes its own fields of s_env[el].
+    //     Rows past the end of a partial tile are filled with the tile's first row: every lane of phases B / C then works on
+    //     valid data, and only stores to global memory look at `live`.
     if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
         const int el = tid - (THREADS - 32);
         EnvU& u = s_env[el];
@@ -467,13 +533,8 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
         const float heading = calc_heading(c_rot);
         u.sh = sinf(heading); u.ch = cosf(heading);
         u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
-        u.vel_rec = lib.vel;
         u.flags = 0;
-#if PARC_VEC_ROWS
         u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
-#else
-        u.row_shift = 0;
-#endif
         if (need_char_q) s_charq[el * J] = quat_to_f4(c_rot);
     } else if (tid >= THREADS - 64 && tid < THREADS - 64 + TILE) {
         const int el = tid - (THREADS - 64);
@@ -498,54 +559,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
         const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
         u.tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3)); u.toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
     }
-#else
-    if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
-        EnvU u;
-        const int el = tid - (THREADS - 32);
-        u.live = el < tile_rows;
-        const long long row = row0 + (u.live ? el : 0);
-        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
-        u.e = e;
-        u.c_pos = view_ld_vec3(env.char_root_pos, e);
-        u.c_rot = view_ld_quat(env.char_root_rot, e);
-        u.c_vel = view_ld_vec3(env.char_root_vel, e);
-        u.c_avel = view_ld_vec3(env.char_root_ang_vel, e);
-        u.eo = make_vec3(__ldg(env.env_offsets + e * 3), __ldg(env.env_offsets + e * 3 + 1), __ldg(env.env_offsets + e * 3 + 2));
-        u.g = u.c_pos + u.eo;                                          // ig_parkour_env.py:522
-        const float heading = calc_heading(u.c_rot);
-        u.sh = sinf(heading); u.ch = cosf(heading);
-        u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
-        if (parts & PARC_STEP_TIME) {                                   // _update_time, ig_env.py:391-394
-            const int ts = env.timestep_buf[e] + 1;
-            u.time = __fmul_rn(cfg.timestep, (float)ts);
-            if (u.live) { env.timestep_buf[e] = ts; env.time_buf[e] = u.time; }
-        } else {
-            u.time = env.time_buf[e];
-        }
-        u.mid = env.motion_ids[e];
-        const long long tidx = env.motion_terrain_ids[e];
-        u.mm = load_motion_meta(lib.meta, u.mid);
-        u.t0 = __fadd_rn(u.time, env.motion_time_offsets[e]);          // dm_env.py:547-552
-        const float* dmo = env.dm_motion_offsets + (u.mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
-        u.tox = __fsub_rn(__ldg(dmo), u.eo.x); u.toy = __fsub_rn(__ldg(dmo + 1), u.eo.y);
-        u.vel_rec = lib.vel;
-        u.flags = 0;
-#if PARC_VEC_ROWS
-        u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
-#else
-        u.row_shift = 0;
-#endif
-        s_env[el] = u;
-        if (need_char_q) s_charq[el * J] = quat_to_f4(u.c_rot);
-    }
-#endif
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
         PARC_COLD_LOOP
         for (int it = tid; it < TILE * (J - 1); it += THREADS) {
             const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
-            if (el >= tile_rows) continue;
-            const long long row = row0 + el;
+            const long long row = row0 + (el < tile_rows ? el : 0);
             const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
             const int jt = cm.joint_type[j], di = cm.dof_idx[j];
             Quat q = quat_identity();
@@ -558,9 +577,17 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
     }
     __syncthreads();
 
+    // A.4 lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares
+    if (LATTICE && do_heights) {
+        PARC_COLD_LOOP
+        for (int k = tid; k < TILE * sp.lat_nx; k += THREADS) {
+            const int el = k / sp.lat_nx, i = k - el * sp.lat_nx;
+            const float x = s_axes[i];
+            s_lat[k] = make_float2(__fmul_rn(x, s_env[el].ch), __fmul_rn(x, s_env[el].sh));
+        }
+    }
     // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
-    //      the two adjacent interp records (and the velocity record of the reference pose); the dof -> quaternion
-    //      work below runs while they arrive
+    //      the two adjacent interp records (and the velocity record of the reference pose)
     if (do_reward || do_done) {
         // simulator state read in phase C (rigid body positions, contact forces, dof velocities): 3 rows per env
         PARC_COLD_LOOP
@@ -594,46 +621,18 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
     }
 
     // ================================ phase B ====================================================
-    static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART tree parts");
+    static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART lanes");
     const bool pose_work = do_obs || need_ref_pose;
-    // ---- B.1 heights: _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145) for the sample points [p0, p1):
-    //      warp w samples the points of env w. Where this runs is a scheduling choice (PARC_HEIGHTS_LATE): the
-    //      samples depend only on the phase A uniforms and write straight to global memory.
-    auto sample_heights = [&](const int p0, const int p1) {
-        if (!(P > 0 && (do_heights || do_obs)) || p1 <= p0) return;
-        const int lane = tid & 31, cnt = p1 - p0;
-        const float2 nmn = make_float2(-terrain.min_x, -terrain.min_y), rd2 = make_float2(sp.rdx, sp.rdy), nd2 = make_float2(-terrain.dx, -terrain.dy);
-        const int imx = terrain.dim_x - 1, imy = terrain.dim_y - 1, dimy = terrain.dim_y;
-        const float lo = cfg.min_obs_h, hi = cfg.max_obs_h;
-        for (int el = tid >> 5; el < tile_rows; el += THREADS / 32) {
-            const EnvU& u = s_env[el];
-            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf + p0 : nullptr;
-            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P + p0 : nullptr;
-            if (do_heights) {
-                const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch), g2 = make_float2(u.g.x, u.g.y);
-                if (cnt % (32 * PARC_HEIGHT_GATHERS) == 0)
-                    heights_of_env<true>(s_pts + p0, cnt, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
-                else
-                    heights_of_env<false>(s_pts + p0, cnt, lane, terrain.hf, dimy, imx, imy, cs, nsc, g2, u.g.z, nmn, rd2, nd2, lo, hi, hrow, orow);
-            } else if (orow) {
-                for (int p = lane; p < cnt; p += 32) orow[p] = hrow[p];
-            }
-        }
-    };
-#if !PARC_HEIGHTS_LATE
-    sample_heights(0, P);
-#endif
-    // ---- B.2 warp w takes poses w, w + 8, ...; lane = (env, part): NPART lanes share one (env, pose) and each
-    //      walks its own ancestor-closed part of the joint tree, so all lanes of a warp run the same code ----
+    // warp w takes poses w, w + 8, ...; lane = (env, part). Rows past a partial tile hold a copy of the tile's first row
+    // (phase A), so no lane leaves the loop early: the __syncwarp() of the joint schedule sees the whole warp.
     for (int pose = (tid >> 5) & 7; pose_work && pose < plan.n_pose; pose += 8) {
         const int lane = tid & 31, el = (tid >> 8) * 8 + lane / NPART, part = lane & (NPART - 1);
         const bool is_ref = pose == 0, is_char = pose == S + 1, is_tar = pose >= 1 && pose <= S;
         const bool wanted = (is_ref && need_ref_pose) || (is_tar && do_obs) || (is_char && do_obs);
-        if (!wanted || !s_env[el].live) continue;
+        if (!wanted) continue;
         const EnvU& u = s_env[el];
         float* row = s_row + el * ROWP + u.row_shift;
-        float* rsec = row + L.o_hf;                    // ref_* section
-        const float *r0 = nullptr, *r1 = nullptr;
+        const float *r0 = nullptr, *r1 = nullptr, *pr0 = nullptr;
         float b = 0.f, omb = 1.f;
         Quat rq = u.c_rot;
         Vec3 rpos = u.c_pos;
@@ -644,8 +643,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
             const FrameBlend fb = calc_frame_blend(u.mm, t);
             r0 = lib.interp + fb.idx0 * lib.irec;
             r1 = lib.interp + fb.idx1 * lib.irec;
+            pr0 = r0 + interp_pair_off(J, C);
             b = fb.blend; omb = __fsub_rn(1.0f, b);
-            rq = slerp(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), b);
+            rq = slerp_pre(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), ldg2(pr0), b, omb);
             const float4 p0 = ldg4(r0 + 4 * J), p1 = ldg4(r1 + 4 * J);
             rpos = make_vec3(__fadd_rn(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x), u.tox),
                              __fadd_rn(__fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y), u.toy),
@@ -658,11 +658,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
         Vec3 rp_obs = make_vec3(0.f, 0.f, 0.f);
         if (is_ref) {
             if (part == 0) {
-                rsec[R.root_pos] = rpos.x; rsec[R.root_pos + 1] = rpos.y; rsec[R.root_pos + 2] = rpos.z;
-                rsec[R.root_rot] = rq.x; rsec[R.root_rot + 1] = rq.y; rsec[R.root_rot + 2] = rq.z; rsec[R.root_rot + 3] = rq.w;
-                rsec[R.body_pos] = rpos.x; rsec[R.body_pos + 1] = rpos.y; rsec[R.body_pos + 2] = rpos.z;
+                float* o = refp(R.root_pos, 3, el); o[0] = rpos.x; o[1] = rpos.y; o[2] = rpos.z;
+                *reinterpret_cast<float4*>(refp(R.root_rot, 4, el)) = quat_to_f4(rq);
+                o = refp(R.body_pos, 3 * J, el); o[0] = rpos.x; o[1] = rpos.y; o[2] = rpos.z;
             }
             // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
+            float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
             PARC_COLD_LOOP
             for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
                 const float4 x = ldg4(vrec + k);
@@ -670,9 +671,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const int kk = k + c;
-                    if (kk < 3) rsec[R.root_vel + kk] = xs[c];
-                    else if (kk < 6) rsec[R.root_ang_vel + kk - 3] = xs[c];
-                    else if (kk < 6 + D) rsec[R.dof_vel + kk - 6] = xs[c];
+                    if (kk < 3) o_rv[kk] = xs[c];
+                    else if (kk < 6) o_rav[kk - 3] = xs[c];
+                    else if (kk < 6 + D) o_dv[kk - 6] = xs[c];
                 }
             }
         } else if (is_tar) {
@@ -711,7 +712,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
         }
         // contact labels: lerp of the two records (motion_lib.py:121)
         if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
-            float* oc = is_ref ? (rsec + R.contacts) : (row + L.o_tarc + (pose - 1) * C);
+            float* oc = is_ref ? refp(R.contacts, C, el) : (row + L.o_tarc + (pose - 1) * C);
             const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
             PARC_COLD_LOOP
             for (int c = 4 * part; c < C; c += 4 * NPART) {
@@ -720,52 +721,6 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                 if (c + 1 < C) oc[c + 1] = lerp_exact(omb, a.y, b, d.y);
                 if (c + 2 < C) oc[c + 2] = lerp_exact(omb, a.z, b, d.z);
                 if (c + 3 < C) oc[c + 3] = lerp_exact(omb, a.w, b, d.w);
-            }
-        }
-        // ---- joints of this part: slerp + forward kinematics (kin_char_model.py:617-649) ----
-        const bool lrot_ident = sp.lrot_ident != 0;
-        float* xf = s_xf + tid;                         // [slot][7][THREADS], this thread's column
-        const int* my_part = s_part + part * PARC_MAX_BODIES;
-        PARC_COLD_LOOP
-        for (int i = 0; i < sp.max_part_len; ++i) {
-            const int entry = my_part[i];
-            if (entry < 0) continue;
-            const int j = entry & 0xff, owned = (entry >> 8) & 1, st_slot = ((entry >> 12) & 0xf) - 1, p_slot = ((entry >> 16) & 0xf) - 1;
-            Quat q;
-            if (is_char) q = quat_from_f4(s_charq[el * J + j]);
-            else q = slerp(quat_from_f4(ldg4(r0 + 4 * j)), quat_from_f4(ldg4(r1 + 4 * j)), b);
-            Vec3 ppos = rpos; Quat prot = rq;
-            if (p_slot >= 0) {
-                const float* x = xf + p_slot * 7 * THREADS;
-                ppos = make_vec3(x[0], x[THREADS], x[2 * THREADS]);
-                prot = make_quat(x[3 * THREADS], x[4 * THREADS], x[5 * THREADS], x[6 * THREADS]);
-            }
-            const float* jc = s_jc + 8 * j;
-            const Vec3 bpos = ppos + quat_rotate(prot, make_vec3(jc[0], jc[1], jc[2]));
-            if (st_slot >= 0) {
-                const Quat cq = lrot_ident ? q : quat_mul(make_quat(jc[3], jc[4], jc[5], jc[6]), q);
-                const Quat brot = quat_mul(prot, cq);
-                float* x = xf + st_slot * 7 * THREADS;
-                x[0] = bpos.x; x[THREADS] = bpos.y; x[2 * THREADS] = bpos.z;
-                x[3 * THREADS] = brot.x; x[4 * THREADS] = brot.y; x[5 * THREADS] = brot.z; x[6 * THREADS] = brot.w;
-            }
-            if (!owned) continue;
-            if (is_ref) {
-                float* jr = rsec + R.joint_rot + 4 * (j - 1);
-                jr[0] = q.x; jr[1] = q.y; jr[2] = q.z; jr[3] = q.w;
-                float* bp = rsec + R.body_pos + 3 * j;
-                bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
-            } else {
-                tan_norm_exact(q, o_pose + 6 * (j - 1));
-                if ((sp.key_mask >> j) & 1u)
-                PARC_COLD_LOOP
-                for (int k = 0; k < K; ++k) {
-                    if (cfg.key_body_ids[k] != j) continue;
-                    Vec3 kp = bpos - rpos;
-                    if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
-                    float* kd = o_key + 3 * k;
-                    kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
-                }
             }
         }
         // a key body may also be the root itself
@@ -777,6 +732,60 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                     float* kd = o_key + 3 * k;
                     kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                 }
+        // ---- joints: slerp + forward kinematics (kin_char_model.py:617-649) along the schedule ----
+        const bool lrot_ident = sp.lrot_ident != 0;
+        float* gx = s_gx + (tid >> 2);                  // [slot][7][NGROUP], this 4-lane group's column
+        Vec3 cpos = rpos; Quat crot = rq;               // transform of the body this lane evaluated last (the root at first)
+        if (sp.root_slot >= 0 && part == 0) {
+            float* x = gx + sp.root_slot * 7 * NGROUP;
+            x[0] = rpos.x; x[NGROUP] = rpos.y; x[2 * NGROUP] = rpos.z;
+            x[3 * NGROUP] = rq.x; x[4 * NGROUP] = rq.y; x[5 * NGROUP] = rq.z; x[6 * NGROUP] = rq.w;
+        }
+        float* o_jr = is_ref ? refp(R.joint_rot, 4 * (J - 1), el) : nullptr;
+        float* o_bp = is_ref ? refp(R.body_pos, 3 * J, el) : nullptr;
+        __syncwarp();
+        PARC_COLD_LOOP
+        for (int it = 0; it < sp.n_iter; ++it) {
+            const int entry = s_sched[it * NPART + part];
+            if (entry >= 0) {
+                const int j = entry & 0xff;
+                Quat q;
+                if (is_char) q = quat_from_f4(s_charq[el * J + j]);
+                else q = slerp_pre(quat_from_f4(ldg4(r0 + 4 * j)), quat_from_f4(ldg4(r1 + 4 * j)), ldg2(pr0 + 2 * j), b, omb);
+                if (entry & SCHED_FROM_SLOT) {
+                    const float* x = gx + ((entry >> SCHED_RSLOT_SHIFT) & 31) * 7 * NGROUP;
+                    cpos = make_vec3(x[0], x[NGROUP], x[2 * NGROUP]);
+                    crot = make_quat(x[3 * NGROUP], x[4 * NGROUP], x[5 * NGROUP], x[6 * NGROUP]);
+                }
+                const float* jc = s_jc + 8 * j;
+                const Vec3 bpos = cpos + quat_rotate(crot, make_vec3(jc[0], jc[1], jc[2]));
+                cpos = bpos;
+                if (entry & SCHED_NEEDS_ROT) {
+                    const Quat cq = lrot_ident ? q : quat_mul(make_quat(jc[3], jc[4], jc[5], jc[6]), q);
+                    crot = quat_mul(crot, cq);
+                    if (entry & SCHED_PUBLISH) {
+                        float* x = gx + ((entry >> SCHED_WSLOT_SHIFT) & 31) * 7 * NGROUP;
+                        x[0] = bpos.x; x[NGROUP] = bpos.y; x[2 * NGROUP] = bpos.z;
+                        x[3 * NGROUP] = crot.x; x[4 * NGROUP] = crot.y; x[5 * NGROUP] = crot.z; x[6 * NGROUP] = crot.w;
+                    }
+                }
+                if (is_ref) {
+                    *reinterpret_cast<float4*>(o_jr + 4 * (j - 1)) = quat_to_f4(q);
+                    float* bp = o_bp + 3 * j;
+                    bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
+                } else {
+                    tan_norm_exact(q, o_pose + 6 * (j - 1));
+                    PARC_COLD_LOOP
+                    for (unsigned km = (entry >> 8) & 0xffu; km; km &= km - 1) {
+                        Vec3 kp = bpos - rpos;
+                        if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
+                        float* kd = o_key + 3 * (__ffs(km) - 1);
+                        kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
+                    }
+                }
+            }
+            __syncwarp();
+        }
     }
     __syncthreads();
 
@@ -784,32 +793,41 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
     // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
     const int o_pose_t = 0, o_vel_t = J - 1, o_con_t = o_vel_t + D, o_key_t = o_con_t + J;
     const int TP = plan.term_pitch;
-    // C.0 scatter map of the ref_* section for phase E: column k -> (base pointer, row stride in bytes). Lives in the
-    //     bytes the FK columns used during phase B; phase E starts behind the barrier that ends phase C.
-    if (do_ref) {
+    // The full-tile fast path of phase E: rows row0 .. row0 + TILE - 1 are consecutive env ids, so the staged ref_* blocks
+    // are the memory image of those rows of every (contiguous) ref_* tensor.
+    const long long e_first = row0 + first_env;
+    const bool ref_bulk = PARC_BULK_ROWS && do_ref && sp.ref_fast && tile_rows == TILE && env_ids == nullptr && env_ids32 == nullptr &&
+                          (e_first & 3) == 0;
+    const bool obs_bulk = PARC_BULK_ROWS && do_obs;
+    // C.0 scatter map of the ref_* values for the general copy-out of phase E: column k of an env's ref_* values ->
+    //     (global base pointer, row stride in bytes, position in the tile's staged block). Lives in the bytes the group
+    //     slots used during phase B; phase E reads it behind the barrier that ends phase C.
+    if (do_ref && !ref_bulk) {
         PARC_COLD_LOOP
         for (int k = tid; k < R.width; k += THREADS) {
-            const parc_view3_t* v; int off;
-            if (k < R.root_rot) { v = &env.ref_root_pos; off = k - R.root_pos; }
-            else if (k < R.root_vel) { v = &env.ref_root_rot; off = k - R.root_rot; }
-            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; off = k - R.root_vel; }
-            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; off = k - R.root_ang_vel; }
-            else if (k < R.joint_rot) { v = &env.ref_body_pos; off = k - R.body_pos; }
-            else if (k < R.dof_pos) { v = &env.ref_joint_rot; off = k - R.joint_rot; }
-            else if (k < R.dof_vel) { v = &env.ref_dof_pos; off = k - R.dof_pos; }
-            else if (k < R.contacts) { v = &env.ref_dof_vel; off = k - R.dof_vel; }
-            else { v = &env.ref_contacts; off = k - R.contacts; }
+            const parc_view3_t* v; int off, fo, w;
+            if (k < R.root_rot) { v = &env.ref_root_pos; fo = R.root_pos; w = 3; }
+            else if (k < R.root_vel) { v = &env.ref_root_rot; fo = R.root_rot; w = 4; }
+            else if (k < R.root_ang_vel) { v = &env.ref_root_vel; fo = R.root_vel; w = 3; }
+            else if (k < R.body_pos) { v = &env.ref_root_ang_vel; fo = R.root_ang_vel; w = 3; }
+            else if (k < R.joint_rot) { v = &env.ref_body_pos; fo = R.body_pos; w = 3 * J; }
+            else if (k < R.dof_pos) { v = &env.ref_joint_rot; fo = R.joint_rot; w = 4 * (J - 1); }
+            else if (k < R.dof_vel) { v = &env.ref_dof_pos; fo = R.dof_pos; w = D; }
+            else if (k < R.contacts) { v = &env.ref_dof_vel; fo = R.dof_vel; w = D; }
+            else { v = &env.ref_contacts; fo = R.contacts; w = C; }
+            off = k - fo;
             long long eoff;
             if (k >= R.body_pos && k < R.joint_rot) eoff = (off / 3) * v->mid_stride + (off % 3) * v->elem_stride;
             else if (k >= R.joint_rot && k < R.dof_pos) eoff = (off / 4) * v->mid_stride + (off % 4) * v->elem_stride;
             else eoff = off * v->elem_stride;
-            s_refmap[2 * k] = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
-            s_refmap[2 * k + 1] = (unsigned long long)(v->row_stride * (long long)sizeof(float));
+            const unsigned long long base = v->ptr ? reinterpret_cast<unsigned long long>(v->ptr + eoff) : 0ull;
+            s_refmap[k] = make_uint4((unsigned)base, (unsigned)(base >> 32), (unsigned)(v->row_stride * (long long)sizeof(float)),
+                                     (unsigned)(fo * TILE + off) | ((unsigned)w << 20));
         }
     }
     {
         // Four item kinds (joints, contacts, key bodies, dof velocities) cut into warp-sized tasks that are dealt
-        // round-robin to the 8 warps: every warp runs about the same number of (prefetched) global reads.
+        // round-robin to the warps: every warp runs about the same number of (prefetched) global reads.
         const bool want_c = (do_reward && cfg.use_contact_info) || (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0);
         const int nt_j = need_ref_pose ? (TILE * (J - 1) + 31) >> 5 : 0;
         const int nt_c = want_c ? (TILE * J + 31) >> 5 : 0;
@@ -825,19 +843,18 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                 if (it >= TILE * (J - 1)) continue;
                 const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
                 if (el >= tile_rows) continue;
-                float* rsec = s_row + el * ROWP + s_env[el].row_shift + L.o_hf;
-                const float* jr = rsec + R.joint_rot + 4 * (j - 1);
-                const Quat q = make_quat(jr[0], jr[1], jr[2], jr[3]);
+                const Quat q = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.joint_rot, 4 * (J - 1), el) + 4 * (j - 1)));
                 if (do_ref) {
                     const int jt = cm.joint_type[j], di = cm.dof_idx[j];
+                    float* dp = refp(R.dof_pos, D, el) + di;
                     if (jt == PARC_JOINT_SPHERICAL) {
                         const Vec3 ex = quat_to_exp_map(q);
-                        rsec[R.dof_pos + di] = ex.x; rsec[R.dof_pos + di + 1] = ex.y; rsec[R.dof_pos + di + 2] = ex.z;
+                        dp[0] = ex.x; dp[1] = ex.y; dp[2] = ex.z;
                     } else if (jt == PARC_JOINT_HINGE) {
                         Vec3 axis; float angle;
                         quat_to_axis_angle(q, axis, angle);
                         const float dd = dot3_seq(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), axis);
-                        rsec[R.dof_pos + di] = (dd < 0.f) ? -angle : angle;
+                        dp[0] = (dd < 0.f) ? -angle : angle;
                     }
                 }
                 if (do_reward) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
@@ -849,7 +866,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                     const EnvU& u = s_env[el];
                     const Vec3 sb = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, j, 0), view_ld3(env.char_rigid_body_pos, u.e, j, 1), view_ld3(env.char_rigid_body_pos, u.e, j, 2));
                     const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, 0, 0), view_ld3(env.char_rigid_body_pos, u.e, 0, 1), view_ld3(env.char_rigid_body_pos, u.e, 0, 2));
-                    const float* bp = rsec + R.body_pos;
+                    const float* bp = refp(R.body_pos, 3 * J, el);
                     const Vec3 a = sb - s0;
                     const Vec3 bb = make_vec3(bp[3 * j], bp[3 * j + 1], bp[3 * j + 2]) - make_vec3(bp[0], bp[1], bp[2]);
                     const Vec3 d = bb - a;
@@ -867,7 +884,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                 if (do_reward && cfg.use_contact_info) {
                     // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
                     const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
-                    const float rc = s_row[el * ROWP + u.row_shift + L.o_hf + R.contacts + c];
+                    const float rc = refp(R.contacts, C, el)[c];
                     float cr = -(1.0f - rc) * f;
                     cr += rc * f;
                     s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
@@ -892,14 +909,13 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                 if (el >= tile_rows) continue;
                 const EnvU& u = s_env[el];
                 const int body = cfg.key_body_ids[k];
-                const float* rsec = s_row + el * ROWP + u.row_shift + L.o_hf;
-                const float* bp = rsec + R.body_pos;
+                const float* bp = refp(R.body_pos, 3 * J, el);
                 const Vec3 ref_rpos = make_vec3(bp[0], bp[1], bp[2]);
                 Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
                                     view_ld3(env.char_rigid_body_pos, u.e, body, 2)) - u.c_pos;
                 Vec3 tkp = make_vec3(bp[3 * body], bp[3 * body + 1], bp[3 * body + 2]) - ref_rpos;
                 if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
-                    const Quat rr = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
+                    const Quat rr = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.root_rot, 4, el)));
                     kp = quat_rotate(u.hinv, kp);
                     tkp = quat_rotate(calc_heading_quat_inv(rr), tkp);
                 }
@@ -912,21 +928,48 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
                 const int el = it / D, k = it - el * D;
                 if (el >= tile_rows) continue;
                 const EnvU& u = s_env[el];
-                const float dv = s_row[el * ROWP + u.row_shift + L.o_hf + R.dof_vel + k] - view_ld(env.char_dof_vel, u.e, k);
+                const float dv = refp(R.dof_vel, D, el)[k] - view_ld(env.char_dof_vel, u.e, k);
                 s_terms[el * TP + o_vel_t + k] = cfg.dof_err_w[k] * dv * dv;
             }
         }
     }
+    if (obs_bulk || ref_bulk) fence_async_smem();   // the staged rows / blocks are about to be read by the bulk-copy engine
     __syncthreads();
+
+    // ================================ phase E (issue) =============================================
+    // Everything staged is final: hand the aligned body of each observation row and the ref_* blocks to the bulk-copy
+    // engine now, so that the copies run while phase D and the height samples execute. The few floats in front of /
+    // behind a row's 16-byte aligned body are stored by the same lane.
+    bool bulk_pending = false;
+    if (obs_bulk && tid < tile_rows) {
+        const EnvU& u = s_env[tid];
+        const float* srow = s_row + tid * ROWP + u.row_shift;
+        float* g = env.obs_buf + u.e * env.obs_row_stride;
+        const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
+        if (nvec > 0) { bulk_store(g + head, srow + head, 16u * nvec); bulk_pending = true; }
+        for (int k = 0; k < head; ++k) g[k] = srow[k];
+        for (int k = t0; k < n; ++k) g[k] = srow[k];
+    } else if (ref_bulk && tid >= 32 && tid < 32 + NREF) {
+        const int f = tid - 32;
+        const parc_view3_t& v = f == 0 ? env.ref_root_pos : f == 1 ? env.ref_root_rot : f == 2 ? env.ref_root_vel : f == 3 ? env.ref_root_ang_vel
+                              : f == 4 ? env.ref_body_pos : f == 5 ? env.ref_joint_rot : f == 6 ? env.ref_dof_pos : f == 7 ? env.ref_dof_vel : env.ref_contacts;
+        const int fo = f == 0 ? R.root_pos : f == 1 ? R.root_rot : f == 2 ? R.root_vel : f == 3 ? R.root_ang_vel : f == 4 ? R.body_pos
+                     : f == 5 ? R.joint_rot : f == 6 ? R.dof_pos : f == 7 ? R.dof_vel : R.contacts;
+        const int fe = f == 0 ? R.root_rot : f == 1 ? R.root_vel : f == 2 ? R.root_ang_vel : f == 3 ? R.body_pos : f == 4 ? R.joint_rot
+                     : f == 5 ? R.dof_pos : f == 6 ? R.dof_vel : f == 7 ? R.contacts : R.width;
+        const int w = fe - fo;
+        if (w > 0 && v.ptr) { bulk_store(v.ptr + e_first * w, s_ref + fo * TILE, (unsigned)(w * TILE * sizeof(float))); bulk_pending = true; }
+    }
+    if (bulk_pending) bulk_commit();
 
     // ================================ phase D ====================================================
     if (tid < tile_rows && (do_reward || do_done)) {
         const int el = tid;
         const EnvU& u = s_env[el];
         const long long e = u.e;
-        const float* rsec = s_row + el * ROWP + u.row_shift + L.o_hf;
-        const Vec3 ref_rpos = make_vec3(rsec[R.root_pos], rsec[R.root_pos + 1], rsec[R.root_pos + 2]);
-        const Quat ref_rrot = make_quat(rsec[R.root_rot], rsec[R.root_rot + 1], rsec[R.root_rot + 2], rsec[R.root_rot + 3]);
+        const float* rp = refp(R.root_pos, 3, el);
+        const Vec3 ref_rpos = make_vec3(rp[0], rp[1], rp[2]);
+        const Quat ref_rrot = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.root_rot, 4, el)));
         if (do_reward) {
             // _update_reward (ig_parkour_env.py:984-1044) + compute_deepmimic_reward (mgdm_dm_util.py:269-332)
             const float* tm = s_terms + el * TP;
@@ -942,8 +985,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
             const float root_pos_err = rpd.x * rpd.x + rpd.y * rpd.y + rpd.z * rpd.z;
             Quat a_rot = u.c_rot, b_rot = ref_rrot;
             Vec3 a_vel = u.c_vel, a_av = u.c_avel;
-            Vec3 b_vel = make_vec3(rsec[R.root_vel], rsec[R.root_vel + 1], rsec[R.root_vel + 2]);
-            Vec3 b_av = make_vec3(rsec[R.root_ang_vel], rsec[R.root_ang_vel + 1], rsec[R.root_ang_vel + 2]);
+            const float* rv = refp(R.root_vel, 3, el); const float* rav = refp(R.root_ang_vel, 3, el);
+            Vec3 b_vel = make_vec3(rv[0], rv[1], rv[2]);
+            Vec3 b_av = make_vec3(rav[0], rav[1], rav[2]);
             if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
                 const Quat hr = calc_heading_quat_inv(ref_rrot);
                 a_rot = quat_mul(u.hinv, u.c_rot); b_rot = quat_mul(hr, ref_rrot);
@@ -1012,44 +1056,74 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_BLOCKS_PER_SM_AT_TILE8 * 8 
         }
     }
 
-#if PARC_HEIGHTS_LATE
-    // heights after the reward / termination phases: nothing waits for them at a barrier, and they fill the issue slots
-    // while the 16 lanes of phase D run their serial sums
-    sample_heights(0, P);
-#endif
-    // ================================ phase E ====================================================
-    // staged rows -> global: warp w streams env w; consecutive lanes write consecutive columns
+    // ================================ phase H ====================================================
+    // _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145): one warp per env, rows handed out by a shared
+    // counter (the warp that ran phase D joins late and takes what is left). The samples depend only on the phase A
+    // uniforms and go straight to global memory.
+    if (P > 0 && (do_heights || do_obs)) {
+        const int lane = tid & 31;
+        HeightArgs ha;
+        ha.hf = terrain.hf; ha.dimy = terrain.dim_y; ha.imx = terrain.dim_x - 1; ha.imy = terrain.dim_y - 1;
+        ha.nmn = make_float2(-terrain.min_x, -terrain.min_y); ha.rd2 = make_float2(sp.rdx, sp.rdy); ha.nd2 = make_float2(-terrain.dx, -terrain.dy);
+        ha.lo = cfg.min_obs_h; ha.hi = cfg.max_obs_h;
+        for (;;) {
+            int el = 0;
+            if (lane == 0) el = atomicAdd(s_ctr, 1);
+            el = __shfl_sync(FULL_MASK, el, 0);
+            if (el >= tile_rows) break;
+            const EnvU& u = s_env[el];
+            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
+            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
+            if (do_heights) {
+                ha.g2 = make_float2(u.g.x, u.g.y); ha.gz = u.g.z;
+                if (LATTICE) {
+                    const float2* a = s_lat + el * sp.lat_nx;
+                    const float y = s_axes[sp.lat_nx + lane];
+                    if (orow && hrow) heights_of_env_lattice<true, true>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
+                    else if (orow) heights_of_env_lattice<false, true>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
+                    else heights_of_env_lattice<true, false>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
+                } else {
+                    const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch);
+                    if (P % (32 * PARC_HEIGHT_GATHERS) == 0) heights_of_env<true>(s_pts, P, lane, ha, cs, nsc, hrow, orow);
+                    else heights_of_env<false>(s_pts, P, lane, ha, cs, nsc, hrow, orow);
+                }
+            } else if (orow) {
+                for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
+            }
+        }
+    }
+
+    // ================================ phase E (general) ===========================================
+    // staged values -> global with plain stores where the bulk path does not apply: warp w streams env w
     {
         const int warp = tid >> 5, lane = tid & 31;
-        for (int el = warp; el < tile_rows; el += THREADS / 32) {
-            const EnvU& u = s_env[el];
-            const float* row = s_row + el * ROWP + u.row_shift;
-            if (do_obs) {
-                float* g = env.obs_buf + u.e * env.obs_row_stride;
-#if PARC_VEC_ROWS
-                // column k is 16-byte aligned in both the staged row and the obs_buf row when (row_shift + k) % 4 == 0
-                const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
-                if (lane < head) g[lane] = row[lane];
-                const float4* r4 = reinterpret_cast<const float4*>(row + head);
-                float4* g4 = reinterpret_cast<float4*>(g + head);
+        if ((do_obs && !obs_bulk) || (do_ref && !ref_bulk)) {
+            for (int el = warp; el < tile_rows; el += THREADS / 32) {
+                const EnvU& u = s_env[el];
+                if (do_obs && !obs_bulk) {
+                    const float* row = s_row + el * ROWP + u.row_shift;
+                    float* g = env.obs_buf + u.e * env.obs_row_stride;
+                    // column k is 16-byte aligned in both the staged row and the obs_buf row when (row_shift + k) % 4 == 0
+                    const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
+                    if (lane < head) g[lane] = row[lane];
+                    const float4* r4 = reinterpret_cast<const float4*>(row + head);
+                    float4* g4 = reinterpret_cast<float4*>(g + head);
 #pragma unroll 2
-                for (int k = lane; k < nvec; k += 32) g4[k] = r4[k];
-                if (t0 + lane < n) g[t0 + lane] = row[t0 + lane];
-#else
-#pragma unroll 4
-                for (int k = lane; k < L.o_hf; k += 32) g[k] = row[k];
-#endif
-            }
-            if (do_ref) {
-                const float* rsec = row + L.o_hf;
+                    for (int k = lane; k < nvec; k += 32) g4[k] = r4[k];
+                    if (t0 + lane < n) g[t0 + lane] = row[t0 + lane];
+                }
+                if (do_ref && !ref_bulk) {
 #pragma unroll 2
-                for (int k = lane; k < R.width; k += 32) {
-                    const unsigned long long base = s_refmap[2 * k];
-                    if (base) *reinterpret_cast<float*>(base + (unsigned long long)u.e * s_refmap[2 * k + 1]) = rsec[k];
+                    for (int k = lane; k < R.width; k += 32) {
+                        const uint4 m = s_refmap[k];
+                        const unsigned long long base = ((unsigned long long)m.y << 32) | m.x;
+                        if (base) *reinterpret_cast<float*>(base + (unsigned long long)u.e * m.z) = s_ref[(m.w & 0xfffffu) + el * (m.w >> 20)];
+                    }
                 }
             }
         }
     }
+    if (bulk_pending) bulk_wait_read();   // the shared-memory sources must outlive the copies
 }
 
 }  // namespace parc
@@ -1098,17 +1172,36 @@ extern "C" int parc_b200_selftest_div(const float* x, int64_t n, float d, float*
     return check_launch("selftest_div");
 }
 
-extern "C" int parc_b200_tree_parts(const parc_char_model_t* m, int32_t* entries, int32_t* max_len, int32_t* num_slots) {
+extern "C" int parc_b200_tree_parts(const parc_char_model_t* m, int32_t* entries, int32_t* max_len, int32_t* num_slots, int32_t* root_slot) {
     if (!model_ok(m, "tree_parts")) return PARC_ERR_INVALID_ARG;
-    PARC_REQUIRE(entries && max_len && num_slots, "tree_parts: NULL output");
+    PARC_REQUIRE(entries && max_len && num_slots && root_slot, "tree_parts: NULL output");
     parc_env_config_t cfg = {};
     parc_terrain_t tr = {};
     tr.dx = tr.dy = 1.f; tr.dim_x = tr.dim_y = 1;
     const StepPlan sp = make_step_plan(*m, 0, cfg, tr);
     for (int p = 0; p < NPART; ++p)
-        for (int i = 0; i < PARC_MAX_BODIES; ++i) entries[p * PARC_MAX_BODIES + i] = sp.part_entry[p][i];
-    *max_len = sp.max_part_len;
-    *num_slots = sp.S.n_slots;
+        for (int i = 0; i < PARC_MAX_BODIES; ++i) entries[p * PARC_MAX_BODIES + i] = i < sp.n_iter ? sp.sched[i * NPART + p] : -1;
+    *max_len = sp.n_iter;
+    *num_slots = sp.S.n_gslots;
+    *root_slot = sp.root_slot;
+    return PARC_OK;
+}
+
+extern "C" int parc_b200_ray_points_lattice(const float* h_pts_xy, int32_t num_points, int32_t* nx, int32_t* ny) {
+    PARC_REQUIRE(nx && ny && num_points >= 0 && (num_points == 0 || h_pts_xy), "ray_points_lattice: bad arguments");
+    *nx = *ny = 0;
+    if (num_points < 2) return PARC_OK;
+    // ny = length of the leading run of points that share x; then every point must be (xs[i], ys[j]) bit for bit
+    int n_y = 1;
+    while (n_y < num_points && h_pts_xy[2 * n_y] == h_pts_xy[0]) ++n_y;
+    if (num_points % n_y != 0) return PARC_OK;
+    const int n_x = num_points / n_y;
+    for (int i = 0; i < n_x; ++i)
+        for (int j = 0; j < n_y; ++j) {
+            const float* p = h_pts_xy + 2 * ((long long)i * n_y + j);
+            if (p[0] != h_pts_xy[2 * (long long)i * n_y] || p[1] != h_pts_xy[2 * j + 1]) return PARC_OK;
+        }
+    *nx = n_x; *ny = n_y;
     return PARC_OK;
 }
 
@@ -1168,6 +1261,8 @@ int validate_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, 
     PARC_REQUIRE(!(parts & PARC_STEP_OBS) || env->obs_row_stride >= L.obs_dim, "env_step: obs_row_stride %lld < obs_dim %d",
                  (long long)env->obs_row_stride, L.obs_dim);
     PARC_REQUIRE((long long)terrain->dim_x * terrain->dim_y < (1ll << 31), "env_step: terrain has more than 2^31 cells");
+    PARC_REQUIRE(cfg->ray_grid_nx >= 0 && cfg->ray_grid_ny >= 0 && (cfg->ray_grid_nx == 0 || (long long)cfg->ray_grid_nx * cfg->ray_grid_ny == cfg->num_ray_points),
+                 "env_step: ray_grid %d x %d does not cover the %d ray points", cfg->ray_grid_nx, cfg->ray_grid_ny, cfg->num_ray_points);
     const StepPlan sp_check = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
     PARC_REQUIRE(sp_check.S.total <= 227 * 1024, "env_step: staging of %zu bytes exceeds shared memory", sp_check.S.total);
     return PARC_OK;
@@ -1193,17 +1288,27 @@ namespace parc {
 int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
                     const parc_env_config_t* cfg, const parc_env_buffers_t* env, uint32_t parts, const int64_t* env_ids,
                     long long max_rows, const int* env_ids32, const int* n_rows_dev, void* stream, long long first_env) {
-    const StepPlan sp = make_step_plan(*m, lib->num_contacts, *cfg, *terrain);
+    const StepPlan sp = make_step_plan(*m, lib->num_contacts, *cfg, *terrain, env);
     const SmemPlan& plan = sp.S;
-    static size_t smem_attr = 0;   // opt-in dynamic shared memory, raised only when a larger plan shows up
-    if (plan.total > smem_attr) {
-        cudaError_t ce = cudaFuncSetAttribute(env_step_kernel<STEP_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
+    const bool lattice = sp.lat_nx > 0;
+    // opt-in dynamic shared memory: a per-device function attribute, raised only when a larger plan shows up
+    static size_t smem_attr[64][2] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& have = smem_attr[dev & 63][lattice ? 1 : 0];
+    if (plan.total > have) {
+        cudaError_t ce = lattice ? cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total)
+                                 : cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
         if (ce != cudaSuccess) { set_error("env_step: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
-        smem_attr = plan.total;
+        have = plan.total;
     }
     const long long blocks = (max_rows + TILE - 1) / TILE;
-    env_step_kernel<STEP_THREADS><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
-        *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
+    if (lattice)
+        env_step_kernel<STEP_THREADS, true><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+            *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
+    else
+        env_step_kernel<STEP_THREADS, false><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+            *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
     return check_launch("env_step");
 }
 }  // namespace parc

@@ -6,8 +6,12 @@
 namespace parc {
 
 // One thread per output float of the interp / vel records; reads are coalesced on the source
-// tensors' trailing dims, writes on the record.
-__global__ void __launch_bounds__(256) pack_frames_kernel(int J, int D, int C, long long F, int irec, int vrec,
+// tensors' trailing dims, writes on the record. The pair block of frame f holds slerp_pair(q_j(f), q_j(f')) for the
+// quaternions j = 0..J-1 (0 = root rotation), f' = the next frame of the same clip (f itself on a clip's last frame:
+// _calc_frame_blend, motion_lib.py:425-438, clamps idx1 to the last frame).
+__global__ void __launch_bounds__(256) pack_frames_kernel(int J, int D, int C, long long F, int irec, int vrec, int M,
+                                                          const long long* __restrict__ start_idx,
+                                                          const long long* __restrict__ num_frames,
                                                           const float* __restrict__ root_pos,
                                                           const float* __restrict__ root_rot,
                                                           const float* __restrict__ root_vel,
@@ -18,6 +22,7 @@ __global__ void __launch_bounds__(256) pack_frames_kernel(int J, int D, int C, l
                                                           float* __restrict__ interp, float* __restrict__ vel) {
     const long long total_i = F * irec;
     const long long total = total_i + F * vrec;
+    const int pair0 = interp_pair_off(J, C);
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
         if (k < total_i) {
             const long long f = k / irec;
@@ -27,6 +32,18 @@ __global__ void __launch_bounds__(256) pack_frames_kernel(int J, int D, int C, l
             else if (e < 4 * J) v = joint_rot[f * (J - 1) * 4 + (e - 4)];
             else if (e < 4 * J + 3) v = root_pos[f * 3 + (e - 4 * J)];
             else if (e >= 4 * J + 4 && e < 4 * J + 4 + C) v = contacts[f * C + (e - 4 * J - 4)];
+            else if (e >= pair0 && e < pair0 + 2 * J) {
+                // clip of frame f: last m with start_idx[m] <= f
+                int lo = 0, hi = M - 1;
+                while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (start_idx[mid] <= f) lo = mid; else hi = mid - 1; }
+                const long long last = start_idx[lo] + num_frames[lo] - 1;
+                const long long f1 = f < last ? f + 1 : f;
+                const int j = (e - pair0) >> 1;
+                const float* a = j == 0 ? root_rot + f * 4 : joint_rot + (f * (J - 1) + (j - 1)) * 4;
+                const float* b = j == 0 ? root_rot + f1 * 4 : joint_rot + (f1 * (J - 1) + (j - 1)) * 4;
+                const float2 pr = slerp_pair(make_quat(a[0], a[1], a[2], a[3]), make_quat(b[0], b[1], b[2], b[3]));
+                v = ((e - pair0) & 1) ? pr.y : pr.x;
+            }
             interp[k] = v;
         } else {
             const long long kk = k - total_i;
@@ -159,12 +176,14 @@ extern "C" int parc_b200_motionlib_pack(const parc_char_model_t* m, int64_t F, i
     PARC_REQUIRE(F < (1ll << 31), "motionlib_pack: more than 2^31 frames");
     PARC_REQUIRE(C >= 0 && C <= m->num_bodies, "motionlib_pack: num_contacts %d must be in [0, num_bodies]", C);
     PARC_REQUIRE(C == 0 || contacts, "motionlib_pack: contacts is NULL");
-    PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel && interp && vel && meta, "motionlib_pack: NULL pointer");
+    PARC_REQUIRE(root_pos && root_rot && root_vel && root_ang_vel && dof_vel && interp && vel && meta && num_frames && start_idx,
+                 "motionlib_pack: NULL pointer");
     const int J = m->num_bodies, D = m->dof_size;
     const int irec = interp_record_floats(J, C), vrec = vel_record_floats(D);
     const long long total = F * (irec + vrec);
     pack_frames_kernel<<<grid_cap((total + 255) / 256), 256, 0, as_stream(stream)>>>(
-        J, D, C, F, irec, vrec, root_pos, root_rot, root_vel, root_ang_vel, joint_rot, dof_vel, contacts, interp, vel);
+        J, D, C, F, irec, vrec, M, (const long long*)start_idx, (const long long*)num_frames, root_pos, root_rot, root_vel, root_ang_vel,
+        joint_rot, dof_vel, contacts, interp, vel);
     int rc = check_launch("motionlib_pack(frames)");
     if (rc) return rc;
     pack_meta_kernel<<<grid_cap((M + 255) / 256), 256, 0, as_stream(stream)>>>(

@@ -183,7 +183,9 @@ __device__ __forceinline__ FrameBlend calc_frame_blend(const MotionMeta& mm, flo
 // Record offsets inside the interp / vel records (see parc_motion_lib_t in include/parc_b200.h).
 __host__ __device__ __forceinline__ int interp_pos_off(int J) { return 4 * J; }
 __host__ __device__ __forceinline__ int interp_contact_off(int J) { return 4 * J + 4; }
-__host__ __device__ __forceinline__ int interp_record_floats(int J, int C) { return (4 * J + 4 + C + 3) & ~3; }
+// slerp constants of the pair (this frame, next frame of the clip): [J][2] floats, 8-byte aligned
+__host__ __device__ __forceinline__ int interp_pair_off(int J, int C) { return (4 * J + 4 + C + 1) & ~1; }
+__host__ __device__ __forceinline__ int interp_record_floats(int J, int C) { return (interp_pair_off(J, C) + 2 * J + 3) & ~3; }
 __host__ __device__ __forceinline__ int vel_record_floats(int D) { return (6 + D + 3) & ~3; }
 
 // One pose sample of MotionLib.calc_motion_frame (motion_lib.py:94-126), lane-parallel:

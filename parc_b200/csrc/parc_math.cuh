@@ -202,6 +202,29 @@ __device__ __forceinline__ Quat slerp(Quat q0, Quat q1, float t) {
     return make_quat(ra * q0.x + rb * q1.x, ra * q0.y + rb * q1.y, ra * q0.z + rb * q1.z, ra * q0.w + rb * q1.w);
 }
 
+// The blend-independent half of slerp (torch_util.py:474-499) for one quaternion pair, computed once when the library is
+// packed: (h, w) such that slerp(q0, q1, t) = ra q0 + rb q1 with
+//   h >= 0 (general case):  ra = sin((1 - t) h) |w|,  rb = sin(t h) w      h = acos|c|, w = sign(c) / sqrt(1 - c c)
+//   h <  0 (special cases): ra = 1 - |w|,             rb = w               |c| >= 1 -> w = 0 (q0);  sin < 0.001 -> w = +-0.5
+// c = sum(q0 q1) left to right, 1 - c c unfused, correctly rounded sqrt: the branch decisions are the reference's.
+__device__ __forceinline__ float2 slerp_pair(Quat q0, Quat q1) {
+    const float c0 = dot4_seq(q0, q1);
+    const float sgn = (c0 < 0.f) ? -1.f : 1.f;
+    const float c = fabsf(c0);
+    if (c >= 1.f) return make_float2(-1.f, 0.f);
+    const float s = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(c, c)));
+    if (s < 0.001f) return make_float2(-1.f, 0.5f * sgn);
+    return make_float2(acosf(c), sgn * __fdiv_rn(1.0f, s));
+}
+// slerp from the packed pair constants; omt = fp32(1 - t) as the reference forms it
+__device__ __forceinline__ Quat slerp_pre(Quat q0, Quat q1, float2 pr, float t, float omt) {
+    const float aw = fabsf(pr.y);
+    float ra = sin_first_quadrant(omt * pr.x) * aw;
+    float rb = sin_first_quadrant(t * pr.x) * pr.y;
+    if (pr.x < 0.f) { ra = 1.f - aw; rb = pr.y; }
+    return make_quat(ra * q0.x + rb * q1.x, ra * q0.y + rb * q1.y, ra * q0.z + rb * q1.z, ra * q0.w + rb * q1.w);
+}
+
 // calc_heading, torch_util.py:501-510: atan2 of the rotated x axis.
 __device__ __forceinline__ float calc_heading(Quat q) {
     Vec3 d = quat_rotate(q, make_vec3(1.f, 0.f, 0.f));

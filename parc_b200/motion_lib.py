@@ -395,7 +395,8 @@ class MotionLib:
         F = int(self._frame_root_pos.shape[0])
         M = self.num_motions()
         C = int(self._frame_contacts.shape[-1]) if self._frame_contacts is not None else 0
-        irec = (4 * J + 4 + C + 3) & ~3
+        pair_off = (4 * J + 4 + C + 1) & ~1                        # csrc/parc_lanes.cuh: interp_pair_off
+        irec = (pair_off + 2 * J + 3) & ~3
         vrec = (6 + D + 3) & ~3
         dev = self._device
         self._blob_interp = torch.empty((F, irec), dtype=torch.float32, device=dev)

@@ -64,7 +64,7 @@ def _f32(x):
     return float(np.float32(x))
 
 
-def build_config_struct(env_config, char_model: KinCharModel, num_ray_points: int) -> _lib.EnvConfigStruct:
+def build_config_struct(env_config, char_model: KinCharModel, num_ray_points: int, ray_xy_points=None) -> _lib.EnvConfigStruct:
     """yaml `env:` dict -> parc_env_config_t, evaluating every derived constant the way the
     reference's Python does (fp32 tensors times Python doubles, ig_parkour_env.py:43-149)."""
     ec = env_config
@@ -84,6 +84,9 @@ def build_config_struct(env_config, char_model: KinCharModel, num_ray_points: in
     for i, k in enumerate(keys):
         c.key_body_ids[i] = k
     c.num_ray_points = int(num_ray_points)
+    if ray_xy_points is not None:                                  # lattice ray sets (get_xy_grid_points) take the shared-product path
+        assert int(ray_xy_points.shape[0]) == c.num_ray_points
+        c.ray_grid_nx, c.ray_grid_ny = _lib.ray_points_lattice(ray_xy_points)
     c.global_obs = int(bool(ec["global_obs"]))
     c.root_height_obs = int(bool(ec["global_root_height_obs"]))
     c.enable_tar_obs = int(bool(ec.get("enable_tar_obs", True)))
@@ -188,7 +191,7 @@ class TrackingEnv:
 
         self._ray_xy_points = ray_xy_points.to(device=dev, dtype=f32).contiguous()
         P = int(self._ray_xy_points.shape[0])
-        self._cfg = build_config_struct(env_config, char_model, P)
+        self._cfg = build_config_struct(env_config, char_model, P, self._ray_xy_points)
         self._dm_motion_offsets = dm_motion_offsets.to(device=dev, dtype=f32).contiguous()
         self._terrains_per_motion = int(self._dm_motion_offsets.shape[1])
         assert self._dm_motion_offsets.shape[0] >= motion_lib.num_motions()

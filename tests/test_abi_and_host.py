@@ -67,43 +67,93 @@ def _tree_parts(model):
     from parc_b200 import _lib
     L = _lib.lib()
     ent = np.full((4, 32), -1, dtype=np.int32)
-    max_len, n_slots = ctypes.c_int32(), ctypes.c_int32()
+    max_len, n_slots, root_slot = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
     _lib.check(L.parc_b200_tree_parts(model._cstruct(), ent.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), ctypes.byref(max_len),
-                                      ctypes.byref(n_slots)))
-    return ent, max_len.value, n_slots.value
+                                      ctypes.byref(n_slots), ctypes.byref(root_slot)))
+    return ent, max_len.value, n_slots.value, root_slot.value
 
 
-def test_tree_parts_partition_the_humanoid():
-    """The fused step walks the joint tree in 4 ancestor-closed parts (one lane each). Every joint is
-    owned by exactly one part, a part contains the ancestors of its joints, and replaying the slot
-    plan never reads a transform that was overwritten."""
+def _replay_schedule(parents, ent, n_iter, n_slots, root_slot):
+    """Replays the joint schedule the way the kernel does: per lane a register holding the transform of the body it
+    evaluated last (the root at first), per 4-lane group `n_slots` shared slots; reads of an iteration happen before its
+    writes become visible to other lanes."""
+    J = len(parents)
+    reg = [0, 0, 0, 0]
+    slots = {root_slot: 0} if root_slot >= 0 else {}
+    done_at = {0: -1}
+    for it in range(n_iter):
+        writes = []
+        for lane in range(4):
+            e = int(ent[lane][it])
+            if e < 0:
+                continue
+            j, from_slot, rslot = e & 0xFF, (e >> 16) & 1, (e >> 17) & 31
+            publish, wslot, has_kids = (e >> 22) & 1, (e >> 23) & 31, (e >> 28) & 1
+            assert 1 <= j < J and j not in done_at, "joint %d evaluated twice" % j
+            par = parents[j]
+            assert par in done_at and done_at[par] < it, "joint %d runs before its parent is available" % j
+            if from_slot:
+                assert rslot < n_slots and slots.get(rslot) == par, "joint %d would read a stale slot" % j
+            else:
+                assert reg[lane] == par, "joint %d: the lane's registers hold body %d, not the parent %d" % (j, reg[lane], par)
+            assert has_kids == int(j in parents)
+            reg[lane] = j
+            done_at[j] = it
+            if publish:
+                assert has_kids and wslot < n_slots
+                writes.append((wslot, j))
+        for w, j in writes:
+            slots[w] = j
+    return done_at
+
+
+def test_joint_schedule_of_the_humanoid():
+    """The fused step evaluates the joint tree on 4 lanes per (env, pose) along a host-made schedule: every joint exactly
+    once, after its parent, with the parent transform where the entry says it is; as many iterations as the tree is deep."""
     model = H.product_model("cpu")
     parents = [int(p) for p in model._parent_indices.tolist()]
     J = len(parents)
-    ent, max_len, n_slots = _tree_parts(model)
-    owned = []
-    for b in range(4):
-        seen, slot_holds = set(), {}
-        entries = [int(e) for e in ent[b] if e >= 0]
-        assert len(entries) <= max_len
-        for e in entries:
-            j, own, st, ps = e & 0xFF, (e >> 8) & 1, ((e >> 12) & 0xF) - 1, ((e >> 16) & 0xF) - 1
-            assert 1 <= j < J
-            par = parents[j]
-            assert par == 0 or par in seen, "part %d is not ancestor-closed at joint %d" % (b, j)
-            if par == 0:
-                assert ps == -1
-            else:
-                assert 0 <= ps < n_slots and slot_holds.get(ps) == par, "joint %d would read a stale parent transform" % j
-            if st >= 0:
-                assert st < n_slots
-                slot_holds[st] = j
-            seen.add(j)
-            if own:
-                owned.append(j)
-    assert sorted(owned) == list(range(1, J)), "each joint must be produced exactly once"
-    assert max_len <= (J - 1 + 3) // 4 + 2          # balanced within the duplicated chain prefix
-    assert n_slots == 1                              # humanoid: chains only, children take over the parent's slot
+    ent, n_iter, n_slots, root_slot = _tree_parts(model)
+    assert root_slot == -1
+    done_at = _replay_schedule(parents, ent, n_iter, n_slots, root_slot)
+    assert sorted(done_at) == list(range(J)), "each joint must be produced exactly once"
+    depth = [0] * J
+    for j in range(1, J):
+        depth[j] = depth[parents[j]] + 1
+    assert n_iter == max(max(depth), -(-(J - 1) // 4))          # humanoid: 4 = tree depth = ceil(14 / 4)
+    assert n_slots == 1                                          # only the torso is needed by other lanes / later
+
+
+def test_joint_schedule_of_random_trees():
+    from parc_b200 import _lib
+    rng = np.random.default_rng(5)
+    for J in (1, 2, 5, 9, 17, 32):
+        for _ in range(6):
+            cs = _lib.CharModelStruct()
+            cs.num_bodies, cs.dof_size = J, 0
+            parents = [-1] + [int(rng.integers(0, j)) for j in range(1, J)]
+            for j in range(J):
+                cs.parent[j] = parents[j]
+                cs.local_rot[j][3] = 1.0
+            ent = np.full((4, 32), -1, dtype=np.int32)
+            n_iter, n_slots, root_slot = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+            _lib.check(_lib.lib().parc_b200_tree_parts(cs, ent.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), ctypes.byref(n_iter),
+                                                       ctypes.byref(n_slots), ctypes.byref(root_slot)))
+            done_at = _replay_schedule([0] + parents[1:], ent, n_iter.value, n_slots.value, root_slot.value)
+            assert sorted(done_at) == list(range(J))
+            assert 1 <= n_slots.value <= 32
+
+
+def test_ray_points_lattice_detection():
+    from parc_b200 import _lib, synth
+    assert _lib.ray_points_lattice(synth.grid_ray_points()) == (32, 32)
+    assert _lib.ray_points_lattice(synth.cone_ray_points()) == (0, 0)
+    pts = synth.grid_ray_points().clone()
+    pts[37, 1] += 1e-7                                           # one point off the lattice by an ulp
+    assert _lib.ray_points_lattice(pts) == (0, 0)
+    xs, ys = torch.linspace(-1, 1, 5), torch.linspace(0, 3, 7)
+    x, y = torch.meshgrid(xs, ys, indexing="ij")
+    assert _lib.ray_points_lattice(torch.stack([x, y], -1).reshape(-1, 2)) == (5, 7)
 
 
 def test_obs_dim_matches_reference_layout():
