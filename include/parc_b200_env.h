@@ -237,6 +237,19 @@ int parc_b200_compute_tracking_error(const float* root_pos, const float* root_ro
 int parc_b200_fail_rate_ema(const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
                             int32_t num_motions, float* cdf, int32_t* scratch, void* stream);
 
+/* Allocation-free variant of parc_b200_fail_rate_ema. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). Same inputs, outputs and results as parc_b200_fail_rate_ema, but the scratch is a
+ * file-scope device array inside the library (PARC_EMA_NOALLOC_MAX_INTS int32 = 4 MiB, held by every GPU that loads the
+ * library until exit); the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: 2 * num_motions + num_envs <= PARC_EMA_NOALLOC_MAX_INTS, otherwise PARC_ERR_INVALID_ARG with a message naming
+ * the limit. All calls on a device share the one array, which keeps the last call's contents (the kernel clears what it
+ * needs at zero before use): calls that overlap on the GPU -- different streams without an ordering between them -- race;
+ * serialise them or use parc_b200_fail_rate_ema with separate scratch buffers. */
+#define PARC_EMA_NOALLOC_MAX_INTS (1 << 20)
+int parc_b200_fail_rate_ema_noalloc(const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
+                                    int32_t num_motions, float* cdf, void* stream);
+
 /* DeepMimicEnv.reset (dm_env.py:567-592) for env_ids [n] i64 given the random draws the reference
  * takes from torch's generator: motion_ids [n] i64 (sample_motions / demo-mode ids),
  * terrain_ids [n] i64 (randint), motion_times [n] f32 (sample_time or len*start_fraction),

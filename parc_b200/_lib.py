@@ -14,6 +14,7 @@ MAX_BODIES = 32
 MAX_TAR_STEPS = 16
 MAX_KEY_BODIES = 8
 MAX_DOFS = 96
+EMA_NOALLOC_MAX_INTS = 1 << 20      # PARC_EMA_NOALLOC_MAX_INTS, include/parc_b200_env.h
 
 PARC_OK = 0
 PARC_ERR_INVALID_ARG = -1
@@ -225,6 +226,7 @@ def _declare(lib):
                                    i32, i64, vp, vp],
         "parc_b200_compute_tracking_error": [vp] * 14 + [i32, i32, i64, vp, vp],
         "parc_b200_fail_rate_ema": [P(EnvConfigStruct), P(EnvBuffersStruct), i32, vp, vp, vp],
+        "parc_b200_fail_rate_ema_noalloc": [P(EnvConfigStruct), P(EnvBuffersStruct), i32, vp, vp],
         "parc_b200_env_reset": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),
                                 vp, i64, vp, vp, vp, vp, vp, vp, vp],
         "parc_b200_env_reset_sampled": [P(CharModelStruct), P(MotionLibStruct), P(TerrainStruct),

@@ -658,3 +658,51 @@ __global__ void zero_int_kernel(int* p) { *p = 0; }
 }  // namespace parc
 
 #include "env_aux_api.cuh"
+
+// ---- allocation-free variant of the fail-rate EMA (no counterpart in the reference) ---------------
+// The scratch of fail_rate_ema_kernel lives in a file-scope device array instead of a caller buffer, so a caller that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) needs nothing but its inputs and
+// outputs. Every GPU that loads the library holds PARC_EMA_NOALLOC_MAX_INTS * 4 bytes (4 MiB) until exit. In host code
+// the array's NAME is a host-side stand-in, not a device address: the address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and passed to the kernel.
+static __device__ __align__(256) int32_t g_ema_noalloc_scratch[PARC_EMA_NOALLOC_MAX_INTS];
+
+extern "C" int parc_b200_fail_rate_ema_noalloc(const parc_env_config_t* cfg, const parc_env_buffers_t* env, int32_t num_motions,
+                                               float* cdf, void* stream) {
+    PARC_REQUIRE(cfg && env && num_motions > 0, "fail_rate_ema_noalloc: bad arguments");
+    PARC_REQUIRE(env->done_count && env->done_list && env->done_code && env->motion_ids && env->motion_id_fail_rates,
+                 "fail_rate_ema_noalloc: done/fail-rate buffers not set");
+    PARC_REQUIRE(cdf == nullptr || env->motion_weights, "fail_rate_ema_noalloc: motion_weights not set");
+    PARC_REQUIRE(env->num_envs >= 0, "fail_rate_ema_noalloc: num_envs < 0");
+    const long long need = 2ll * num_motions + env->num_envs;      // hist[M] | offs[M] | bucket[<= N]
+    PARC_REQUIRE(need <= (long long)PARC_EMA_NOALLOC_MAX_INTS,
+                 "fail_rate_ema_noalloc: 2 * num_motions + num_envs = %lld exceeds the built-in scratch of %d int32 "
+                 "(PARC_EMA_NOALLOC_MAX_INTS); use parc_b200_fail_rate_ema with a caller-provided scratch",
+                 need, (int)PARC_EMA_NOALLOC_MAX_INTS);
+    // per-device set-up, done once with that device current: address of the scratch, opt-in shared memory of the kernel
+    static int32_t* scratch_of_device[64] = {};
+    int dev = -1;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess) { set_error("fail_rate_ema_noalloc: cudaGetDevice: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+    PARC_REQUIRE(dev >= 0 && dev < 64, "fail_rate_ema_noalloc: device ordinal %d outside [0, 64)", dev);
+    if (scratch_of_device[dev] == nullptr) {
+        int32_t* p = nullptr;
+        ce = cudaGetSymbolAddress((void**)&p, g_ema_noalloc_scratch);
+        if (ce != cudaSuccess || p == nullptr) {
+            set_error("fail_rate_ema_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(ce));
+            return PARC_ERR_CUDA;
+        }
+        ce = cudaFuncSetAttribute(fail_rate_ema_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
+        if (ce != cudaSuccess) { set_error("fail_rate_ema_noalloc: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+        scratch_of_device[dev] = p;
+    }
+    // same staging rule as parc_b200_fail_rate_ema: per-motion tables in shared memory when they fit in 64 KB, then as much
+    // bucket as is left of 200 KB. The kernel zeroes the histogram it uses before counting, so the array's stale contents
+    // (every call shares it and leaves its last state behind) are never read.
+    const int tables = (size_t)num_motions * 8 <= 64 * 1024;
+    const size_t table_bytes = tables ? (size_t)num_motions * 8 : 0;
+    const long long cap = std::min<long long>(env->num_envs, (long long)((200 * 1024 - table_bytes) / 4));
+    const size_t smem = table_bytes + (size_t)cap * 4;
+    fail_rate_ema_kernel<<<1, EMA_THREADS, smem, as_stream(stream)>>>(*cfg, *env, num_motions, cdf, scratch_of_device[dev], tables, (int)cap);
+    return check_launch("fail_rate_ema_noalloc");
+}
