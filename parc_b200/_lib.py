@@ -270,7 +270,8 @@ def lib():
     global _lib, EXPORTED_SYMBOLS
     with _lock:
         if _lib is None:
-            path = _build.build()
+            import os
+            path = os.environ.get("PARC_B200_LIB") or _build.build()      # PARC_B200_LIB: a debug build of the same sources (profiles/)
             handle = C.CDLL(str(path))
             EXPORTED_SYMBOLS = sorted(_declare(handle).keys()) + ["parc_b200_version", "parc_b200_last_error"]
             _lib = handle

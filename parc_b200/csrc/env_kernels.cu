@@ -36,6 +36,14 @@
 
 namespace parc {
 
+// Debug build only (-DPARC_STEP_TIMING, profiles/step_stamps.py): per-block clock stamps at the phase boundaries.
+#ifdef PARC_STEP_TIMING
+__device__ long long g_step_stamps[16 * 16384];
+#define PARC_STAMP(k) do { if (threadIdx.x == 0 && blockIdx.x < 16384) g_step_stamps[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+#else
+#define PARC_STAMP(k) do { } while (0)
+#endif
+
 #ifndef PARC_STEP_TILE
 #define PARC_STEP_TILE 16                      // envs per block; a multiple of 8
 #endif
@@ -491,6 +499,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     auto refp = [&](int field_off, int w, int el) -> float* { return s_ref + field_off * TILE + el * w; };
 
     // ================================ phase A ====================================================
+    PARC_STAMP(0);
     PARC_COLD_LOOP
     for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_sched[k] = sp.sched[k];
     PARC_COLD_LOOP
@@ -576,6 +585,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         }
     }
     __syncthreads();
+    PARC_STAMP(1);
 
     // A.4 lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares
     if (LATTICE && do_heights) {
@@ -621,6 +631,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     }
 
     // ================================ phase B ====================================================
+    PARC_STAMP(2);
     static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART lanes");
     const bool pose_work = do_obs || need_ref_pose;
     // warp w takes poses w, w + 8, ...; lane = (env, part). Rows past a partial tile hold a copy of the tile's first row
@@ -788,6 +799,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         }
     }
     __syncthreads();
+    PARC_STAMP(3);
 
     // ================================ phase C ====================================================
     // per-(env, item) terms; item lists are flattened over the tile so that every lane has work
@@ -935,6 +947,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     }
     if (obs_bulk || ref_bulk) fence_async_smem();   // the staged rows / blocks are about to be read by the bulk-copy engine
     __syncthreads();
+    PARC_STAMP(4);
 
     // ================================ phase E (issue) =============================================
     // Everything staged is final: hand the aligned body of each observation row and the ref_* blocks to the bulk-copy
@@ -963,6 +976,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     if (bulk_pending) bulk_commit();
 
     // ================================ phase D ====================================================
+    PARC_STAMP(5);
     if (tid < tile_rows && (do_reward || do_done)) {
         const int el = tid;
         const EnvU& u = s_env[el];
@@ -1056,6 +1070,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         }
     }
 
+    PARC_STAMP(6);
     // ================================ phase H ====================================================
     // _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145): one warp per env, rows handed out by a shared
     // counter (the warp that ran phase D joins late and takes what is left). The samples depend only on the phase A
@@ -1093,6 +1108,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         }
     }
 
+    PARC_STAMP(7);
     // ================================ phase E (general) ===========================================
     // staged values -> global with plain stores where the bulk path does not apply: warp w streams env w
     {
@@ -1124,6 +1140,10 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         }
     }
     if (bulk_pending) bulk_wait_read();   // the shared-memory sources must outlive the copies
+    PARC_STAMP(8);
+#ifdef PARC_STEP_TIMING
+    if (threadIdx.x == 0 && blockIdx.x < 16384) { unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); g_step_stamps[blockIdx.x * 16 + 15] = smid; }
+#endif
 }
 
 }  // namespace parc
@@ -1139,6 +1159,13 @@ __global__ void selftest_div_kernel(const float* __restrict__ x, long long n, fl
 }  // namespace parc
 
 using namespace parc;
+
+#ifdef PARC_STEP_TIMING
+extern "C" int parc_b200_debug_step_stamps(long long* h_out, int n_blocks) {
+    cudaError_t ce = cudaMemcpyFromSymbol(h_out, g_step_stamps, sizeof(long long) * 16 * (size_t)n_blocks);
+    return ce == cudaSuccess ? 0 : -3;
+}
+#endif
 
 namespace parc {
 // packed_cell against the scalar, separately rounded ray_world + grid_index for n points of one (heading, root) pair

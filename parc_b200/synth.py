@@ -107,6 +107,14 @@ def make_clips(spec, num_motions, seed=1234, min_frames=60, max_frames=300, fps=
     return clips
 
 
+def num_padding_cells(padding, dx):
+    """dm_env.py:159-166: `int(padding / dx)` after asserting that the quotient is (nearly) whole -- int() TRUNCATES, so
+    padding 1.2 at dx 0.4 (2.9999999999999996) gives 2 cells; reproduced as is."""
+    n = float(padding) / float(dx)
+    assert (round(n) - n) < 1e-5
+    return int(n)
+
+
 def build_terrain_square(clips, padding_cells=1, x_offset=0.0, y_offset=0.0):
     """Blocky grid tiling all clips' terrains, same placement rule as
     DeepMimicEnv.build_terrain_square (PARC/motion_tracker/envs/ig_parkour/dm_env.py:157-316):
@@ -143,11 +151,18 @@ def build_terrain_square(clips, padding_cells=1, x_offset=0.0, y_offset=0.0):
     return hf, min_point, dx, offs
 
 
+def xy_grid_points(dx, dy, num_x_neg, num_x_pos, num_y_neg, num_y_pos, center=(0.0, 0.0)):
+    """geom_util.get_xy_grid_points (PARC/util/geom_util.py:212-224) flattened to [P, 2]: meshgrid(xs, ys, 'ij')."""
+    c = torch.tensor(center, dtype=torch.float32)
+    xs = torch.linspace(c[0] - dx * num_x_neg, c[0] + dx * num_x_pos, num_x_neg + num_x_pos + 1)
+    ys = torch.linspace(c[1] - dy * num_y_neg, c[1] + dy * num_y_pos, num_y_neg + num_y_pos + 1)
+    x, y = torch.meshgrid(xs, ys, indexing="ij")
+    return torch.stack([x, y], dim=-1).reshape(-1, 2).contiguous()
+
+
 def grid_ray_points(n_neg=15, n_pos=16, d=0.1):
     """geom_util.get_xy_grid_points(center=0, dx=dy=d, 15/16/15/16) -> [1024, 2] for the 32x32 config."""
-    xs = torch.linspace(-d * n_neg, d * n_pos, n_neg + n_pos + 1)
-    x, y = torch.meshgrid(xs, xs, indexing="ij")
-    return torch.stack([x, y], dim=-1).reshape(-1, 2).contiguous()
+    return xy_grid_points(d, d, n_neg, n_pos, n_neg, n_pos)
 
 
 def cone_ray_points(dx=0.05, num_neg=2, num_pos=60, rays_neg=3, rays_pos=3, angle=0.26179938779):
