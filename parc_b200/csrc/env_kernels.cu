@@ -17,6 +17,8 @@
 //   H  all warps sample the heightmaps (straight to global memory); rows are handed out by a shared counter
 //   E  copy-out: cp.async.bulk (TMA) of each staged observation row and of the ref_* blocks, issued right after phase C
 //      so that the copies run under D / H; plain stores for partial tiles, row subsets and strided ref views
+#include <string.h>
+
 #include "parc_common.cuh"
 #include "parc_lanes.cuh"
 
@@ -30,8 +32,33 @@
 #ifndef PARC_LATTICE_ROWS
 #define PARC_LATTICE_ROWS 4                   // lattice ray sets: lattice rows (= independent gathers) per lane and loop iteration
 #endif
+#ifndef PARC_HEIGHT_SPLIT
+#define PARC_HEIGHT_SPLIT 1                   // an env's sample points are handed out in this many pieces (load balance across the warps)
+#endif
+#ifndef PARC_PREFETCH_FRAMES
+#define PARC_PREFETCH_FRAMES 0                // 1: a separate stage prefetches the frame records before the pose loop (measured slower: the
+#endif                                        //    root part of a pose touches nearly every line of its two records anyway)
+#ifndef PARC_SPLIT_JOINT_TASKS
+#define PARC_SPLIT_JOINT_TASKS 0              // 1: phase C deals rot_to_dof / pose error / pose termination as separate tasks
+#endif
+#ifndef PARC_TAIL_ROLES
+#define PARC_TAIL_ROLES 1                     // 1: after phase C reward, termination and the bulk hand-over run in different warps
+#endif
+#ifndef PARC_FILL_HEIGHTS
+#define PARC_FILL_HEIGHTS 0                   // 1 (lattice ray sets): warps that would wait at the barriers behind phases A and B sample
+#endif                                        //    heights meanwhile; whatever is left is sampled after phase C. Measured 10 % SLOWER (a unit
+                                              //    once taken delays the barrier it was meant to fill), kept switchable for the record
+#ifndef PARC_STEP_FAST
+#define PARC_STEP_FAST 1                      // 1: full steps of the default humanoid layout run the compile-time-specialised instantiation
+#endif
+#ifndef PARC_STAGGER_NS
+#define PARC_STAGGER_NS 0                     // > 0: the second block of every SM's first wave starts this much later, so that the
+#endif                                        //      latency-bound phases of an SM's two resident blocks do not coincide
 #ifndef PARC_BULK_ROWS
-#define PARC_BULK_ROWS 1                      // 1: staged rows / ref blocks leave through cp.async.bulk where alignment allows
+#define PARC_BULK_ROWS 1                      // 1: the tile's ref_* blocks leave through cp.async.bulk where alignment allows
+#endif
+#ifndef PARC_BULK_OBS
+#define PARC_BULK_OBS 1                       // 1: so do the staged observation rows
 #endif
 
 namespace parc {
@@ -48,6 +75,9 @@ __device__ long long g_step_stamps[16 * 16384];
 #define PARC_STEP_TILE 16                      // envs per block; a multiple of 8
 #endif
 constexpr int TILE = PARC_STEP_TILE;      // envs per block (== warps per block)
+#ifndef PARC_STEP_MIN_BLOCKS
+#define PARC_STEP_MIN_BLOCKS (32 / PARC_STEP_TILE)   // launch bound: 1,024 threads per SM at 64 registers
+#endif
 constexpr int STEP_THREADS = 32 * TILE;
 constexpr int NPART = 4;                  // lanes cooperating on one (env, pose)
 constexpr int NGROUP = STEP_THREADS / NPART;
@@ -63,18 +93,21 @@ struct ObsLayout {
     int obs_dim;
 };
 
-__host__ __device__ inline ObsLayout make_layout(int J, int D, int C, const parc_env_config_t& cfg) {
-    ObsLayout L;
-    const int K = cfg.num_key_bodies, S = cfg.num_tar_steps;
-    L.root_h = cfg.root_height_obs ? 1 : 0;
+__host__ __device__ constexpr ObsLayout layout_of(int J, int D, int C, int K, int S, int P, bool root_h, bool tar_obs, bool contact_info) {
+    ObsLayout L{};
+    L.root_h = root_h ? 1 : 0;
     L.char_dim = L.root_h + 12 + 6 * (J - 1) + D + 3 * K;
     L.tar_step_dim = 9 + 6 * (J - 1) + 3 * K;
     L.o_tar = L.char_dim;
-    L.o_tarc = L.o_tar + (cfg.enable_tar_obs ? S * L.tar_step_dim : 0);
-    L.o_charc = L.o_tarc + ((cfg.use_contact_info && cfg.enable_tar_obs) ? S * C : 0);
-    L.o_hf = L.o_charc + (cfg.use_contact_info ? J : 0);
-    L.obs_dim = L.o_hf + cfg.num_ray_points;
+    L.o_tarc = L.o_tar + (tar_obs ? S * L.tar_step_dim : 0);
+    L.o_charc = L.o_tarc + ((contact_info && tar_obs) ? S * C : 0);
+    L.o_hf = L.o_charc + (contact_info ? J : 0);
+    L.obs_dim = L.o_hf + P;
     return L;
+}
+__host__ __device__ inline ObsLayout make_layout(int J, int D, int C, const parc_env_config_t& cfg) {
+    return layout_of(J, D, C, cfg.num_key_bodies, cfg.num_tar_steps, cfg.num_ray_points, cfg.root_height_obs != 0, cfg.enable_tar_obs != 0,
+                     cfg.use_contact_info != 0);
 }
 
 // Reference-motion outputs (DeepMimicEnv._update_ref_motion, dm_env.py:523-545). The tile's ref_* values are staged
@@ -84,8 +117,8 @@ __host__ __device__ inline ObsLayout make_layout(int J, int D, int C, const parc
 struct RefLayout {
     int root_pos, root_rot, root_vel, root_ang_vel, body_pos, joint_rot, dof_pos, dof_vel, contacts, width;
 };
-__host__ __device__ inline RefLayout make_ref_layout(int J, int D, int C) {
-    RefLayout R;
+__host__ __device__ constexpr RefLayout make_ref_layout(int J, int D, int C) {
+    RefLayout R{};
     R.root_pos = 0; R.root_rot = 3; R.root_vel = 7; R.root_ang_vel = 10; R.body_pos = 13;
     R.joint_rot = R.body_pos + 3 * J;
     R.dof_pos = R.joint_rot + 4 * (J - 1);
@@ -235,42 +268,59 @@ inline void plan_schedule(const parc_char_model_t& cm, const parc_env_config_t& 
     sp.S.n_gslots = ns > 0 ? ns : 1;
 }
 
-inline void make_smem_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, StepPlan& sp) {
-    SmemPlan& p = sp.S;
-    const int J = cm.num_bodies, D = cm.dof_size;
-    const ObsLayout& L = sp.L;
-    const RefLayout& R = sp.R;
+__host__ __device__ constexpr size_t plan_take(size_t& o, size_t bytes) { const size_t at = o; o = (o + bytes + 15) & ~size_t(15); return at; }
+__host__ __device__ constexpr size_t plan_max(size_t a, size_t b) { return a > b ? a : b; }
+// o_hf = staged observation columns, ref_w = RefLayout::width, n_pose = S + 2, lat_nx / lat_ny > 0 for a lattice ray set
+__host__ __device__ constexpr SmemPlan smem_plan_of(int J, int D, int K, int P, int o_hf, int ref_w, int n_pose, int n_gslots, int lat_nx, int lat_ny) {
+    SmemPlan p{};
     // A row starts at a multiple of 4 floats plus the env's shift (0..3), so that column k of the staged row and of the
     // obs_buf row have the same 16-byte phase. Pitch = 4 (mod 32): the 8 envs a warp touches at one column land in
     // banks 4 el + shift -- all different.
-    p.row_pitch = (L.o_hf + 3 + 3) & ~3;
+    p.row_pitch = (o_hf + 3 + 3) & ~3;
     while ((p.row_pitch & 31) != 4) p.row_pitch += 4;
-    p.n_pose = (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2;
-    p.term_pitch = (J - 1) + D + J + cfg.num_key_bodies;
+    p.n_pose = n_pose;
+    p.n_gslots = n_gslots;
+    p.term_pitch = (J - 1) + D + J + K;
     size_t o = 0;
-    auto take = [&](size_t bytes) { const size_t at = o; o = (o + bytes + 15) & ~size_t(15); return at; };
-    p.off_env = take(sizeof(EnvU) * TILE);
-    p.off_row = take(sizeof(float) * TILE * p.row_pitch);
-    p.off_ref = take(sizeof(float) * TILE * R.width);
-    p.off_charq = take(sizeof(float4) * TILE * J);
+    p.off_env = plan_take(o, sizeof(EnvU) * TILE);
+    p.off_row = plan_take(o, sizeof(float) * TILE * p.row_pitch);
+    p.off_ref = plan_take(o, sizeof(float) * TILE * ref_w);
+    p.off_charq = plan_take(o, sizeof(float4) * TILE * J);
     // The group slots are only live in phase B; the reward terms (phase C/D) and the ref_* scatter map (built in phase C,
     // read in phase E) reuse the same bytes.
-    const size_t gx_bytes = sizeof(float) * 7 * p.n_gslots * NGROUP;
+    const size_t gx_bytes = sizeof(float) * 7 * n_gslots * NGROUP;
     const size_t terms_bytes = (sizeof(float) * TILE * p.term_pitch + 15) & ~size_t(15);
     p.off_gx = p.off_terms = o;
     p.off_refmap = o + terms_bytes;
-    take(std::max(gx_bytes, terms_bytes + 16 * (size_t)R.width));
-    p.off_tab = take(sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J);
-    if (sp.lat_nx > 0) {
-        p.off_pts = take(sizeof(float) * (sp.lat_nx + sp.lat_ny));            // lattice axes xs | ys
-        p.off_lat = take(sizeof(float2) * TILE * sp.lat_nx);                   // per env and lattice row: (x c, x s)
+    plan_take(o, plan_max(gx_bytes, terms_bytes + 16 * (size_t)ref_w));
+    p.off_tab = plan_take(o, sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J);
+    if (lat_nx > 0) {
+        p.off_pts = plan_take(o, sizeof(float) * (lat_nx + lat_ny));            // lattice axes xs | ys
+        p.off_lat = plan_take(o, sizeof(float2) * TILE * lat_nx);                // per env and lattice row: (x c, x s)
     } else {
-        p.off_pts = take(sizeof(float2) * (size_t)cfg.num_ray_points);        // ray_xy_points, shared by the tile's envs
+        p.off_pts = plan_take(o, sizeof(float2) * (size_t)P);                   // ray_xy_points, shared by the tile's envs
         p.off_lat = o;
     }
-    p.off_ctr = take(16);
+    p.off_ctr = plan_take(o, 16);
     p.total = o;
+    return p;
 }
+inline void make_smem_plan(const parc_char_model_t& cm, int C, const parc_env_config_t& cfg, StepPlan& sp) {
+    const int n_gslots = sp.S.n_gslots;      // set by plan_schedule
+    sp.S = smem_plan_of(cm.num_bodies, cm.dof_size, cfg.num_key_bodies, cfg.num_ray_points, sp.L.o_hf, sp.R.width,
+                        (cfg.enable_tar_obs ? cfg.num_tar_steps : 0) + 2, n_gslots, sp.lat_nx, sp.lat_ny);
+}
+
+// The layout the specialised instantiation of the step kernel is compiled for: the reference's shipped humanoid
+// (data/assets/humanoid.xml: 15 bodies, 28 dofs) with the shipped observation config (dm_env_default.yaml: 6 target steps,
+// 4 key bodies, contact labels, local observations) on a 32 x 32 lattice of ray points. Every size, column offset and
+// shared-memory offset is then a compile-time constant; anything else runs the generic instantiation.
+struct FastDims {
+    static constexpr int J = 15, D = 28, C = 15, S = 6, K = 4, NX = 32, NY = 32, P = NX * NY, N_ITER = 4;
+};
+constexpr ObsLayout kFastL = layout_of(FastDims::J, FastDims::D, FastDims::C, FastDims::K, FastDims::S, FastDims::P, false, true, true);
+constexpr RefLayout kFastR = make_ref_layout(FastDims::J, FastDims::D, FastDims::C);
+constexpr SmemPlan kFastS = smem_plan_of(FastDims::J, FastDims::D, FastDims::K, FastDims::P, kFastL.o_hf, kFastR.width, FastDims::S + 2, 1, FastDims::NX, FastDims::NY);
 
 static bool view_is_rows(const parc_view3_t& v, int a, int b) {
     // [N, a, b] (b = 0: [N, a]) row-major without gaps, base 16-byte aligned
@@ -445,6 +495,8 @@ __device__ __forceinline__ void heights_of_env_lattice(const float2* __restrict_
     }
 }
 
+__device__ __forceinline__ int ld_flag(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ void st_flag(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 // shared -> global bulk copy (TMA, no tensor map): both addresses 16-byte aligned, bytes a multiple of 16
 __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
@@ -454,24 +506,43 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-template <int THREADS, bool LATTICE>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
+// FAST: the layout of FastDims / kFastL / kFastR / kFastS with the shipped default flags, all rows (no env_ids), every part --
+// the launcher checks all of that; sizes, offsets and flags are then compile-time constants.
+template <int THREADS, bool LATTICE, bool FAST>
+__global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel(
     const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
     const __grid_constant__ parc_terrain_t terrain, const __grid_constant__ parc_env_config_t cfg,
     const __grid_constant__ parc_env_buffers_t env, const __grid_constant__ StepPlan sp, const unsigned parts,
     const long long* __restrict__ env_ids, const long long n_rows_host, const int* __restrict__ env_ids32,
     const int* __restrict__ n_rows_dev, const long long first_env) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const long long n_rows = n_rows_dev ? min((long long)*n_rows_dev, n_rows_host) : n_rows_host;
+    static_assert(!FAST || LATTICE, "the specialised instantiation is a lattice one");
+    const int* n_rows_dev_ = FAST ? nullptr : n_rows_dev;
+    const long long* env_ids_ = FAST ? nullptr : env_ids;
+    const int* env_ids32_ = FAST ? nullptr : env_ids32;
+    const long long n_rows = n_rows_dev_ ? min((long long)*n_rows_dev_, n_rows_host) : n_rows_host;
     const long long row0 = (long long)blockIdx.x * TILE;
     if (row0 >= n_rows) return;
     const int tid = threadIdx.x;
-    const int J = cm.num_bodies, D = cm.dof_size, C = lib.num_contacts;
-    const int S = cfg.enable_tar_obs ? cfg.num_tar_steps : 0;
-    const int K = cfg.num_key_bodies, P = cfg.num_ray_points;
-    const ObsLayout& L = sp.L;
-    const RefLayout& R = sp.R;
-    const SmemPlan& plan = sp.S;
+    const int J = FAST ? FastDims::J : cm.num_bodies, D = FAST ? FastDims::D : cm.dof_size, C = FAST ? FastDims::C : lib.num_contacts;
+    const int S = FAST ? FastDims::S : (cfg.enable_tar_obs ? cfg.num_tar_steps : 0);
+    const int K = FAST ? FastDims::K : cfg.num_key_bodies, P = FAST ? FastDims::P : cfg.num_ray_points;
+    constexpr ObsLayout FL = layout_of(FastDims::J, FastDims::D, FastDims::C, FastDims::K, FastDims::S, FastDims::P, false, true, true);
+    constexpr RefLayout FR = make_ref_layout(FastDims::J, FastDims::D, FastDims::C);
+    constexpr SmemPlan FS = smem_plan_of(FastDims::J, FastDims::D, FastDims::K, FastDims::P, FL.o_hf, FR.width, FastDims::S + 2, 1, FastDims::NX, FastDims::NY);
+    const ObsLayout L = FAST ? FL : sp.L;
+    const RefLayout R = FAST ? FR : sp.R;
+    const SmemPlan plan = FAST ? FS : sp.S;
+    const int lat_nx = FAST ? FastDims::NX : sp.lat_nx, lat_ny = FAST ? FastDims::NY : sp.lat_ny;
+    const int irec_f = FAST ? interp_record_floats(FastDims::J, FastDims::C) : lib.irec, vrec_f = FAST ? vel_record_floats(FastDims::D) : lib.vrec;
+    // config flags (dm_env_default.yaml values in the specialised instantiation)
+    const bool c_global_obs = FAST ? false : cfg.global_obs != 0, c_contact_info = FAST ? true : cfg.use_contact_info != 0;
+    const bool c_track_root = FAST ? true : cfg.track_root != 0, c_track_root_h = FAST ? true : cfg.track_root_h != 0;
+    const bool c_early_term = FAST ? true : cfg.enable_early_termination != 0, c_pose_term = FAST ? true : cfg.pose_termination != 0;
+    const int c_n_fall = FAST ? 0 : cfg.num_fall_contact_bodies;
+    const bool c_never_done = FAST ? false : cfg.never_done != 0;
+    const bool lrot_ident_ = FAST ? true : sp.lrot_ident != 0;
+    const int n_iter = FAST ? FastDims::N_ITER : sp.n_iter, root_slot = FAST ? -1 : sp.root_slot;
     EnvU* s_env = reinterpret_cast<EnvU*>(smem_raw + plan.off_env);
     float* s_row = reinterpret_cast<float*>(smem_raw + plan.off_row);
     float* s_ref = reinterpret_cast<float*>(smem_raw + plan.off_ref);
@@ -484,20 +555,68 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     float2* s_pts = reinterpret_cast<float2*>(smem_raw + plan.off_pts);     // general ray set
     float* s_axes = reinterpret_cast<float*>(smem_raw + plan.off_pts);      // lattice: xs[nx] | ys[ny]
     float2* s_lat = reinterpret_cast<float2*>(smem_raw + plan.off_lat);     // lattice: [TILE][nx] (x c, x s)
-    int* s_ctr = reinterpret_cast<int*>(smem_raw + plan.off_ctr);
+    int* s_ctr = reinterpret_cast<int*>(smem_raw + plan.off_ctr);          // [0] height-unit counter [1] uniforms + lattice table ready [2] clip chain done [3] poses done
     const int ROWP = plan.row_pitch;
 
-    const bool do_heights = parts & PARC_STEP_HEIGHTS;
-    const bool do_obs = parts & PARC_STEP_OBS;
-    const bool do_ref = parts & PARC_STEP_REF;
-    const bool do_reward = parts & PARC_STEP_REWARD;
-    const bool do_done = parts & PARC_STEP_DONE;
+    const bool do_heights = FAST || (parts & PARC_STEP_HEIGHTS);
+    const bool do_obs = FAST || (parts & PARC_STEP_OBS);
+    const bool do_ref = FAST || (parts & PARC_STEP_REF);
+    const bool do_reward = FAST || (parts & PARC_STEP_REWARD);
+    const bool do_done = FAST || (parts & PARC_STEP_DONE);
+    const bool do_time = FAST || (parts & PARC_STEP_TIME);
     const bool need_ref_pose = do_ref || do_reward || do_done;
     const bool need_char_q = do_obs || do_reward;
     const int tile_rows = (int)min((long long)TILE, n_rows - row0);
     // the tile's ref_* block of field f (see RefLayout): [TILE][w] floats
     auto refp = [&](int field_off, int w, int el) -> float* { return s_ref + field_off * TILE + el * w; };
 
+    // ---- height units -------------------------------------------------------------------------------------------------
+    // _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145): a unit = one piece of one env's sample points, done
+    // by one warp; units are handed out by a shared counter. The samples depend only on the root / heading uniforms of
+    // phase A and go straight to global memory, so a unit can run whenever a warp has nothing else to do. `stop` (may be
+    // NULL): give up as soon as *stop >= stop_val (the event the caller is waiting for has happened).
+    auto height_units = [&](const int* stop, const int stop_val) {
+        if (!(P > 0 && (do_heights || do_obs))) return;
+        const int lane = tid & 31;
+        HeightArgs ha;
+        ha.hf = terrain.hf; ha.dimy = terrain.dim_y; ha.imx = terrain.dim_x - 1; ha.imy = terrain.dim_y - 1;
+        ha.nmn = make_float2(-terrain.min_x, -terrain.min_y); ha.rd2 = make_float2(sp.rdx, sp.rdy); ha.nd2 = make_float2(-terrain.dx, -terrain.dy);
+        ha.lo = cfg.min_obs_h; ha.hi = cfg.max_obs_h;
+        // an env's sample points in PARC_HEIGHT_SPLIT pieces, so that the warps finish together
+        constexpr int HS = PARC_HEIGHT_SPLIT;
+        const bool split = LATTICE ? (lat_nx % (HS * PARC_LATTICE_ROWS) == 0) : (P % (HS * 32 * PARC_HEIGHT_GATHERS) == 0);
+        const int n_piece = split ? HS : 1;
+        const int ppp = P / n_piece;                 // points per piece
+        for (;;) {
+            int unit = 0x7fffffff;
+            if (lane == 0 && !(stop && ld_flag(stop) >= stop_val)) unit = atomicAdd(s_ctr, 1);
+            unit = __shfl_sync(FULL_MASK, unit, 0);
+            if (unit >= tile_rows * n_piece) break;
+            const int el = unit / n_piece, p0 = (unit - el * n_piece) * ppp;
+            const EnvU& u = s_env[el];
+            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf + p0 : nullptr;
+            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P + p0 : nullptr;
+            if (do_heights) {
+                ha.g2 = make_float2(u.g.x, u.g.y); ha.gz = u.g.z;
+                if (LATTICE) {
+                    const int nxp = lat_nx / n_piece;
+                    const float2* a = s_lat + el * lat_nx + (unit - el * n_piece) * nxp;
+                    const float y = s_axes[lat_nx + lane];
+                    if (orow && hrow) heights_of_env_lattice<true, true>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                    else if (orow) heights_of_env_lattice<false, true>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                    else heights_of_env_lattice<true, false>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                } else {
+                    const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch);
+                    if (ppp % (32 * PARC_HEIGHT_GATHERS) == 0) heights_of_env<true>(s_pts + p0, ppp, lane, ha, cs, nsc, hrow, orow);
+                    else heights_of_env<false>(s_pts + p0, ppp, lane, ha, cs, nsc, hrow, orow);
+                }
+            } else if (orow) {
+                for (int p = lane; p < ppp; p += 32) orow[p] = hrow[p];
+            }
+        }
+    };
+
+    if (PARC_STAGGER_NS > 0 && blockIdx.x >= kNumSMs && blockIdx.x < 2 * kNumSMs) __nanosleep(PARC_STAGGER_NS);
     // ================================ phase A ====================================================
     PARC_STAMP(0);
     PARC_COLD_LOOP
@@ -507,13 +626,18 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
-    if (tid == 0) *s_ctr = 0;
+    // Heights as filler work (PARC_FILL_HEIGHTS): the lattice kernel hands height units to warps that would otherwise wait at a
+    // barrier. The flags must read zero before anybody polls them (shared memory keeps the previous block's bytes).
+    const bool fill = PARC_FILL_HEIGHTS && LATTICE && do_heights && P > 0;
+    if (tid < 4) s_ctr[tid] = 0;
+    if (fill) __syncthreads();
     if (do_heights) {
         if (LATTICE) {
-            // xs[i] = x of point i * ny, ys[j] = y of point j
+            // xs[i] = x of point i * ny, ys[j] = y of point j (by the uniforms warp alone when the heights are filler work:
+            // its ready flag then covers them)
             PARC_COLD_LOOP
-            for (int k = tid; k < sp.lat_nx + sp.lat_ny; k += THREADS)
-                s_axes[k] = k < sp.lat_nx ? __ldg(env.ray_xy_points + 2 * (long long)k * sp.lat_ny) : __ldg(env.ray_xy_points + 2 * (k - sp.lat_nx) + 1);
+            for (int k = fill ? tid - (THREADS - 32) : tid; k >= 0 && k < lat_nx + lat_ny; k += fill ? 32 : THREADS)
+                s_axes[k] = k < lat_nx ? __ldg(env.ray_xy_points + 2 * (long long)k * lat_ny) : __ldg(env.ray_xy_points + 2 * (k - lat_nx) + 1);
         } else {
             PARC_COLD_LOOP
             for (int k = tid; k < P; k += THREADS) s_pts[k] = __ldg(reinterpret_cast<const float2*>(env.ray_xy_points) + k);
@@ -523,12 +647,13 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     //     time -> motion id -> clip meta -> terrain offset (the warp before it); each writes its own fields of s_env[el].
     //     Rows past the end of a partial tile are filled with the tile's first row: every lane of phases B / C then works on
     //     valid data, and only stores to global memory look at `live`.
-    if (tid >= THREADS - 32 && tid < THREADS - 32 + TILE) {
+    if (tid >= THREADS - 32) {
+      if (tid < THREADS - 32 + TILE) {
         const int el = tid - (THREADS - 32);
         EnvU& u = s_env[el];
         const int live = el < tile_rows;
         const long long row = row0 + (live ? el : 0);
-        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
+        const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
         u.live = live;
         u.e = e;
         const Vec3 c_pos = view_ld_vec3(env.char_root_pos, e);
@@ -545,14 +670,30 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         u.flags = 0;
         u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
         if (need_char_q) s_charq[el * J] = quat_to_f4(c_rot);
-    } else if (tid >= THREADS - 64 && tid < THREADS - 64 + TILE) {
+      }
+      if (fill) {
+        // lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares; then
+        // publish: from here on any warp may sample the heights of this tile's envs
+        __syncwarp();
+        PARC_COLD_LOOP
+        for (int k = tid - (THREADS - 32); k < TILE * lat_nx; k += 32) {
+            const int el = k / lat_nx, i = k - el * lat_nx;
+            const float x = s_axes[i];
+            s_lat[k] = make_float2(__fmul_rn(x, s_env[el].ch), __fmul_rn(x, s_env[el].sh));
+        }
+        __threadfence_block();
+        __syncwarp();
+        if (tid == THREADS - 32) st_flag(s_ctr + 1, 1);
+      }
+    } else if (tid >= THREADS - 64) {
+      if (tid < THREADS - 64 + TILE) {
         const int el = tid - (THREADS - 64);
         EnvU& u = s_env[el];
         const int live = el < tile_rows;
         const long long row = row0 + (live ? el : 0);
-        const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
+        const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
         float time;
-        if (parts & PARC_STEP_TIME) {                                   // _update_time, ig_env.py:391-394
+        if (do_time) {                                   // _update_time, ig_env.py:391-394
             const int ts = env.timestep_buf[e] + 1;
             time = __fmul_rn(cfg.timestep, (float)ts);
             if (live) { env.timestep_buf[e] = ts; env.time_buf[e] = time; }
@@ -567,6 +708,8 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         u.t0 = __fadd_rn(time, env.motion_time_offsets[e]);            // dm_env.py:547-552
         const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
         u.tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3)); u.toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
+      }
+      if (fill) { __syncwarp(); if (tid == THREADS - 64) st_flag(s_ctr + 2, 1); }
     }
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
@@ -574,7 +717,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         for (int it = tid; it < TILE * (J - 1); it += THREADS) {
             const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
             const long long row = row0 + (el < tile_rows ? el : 0);
-            const long long e = env_ids ? env_ids[row] : (env_ids32 ? (long long)env_ids32[row] : row + first_env);
+            const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
             const int jt = cm.joint_type[j], di = cm.dof_idx[j];
             Quat q = quat_identity();
             if (jt == PARC_JOINT_SPHERICAL)
@@ -584,14 +727,20 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             s_charq[el * J + j] = quat_to_f4(q);
         }
     }
+    if (fill && tid < THREADS - 64) {
+        // the clip chain (time -> motion id -> clip meta -> terrain offset) is the last to arrive: sample heights until it does
+        while (ld_flag(s_ctr + 1) == 0) __nanosleep(64);
+        __threadfence_block();
+        height_units(s_ctr + 2, 1);
+    }
     __syncthreads();
     PARC_STAMP(1);
 
     // A.4 lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares
-    if (LATTICE && do_heights) {
+    if (LATTICE && do_heights && !fill) {
         PARC_COLD_LOOP
-        for (int k = tid; k < TILE * sp.lat_nx; k += THREADS) {
-            const int el = k / sp.lat_nx, i = k - el * sp.lat_nx;
+        for (int k = tid; k < TILE * lat_nx; k += THREADS) {
+            const int el = k / lat_nx, i = k - el * lat_nx;
             const float x = s_axes[i];
             s_lat[k] = make_float2(__fmul_rn(x, s_env[el].ch), __fmul_rn(x, s_env[el].sh));
         }
@@ -610,7 +759,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(v.ptr + s_env[el].e * v.row_stride) + ln * 128));
         }
     }
-    if (do_obs || need_ref_pose) {
+    if (PARC_PREFETCH_FRAMES && (do_obs || need_ref_pose)) {
         PARC_COLD_LOOP
         for (int it = tid; it < TILE * (S + 1); it += THREADS) {
             const int el = it / (S + 1), pose = it - el * (S + 1);
@@ -618,14 +767,14 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             const EnvU& u = s_env[el];
             const float t = pose == 0 ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
             const FrameBlend fb = calc_frame_blend(u.mm, t);
-            const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * lib.irec);
-            const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * lib.irec * sizeof(float));
+            const char* r0 = reinterpret_cast<const char*>(lib.interp + fb.idx0 * irec_f);
+            const int bytes = (int)((fb.idx1 - fb.idx0 + 1) * irec_f * sizeof(float));
             PARC_COLD_LOOP
             for (int off = 0; off < bytes; off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(r0 + off));
             if (pose == 0) {
-                const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * lib.vrec);
+                const char* v = reinterpret_cast<const char*>(lib.vel + fb.idx0 * vrec_f);
                 PARC_COLD_LOOP
-                for (int off = 0; off < (int)(lib.vrec * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
+                for (int off = 0; off < (int)(vrec_f * sizeof(float)); off += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + off));
             }
         }
     }
@@ -652,8 +801,8 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             // MotionLib.calc_motion_frame (motion_lib.py:94-126); fetch_tar_obs_data (mgdm_dm_util.py:221-244)
             const float t = is_ref ? u.t0 : __fadd_rn(u.t0, cfg.tar_dt[pose - 1]);
             const FrameBlend fb = calc_frame_blend(u.mm, t);
-            r0 = lib.interp + fb.idx0 * lib.irec;
-            r1 = lib.interp + fb.idx1 * lib.irec;
+            r0 = lib.interp + fb.idx0 * irec_f;
+            r1 = lib.interp + fb.idx1 * irec_f;
             pr0 = r0 + interp_pair_off(J, C);
             b = fb.blend; omb = __fsub_rn(1.0f, b);
             rq = slerp_pre(quat_from_f4(ldg4(r0)), quat_from_f4(ldg4(r1)), ldg2(pr0), b, omb);
@@ -661,7 +810,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             rpos = make_vec3(__fadd_rn(__fadd_rn(lerp_exact(omb, p0.x, b, p1.x), fb.loop_offset.x), u.tox),
                              __fadd_rn(__fadd_rn(lerp_exact(omb, p0.y, b, p1.y), fb.loop_offset.y), u.toy),
                              __fadd_rn(lerp_exact(omb, p0.z, b, p1.z), fb.loop_offset.z));
-            vrec = lib.vel + fb.idx0 * lib.vrec;
+            vrec = lib.vel + fb.idx0 * vrec_f;
         }
         // ---- root-level outputs (scalar pieces by part 0, the per-dof / per-body lists strided over the parts) ----
         float* o_pose = nullptr;        // start of this pose's joint tan-norm block
@@ -692,7 +841,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             float* o = row + L.o_tar + (pose - 1) * L.tar_step_dim;
             rp_obs = rpos - u.c_pos;
             Quat oq = rq;
-            if (!cfg.global_obs) { rp_obs = quat_rotate(u.hinv, rp_obs); oq = quat_mul(u.hinv, rq); }
+            if (!c_global_obs) { rp_obs = quat_rotate(u.hinv, rp_obs); oq = quat_mul(u.hinv, rq); }
             if (part == 0) {
                 o[0] = rp_obs.x; o[1] = rp_obs.y; o[2] = rp_obs.z;
                 tan_norm_exact(oq, o + 3);
@@ -704,14 +853,14 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             if (part == 0) {
                 if (L.root_h) row[0] = u.c_pos.z;
                 Quat oq = u.c_rot; Vec3 v = u.c_vel, w = u.c_avel;
-                if (!cfg.global_obs) { oq = quat_mul(u.hinv, u.c_rot); v = quat_rotate(u.hinv, u.c_vel); w = quat_rotate(u.hinv, u.c_avel); }
+                if (!c_global_obs) { oq = quat_mul(u.hinv, u.c_rot); v = quat_rotate(u.hinv, u.c_vel); w = quat_rotate(u.hinv, u.c_avel); }
                 tan_norm_exact(oq, o);
                 o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
             }
             o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
             PARC_COLD_LOOP
             for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
-            if (cfg.use_contact_info) {
+            if (c_contact_info) {
                 // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
                 PARC_COLD_LOOP
                 for (int c = part; c < J; c += NPART) {
@@ -722,7 +871,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             }
         }
         // contact labels: lerp of the two records (motion_lib.py:121)
-        if (!is_char && C > 0 && (is_ref || cfg.use_contact_info)) {
+        if (!is_char && C > 0 && (is_ref || c_contact_info)) {
             float* oc = is_ref ? refp(R.contacts, C, el) : (row + L.o_tarc + (pose - 1) * C);
             const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
             PARC_COLD_LOOP
@@ -739,16 +888,16 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             for (int k = 0; k < K; ++k)
                 if (cfg.key_body_ids[k] == 0) {
                     Vec3 kp = make_vec3(0.f, 0.f, 0.f);
-                    if (!cfg.global_obs && is_tar) kp = kp + rp_obs;
+                    if (!c_global_obs && is_tar) kp = kp + rp_obs;
                     float* kd = o_key + 3 * k;
                     kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                 }
         // ---- joints: slerp + forward kinematics (kin_char_model.py:617-649) along the schedule ----
-        const bool lrot_ident = sp.lrot_ident != 0;
+        const bool lrot_ident = lrot_ident_;
         float* gx = s_gx + (tid >> 2);                  // [slot][7][NGROUP], this 4-lane group's column
         Vec3 cpos = rpos; Quat crot = rq;               // transform of the body this lane evaluated last (the root at first)
-        if (sp.root_slot >= 0 && part == 0) {
-            float* x = gx + sp.root_slot * 7 * NGROUP;
+        if (root_slot >= 0 && part == 0) {
+            float* x = gx + root_slot * 7 * NGROUP;
             x[0] = rpos.x; x[NGROUP] = rpos.y; x[2 * NGROUP] = rpos.z;
             x[3 * NGROUP] = rq.x; x[4 * NGROUP] = rq.y; x[5 * NGROUP] = rq.z; x[6 * NGROUP] = rq.w;
         }
@@ -756,7 +905,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         float* o_bp = is_ref ? refp(R.body_pos, 3 * J, el) : nullptr;
         __syncwarp();
         PARC_COLD_LOOP
-        for (int it = 0; it < sp.n_iter; ++it) {
+        for (int it = 0; it < n_iter; ++it) {
             const int entry = s_sched[it * NPART + part];
             if (entry >= 0) {
                 const int j = entry & 0xff;
@@ -789,7 +938,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                     PARC_COLD_LOOP
                     for (unsigned km = (entry >> 8) & 0xffu; km; km &= km - 1) {
                         Vec3 kp = bpos - rpos;
-                        if (!cfg.global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
+                        if (!c_global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
                         float* kd = o_key + 3 * (__ffs(km) - 1);
                         kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                     }
@@ -797,6 +946,12 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             }
             __syncwarp();
         }
+    }
+    if (fill && pose_work) {
+        // this warp's pose is done: sample heights until the other warps' poses are
+        __syncwarp();
+        if ((tid & 31) == 0) atomicAdd(s_ctr + 3, 1);
+        height_units(s_ctr + 3, THREADS / 32);
     }
     __syncthreads();
     PARC_STAMP(3);
@@ -808,9 +963,9 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     // The full-tile fast path of phase E: rows row0 .. row0 + TILE - 1 are consecutive env ids, so the staged ref_* blocks
     // are the memory image of those rows of every (contiguous) ref_* tensor.
     const long long e_first = row0 + first_env;
-    const bool ref_bulk = PARC_BULK_ROWS && do_ref && sp.ref_fast && tile_rows == TILE && env_ids == nullptr && env_ids32 == nullptr &&
+    const bool ref_bulk = PARC_BULK_ROWS && do_ref && (FAST || sp.ref_fast) && tile_rows == TILE && env_ids_ == nullptr && env_ids32_ == nullptr &&
                           (e_first & 3) == 0;
-    const bool obs_bulk = PARC_BULK_ROWS && do_obs;
+    const bool obs_bulk = PARC_BULK_OBS && do_obs;
     // C.0 scatter map of the ref_* values for the general copy-out of phase E: column k of an env's ref_* values ->
     //     (global base pointer, row stride in bytes, position in the tile's staged block). Lives in the bytes the group
     //     slots used during phase B; phase E reads it behind the barrier that ends phase C.
@@ -840,8 +995,9 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     {
         // Four item kinds (joints, contacts, key bodies, dof velocities) cut into warp-sized tasks that are dealt
         // round-robin to the warps: every warp runs about the same number of (prefetched) global reads.
-        const bool want_c = (do_reward && cfg.use_contact_info) || (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0);
-        const int nt_j = need_ref_pose ? (TILE * (J - 1) + 31) >> 5 : 0;
+        const bool want_c = (do_reward && c_contact_info) || (do_done && c_early_term && c_n_fall > 0);
+        const int nt_j1 = need_ref_pose ? (TILE * (J - 1) + 31) >> 5 : 0;      // tasks per joint sub-kind
+        const int nt_j = PARC_SPLIT_JOINT_TASKS ? 3 * nt_j1 : nt_j1;
         const int nt_c = want_c ? (TILE * J + 31) >> 5 : 0;
         const int nt_k = do_reward ? (TILE * K + 31) >> 5 : 0;
         const int nt_d = do_reward ? (TILE * D + 31) >> 5 : 0;
@@ -850,13 +1006,15 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
         PARC_COLD_LOOP
         for (int task = tid >> 5; task < n_task; task += THREADS / 32) {
             if (task < b_c) {
-                // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615) + pose error term
-                const int it = task * 32 + lane;
+                // joints: rot_to_dof of the reference pose (kin_char_model.py:601-615), pose error term, pose termination test
+                // -- one task does all three (sub < 0), or they are three tasks of similar length (sub = 0, 1, 2)
+                const int sub = PARC_SPLIT_JOINT_TASKS ? task / nt_j1 : -1;
+                const int it = (PARC_SPLIT_JOINT_TASKS ? task - sub * nt_j1 : task) * 32 + lane;
                 if (it >= TILE * (J - 1)) continue;
                 const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
                 if (el >= tile_rows) continue;
                 const Quat q = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.joint_rot, 4 * (J - 1), el) + 4 * (j - 1)));
-                if (do_ref) {
+                if (do_ref && sub <= 0) {
                     const int jt = cm.joint_type[j], di = cm.dof_idx[j];
                     float* dp = refp(R.dof_pos, D, el) + di;
                     if (jt == PARC_JOINT_SPHERICAL) {
@@ -869,11 +1027,11 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                         dp[0] = (dd < 0.f) ? -angle : angle;
                     }
                 }
-                if (do_reward) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
+                if (do_reward && (sub < 0 || sub == 1)) {   // compute_deepmimic_reward pose term (mgdm_dm_util.py:285-287)
                     const float a = quat_diff_angle(quat_from_f4(s_charq[el * J + j]), q);
                     s_terms[el * TP + o_pose_t + (j - 1)] = cfg.joint_err_w[j - 1] * a * a;
                 }
-                if (do_done && cfg.enable_early_termination && cfg.pose_termination) {
+                if (do_done && c_early_term && c_pose_term && (sub < 0 || sub == 2)) {
                     // compute_done pose test (mgdm_dm_util.py:372-384): squared norm summed left to right
                     const EnvU& u = s_env[el];
                     const Vec3 sb = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, j, 0), view_ld3(env.char_rigid_body_pos, u.e, j, 1), view_ld3(env.char_rigid_body_pos, u.e, j, 2));
@@ -893,7 +1051,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                 const EnvU& u = s_env[el];
                 const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
                             fz = view_ld3(env.char_contact_forces, u.e, c, 2);
-                if (do_reward && cfg.use_contact_info) {
+                if (do_reward && c_contact_info) {
                     // compute_contact_reward (mgdm_dm_util.py:497-518); contact bodies == all bodies
                     const float f = fminf(sqrtf(fx * fx + fy * fy + fz * fz), 1.0f);
                     const float rc = refp(R.contacts, C, el)[c];
@@ -901,7 +1059,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                     cr += rc * f;
                     s_terms[el * TP + o_con_t + c] = cfg.contact_weights[c] * cr;
                 }
-                if (do_done && cfg.enable_early_termination && cfg.num_fall_contact_bodies > 0 && !((cfg.fall_contact_body_mask >> c) & 1u)) {
+                if (do_done && c_early_term && c_n_fall > 0 && !((cfg.fall_contact_body_mask >> c) & 1u)) {
                     // fall test (mgdm_dm_util.py:147-150, 349-362)
                     int fl = 0;
                     if (fabsf(fx) > 0.1f || fabsf(fy) > 0.1f || fabsf(fz) > 0.1f) fl |= 1;
@@ -926,7 +1084,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                 Vec3 kp = make_vec3(view_ld3(env.char_rigid_body_pos, u.e, body, 0), view_ld3(env.char_rigid_body_pos, u.e, body, 1),
                                     view_ld3(env.char_rigid_body_pos, u.e, body, 2)) - u.c_pos;
                 Vec3 tkp = make_vec3(bp[3 * body], bp[3 * body + 1], bp[3 * body + 2]) - ref_rpos;
-                if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
+                if (!c_track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
                     const Quat rr = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.root_rot, 4, el)));
                     kp = quat_rotate(u.hinv, kp);
                     tkp = quat_rotate(calc_heading_quat_inv(rr), tkp);
@@ -954,37 +1112,49 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
     // engine now, so that the copies run while phase D and the height samples execute. The few floats in front of /
     // behind a row's 16-byte aligned body are stored by the same lane.
     bool bulk_pending = false;
-    if (obs_bulk && tid < tile_rows) {
-        const EnvU& u = s_env[tid];
-        const float* srow = s_row + tid * ROWP + u.row_shift;
-        float* g = env.obs_buf + u.e * env.obs_row_stride;
-        const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
-        if (nvec > 0) { bulk_store(g + head, srow + head, 16u * nvec); bulk_pending = true; }
-        for (int k = 0; k < head; ++k) g[k] = srow[k];
-        for (int k = t0; k < n; ++k) g[k] = srow[k];
-    } else if (ref_bulk && tid >= 32 && tid < 32 + NREF) {
-        const int f = tid - 32;
-        const parc_view3_t& v = f == 0 ? env.ref_root_pos : f == 1 ? env.ref_root_rot : f == 2 ? env.ref_root_vel : f == 3 ? env.ref_root_ang_vel
-                              : f == 4 ? env.ref_body_pos : f == 5 ? env.ref_joint_rot : f == 6 ? env.ref_dof_pos : f == 7 ? env.ref_dof_vel : env.ref_contacts;
-        const int fo = f == 0 ? R.root_pos : f == 1 ? R.root_rot : f == 2 ? R.root_vel : f == 3 ? R.root_ang_vel : f == 4 ? R.body_pos
-                     : f == 5 ? R.joint_rot : f == 6 ? R.dof_pos : f == 7 ? R.dof_vel : R.contacts;
-        const int fe = f == 0 ? R.root_rot : f == 1 ? R.root_vel : f == 2 ? R.root_ang_vel : f == 3 ? R.body_pos : f == 4 ? R.joint_rot
-                     : f == 5 ? R.dof_pos : f == 6 ? R.dof_vel : f == 7 ? R.contacts : R.width;
-        const int w = fe - fo;
-        if (w > 0 && v.ptr) { bulk_store(v.ptr + e_first * w, s_ref + fo * TILE, (unsigned)(w * TILE * sizeof(float))); bulk_pending = true; }
+    {
+        // Issuing lanes: the first tile_rows lanes of one warp hand over an observation row each, NREF further lanes of it
+        // one ref_* tensor each. (UBLKCP takes uniform operands, so the lanes of a warp issue one after the other; one lane
+        // per warp instead measured slower.) With PARC_TAIL_ROLES that warp is warp 1, so that it delays neither the reward
+        // (warp 0) nor the termination lanes (warp 2).
+        const int warp = tid >> 5, lane = tid & 31;
+        constexpr int W_ISSUE = PARC_TAIL_ROLES ? 1 : 0;
+        if (obs_bulk && warp == W_ISSUE && lane < tile_rows) {
+            const EnvU& u = s_env[lane];
+            const float* srow = s_row + lane * ROWP + u.row_shift;
+            float* g = env.obs_buf + u.e * env.obs_row_stride;
+            const int n = L.o_hf, head = min((4 - u.row_shift) & 3, n), nvec = (n - head) >> 2, t0 = head + 4 * nvec;
+            if (nvec > 0) { bulk_store(g + head, srow + head, 16u * nvec); bulk_pending = true; }
+            for (int k = 0; k < head; ++k) g[k] = srow[k];
+            for (int k = t0; k < n; ++k) g[k] = srow[k];
+        } else if (ref_bulk && warp == W_ISSUE && lane >= TILE && lane < TILE + NREF) {
+            const int f = lane - TILE;
+            const parc_view3_t& v = f == 0 ? env.ref_root_pos : f == 1 ? env.ref_root_rot : f == 2 ? env.ref_root_vel : f == 3 ? env.ref_root_ang_vel
+                                  : f == 4 ? env.ref_body_pos : f == 5 ? env.ref_joint_rot : f == 6 ? env.ref_dof_pos : f == 7 ? env.ref_dof_vel : env.ref_contacts;
+            const int fo = f == 0 ? R.root_pos : f == 1 ? R.root_rot : f == 2 ? R.root_vel : f == 3 ? R.root_ang_vel : f == 4 ? R.body_pos
+                         : f == 5 ? R.joint_rot : f == 6 ? R.dof_pos : f == 7 ? R.dof_vel : R.contacts;
+            const int fe = f == 0 ? R.root_rot : f == 1 ? R.root_vel : f == 2 ? R.root_ang_vel : f == 3 ? R.body_pos : f == 4 ? R.joint_rot
+                         : f == 5 ? R.dof_pos : f == 6 ? R.dof_vel : f == 7 ? R.contacts : R.width;
+            const int w = fe - fo;
+            if (w > 0 && v.ptr) { bulk_store(v.ptr + e_first * w, s_ref + fo * TILE, (unsigned)(w * TILE * sizeof(float))); bulk_pending = true; }
+        }
     }
     if (bulk_pending) bulk_commit();
 
     // ================================ phase D ====================================================
     PARC_STAMP(5);
-    if (tid < tile_rows && (do_reward || do_done)) {
-        const int el = tid;
+    static_assert(TILE + NREF <= 32 && THREADS >= 96, "issuing lanes fit one warp; three warps take the tail roles");
+    // 16 lanes each: the reward in warp 0, the termination flags in warp 2 (PARC_TAIL_ROLES; else both in warp 0)
+    const bool run_reward = do_reward && (tid >> 5) == 0 && (tid & 31) < tile_rows;
+    const bool run_done = do_done && (tid >> 5) == (PARC_TAIL_ROLES ? 2 : 0) && (tid & 31) < tile_rows;
+    if (run_reward || run_done) {
+        const int el = tid & 31;
         const EnvU& u = s_env[el];
         const long long e = u.e;
         const float* rp = refp(R.root_pos, 3, el);
         const Vec3 ref_rpos = make_vec3(rp[0], rp[1], rp[2]);
         const Quat ref_rrot = quat_from_f4(*reinterpret_cast<const float4*>(refp(R.root_rot, 4, el)));
-        if (do_reward) {
+        if (run_reward) {
             // _update_reward (ig_parkour_env.py:984-1044) + compute_deepmimic_reward (mgdm_dm_util.py:269-332)
             const float* tm = s_terms + el * TP;
             float pose_t = 0.f, vel_t = 0.f, key_t = 0.f, con_t = 0.f;
@@ -994,15 +1164,15 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             for (int k = 0; k < D; ++k) vel_t += tm[o_vel_t + k];
             for (int k = 0; k < K; ++k) key_t += tm[o_key_t + k];
             Vec3 rpd = ref_rpos - u.c_pos;
-            if (!cfg.track_root) { rpd.x = 0.f; rpd.y = 0.f; }
-            if (!cfg.track_root_h) rpd.z = 0.f;
+            if (!c_track_root) { rpd.x = 0.f; rpd.y = 0.f; }
+            if (!c_track_root_h) rpd.z = 0.f;
             const float root_pos_err = rpd.x * rpd.x + rpd.y * rpd.y + rpd.z * rpd.z;
             Quat a_rot = u.c_rot, b_rot = ref_rrot;
             Vec3 a_vel = u.c_vel, a_av = u.c_avel;
             const float* rv = refp(R.root_vel, 3, el); const float* rav = refp(R.root_ang_vel, 3, el);
             Vec3 b_vel = make_vec3(rv[0], rv[1], rv[2]);
             Vec3 b_av = make_vec3(rav[0], rav[1], rav[2]);
-            if (!cfg.track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
+            if (!c_track_root) {   // convert_to_local (mgdm_dm_util.py:246-267)
                 const Quat hr = calc_heading_quat_inv(ref_rrot);
                 a_rot = quat_mul(u.hinv, u.c_rot); b_rot = quat_mul(hr, ref_rrot);
                 a_vel = quat_rotate(u.hinv, a_vel); b_vel = quat_rotate(hr, b_vel);
@@ -1020,7 +1190,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             const float key_r = expf(-10.0f * key_t);
             float total = cfg.pose_w * pose_r + cfg.vel_w * vel_r + cfg.root_pos_w * root_pose_r + cfg.root_vel_w * root_vel_r + cfg.key_pos_w * key_r;
             float pen = 0.f;
-            if (cfg.use_contact_info) {
+            if (c_contact_info) {
 #pragma unroll 4
                 for (int k = 0; k < J; ++k) con_t += tm[o_con_t + k];
                 pen = con_t / (float)C;
@@ -1033,16 +1203,16 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
                 t4[1] = make_float4(key_r, pen, total, 0.f);
             }
         }
-        if (do_done) {
+        if (run_done) {
             // _update_done (ig_parkour_env.py:967-982; mgdm_dm_util.py:147-172, 334-402; dm_env.py:628-665)
             int done = PARC_DONE_NULL;
             if (u.time >= cfg.episode_length) done = PARC_DONE_TIME;
-            if (cfg.enable_early_termination) {
+            if (c_early_term) {
                 bool failed = false;
-                if (cfg.num_fall_contact_bodies > 0) failed = (u.flags & 1) && (u.flags & 2);
-                if (cfg.pose_termination) {
+                if (c_n_fall > 0) failed = (u.flags & 1) && (u.flags & 2);
+                if (c_pose_term) {
                     bool pf = (u.flags & 4) != 0;
-                    if (cfg.track_root) {
+                    if (c_track_root) {
                         const Vec3 s0 = make_vec3(view_ld3(env.char_rigid_body_pos, e, 0, 0), view_ld3(env.char_rigid_body_pos, e, 0, 1),
                                                   view_ld3(env.char_rigid_body_pos, e, 0, 2));
                         const Vec3 d = s0 - ref_rpos;
@@ -1060,7 +1230,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
             if (done == PARC_DONE_FAIL) code = 1;
             else if (done != PARC_DONE_NULL || motion_end) code = 2;
             if (motion_end) done = PARC_DONE_FAIL;
-            if (cfg.never_done) done = PARC_DONE_NULL;
+            if (c_never_done) done = PARC_DONE_NULL;
             env.done_buf[e] = done;
             if (env.done_code) env.done_code[e] = (unsigned char)code;
             if (code != 0 && env.done_list) {
@@ -1072,41 +1242,8 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) env_step_kernel(
 
     PARC_STAMP(6);
     // ================================ phase H ====================================================
-    // _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145): one warp per env, rows handed out by a shared
-    // counter (the warp that ran phase D joins late and takes what is left). The samples depend only on the phase A
-    // uniforms and go straight to global memory.
-    if (P > 0 && (do_heights || do_obs)) {
-        const int lane = tid & 31;
-        HeightArgs ha;
-        ha.hf = terrain.hf; ha.dimy = terrain.dim_y; ha.imx = terrain.dim_x - 1; ha.imy = terrain.dim_y - 1;
-        ha.nmn = make_float2(-terrain.min_x, -terrain.min_y); ha.rd2 = make_float2(sp.rdx, sp.rdy); ha.nd2 = make_float2(-terrain.dx, -terrain.dy);
-        ha.lo = cfg.min_obs_h; ha.hi = cfg.max_obs_h;
-        for (;;) {
-            int el = 0;
-            if (lane == 0) el = atomicAdd(s_ctr, 1);
-            el = __shfl_sync(FULL_MASK, el, 0);
-            if (el >= tile_rows) break;
-            const EnvU& u = s_env[el];
-            float* orow = do_obs ? env.obs_buf + u.e * env.obs_row_stride + L.o_hf : nullptr;
-            float* hrow = env.ray_hfs ? env.ray_hfs + u.e * P : nullptr;
-            if (do_heights) {
-                ha.g2 = make_float2(u.g.x, u.g.y); ha.gz = u.g.z;
-                if (LATTICE) {
-                    const float2* a = s_lat + el * sp.lat_nx;
-                    const float y = s_axes[sp.lat_nx + lane];
-                    if (orow && hrow) heights_of_env_lattice<true, true>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
-                    else if (orow) heights_of_env_lattice<false, true>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
-                    else heights_of_env_lattice<true, false>(a, y, sp.lat_nx, lane, ha, u.ch, u.sh, hrow, orow);
-                } else {
-                    const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch);
-                    if (P % (32 * PARC_HEIGHT_GATHERS) == 0) heights_of_env<true>(s_pts, P, lane, ha, cs, nsc, hrow, orow);
-                    else heights_of_env<false>(s_pts, P, lane, ha, cs, nsc, hrow, orow);
-                }
-            } else if (orow) {
-                for (int p = lane; p < P; p += 32) orow[p] = hrow[p];
-            }
-        }
-    }
+    // the height units nobody has taken yet (all of them unless the heights were filler work)
+    height_units(nullptr, 0);
 
     PARC_STAMP(7);
     // ================================ phase E (general) ===========================================
@@ -1318,23 +1455,43 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
     const StepPlan sp = make_step_plan(*m, lib->num_contacts, *cfg, *terrain, env);
     const SmemPlan& plan = sp.S;
     const bool lattice = sp.lat_nx > 0;
+    // the specialised instantiation: exactly the layout and flags it was compiled for (see FastDims), every part, all rows
+    const bool fast = PARC_STEP_FAST && lattice && parts == PARC_STEP_ALL && env_ids == nullptr && env_ids32 == nullptr && n_rows_dev == nullptr &&
+                      m->num_bodies == FastDims::J && m->dof_size == FastDims::D && lib->num_contacts == FastDims::C &&
+                      cfg->enable_tar_obs && cfg->num_tar_steps == FastDims::S && cfg->num_key_bodies == FastDims::K &&
+                      cfg->num_ray_points == FastDims::P && sp.lat_nx == FastDims::NX && sp.lat_ny == FastDims::NY &&
+                      !cfg->global_obs && !cfg->root_height_obs && cfg->use_contact_info && cfg->track_root && cfg->track_root_h &&
+                      cfg->enable_early_termination && cfg->pose_termination && cfg->num_fall_contact_bodies == 0 && !cfg->never_done &&
+                      sp.lrot_ident && sp.n_iter == FastDims::N_ITER && sp.root_slot == -1 && sp.ref_fast &&
+                      lib->irec == interp_record_floats(FastDims::J, FastDims::C) && lib->vrec == vel_record_floats(FastDims::D) &&
+                      memcmp(&sp.L, &kFastL, sizeof(ObsLayout)) == 0 && memcmp(&sp.R, &kFastR, sizeof(RefLayout)) == 0 &&
+                      sp.S.row_pitch == kFastS.row_pitch && sp.S.n_pose == kFastS.n_pose && sp.S.n_gslots == kFastS.n_gslots &&
+                      sp.S.term_pitch == kFastS.term_pitch && sp.S.off_env == kFastS.off_env && sp.S.off_row == kFastS.off_row &&
+                      sp.S.off_ref == kFastS.off_ref && sp.S.off_charq == kFastS.off_charq && sp.S.off_gx == kFastS.off_gx &&
+                      sp.S.off_refmap == kFastS.off_refmap && sp.S.off_tab == kFastS.off_tab && sp.S.off_pts == kFastS.off_pts &&
+                      sp.S.off_lat == kFastS.off_lat && sp.S.off_ctr == kFastS.off_ctr && sp.S.total == kFastS.total;
+    const int variant = fast ? 2 : (lattice ? 1 : 0);
     // opt-in dynamic shared memory: a per-device function attribute, raised only when a larger plan shows up
-    static size_t smem_attr[64][2] = {};
+    static size_t smem_attr[64][3] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    size_t& have = smem_attr[dev & 63][lattice ? 1 : 0];
+    size_t& have = smem_attr[dev & 63][variant];
     if (plan.total > have) {
-        cudaError_t ce = lattice ? cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total)
-                                 : cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
+        cudaError_t ce = variant == 2 ? cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total)
+                       : variant == 1 ? cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total)
+                                      : cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
         if (ce != cudaSuccess) { set_error("env_step: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
         have = plan.total;
     }
     const long long blocks = (max_rows + TILE - 1) / TILE;
-    if (lattice)
-        env_step_kernel<STEP_THREADS, true><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+    if (variant == 2)
+        env_step_kernel<STEP_THREADS, true, true><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+            *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
+    else if (variant == 1)
+        env_step_kernel<STEP_THREADS, true, false><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
             *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
     else
-        env_step_kernel<STEP_THREADS, false><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
+        env_step_kernel<STEP_THREADS, false, false><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
             *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
     return check_launch("env_step");
 }

@@ -39,5 +39,11 @@ for parts in (63, 2):
     print("  %-28s mean %8.0f  median %8.0f  p90 %8.0f" % ("block total", tot.mean(), np.median(tot), np.percentile(tot, 90)))
     # per SM: busy span vs sum of block times -> resident blocks
     sm = out[:, 15]
+    # phase offset between the two blocks that run side by side on an SM: start-time gap to the nearest other start, in units of a block time
+    gaps = []
+    for s_ in np.unique(sm):
+        st = np.sort(out[sm == s_, 0])
+        gaps.extend(np.diff(st))
+    print("  start-to-start gaps on an SM (cycles): p10 %.0f median %.0f p90 %.0f" % (np.percentile(gaps, 10), np.median(gaps), np.percentile(gaps, 90)))
     span = [out[sm == s, 8].max() - out[sm == s, 0].min() for s in np.unique(sm)]
     print("  SMs %d, mean span %.0f cycles, blocks per SM %.1f, mean concurrency %.2f" % (len(span), np.mean(span), nb / len(span), tot.sum() / np.sum(span)))
