@@ -30,7 +30,7 @@
 #define PARC_HEIGHT_GATHERS 2                 // general ray sets: independent heightfield gathers per lane and loop iteration
 #endif
 #ifndef PARC_LATTICE_ROWS
-#define PARC_LATTICE_ROWS 4                   // lattice ray sets: lattice rows (= independent gathers) per lane and loop iteration
+#define PARC_LATTICE_ROWS 8                   // lattice ray sets: lattice rows (= independent gathers) per lane and loop iteration
 #endif
 #ifndef PARC_HEIGHT_SPLIT
 #define PARC_HEIGHT_SPLIT 1                   // an env's sample points are handed out in this many pieces (load balance across the warps)
@@ -39,15 +39,17 @@
 #define PARC_PREFETCH_FRAMES 0                // 1: a separate stage prefetches the frame records before the pose loop (measured slower: the
 #endif                                        //    root part of a pose touches nearly every line of its two records anyway)
 #ifndef PARC_SPLIT_JOINT_TASKS
-#define PARC_SPLIT_JOINT_TASKS 0              // 1: phase C deals rot_to_dof / pose error / pose termination as separate tasks
+#define PARC_SPLIT_JOINT_TASKS 1              // 1: phase C deals rot_to_dof / pose error / pose termination as separate tasks
 #endif
 #ifndef PARC_TAIL_ROLES
 #define PARC_TAIL_ROLES 1                     // 1: after phase C reward, termination and the bulk hand-over run in different warps
 #endif
-#ifndef PARC_FILL_HEIGHTS
-#define PARC_FILL_HEIGHTS 0                   // 1 (lattice ray sets): warps that would wait at the barriers behind phases A and B sample
-#endif                                        //    heights meanwhile; whatever is left is sampled after phase C. Measured 10 % SLOWER (a unit
-                                              //    once taken delays the barrier it was meant to fill), kept switchable for the record
+#ifndef PARC_HEIGHT_PATCH
+#define PARC_HEIGHT_PATCH 0                   // 1 (lattice ray sets): the env's heightfield neighbourhood is staged in shared memory
+#endif
+#ifndef PARC_STREAM_HINTS
+#define PARC_STREAM_HINTS 1                   // 1: height rows are stored with the streaming hint (st.global.cs): phase B's frame records
+#endif                                        //    want every byte of the L1 the block's shared memory leaves
 #ifndef PARC_STEP_FAST
 #define PARC_STEP_FAST 1                      // 1: full steps of the default humanoid layout run the compile-time-specialised instantiation
 #endif
@@ -132,7 +134,6 @@ constexpr int NREF = 9;   // ref_* tensors
 // Per-env uniforms computed once (phase A) and read by every later phase.
 struct EnvU {
     long long e;             // env index of this row
-    long long mid;           // motion id
     Vec3 c_pos; Quat c_rot; Vec3 c_vel; Vec3 c_avel;
     Quat hinv;               // inverse heading rotation of the CHARACTER root
     Vec3 eo;                 // env offset
@@ -151,7 +152,7 @@ struct SmemPlan {
     int n_pose;              // poses per env: S + 2
     int n_gslots;            // transforms a 4-lane group keeps in shared memory
     int term_pitch;          // floats of reward terms per env: (J-1) + D + J + K
-    size_t off_env, off_row, off_ref, off_charq, off_gx, off_terms, off_refmap, off_tab, off_pts, off_lat, off_ctr, total;
+    size_t off_env, off_row, off_ref, off_charq, off_gx, off_terms, off_refmap, off_tab, off_pts, off_lat, off_patch, off_ctr, total;
 };
 
 // One entry of the joint schedule: what lane `part` of an (env, pose) group does in iteration `it`.
@@ -274,10 +275,10 @@ __host__ __device__ constexpr size_t plan_max(size_t a, size_t b) { return a > b
 __host__ __device__ constexpr SmemPlan smem_plan_of(int J, int D, int K, int P, int o_hf, int ref_w, int n_pose, int n_gslots, int lat_nx, int lat_ny) {
     SmemPlan p{};
     // A row starts at a multiple of 4 floats plus the env's shift (0..3), so that column k of the staged row and of the
-    // obs_buf row have the same 16-byte phase. Pitch = 4 (mod 32): the 8 envs a warp touches at one column land in
-    // banks 4 el + shift -- all different.
+    // obs_buf row have the same 16-byte phase. Pitch = 4 x odd: the 8 envs a warp touches at one column land in banks
+    // 4 (el x odd mod 8) + shift -- all different.
     p.row_pitch = (o_hf + 3 + 3) & ~3;
-    while ((p.row_pitch & 31) != 4) p.row_pitch += 4;
+    if (((p.row_pitch >> 2) & 1) == 0) p.row_pitch += 4;
     p.n_pose = n_pose;
     p.n_gslots = n_gslots;
     p.term_pitch = (J - 1) + D + J + K;
@@ -285,7 +286,8 @@ __host__ __device__ constexpr SmemPlan smem_plan_of(int J, int D, int K, int P, 
     p.off_env = plan_take(o, sizeof(EnvU) * TILE);
     p.off_row = plan_take(o, sizeof(float) * TILE * p.row_pitch);
     p.off_ref = plan_take(o, sizeof(float) * TILE * ref_w);
-    p.off_charq = plan_take(o, sizeof(float4) * TILE * J);
+    // character joint quaternions (phases A..C); the heights (after phase C) keep one lattice-row table per warp in the same bytes
+    p.off_charq = p.off_lat = plan_take(o, plan_max(sizeof(float4) * TILE * J, lat_nx > 0 ? sizeof(float2) * TILE * lat_nx : 0));
     // The group slots are only live in phase B; the reward terms (phase C/D) and the ref_* scatter map (built in phase C,
     // read in phase E) reuse the same bytes.
     const size_t gx_bytes = sizeof(float) * 7 * n_gslots * NGROUP;
@@ -296,10 +298,10 @@ __host__ __device__ constexpr SmemPlan smem_plan_of(int J, int D, int K, int P, 
     p.off_tab = plan_take(o, sizeof(int) * NPART * PARC_MAX_BODIES + sizeof(float) * 8 * J);
     if (lat_nx > 0) {
         p.off_pts = plan_take(o, sizeof(float) * (lat_nx + lat_ny));            // lattice axes xs | ys
-        p.off_lat = plan_take(o, sizeof(float2) * TILE * lat_nx);                // per env and lattice row: (x c, x s)
+        p.off_patch = PARC_HEIGHT_PATCH ? plan_take(o, sizeof(float) * 16 * 17 * TILE) : o;   // one heightfield patch per warp (PATCH x PATCH_PITCH)
     } else {
         p.off_pts = plan_take(o, sizeof(float2) * (size_t)P);                   // ray_xy_points, shared by the tile's envs
-        p.off_lat = o;
+        p.off_patch = o;
     }
     p.off_ctr = plan_take(o, 16);
     p.total = o;
@@ -357,6 +359,13 @@ inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_en
     return sp;
 }
 
+__device__ __forceinline__ void st_stream(float* p, float x) {
+#if PARC_STREAM_HINTS
+    __stcs(p, x);
+#else
+    *p = x;
+#endif
+}
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ float2 ldg2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
@@ -457,8 +466,8 @@ __device__ __forceinline__ void heights_of_env(const float2* __restrict__ s_pts,
         for (int k = 0; k < U; ++k) {
             const float x = fminf(fmaxf(__fsub_rn(v[k], h.gz), h.lo), h.hi);
             if (FULL || p + 32 * k < P) {
-                if (HAS_H) ph[32 * k] = x;
-                if (HAS_O) po[32 * k] = x;
+                if (HAS_H) st_stream(ph + 32 * k, x);
+                if (HAS_O) st_stream(po + 32 * k, x);
             }
         }
     }
@@ -487,16 +496,73 @@ __device__ __forceinline__ void heights_of_env_lattice(const float2* __restrict_
 #pragma unroll
         for (int k = 0; k < U; ++k) {
             const float x = fminf(fmaxf(__fsub_rn(v[k], h.gz), h.lo), h.hi);
-            if (HAS_H) ph[k * LATTICE_NY] = x;
-            if (HAS_O) po[k * LATTICE_NY] = x;
+            if (HAS_H) st_stream(ph + k * LATTICE_NY, x);
+            if (HAS_O) st_stream(po + k * LATTICE_NY, x);
         }
         if (HAS_H) ph += U * LATTICE_NY;
         if (HAS_O) po += U * LATTICE_NY;
     }
 }
 
-__device__ __forceinline__ int ld_flag(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
-__device__ __forceinline__ void st_flag(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
+// The lattice sampler with the env's heightfield neighbourhood staged in shared memory. The cell of a lattice point is
+// monotone in its row i and in its column j (every step -- the rounded products, the three sums, the correctly rounded
+// division, round-half-even -- is monotone), so the cells of all points lie between the cells of the four lattice corners.
+// If that range spans at most PATCH x PATCH cells (3.1 m lattices on 0.4 m cells: <= 12), the warp copies hf[clamp(range)]
+// into its patch with one round of independent loads -- the clamps of get_grid_index (terrain_util.py:139-141) are applied
+// there -- and every sample is an LDS with no clamp and no global latency. Returns false (nothing written) if the range
+// is too large: the caller then takes the gather path.
+constexpr int PATCH = 16, PATCH_PITCH = 17, PATCH_FLOATS = PATCH * PATCH_PITCH;
+__device__ __forceinline__ int2 packed_cell_raw(float2 a, float2 b, float2 g2, float2 nmn, float2 rd2, float2 nd2) {
+    const float2 w = __fadd2_rn(__fadd2_rn(a, b), g2);
+    const float2 x = __fadd2_rn(w, nmn);
+    float2 q = __fmul2_rn(x, rd2);
+    const float2 r = __ffma2_rn(q, nd2, x);
+    q = __ffma2_rn(r, rd2, q);
+    return make_int2(__float2int_rn(q.x), __float2int_rn(q.y));
+}
+template <bool HAS_H, bool HAS_O>
+__device__ __forceinline__ bool heights_of_env_patch(const float2* __restrict__ s_a, float y, int i0, int i1, int nx_all, int lane, const HeightArgs& h,
+                                                     float c, float s, float* __restrict__ hrow, float* __restrict__ orow, float* __restrict__ s_patch) {
+    constexpr int U = PARC_LATTICE_ROWS;
+    const float2 b = make_float2(__fmul_rn(y, -s), __fmul_rn(y, c));
+    // cell range of the env's whole lattice: the first and the last lattice row contain the four corners
+    const int2 ca = packed_cell_raw(s_a[0], b, h.g2, h.nmn, h.rd2, h.nd2), cb = packed_cell_raw(s_a[nx_all - 1], b, h.g2, h.nmn, h.rd2, h.nd2);
+    const int lo_x = __reduce_min_sync(FULL_MASK, min(ca.x, cb.x)), hi_x = __reduce_max_sync(FULL_MASK, max(ca.x, cb.x));
+    const int lo_y = __reduce_min_sync(FULL_MASK, min(ca.y, cb.y)), hi_y = __reduce_max_sync(FULL_MASK, max(ca.y, cb.y));
+    constexpr int LIM = 1 << 28;
+    if (lo_x < -LIM || lo_y < -LIM || hi_x > LIM || hi_y > LIM || hi_x - lo_x >= PATCH || hi_y - lo_y >= PATCH) return false;
+    __syncwarp();                                       // the previous unit's samples have been read
+#pragma unroll
+    for (int k = 0; k < PATCH * PATCH / 32; ++k) {
+        const int idx = lane + 32 * k, pa = idx / PATCH, pb = idx % PATCH;
+        const int gx = max(0, min(lo_x + pa, h.imx)), gy = max(0, min(lo_y + pb, h.imy));
+        s_patch[pa * PATCH_PITCH + pb] = __ldg(h.hf + gx * h.dimy + gy);
+    }
+    __syncwarp();
+    const float* pz = s_patch - (lo_x * PATCH_PITCH + lo_y);
+    float* ph = HAS_H ? hrow + lane : nullptr;
+    float* po = HAS_O ? orow + lane : nullptr;
+    const float2* a = s_a + i0;
+    PARC_COLD_LOOP
+    for (int i = i0; i < i1; i += U, a += U) {
+        float v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            const int2 cc = packed_cell_raw(a[k], b, h.g2, h.nmn, h.rd2, h.nd2);
+            v[k] = pz[cc.x * PATCH_PITCH + cc.y];
+        }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            const float x = fminf(fmaxf(__fsub_rn(v[k], h.gz), h.lo), h.hi);
+            if (HAS_H) st_stream(ph + k * LATTICE_NY, x);
+            if (HAS_O) st_stream(po + k * LATTICE_NY, x);
+        }
+        if (HAS_H) ph += U * LATTICE_NY;
+        if (HAS_O) po += U * LATTICE_NY;
+    }
+    return true;
+}
+
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 // shared -> global bulk copy (TMA, no tensor map): both addresses 16-byte aligned, bytes a multiple of 16
 __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
@@ -554,8 +620,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     float* s_jc = reinterpret_cast<float*>(smem_raw + plan.off_tab + sizeof(int) * NPART * PARC_MAX_BODIES);
     float2* s_pts = reinterpret_cast<float2*>(smem_raw + plan.off_pts);     // general ray set
     float* s_axes = reinterpret_cast<float*>(smem_raw + plan.off_pts);      // lattice: xs[nx] | ys[ny]
-    float2* s_lat = reinterpret_cast<float2*>(smem_raw + plan.off_lat);     // lattice: [TILE][nx] (x c, x s)
-    int* s_ctr = reinterpret_cast<int*>(smem_raw + plan.off_ctr);          // [0] height-unit counter [1] uniforms + lattice table ready [2] clip chain done [3] poses done
+    float2* s_lat = reinterpret_cast<float2*>(smem_raw + plan.off_lat);     // lattice, after phase C: per warp [nx] (x c, x s) of the env it samples
+    float* s_patch = reinterpret_cast<float*>(smem_raw + plan.off_patch);   // lattice: one heightfield patch per warp
+    int* s_ctr = reinterpret_cast<int*>(smem_raw + plan.off_ctr);          // height-unit counter
     const int ROWP = plan.row_pitch;
 
     const bool do_heights = FAST || (parts & PARC_STEP_HEIGHTS);
@@ -573,9 +640,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     // ---- height units -------------------------------------------------------------------------------------------------
     // _refresh_obs_hfs (ig_parkour_env.py:518-533, mgdm_dm_util.py:128-145): a unit = one piece of one env's sample points, done
     // by one warp; units are handed out by a shared counter. The samples depend only on the root / heading uniforms of
-    // phase A and go straight to global memory, so a unit can run whenever a warp has nothing else to do. `stop` (may be
-    // NULL): give up as soon as *stop >= stop_val (the event the caller is waiting for has happened).
-    auto height_units = [&](const int* stop, const int stop_val) {
+    // phase A and go straight to global memory. (Handing units to warps that wait at the barriers behind phases A / B was
+    // tried and measured 10 % slower: a unit once taken delays the barrier it was meant to fill.)
+    auto height_units = [&]() {
         if (!(P > 0 && (do_heights || do_obs))) return;
         const int lane = tid & 31;
         HeightArgs ha;
@@ -589,7 +656,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         const int ppp = P / n_piece;                 // points per piece
         for (;;) {
             int unit = 0x7fffffff;
-            if (lane == 0 && !(stop && ld_flag(stop) >= stop_val)) unit = atomicAdd(s_ctr, 1);
+            if (lane == 0) unit = atomicAdd(s_ctr, 1);
             unit = __shfl_sync(FULL_MASK, unit, 0);
             if (unit >= tile_rows * n_piece) break;
             const int el = unit / n_piece, p0 = (unit - el * n_piece) * ppp;
@@ -599,12 +666,25 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             if (do_heights) {
                 ha.g2 = make_float2(u.g.x, u.g.y); ha.gz = u.g.z;
                 if (LATTICE) {
-                    const int nxp = lat_nx / n_piece;
-                    const float2* a = s_lat + el * lat_nx + (unit - el * n_piece) * nxp;
+                    // (xs[i] c, xs[i] s): the two products of rotate_2d_vec that a whole lattice row shares
+                    const int nxp = lat_nx / n_piece, i0 = (unit - el * n_piece) * nxp;
+                    float2* a = s_lat + (tid >> 5) * lat_nx;
+                    __syncwarp();
+                    for (int i = lane; i < lat_nx; i += 32) a[i] = make_float2(__fmul_rn(s_axes[i], u.ch), __fmul_rn(s_axes[i], u.sh));
+                    __syncwarp();
                     const float y = s_axes[lat_nx + lane];
-                    if (orow && hrow) heights_of_env_lattice<true, true>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
-                    else if (orow) heights_of_env_lattice<false, true>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
-                    else heights_of_env_lattice<true, false>(a, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                    bool done = false;
+                    if (PARC_HEIGHT_PATCH) {
+                        float* patch = s_patch + (tid >> 5) * PATCH_FLOATS;
+                        if (orow && hrow) done = heights_of_env_patch<true, true>(a, y, i0, i0 + nxp, lat_nx, lane, ha, u.ch, u.sh, hrow, orow, patch);
+                        else if (orow) done = heights_of_env_patch<false, true>(a, y, i0, i0 + nxp, lat_nx, lane, ha, u.ch, u.sh, hrow, orow, patch);
+                        else done = heights_of_env_patch<true, false>(a, y, i0, i0 + nxp, lat_nx, lane, ha, u.ch, u.sh, hrow, orow, patch);
+                    }
+                    if (!done) {
+                        if (orow && hrow) heights_of_env_lattice<true, true>(a + i0, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                        else if (orow) heights_of_env_lattice<false, true>(a + i0, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                        else heights_of_env_lattice<true, false>(a + i0, y, nxp, lane, ha, u.ch, u.sh, hrow, orow);
+                    }
                 } else {
                     const float2 cs = make_float2(u.ch, u.sh), nsc = make_float2(-u.sh, u.ch);
                     if (ppp % (32 * PARC_HEIGHT_GATHERS) == 0) heights_of_env<true>(s_pts + p0, ppp, lane, ha, cs, nsc, hrow, orow);
@@ -626,17 +706,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         const int j = k >> 3, c = k & 7;
         s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
     }
-    // Heights as filler work (PARC_FILL_HEIGHTS): the lattice kernel hands height units to warps that would otherwise wait at a
-    // barrier. The flags must read zero before anybody polls them (shared memory keeps the previous block's bytes).
-    const bool fill = PARC_FILL_HEIGHTS && LATTICE && do_heights && P > 0;
-    if (tid < 4) s_ctr[tid] = 0;
-    if (fill) __syncthreads();
+    if (tid == 0) *s_ctr = 0;
     if (do_heights) {
         if (LATTICE) {
-            // xs[i] = x of point i * ny, ys[j] = y of point j (by the uniforms warp alone when the heights are filler work:
-            // its ready flag then covers them)
+            // xs[i] = x of point i * ny, ys[j] = y of point j
             PARC_COLD_LOOP
-            for (int k = fill ? tid - (THREADS - 32) : tid; k >= 0 && k < lat_nx + lat_ny; k += fill ? 32 : THREADS)
+            for (int k = tid; k < lat_nx + lat_ny; k += THREADS)
                 s_axes[k] = k < lat_nx ? __ldg(env.ray_xy_points + 2 * (long long)k * lat_ny) : __ldg(env.ray_xy_points + 2 * (k - lat_nx) + 1);
         } else {
             PARC_COLD_LOOP
@@ -671,20 +746,6 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
         if (need_char_q) s_charq[el * J] = quat_to_f4(c_rot);
       }
-      if (fill) {
-        // lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares; then
-        // publish: from here on any warp may sample the heights of this tile's envs
-        __syncwarp();
-        PARC_COLD_LOOP
-        for (int k = tid - (THREADS - 32); k < TILE * lat_nx; k += 32) {
-            const int el = k / lat_nx, i = k - el * lat_nx;
-            const float x = s_axes[i];
-            s_lat[k] = make_float2(__fmul_rn(x, s_env[el].ch), __fmul_rn(x, s_env[el].sh));
-        }
-        __threadfence_block();
-        __syncwarp();
-        if (tid == THREADS - 32) st_flag(s_ctr + 1, 1);
-      }
     } else if (tid >= THREADS - 64) {
       if (tid < THREADS - 64 + TILE) {
         const int el = tid - (THREADS - 64);
@@ -702,14 +763,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         }
         u.time = time;
         const long long mid = env.motion_ids[e];
-        u.mid = mid;
         const long long tidx = env.motion_terrain_ids[e];
         u.mm = load_motion_meta(lib.meta, mid);
         u.t0 = __fadd_rn(time, env.motion_time_offsets[e]);            // dm_env.py:547-552
         const float* dmo = env.dm_motion_offsets + (mid * env.terrains_per_motion + tidx) * 2;   // dm_env.py:554-565
         u.tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3)); u.toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
       }
-      if (fill) { __syncwarp(); if (tid == THREADS - 64) st_flag(s_ctr + 2, 1); }
     }
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
@@ -727,24 +786,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             s_charq[el * J + j] = quat_to_f4(q);
         }
     }
-    if (fill && tid < THREADS - 64) {
-        // the clip chain (time -> motion id -> clip meta -> terrain offset) is the last to arrive: sample heights until it does
-        while (ld_flag(s_ctr + 1) == 0) __nanosleep(64);
-        __threadfence_block();
-        height_units(s_ctr + 2, 1);
-    }
     __syncthreads();
     PARC_STAMP(1);
 
-    // A.4 lattice rows: (xs[i] c, xs[i] s) per env, the two products of rotate_2d_vec that a whole lattice row shares
-    if (LATTICE && do_heights && !fill) {
-        PARC_COLD_LOOP
-        for (int k = tid; k < TILE * lat_nx; k += THREADS) {
-            const int el = k / lat_nx, i = k - el * lat_nx;
-            const float x = s_axes[i];
-            s_lat[k] = make_float2(__fmul_rn(x, s_env[el].ch), __fmul_rn(x, s_env[el].sh));
-        }
-    }
     // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
     //      the two adjacent interp records (and the velocity record of the reference pose)
     if (do_reward || do_done) {
@@ -946,12 +990,6 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
             __syncwarp();
         }
-    }
-    if (fill && pose_work) {
-        // this warp's pose is done: sample heights until the other warps' poses are
-        __syncwarp();
-        if ((tid & 31) == 0) atomicAdd(s_ctr + 3, 1);
-        height_units(s_ctr + 3, THREADS / 32);
     }
     __syncthreads();
     PARC_STAMP(3);
@@ -1243,7 +1281,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     PARC_STAMP(6);
     // ================================ phase H ====================================================
     // the height units nobody has taken yet (all of them unless the heights were filler work)
-    height_units(nullptr, 0);
+    height_units();
 
     PARC_STAMP(7);
     // ================================ phase E (general) ===========================================
@@ -1469,7 +1507,7 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
                       sp.S.term_pitch == kFastS.term_pitch && sp.S.off_env == kFastS.off_env && sp.S.off_row == kFastS.off_row &&
                       sp.S.off_ref == kFastS.off_ref && sp.S.off_charq == kFastS.off_charq && sp.S.off_gx == kFastS.off_gx &&
                       sp.S.off_refmap == kFastS.off_refmap && sp.S.off_tab == kFastS.off_tab && sp.S.off_pts == kFastS.off_pts &&
-                      sp.S.off_lat == kFastS.off_lat && sp.S.off_ctr == kFastS.off_ctr && sp.S.total == kFastS.total;
+                      sp.S.off_lat == kFastS.off_lat && sp.S.off_patch == kFastS.off_patch && sp.S.off_ctr == kFastS.off_ctr && sp.S.total == kFastS.total;
     const int variant = fast ? 2 : (lattice ? 1 : 0);
     // opt-in dynamic shared memory: a per-device function attribute, raised only when a larger plan shows up
     static size_t smem_attr[64][3] = {};
@@ -1481,6 +1519,9 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
                        : variant == 1 ? cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total)
                                       : cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
         if (ce != cudaSuccess) { set_error("env_step: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+#ifdef PARC_STEP_CARVEOUT
+        if (variant == 2) cudaFuncSetAttribute(env_step_kernel<STEP_THREADS, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, PARC_STEP_CARVEOUT);
+#endif
         have = plan.total;
     }
     const long long blocks = (max_rows + TILE - 1) / TILE;
