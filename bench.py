@@ -49,6 +49,8 @@ def parse_args():
                     help="share of the envs the simulator stand-in pushes off their reference every step (they terminate and are "
                          "reset): 0.02 is the stationary BASELINE configs[1] workload, 0.1 with --envs 262144 is configs[4] (reset-heavy)")
     ap.add_argument("--chunks", type=int, default=6, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the `extra` block (BASELINE configs[2], [3], [4] measured beside the headline)")
+    ap.add_argument("--four-tensor-state", action="store_true", help="host-fed step with Isaac Gym's four state tensors instead of one interleaved row per env")
     return ap.parse_args()
 
 
@@ -118,7 +120,7 @@ def build_world(num_motions, seed=1234):
     return dict(clips=clips, hf=hf, min_point=min_point, dx=dx, dm_offsets=dm_offsets, ray=synth.grid_ray_points())
 
 
-def build_gpu_env(world, num_envs, first_env, total_envs, device):
+def build_gpu_env(world, num_envs, first_env, total_envs, device, interleaved=True):
     """Rank-local env over global env ids [first_env, first_env + num_envs) of a total_envs grid."""
     from parc_b200 import KinCharModel, MotionLib, SubTerrain, synth
     from parc_b200.tracking_env import TrackingEnv, default_env_config
@@ -133,7 +135,7 @@ def build_gpu_env(world, num_envs, first_env, total_envs, device):
     terrain.hf = hf.to(device).contiguous()
     offs = synth.env_offsets(total_envs)[first_env:first_env + num_envs]
     env = TrackingEnv(default_env_config(), num_envs, device, model, lib, terrain, world["dm_offsets"], world["ray"],
-                      env_offsets=offs, seed=20260 + first_env)
+                      env_offsets=offs, seed=20260 + first_env, interleaved_state=interleaved)
     return env
 
 
@@ -231,13 +233,42 @@ def run_cpu_port(world, num_envs, steps, warmup, threads, fail_fraction=0.02):
             "resets_per_step": float(np.mean(resets[warmup:]))}
 
 
-def cpu_baseline_block(world, args, steps, warmup):
-    cores = os.cpu_count() or 1
-    r = run_cpu_port(world, args.cpu_envs, steps, warmup, cores, args.fail_fraction)
-    return {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d envs x %d steps (+%d warm-up) of the same %d-clip / 32x32-heightmap workload, torch CPU eager, "
-                      "%d threads; median %.3f s/step, min %.3f s/step; %.1f resets/step"
-                      % (args.cpu_envs, steps, warmup, args.motions, cores, r["median_s"], r["min_s"], r["resets_per_step"])}, r
+def physical_cores():
+    try:
+        import psutil
+        return psutil.cpu_count(logical=False) or (os.cpu_count() or 1)
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline_block(world, args, steps, warmup, full_config_sample=True):
+    """The CPU arm: torch.set_num_threads swept over {1, physical cores} on a 4,096-env sample of
+    the workload, the best median kept; then, memory and time allowing, a short sample at the FULL 65,536 envs per step with
+    that thread count, so that the reported value is measured on the same configuration as the GPU arm."""
+    logical, phys = os.cpu_count() or 1, physical_cores()
+    sweep = []
+    for th in sorted({1, phys}):
+        st, wu = (max(4, steps // 3), 2) if th == 1 and phys > 1 else (steps, warmup)
+        r = run_cpu_port(world, args.cpu_envs, st, wu, th, args.fail_fraction)
+        sweep.append({"threads": th, "envs_per_step": args.cpu_envs, "steps": st, "value": args.cpu_envs / r["median_s"], "median_s": r["median_s"],
+                      "min_s": r["min_s"], "resets_per_step": r["resets_per_step"]})
+    best = max(sweep, key=lambda x: x["value"])
+    chosen, same_config = dict(best), False
+    if full_config_sample and args.envs >= args.cpu_envs * 2:
+        try:
+            r = run_cpu_port(world, args.envs, 3, 1, best["threads"], args.fail_fraction)
+            chosen = {"threads": best["threads"], "envs_per_step": args.envs, "steps": 3, "value": args.envs / r["median_s"], "median_s": r["median_s"],
+                      "min_s": r["min_s"], "resets_per_step": r["resets_per_step"]}
+            same_config = args.envs == ENVS_PER_GPU and args.motions == NUM_MOTIONS
+        except (RuntimeError, MemoryError) as exc:      # not enough host memory for the 65,536-env torch temporaries
+            chosen["full_config_error"] = str(exc)[:120]
+    cb = {"value": chosen["value"], "unit": UNIT, "cores": chosen["threads"], "kind": "port", "threads": chosen["threads"],
+          "physical_cores": phys, "logical_cores": logical, "envs_per_step": chosen["envs_per_step"], "median_s": chosen["median_s"],
+          "min_s": chosen["min_s"], "same_config": same_config, "thread_sweep": sweep,
+          "sample": "oracle port (torch CPU eager) of the same %d-clip / 32x32-heightmap workload incl. its resets: %d envs x %d steps at %d threads "
+                    "(median %.3f s/step, min %.3f s/step); thread sweep over {1, %d physical cores} at %d envs/step"
+                    % (args.motions, chosen["envs_per_step"], chosen["steps"], chosen["threads"], chosen["median_s"], chosen["min_s"], phys, args.cpu_envs)}
+    return cb, chosen
 
 
 def run_reference_arm(args):
@@ -248,18 +279,18 @@ def run_reference_arm(args):
         return
     world = build_world(args.motions)
     steps, warmup = max(args.steps, 1), max(args.warmup, 1)
-    # bounded: ~0.25 s/step at 4,096 envs on 8 threads -> cap the sample so the run stays within minutes
-    steps_cpu, warm_cpu = min(steps, 40), min(warmup, 5)
-    cb, r = cpu_baseline_block(world, args, steps_cpu, warm_cpu)
-    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps_cpu,
-            "warmup": warm_cpu, "ms_per_step": 1e3 * r["total_s"] / steps_cpu, "higher_is_better": True, "scaling": "weak",
+    # bounded: ~0.1-0.25 s/step at 4,096 envs -> cap the sample so the run stays within minutes
+    steps_cpu, warm_cpu = min(steps, 30), min(warmup, 5)
+    cb, ch = cpu_baseline_block(world, args, steps_cpu, warm_cpu)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": ch["steps"],
+            "warmup": warm_cpu, "ms_per_step": 1e3 * ch["median_s"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "65,536-env / 1,000-clip / 32x32-heightmap tracking step (same stand-in + step + reset as the b200 "
-                                   "arm); CPU arm runs a %d-env sample per step"
-                                   % args.cpu_envs, "envs_per_step": args.cpu_envs, "clips": args.motions, "ray_points": 1024,
-                       "obs_dim": 1895},
+                                   "arm); the CPU arm's value is measured at %d envs per step" % ch["envs_per_step"],
+                       "envs_per_step": ch["envs_per_step"], "clips": args.motions, "ray_points": 1024, "obs_dim": 1895,
+                       "same_config": cb["same_config"]},
             "cpu_baseline": cb,
-            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
 
@@ -267,6 +298,51 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def device_loop(env, noise, K, W, barrier, max_over_ranks):
+    """K control steps with the state resident in HBM, through the repo's API (TrackingEnv.sim_standin + TrackingEnv.step):
+    total time by CUDA events over the loop, the dominant kernel by events around each fused-step launch."""
+    env._kernel_events = None
+    for _ in range(W - 1):
+        env.sim_standin(noise)
+        env.step()
+    env.sim_standin(noise)
+    env.post_physics_step()
+    done_per_step = int(env._done_count.item())      # envs that finish (and are reset) in a steady-state step
+    env.reset_done()
+    barrier()
+    env._kernel_events = []
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    host_t0 = time.perf_counter()
+    for _ in range(K):
+        env.sim_standin(noise)                 # "physics": the character follows its reference with a fixed error
+        env.step()                             # fused post-physics pass + fail-rate EMA + device-side RSI reset + obs refresh
+    host_enqueue_ms = (time.perf_counter() - host_t0) * 1e3 / K
+    t_end.record()
+    barrier()
+    ev, env._kernel_events = env._kernel_events, None
+    ms_total = max_over_ranks(t_start.elapsed_time(t_end))
+    kern_ms = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in ev])))
+    return {"ms_total": ms_total, "kern_ms": kern_ms, "done_per_step": done_per_step, "host_enqueue_ms": host_enqueue_ms}
+
+
+def roofline_block(env, kern_ms, ms_per_step, traffic=None, warp_inst=None, sm_mhz=None):
+    step_bytes, b_env = algorithmic_bytes(env)
+    peak, peak_src = measured_peaks()
+    achieved = step_bytes / (kern_ms * 1e-3) / 1e9
+    out = {"bound": "hbm", "kernel": "env_step_kernel<512, lattice, fast>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+           "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": step_bytes,
+           "bytes_per_env": b_env, "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_per_step}
+    if warp_inst:
+        # the second roofline of this kernel: instruction issue = warp instructions (ncu, profiled launch) / (148 SMs x 4 warp
+        # schedulers x SM clock): the time the launch would take if every scheduler issued every cycle
+        floor_ms = warp_inst / (148 * 4 * (sm_mhz or 1965.0) * 1e6) * 1e3
+        out["issue"] = {"warp_instructions_per_launch": warp_inst, "warp_instructions_per_env": warp_inst / env.get_num_envs(),
+                        "floor_ms": floor_ms, "frac": floor_ms / kern_ms}
+    return out
+
+
 def run_gpu_arm(args):
     import torch.distributed as dist
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -283,9 +359,8 @@ def run_gpu_arm(args):
     K, W = max(args.steps, 1), max(args.warmup, 3)
 
     world = build_world(args.motions)
-    env = build_gpu_env(world, N, rank * N, n_gpus * N, dev)
+    env = build_gpu_env(world, N, rank * N, n_gpus * N, dev, interleaved=not args.four_tensor_state)
     init_gpu_state(env, rank * N)
-    step_bytes, b_env = algorithmic_bytes(env)
     from parc_b200 import synth
     noise = synth.standin_noise(N, env._J, env._D, seed=5678 + rank * N, fail_fraction=args.fail_fraction).to(dev)   # simulator stand-in
 
@@ -301,53 +376,26 @@ def run_gpu_arm(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return float(tt.item())
 
-    # ---- device-resident timing: K steps, per-launch events around the dominant kernel ---------------
-    def final_stats():
+    def final_stats(e):
         # final scalar reward / termination statistics: the only cross-rank exchange of the path
-        st = torch.stack([env._reward_buf.sum().double(), (env._done_buf != 0).sum().double(),
-                          env._motion_id_fail_rates.mean().double()])
+        st = torch.stack([e._reward_buf.sum().double(), e._done_count.sum().double(), e._motion_id_fail_rates.mean().double()])
         if distributed:
             dist.all_reduce(st, op=dist.ReduceOp.SUM)
         return st
 
-    for _ in range(W - 1):
-        env.sim_standin(noise)
-        env.step()
-    env.sim_standin(noise)
-    env.post_physics_step()
-    done_per_step = int(env._done_count.item())      # envs that finish (and are reset) in a steady-state step
-    env.reset_done()
-    final_stats()          # warm-up covers the statistics reduction too (first use loads its kernels / NCCL channels)
-    barrier()
+    final_stats(env)       # warm-up covers the statistics reduction too (first use loads its kernels / NCCL channels)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    from parc_b200 import _lib
-    L = _lib.lib()
-    km, lib_cs = env._kin_char_model._cstruct(), env._mlib.cstruct()
-    stream = env._stream()
-    barrier()
-    t_start.record()
-    host_t0 = time.perf_counter()
-    for i in range(K):
-        env.sim_standin(noise)                 # "physics": the character follows its reference with a fixed error
-        ev[i][0].record()
-        _lib.check(L.parc_b200_env_step(km, lib_cs, env._terrain_cs, env._cfg, env._bufs, _lib.STEP_ALL, None, 0, stream))
-        ev[i][1].record()
-        _lib.check(L.parc_b200_fail_rate_ema(env._cfg, env._bufs, env._mlib.num_motions(), _lib.ptr(env._cdf),
-                                             _lib.ptr(env._ema_scratch), stream))
-        env._step_count += 1
-        env.reset_done()
-    host_enqueue_ms = (time.perf_counter() - host_t0) * 1e3 / K
-    stats = final_stats()
-    t_end.record()
+    # ---- device-resident timing -------------------------------------------------------------------------
+    dl = device_loop(env, noise, K, W, barrier, max_over_ranks)
+    env.sim_standin(noise)
+    env.post_physics_step()
+    stats = final_stats(env)             # done count of a steady-state step, before the reset clears the flags
+    env.reset_done()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    ms_total = max_over_ranks(t_start.elapsed_time(t_end))
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    kern_ms = max_over_ranks(kern_ms)
+    ms_total, kern_ms = dl["ms_total"], dl["kern_ms"]
     value = n_gpus * N * K / (ms_total * 1e-3)
 
     # ---- end to end: host buffers in, host results out, every step -----------------------------------
@@ -385,47 +433,100 @@ def run_gpu_arm(args):
         # the public host-buffer call: parc_b200_env_step_host uploads range c+1 while range c is stepped
         env.step_host(host_state, host_res, num_chunks=args.chunks, standin_noise=noise)
 
+    def h2d_only():
+        env.upload_sim_state(host_state)       # the PCIe floor of the host-fed step: the upload alone
+
+    h2d_ms = time_e2e(h2d_only)
     e2e_serial_ms = time_e2e(e2e_serial)
     e2e_ms = time_e2e(e2e_chunked)
     e2e_value = n_gpus * N * Ke / (e2e_ms * 1e-3)
 
+    # ---- the other BASELINE configs, measured by the same invocation (`extra`) -------------------------
+    extra = None
+    if not args.no_extra:
+        extra = {}
+        del env, noise, host_state, host_res
+        torch.cuda.empty_cache()
+        Kx, Wx = min(K, 20), 3
+
+        def side_config(envs_per_rank, fail_fraction, label):
+            e = build_gpu_env(world, envs_per_rank, rank * envs_per_rank, n_gpus * envs_per_rank, dev)
+            init_gpu_state(e, rank * envs_per_rank)
+            nz = synth.standin_noise(envs_per_rank, e._J, e._D, seed=5678 + rank * envs_per_rank, fail_fraction=fail_fraction).to(dev)
+            smp = ClockSampler(local_rank)
+            if rank == 0:
+                smp.start()
+            r = device_loop(e, nz, Kx, Wx, barrier, max_over_ranks)
+            ck = smp.stop() if rank == 0 else None
+            out = {"workload": label, "n_gpus": n_gpus, "envs_per_gpu": envs_per_rank, "envs_total": n_gpus * envs_per_rank, "steps": Kx, "warmup": Wx,
+                   "value": n_gpus * envs_per_rank * Kx / (r["ms_total"] * 1e-3), "unit": UNIT, "ms_per_step": r["ms_total"] / Kx,
+                   "resets_per_step_per_gpu": r["done_per_step"], "standin_fail_fraction": fail_fraction,
+                   "roofline": roofline_block(e, r["kern_ms"], r["ms_total"] / Kx), "clocks": ck}
+            del e, nz
+            torch.cuda.empty_cache()
+            return out
+
+        # configs[4]: reset-heavy sweep, 262,144 envs in total over the invoked ranks, ~10 % terminate and are RSI-reset per step
+        extra["config5_reset_heavy"] = side_config(262144 // n_gpus, 0.1, "BASELINE configs[4]: 262,144 envs over %d GPU(s), 10 %% early "
+                                                   "termination + RSI reset per step" % n_gpus)
+        # configs[2]: one GPU's share of 1,048,576 envs over 8 GPUs (the full config when invoked with --gpus 8)
+        extra["config3_share"] = side_config(131072, args.fail_fraction, "BASELINE configs[2]: 131,072 envs per GPU (= 1,048,576 over 8 GPUs%s)"
+                                             % ("" if n_gpus == 8 else "; this run has %d" % n_gpus))
+        # configs[3]: kinematic optimizer batch, rank 0 only (it does not shard in the reference either: independent motions)
+        if rank == 0:
+            import bench_optimizer
+            extra["config4_optimizer"] = bench_optimizer.run(1024, 300, steps=5, warmup=3, cpu_motions=0, dev=dev, peak_gbs=measured_peaks()[0])
+        barrier()
+
     # ---- CPU baseline (rank 0, N=1 only) ------------------------------------------------------------
     cb = None
     if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
-        cb, _ = cpu_baseline_block(world, args, 30, 5)
+        cb, _ = cpu_baseline_block(world, args, 20, 3)
 
     if rank == 0:
-        peak, peak_src = measured_peaks()
-        achieved = step_bytes / (kern_ms * 1e-3) / 1e9
-        traffic = None
+        traffic, traffic_src, warp_inst = None, None, None
         tpath = os.path.join(ROOT, "profiles", "env_step_traffic.json")
         if os.path.exists(tpath):
             with open(tpath) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                tj = json.load(f)
+            traffic, traffic_src = tj.get("dram_bytes_per_launch"), tj.get("source")
+            warp_inst = tj.get("warp_instructions_per_launch") if N == ENVS_PER_GPU else None
+        # re-create what the roofline needs (the env object is gone when extras ran): sizes only
+        class _Sizes:
+            pass
+        rf_env = _Sizes()
+        rf_env.get_num_envs = lambda: N
+        rf_env._ray_xy_points = world["ray"]
+        rf_env._mlib = _Sizes()
+        rf_env._mlib._frame_root_pos = torch.empty(sum(int(c["root_pos"].shape[0]) for c in world["clips"]), 0)
+        rf_env._terrain = _Sizes()
+        rf_env._terrain.hf = world["hf"]
+        roof = roofline_block(rf_env, kern_ms, ms_total / K, traffic if N == ENVS_PER_GPU else None, warp_inst, (clocks or {}).get("sm_mhz"))
+        roof["traffic_source"] = traffic_src
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
-            "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": host_enqueue_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": dl["host_enqueue_ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "65,536 envs/GPU, 1,000-clip synthetic library of the repo humanoid, 32x32 local heightmap "
                                    "observations (BASELINE configs[1]); step = simulator stand-in (char := ref + fixed noise, FK) + post-physics "
-                                   "pass + fail-rate EMA + device-side RSI reset + obs refresh of the reset envs",
-                       "envs_per_gpu": N, "clips": args.motions, "frames": int(env._mlib._frame_root_pos.shape[0]),
-                       "ray_points": int(env._ray_xy_points.shape[0]), "resets_per_step": done_per_step,
-                       "standin_fail_fraction": args.fail_fraction, "obs_dim": env.get_obs_dim(),
-                       "terrain_cells": list(env._terrain.hf.shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,
-                       "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (step_bytes / 1e9)},
+                                   "pass + fail-rate EMA + device-side RSI reset + obs refresh of the reset envs, through TrackingEnv.step()",
+                       "envs_per_gpu": N, "clips": args.motions, "frames": int(rf_env._mlib._frame_root_pos.shape[0]),
+                       "ray_points": int(world["ray"].shape[0]), "resets_per_step": dl["done_per_step"],
+                       "standin_fail_fraction": args.fail_fraction, "obs_dim": 871 + int(world["ray"].shape[0]),
+                       "terrain_cells": list(world["hf"].shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,
+                       "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (roof["algorithmic_bytes_per_launch"] / 1e9)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / Ke, "chunks": args.chunks, "ms_per_step_unpipelined": e2e_serial_ms / Ke,
-                    "note": "TrackingEnv.step_host -> parc_b200_env_step_host: every step uploads root/dof/rigid-body/contact state from "
-                            "pinned host memory in row ranges (range c+1 in flight while range c is stepped), fail-rate EMA, D2H of "
-                            "reward+done, RSI reset, host sync; the observation stays on the device for the policy, as in the reference"},
+                    "h2d_ms": h2d_ms / Ke, "h2d_gbs": h2d / (h2d_ms / Ke * 1e-3) / 1e9,
+                    "state_layout": "four tensors" if args.four_tensor_state else "one interleaved row per env (one copy per range)",
+                    "note": "TrackingEnv.step_host -> parc_b200_env_step_host: every step uploads the simulator state from pinned host memory "
+                            "in row ranges (range c+1 in flight while range c is stepped), fail-rate EMA, D2H of reward+done, RSI reset, host "
+                            "sync; the observation stays on the device for the policy, as in the reference. h2d_ms = the upload alone (PCIe floor)"},
             "gpu_launches": LAUNCHES_PER_STEP * K,
-            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<512>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": step_bytes, "bytes_per_env": b_env,
-                         "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / (ms_total / K)},
+            "roofline": roof,
             "cpu_baseline": cb,
+            "extra": extra,
             "stats": {"reward_sum": float(stats[0]), "done_last_step": float(stats[1]), "mean_fail_rate": float(stats[2]) / n_gpus},
         }
         print(json.dumps(line))

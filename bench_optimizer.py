@@ -24,10 +24,10 @@ KIN_GEN = dict(w_root_pos=1.0, w_root_rot=10.0, w_joint_rot=1.0, w_smoothness=10
 NAMES = ("src_root_pos", "src_root_rot_quat", "src_joint_rot", "src_body_vels", "src_body_rot_vels", "contacts")
 
 
-def build_batch(model, B, T, seed, dev):
+def build_batch(model, B, T, seed, dev, distinct=True):
     """Synthetic clips (SURVEY 8d generator) with their own 32x32 terrains; source features by the CUDA FK."""
     from parc_b200 import synth
-    gen = min(B, 64)
+    gen = B if distinct else min(B, 64)
     clips = synth.make_clips(synth.humanoid_spec(), gen, seed=seed, min_frames=T, max_frames=T, wrap_fraction=0.0)
     rp = torch.stack([c["root_pos"] for c in clips]).to(dev)
     rr = torch.stack([c["root_rot"] for c in clips]).to(dev)
@@ -72,23 +72,16 @@ def model_rot_to_exp(q):
     return torch.where(ln > 1e-5, axis * ang, torch.zeros_like(axis))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--motions", type=int, default=1024)
-    ap.add_argument("--frames", type=int, default=300)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--cpu-motions", type=int, default=2)
-    args = ap.parse_args()
+def run(B=1024, T=300, steps=10, warmup=3, cpu_motions=2, dev=None, peak_gbs=None):
+    """One measurement of BASELINE configs[3]; returns the JSON-able dict (bench.py's `extra.config4` calls this too)."""
     assert torch.cuda.is_available(), "needs a CUDA device (no CPU fallback on the product path)"
-    dev = torch.device("cuda", 0)
+    dev = dev or torch.device("cuda", 0)
     from parc_b200 import KinCharModel, geom_util, synth
     from parc_b200.motion_optimization import motion_loss_batched
     model = KinCharModel(dev)
     model.load_char_file(synth.HUMANOID_JSON)
     pts = geom_util.get_char_point_samples(model)
-    B, T = args.motions, args.frames
-    d, dx = build_batch(model, B, T, 77, dev)
+    d, dx = build_batch(model, B, T, 77, dev, distinct=True)
     dxdy = torch.tensor([dx, dx])
 
     def step():
@@ -97,19 +90,19 @@ def main():
         loss.sum().backward()
         return loss, terms, p
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(max(warmup, 3)):
         step()
-    torch.cuda.synchronize()
+    torch.cuda.synchronize(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         loss, terms, p = step()
     e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / args.steps
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
     # CPU oracle port on a bounded sample (test infrastructure used as the reported baseline only)
     cpu = None
-    if args.cpu_motions > 0:
+    if cpu_motions > 0:
         from oracle import parc_oracle_opt as OO
         from tests import helpers as H
         om = H.oracle_model()
@@ -119,21 +112,41 @@ def main():
                                   "w_body_constraints", "w_jerk", "max_jerk")]
         torch.set_num_threads(os.cpu_count() or 1)
         t0 = time.perf_counter()
-        for b in range(args.cpu_motions):
+        for b in range(cpu_motions):
             po = [d[k][b].cpu().clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
             lo, _ = OO.motion_loss(om, bp, counts, d["hf"][b].cpu(), d["min_point"][b].cpu(), dxdy, po[0], po[1], po[2],
                                    *[d[k][b].cpu() for k in NAMES], w)
             lo.backward()
-        dt = (time.perf_counter() - t0) / args.cpu_motions
+        dt = (time.perf_counter() - t0) / cpu_motions
         cpu = {"value": 1.0 / dt, "unit": "motions/s", "cores": os.cpu_count(), "kind": "port",
-               "sample": "%d of the %d motions, torch CPU autograd, %.2f s per motion fwd+bwd" % (args.cpu_motions, B, dt)}
+               "sample": "%d of the %d motions, torch CPU autograd, %.2f s per motion fwd+bwd" % (cpu_motions, B, dt)}
     frames = B * T
     alg_bytes = frames * 266 * 4            # params + grads + source pose + contacts + source body vels per frame
-    print(json.dumps({"metric": "optimizer loss fwd+bwd, motions/s (1,024 x 300 frames)", "value": B / (ms * 1e-3), "unit": "motions/s",
-                      "ms_per_eval": ms, "frames_per_s": frames / (ms * 1e-3), "config": {"workload": "BASELINE configs[3]", "motions": B,
-                      "frames": T, "body_points": int(sum(x.shape[0] for x in pts)), "terrain": list(d["hf"].shape[1:])},
-                      "hbm_floor_ms": alg_bytes / 6546.6e9 * 1e3, "cpu_baseline": cpu,
-                      "stats": {"mean_loss": float(loss.mean()), "mean_penetration": float(terms[:, 4].mean())}}))
+    if peak_gbs is None:
+        peak_gbs = 6550.7
+        mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(mp):
+            peak_gbs = float(json.load(open(mp))["hbm_gbs"])
+    achieved = alg_bytes / (ms * 1e-3) / 1e9
+    return {"metric": "optimizer loss fwd+bwd, motions/s (1,024 x 300 frames)", "value": B / (ms * 1e-3), "unit": "motions/s",
+            "ms_per_eval": ms, "frames_per_s": frames / (ms * 1e-3),
+            "config": {"workload": "BASELINE configs[3]: %d distinct synthetic motions x %d frames, own 32x32 terrains" % (B, T), "motions": B,
+                       "frames": T, "body_points": int(sum(x.shape[0] for x in pts)), "terrain": list(d["hf"].shape[1:])},
+            "roofline": {"bound": "fp32 ALU / shared memory (SURVEY 8d); HBM floor shown", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
+                         "frac": achieved / peak_gbs, "algorithmic_bytes_per_eval": alg_bytes, "hbm_floor_ms": alg_bytes / (peak_gbs * 1e9) * 1e3},
+            "cpu_baseline": cpu,
+            "stats": {"mean_loss": float(loss.mean()), "mean_penetration": float(terms[:, 4].mean())}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--motions", type=int, default=1024)
+    ap.add_argument("--frames", type=int, default=300)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--cpu-motions", type=int, default=2)
+    args = ap.parse_args()
+    print(json.dumps(run(args.motions, args.frames, args.steps, args.warmup, args.cpu_motions)))
 
 
 if __name__ == "__main__":

@@ -175,7 +175,7 @@ class TrackingEnv:
 
     def __init__(self, env_config, num_envs, device, char_model: KinCharModel, motion_lib: MotionLib,
                  terrain: SubTerrain, dm_motion_offsets, ray_xy_points, env_offsets=None, seed=0,
-                 keep_ray_hfs=False):
+                 keep_ray_hfs=False, interleaved_state=False):
         dev = torch.device(device)
         assert dev.type == "cuda", "TrackingEnv runs on a CUDA device only (no CPU fallback)"
         self._device = dev
@@ -198,20 +198,33 @@ class TrackingEnv:
         self._env_offsets = (z(N, 3) if env_offsets is None else env_offsets.to(device=dev, dtype=f32)).contiguous()
         assert self._env_offsets.shape == (N, 3)
 
-        # simulator tensors in Isaac Gym's layout (ig_char_env.py:172-196): the char_* names are views
-        self._root_state = z(N, 13)
+        # simulator tensors in Isaac Gym's layout (ig_char_env.py:172-196): the char_* names are views.
+        # interleaved_state: the four tensors a simulator hands over every step are column blocks of ONE [N, 13 + 2D + 6J] row
+        # (root 13 | dof D x 2 | rigid-body pos 3J | contact forces 3J; 636 bytes for the humanoid), so a host-fed step uploads a
+        # row range with one copy instead of four. The kernels read through strided views either way.
+        self._interleaved = bool(interleaved_state)
+        if self._interleaved:
+            W = 13 + 2 * D + 6 * J
+            self._sim_state = z(N, W)
+            self._root_state = self._sim_state[:, 0:13]
+            self._dof_state = self._sim_state[:, 13:13 + 2 * D].unflatten(1, (D, 2))
+            self._char_rigid_body_pos = self._sim_state[:, 13 + 2 * D:13 + 2 * D + 3 * J].unflatten(1, (J, 3))
+            self._char_contact_forces = self._sim_state[:, 13 + 2 * D + 3 * J:W].unflatten(1, (J, 3))
+        else:
+            self._sim_state = None
+            self._root_state = z(N, 13)
+            self._dof_state = z(N, D, 2)
+            self._char_rigid_body_pos = z(N, J, 3)
+            self._char_contact_forces = z(N, J, 3)
         self._root_state[:, 6] = 1.0
-        self._dof_state = z(N, D, 2)
         self._char_root_pos = self._root_state[:, 0:3]
         self._char_root_rot = self._root_state[:, 3:7]
         self._char_root_vel = self._root_state[:, 7:10]
         self._char_root_ang_vel = self._root_state[:, 10:13]
         self._char_dof_pos = self._dof_state[:, :, 0]
         self._char_dof_vel = self._dof_state[:, :, 1]
-        self._char_rigid_body_pos = z(N, J, 3)
         self._char_rigid_body_vel = z(N, J, 3)
         self._char_rigid_body_ang_vel = z(N, J, 3)
-        self._char_contact_forces = z(N, J, 3)
         # reference-motion state
         self._ref_root_pos, self._ref_root_rot = z(N, 3), z(N, 4)
         self._ref_root_vel, self._ref_root_ang_vel = z(N, 3), z(N, 3)
@@ -243,6 +256,7 @@ class TrackingEnv:
         self._demo_mode = bool(env_config.get("demo_mode", False))
         self._root_pos_offset = None
         self._root_rot_offset = None
+        self._kernel_events = None        # a list: post_physics_step appends (start, end) CUDA events around the fused step launch
         self._build_buffers_struct()
 
     # ---------------------------------------------------------------- descriptors
@@ -293,7 +307,15 @@ class TrackingEnv:
             self._ref_dof_vel)
 
     def sim_state_tensors(self):
-        """The tensors an external integrator (or a host upload) writes every step."""
+        """The tensors an external integrator (or a host upload) writes every step: one interleaved [N, W] row per env
+        (interleaved_state=True) or Isaac Gym's four tensors."""
+        if self._interleaved:
+            return {"sim_state": self._sim_state}
+        return {"root_state": self._root_state, "dof_state": self._dof_state,
+                "rigid_body_pos": self._char_rigid_body_pos, "contact_forces": self._char_contact_forces}
+
+    def sim_state_parts(self):
+        """The same state by Isaac Gym's tensor names (views of the interleaved row when interleaved_state=True)."""
         return {"root_state": self._root_state, "dof_state": self._dof_state,
                 "rigid_body_pos": self._char_rigid_body_pos, "contact_forces": self._char_contact_forces}
 
@@ -328,8 +350,15 @@ class TrackingEnv:
         L = _lib.lib()
         if parts & _lib.STEP_DONE:
             self._done_count.zero_()      # the step kernel appends finished envs to done_list
+        ev = None
+        if self._kernel_events is not None:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         _lib.check(L.parc_b200_env_step(km, self._mlib.cstruct(), self._terrain_cs, self._cfg, self._bufs, parts, None, 0,
                                         self._stream()))
+        if ev is not None:
+            ev[1].record()
+            self._kernel_events.append(ev)
         if (parts & _lib.STEP_DONE) and update_fail_rates:
             _lib.check(L.parc_b200_fail_rate_ema(self._cfg, self._bufs, self._mlib.num_motions(), _lib.ptr(self._cdf),
                                                  _lib.ptr(self._ema_scratch), self._stream()))
