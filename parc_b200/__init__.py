@@ -11,6 +11,7 @@ from .motion_lib import MotionLib, LoopMode                                   # 
 from .terrain import SubTerrain                                               # noqa: F401
 from .file_io import MotionFrames, load_ms_file, save_ms_file                 # noqa: F401
 from . import dm_util                                                         # noqa: F401
+from .dm_env import DeepMimicEnv, DeepMimicEnvB200, RefCharEnv                # noqa: F401
 
 __all__ = ["KinCharModel", "Joint", "JointType", "Geom", "GeomType", "MotionLib", "LoopMode", "SubTerrain",
-           "MotionFrames", "load_ms_file", "save_ms_file", "dm_util"]
+           "MotionFrames", "load_ms_file", "save_ms_file", "dm_util", "DeepMimicEnv", "DeepMimicEnvB200", "RefCharEnv"]

@@ -66,6 +66,19 @@ def compute_tar_obs(ref_root_pos, ref_root_rot, tar_root_pos, tar_root_rot, join
     return obs
 
 
+def compute_deepmimic_obs(root_pos, root_rot, root_vel, root_ang_vel, joint_rot, dof_vel, key_pos, global_obs, root_height_obs,
+                          enable_tar_obs, tar_root_pos, tar_root_rot, tar_joint_rot, tar_key_pos):
+    """mgdm_dm_util.py:463-495 -> OrderedDict(char_obs [n, .], tar_obs [n, S, .])."""
+    from collections import OrderedDict
+    obs = OrderedDict()
+    obs["char_obs"] = compute_char_obs(root_pos=root_pos, root_rot=root_rot, root_vel=root_vel, root_ang_vel=root_ang_vel, joint_rot=joint_rot,
+                                       dof_vel=dof_vel, key_pos=key_pos, global_obs=global_obs, root_height_obs=root_height_obs)
+    if enable_tar_obs:
+        obs["tar_obs"] = compute_tar_obs(ref_root_pos=root_pos, ref_root_rot=root_rot, tar_root_pos=tar_root_pos, tar_root_rot=tar_root_rot,
+                                         joint_rot=tar_joint_rot, tar_key_pos=tar_key_pos, global_obs=global_obs, global_tar_root_h_obs=False)
+    return obs
+
+
 def compute_deepmimic_reward(root_pos, root_rot, root_vel, root_ang_vel, joint_rot, dof_vel, key_pos, tar_root_pos, tar_root_rot,
                              tar_root_vel, tar_root_ang_vel, tar_joint_rot, tar_dof_vel, tar_key_pos, joint_rot_err_w, dof_err_w,
                              track_root_h: bool, track_root: bool):
