@@ -262,16 +262,28 @@ int parc_b200_env_reset(const parc_char_model_t* h_model, const parc_motion_lib_
                         const float* xy_noise, const float* root_pos_offset,
                         const float* root_rot_offset, void* stream);
 
+/* The per-call knobs of DeepMimicEnv.reset that are not random draws (all optional; a NULL struct = all defaults). */
+typedef struct parc_reset_options_t {
+    const float* root_pos_offset;              /* [N,3] RefCharEnv._root_pos_offset (mgdm_dm_util.py:108-112), indexed by env id, or NULL */
+    const float* root_rot_offset;              /* [N,4] RefCharEnv._root_rot_offset (:113-115), or NULL */
+    const float* motion_start_time_fraction;   /* [N] DeepMimicEnv._motion_start_time_fraction (dm_env.py:92, 500-502): used when
+                                                  rand_reset == 0; NULL = zeros */
+    int32_t demo_mode;                         /* dm_env.py:479-480: motion id = env id % num_motions instead of a draw */
+} parc_reset_options_t;
+
 /* Device-side RSI for the graph-captured loop: for each entry of done_list (count read on the
  * device) draw motion id (inverse CDF over `cdf`, binary search), terrain id and phase from a
  * Philox4x32-10 counter keyed by (seed, env id, step), then do everything parc_b200_env_reset does
  * and re-evaluate heights + observation of the reset envs (IGParkourEnv.reset,
- * ig_parkour_env.py:809-829). Zeroes done_count when finished iff reset_count != 0. */
+ * ig_parkour_env.py:809-829). Zeroes done_count when finished.
+ * `cdf` [M] is the inclusive prefix sum of the sampling weights: clamp(fail_rate, min_motion_weight) * motion_weight as
+ * parc_b200_fail_rate_ema leaves it (dm_env.py:487-490), or of motion_weight alone for dm.ignore_fail_rates (:485-486);
+ * it must be positive at the end (an all-zero CDF would send every env to the last motion). */
 int parc_b200_env_reset_sampled(const parc_char_model_t* h_model, const parc_motion_lib_t* h_lib,
                                 const parc_terrain_t* h_terrain, const parc_env_config_t* h_cfg,
                                 const parc_env_buffers_t* h_env, const float* cdf,
                                 int32_t num_motions, uint64_t seed, uint64_t step,
-                                int32_t rand_reset, void* stream);
+                                int32_t rand_reset, const parc_reset_options_t* h_options, void* stream);
 
 /* Inverse-CDF sampler alone (MotionLib.sample_motions semantics given uniforms u [n] in [0,1)):
  * ids[i] = first m with cdf[m] > u[i] * cdf[M-1]. */

@@ -62,6 +62,11 @@ class RecordTapeStruct(C.Structure):         # parc_record_tape_t, include/parc_
                 ("overflow", C.c_void_p), ("max_frames", C.c_int32), ("obs_dim", C.c_int32)]
 
 
+class ResetOptionsStruct(C.Structure):       # parc_reset_options_t, include/parc_b200_env.h
+    _fields_ = [("root_pos_offset", C.c_void_p), ("root_rot_offset", C.c_void_p), ("motion_start_time_fraction", C.c_void_p),
+                ("demo_mode", C.c_int32)]
+
+
 class HostRowsStruct(C.Structure):
     _fields_ = [("dst_device", C.c_void_p), ("src_host", C.c_void_p), ("row_bytes", C.c_int64)]
 
@@ -230,7 +235,7 @@ def _declare(lib):
         "parc_b200_env_reset": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),
                                 vp, i64, vp, vp, vp, vp, vp, vp, vp],
         "parc_b200_env_reset_sampled": [P(CharModelStruct), P(MotionLibStruct), P(TerrainStruct),
-                                        P(EnvConfigStruct), P(EnvBuffersStruct), vp, i32, u64, u64, i32, vp],
+                                        P(EnvConfigStruct), P(EnvBuffersStruct), vp, i32, u64, u64, i32, P(ResetOptionsStruct), vp],
         "parc_b200_sample_motions_cdf": [vp, i32, vp, i64, vp, vp],
         "parc_b200_sim_standin": [P(CharModelStruct), P(EnvBuffersStruct), vp, vp],
         "parc_b200_points_hf_sdf": [vp, i64, i64, vp, i32, i32, vp, f32, f32, f32, i32, vp, vp, vp],

@@ -133,7 +133,10 @@ extern "C" int parc_b200_fail_rate_ema(const parc_env_config_t* cfg, const parc_
     const size_t table_bytes = tables ? (size_t)num_motions * 8 : 0;
     const long long cap = std::min<long long>(env->num_envs, (long long)((200 * 1024 - table_bytes) / 4));
     const size_t smem = table_bytes + (size_t)cap * 4;
-    static size_t smem_set = 0;
+    static size_t smem_set_of_device[64] = {};             // the opt-in is a per-device function attribute
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& smem_set = smem_set_of_device[dev & 63];
     if (smem > smem_set) {
         cudaError_t ce = cudaFuncSetAttribute(fail_rate_ema_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
         if (ce != cudaSuccess) { set_error("fail_rate_ema: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
@@ -173,8 +176,11 @@ extern "C" int parc_b200_env_reset(const parc_char_model_t* m, const parc_motion
 
 extern "C" int parc_b200_env_reset_sampled(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrain,
                                            const parc_env_config_t* cfg, const parc_env_buffers_t* env, const float* cdf,
-                                           int32_t num_motions, uint64_t seed, uint64_t step, int32_t rand_reset, void* stream) {
+                                           int32_t num_motions, uint64_t seed, uint64_t step, int32_t rand_reset,
+                                           const parc_reset_options_t* options, void* stream) {
     if (!model_ok(m, "env_reset_sampled")) return PARC_ERR_INVALID_ARG;
+    parc_reset_options_t opt = {};
+    if (options) opt = *options;
     PARC_REQUIRE(lib && lib->interp && cfg && env && terrain && cdf && num_motions > 0, "env_reset_sampled: NULL descriptor");
     PARC_REQUIRE(env->done_count && env->done_list, "env_reset_sampled: done list not set");
     int rc = check_reset_views(env, "env_reset_sampled");
@@ -182,7 +188,7 @@ extern "C" int parc_b200_env_reset_sampled(const parc_char_model_t* m, const par
     if (env->num_envs == 0) return PARC_OK;
     // sized for the worst case (every env finished); groups beyond the device-side count exit at once
     G_DISPATCH(env_reset_sampled_kernel, env->num_envs, *m, *lib, *cfg, *env, cdf, num_motions, (unsigned long long)seed,
-               (unsigned long long)step, rand_reset);
+               (unsigned long long)step, rand_reset, opt);
     rc = check_launch("env_reset_sampled(reset)");
     if (rc) return rc;
     // IGParkourEnv.reset (ig_parkour_env.py:809-829): heights + observation of the reset envs

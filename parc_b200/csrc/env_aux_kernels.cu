@@ -448,7 +448,8 @@ __device__ __forceinline__ int sample_cdf(const float* __restrict__ cdf, int M, 
 template <int G>
 __global__ void __launch_bounds__(256) env_reset_sampled_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_motion_lib_t lib,
                                                                 const __grid_constant__ parc_env_config_t cfg, const __grid_constant__ parc_env_buffers_t env,
-                                                                const float* __restrict__ cdf, int M, unsigned long long seed, unsigned long long step, int rand_reset) {
+                                                                const float* __restrict__ cdf, int M, unsigned long long seed, unsigned long long step, int rand_reset,
+                                                                const parc_reset_options_t opt) {
     const LaneBody lb = load_lane_body<G>(cm);
     const long long gpb = blockDim.x / G;
     const long long n = min((long long)*env.done_count, (long long)env.num_envs);
@@ -457,13 +458,15 @@ __global__ void __launch_bounds__(256) env_reset_sampled_kernel(const __grid_con
         if (env.done_buf[e] == PARC_DONE_NULL) continue;   // never_done: counted for the EMA, not reset
         const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
         const uint4 r0 = philox4x32_10(make_uint4((unsigned)e, (unsigned)(e >> 32), (unsigned)step, (unsigned)(step >> 32)), key);
-        const long long mid = sample_cdf(cdf, M, u01(r0.x));                                       // sample_motions, motion_lib.py:56-60
+        // demo mode: env_id % num_motions (dm_env.py:479-480); else sample_motions over the CDF (motion_lib.py:56-60)
+        const long long mid = opt.demo_mode ? e % M : sample_cdf(cdf, M, u01(r0.x));
         const long long tid = (long long)(r0.y % (unsigned)env.terrains_per_motion);               // randint, dm_env.py:496
         const float len = __int_as_float(__ldg(lib.meta + 8 * mid + 2));
-        const float mtime = rand_reset ? u01(r0.z) * len : 0.f;                                    // sample_time, motion_lib.py:62-71
+        // sample_time (motion_lib.py:62-71), or length * _motion_start_time_fraction[env] (dm_env.py:500-502; zeros when not set)
+        const float mtime = rand_reset ? u01(r0.z) * len : (opt.motion_start_time_fraction ? __fmul_rn(len, opt.motion_start_time_fraction[e]) : 0.f);
         const uint4 r1 = philox4x32_10(make_uint4((unsigned)e, (unsigned)(e >> 32), (unsigned)step, (unsigned)(step >> 32) ^ 0x80000000u), key);
         const float nx = u01(r1.x) * 2.0f - 1.0f, ny = u01(r1.y) * 2.0f - 1.0f;                    // mgdm_dm_util.py:103
-        reset_one_env<G>(cm, lib, cfg, env, lb, e, mid, tid, mtime, nx, ny, nullptr, nullptr);
+        reset_one_env<G>(cm, lib, cfg, env, lb, e, mid, tid, mtime, nx, ny, opt.root_pos_offset, opt.root_rot_offset);
     }
 }
 

@@ -11,6 +11,7 @@ namespace parc {
 
 // float min through integer atomics (values of either sign)
 __device__ __forceinline__ void atomic_min_float(float* addr, float v) {
+    v += 0.0f;                                           // -0.0 -> +0.0: its bit pattern (INT_MIN) would win every signed min
     if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
     else atomicMax(reinterpret_cast<unsigned*>(addr), __float_as_uint(v));
 }
@@ -116,7 +117,11 @@ extern "C" int parc_b200_hf_mask_inds(const parc_char_model_t* m, const parc_ter
     PARC_REQUIRE(body_pos && body_rot && body_points && point_start && inds && counts, "hf_mask_inds: NULL pointer");
     PARC_REQUIRE(num_points > 0 && num_points <= 2048, "hf_mask_inds: %d body sample points (1..2048 supported)", num_points);
     const size_t smem = sizeof(unsigned) * (size_t)((cells + 31) / 32);
-    static size_t smem_attr = 48 * 1024;
+    static size_t smem_attr_of_device[64] = {};            // the opt-in is a per-device function attribute
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& smem_attr = smem_attr_of_device[dev & 63];
+    if (smem_attr == 0) smem_attr = 48 * 1024;
     if (smem > smem_attr) {
         cudaError_t ce = cudaFuncSetAttribute(hf_mask_inds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (ce != cudaSuccess) { set_error("hf_mask_inds: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }

@@ -132,7 +132,7 @@ class MotionLib:
             rp_l.append(root_pos); rr_l.append(root_rot); jr_l.append(joint_rot)
             if self._contact_info:
                 con = c.get("contacts")
-                c_l.append(con if con is not None else torch.zeros((nf, J), dtype=torch.float32))
+                c_l.append(con if con is not None else torch.zeros((nf, J), dtype=torch.float32, device=root_pos.device))
             terrains.append(c.get("terrain"))
         f32 = torch.float32
         # one concatenation + one upload per tensor kind instead of one per clip

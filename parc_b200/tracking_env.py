@@ -248,7 +248,11 @@ class TrackingEnv:
         self._done_count = z(1, dt=i32)
         self._done_list = z(N, dt=i32)
         self._done_code = torch.zeros(N, dtype=torch.uint8, device=dev)
-        self._cdf = z(M)
+        # RSI sampling CDF (dm_env.py:485-490): clamp(fail_rate, min_motion_weight) * motion_weight, inclusive prefix sum. Valid from
+        # the start (fail rates are 1) -- parc_b200_fail_rate_ema refreshes it whenever the rates change
+        self._cdf = torch.cumsum(torch.clamp(self._motion_id_fail_rates, min=float(self._cfg.min_motion_weight)) * motion_lib._motion_weights, 0).contiguous()
+        self._cdf_weights_only = torch.cumsum(motion_lib._motion_weights, 0).contiguous()      # dm.ignore_fail_rates
+        self._ignore_fail_rates = bool(env_config.get("dm", {}).get("ignore_fail_rates", False))
         self._ema_scratch = z(2 * M + N, dt=i32)
         self._seed = int(seed)
         self._step_count = 0
@@ -324,7 +328,8 @@ class TrackingEnv:
         return self._demo_mode
 
     def set_motion_start_time_fraction(self, val):
-        self._motion_start_time_fraction = val.to(self._device)
+        assert val.shape == (self._num_envs,)
+        self._motion_start_time_fraction = val.to(device=self._device, dtype=torch.float32).contiguous()
 
     def set_rand_root_pos_offset_scale(self, val):
         self._env_config["rand_root_pos_offset_scale"] = val
@@ -368,9 +373,14 @@ class TrackingEnv:
         """env.reset(done_ids) of the rollout loop (base_agent.py:366-370) without leaving the
         device: RSI draws from a Philox counter keyed by (seed, env id, step), state reset, heights
         and observation rows of the reset envs. Consumes the done list of the last step."""
+        opt = _lib.ResetOptionsStruct()
+        opt.root_pos_offset, opt.root_rot_offset = _lib.ptr(self._root_pos_offset), _lib.ptr(self._root_rot_offset)
+        opt.motion_start_time_fraction = _lib.ptr(self._motion_start_time_fraction)
+        opt.demo_mode = int(self._demo_mode)
+        cdf = self._cdf_weights_only if self._ignore_fail_rates else self._cdf
         _lib.check(_lib.lib().parc_b200_env_reset_sampled(
             self._kin_char_model._cstruct(), self._mlib.cstruct(), self._terrain_cs, self._cfg, self._bufs,
-            _lib.ptr(self._cdf), self._mlib.num_motions(), self._seed, self._step_count, int(self._rand_reset),
+            _lib.ptr(cdf), self._mlib.num_motions(), self._seed, self._step_count, int(self._rand_reset), opt,
             self._stream()))
 
     def sim_standin(self, noise):
@@ -394,7 +404,7 @@ class TrackingEnv:
         mlib = self._mlib
         if self._demo_mode:
             motion_ids = env_ids % mlib.num_motions()
-        elif self._env_config.get("dm", {}).get("ignore_fail_rates", False):
+        elif self._ignore_fail_rates:
             motion_ids = mlib.sample_motions(n)
         else:
             w = torch.clamp(self._motion_id_fail_rates, min=self._cfg.min_motion_weight) * mlib._motion_weights

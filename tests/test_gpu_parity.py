@@ -10,6 +10,7 @@ import yaml
 
 from oracle import parc_oracle as O
 from parc_b200 import synth
+from parc_b200._lib import ParcB200Error
 from tests import helpers as H
 from tests.helpers import assert_close, load_npz, t
 
@@ -69,7 +70,7 @@ def test_fk_backward_matches_autograd_of_oracle(model):
 
 
 def test_cpu_tensor_is_refused(model):
-    with pytest.raises(Exception):
+    with pytest.raises(ParcB200Error):
         model.dof_to_rot(torch.zeros(4, 28))
 
 
@@ -321,6 +322,77 @@ def test_reset_subset_and_obs_refresh_vs_oracle():
     H.assert_close_world(penv._obs_buf, oenv.obs_buf, W, what="obs after reset")
     # empty reset is a no-op
     penv.reset(torch.zeros(0, dtype=torch.int64, device=DEV))
+
+
+def test_reset_done_honours_offsets_start_fractions_demo_and_ignore_fail_rates():
+    """TrackingEnv.reset_done (device-side draws) against TrackingEnv.reset(draws=...) -- the reference-order path that is
+    itself pinned to DeepMimicEnv.reset -- with every non-random knob of the reference's reset set: root position / rotation
+    offsets (mgdm_dm_util.py:108-115), rand_reset False with per-env start fractions (dm_env.py:500-502), then demo mode
+    (:479-480) and dm.ignore_fail_rates (:485-486). Also: the sampling CDF is valid before the first EMA."""
+    def twins(**ecu):
+        sc = H.Scenario(num_envs=384, num_motions=11, ray="grid", seed=29, wrap_fraction=0.1, max_frames=80)
+        sc.ec.update(ecu)
+        oenv = sc.oracle_env()
+        H.randomize_oracle_state(oenv, seed=4, fail_fraction=0.25)
+        out = []
+        for _ in range(2):
+            pe = sc.product_env(DEV)
+            H.copy_oracle_state_to_product(oenv, pe)
+            out.append(pe)
+        return sc, oenv, out[0], out[1]
+
+    g = torch.Generator().manual_seed(8)
+    # --- offsets + start-time fractions, rand_reset off ---
+    sc, oenv, a, b = twins(rand_reset=False)
+    N = sc.N
+    assert float(a._cdf[-1]) > 0.99 and torch.all(a._cdf[1:] >= a._cdf[:-1])        # valid before any EMA has run
+    pos_off = (torch.rand(N, 3, generator=g) - 0.5).to(DEV)
+    rot_off = torch.nn.functional.normalize(torch.randn(N, 4, generator=g), dim=-1).to(DEV)
+    frac = torch.rand(N, generator=g).to(DEV)
+    for e in (a, b):
+        e.set_root_pos_offset(pos_off); e.set_root_rot_offset(rot_off); e.set_motion_start_time_fraction(frac)
+        e.post_physics_step(update_fail_rates=False)          # the CDF must still be usable without the EMA
+    torch.cuda.synchronize()
+    n = int(a._done_count.item())
+    done_ids = torch.sort(a._done_list[:n].long()).values
+    assert n > 20
+    step = a._step_count
+    a.reset_done()
+    cdf = a._cdf.cpu().numpy()
+    lengths = oenv.lib.lengths.numpy()
+    d = [O.rsi_draws(int(e), a._seed, step, cdf, 1, lengths, False) for e in done_ids.tolist()]
+    mids = torch.tensor([x[0] for x in d], dtype=torch.int64)
+    times = b._mlib.get_motion_length(mids.to(DEV)) * frac[done_ids]
+    noise = torch.tensor(np.array([[x[3], x[4]] for x in d], dtype=np.float32))
+    assert torch.equal(a._motion_ids[done_ids].cpu(), mids)
+    assert torch.equal(a._motion_time_offsets[done_ids], times), "start time = length * fraction, rounded as the reference does"
+    b.reset(done_ids, draws=(mids, torch.tensor([x[1] for x in d], dtype=torch.int64), times, noise))
+    torch.cuda.synchronize()
+    for k in ("_root_state", "_dof_state", "_ref_root_pos", "_ref_root_rot", "_ref_joint_rot", "_ref_dof_pos", "_ref_dof_vel", "_ref_contacts",
+              "_obs_buf", "_motion_ids", "_motion_terrain_ids", "_motion_time_offsets", "_timestep_buf", "_done_buf"):
+        assert torch.equal(getattr(a, k), getattr(b, k)), k
+    assert float((a._char_root_pos[done_ids] - a._ref_root_pos[done_ids]).abs().max()) > 0.05      # the offsets were applied
+    # --- demo mode: motion id = env id % M ---
+    sc, oenv, a, _ = twins()
+    a.set_demo_mode(True)
+    a.post_physics_step()
+    n = int(a._done_count.item())
+    done_ids = a._done_list[:n].long()
+    a.reset_done()
+    assert torch.equal(a._motion_ids[done_ids], done_ids % sc.M)
+    # --- ignore_fail_rates: motion weights alone, whatever the fail rates are ---
+    sc, oenv, a, _ = twins(dm={"min_motion_weight": 0.01, "terrains_per_motion": 1, "ignore_fail_rates": True})
+    a._motion_id_fail_rates.copy_(torch.linspace(0.0, 1.0, sc.M))
+    a.post_physics_step()
+    n = int(a._done_count.item())
+    done_ids = torch.sort(a._done_list[:n].long()).values
+    step = a._step_count
+    a.reset_done()
+    cdf_w = np.cumsum(a._mlib._motion_weights.cpu().numpy(), dtype=np.float32)
+    assert np.array_equal(a._cdf_weights_only.cpu().numpy(), torch.cumsum(a._mlib._motion_weights, 0).cpu().numpy())
+    d = [O.rsi_draws(int(e), a._seed, step, a._cdf_weights_only.cpu().numpy(), 1, oenv.lib.lengths.numpy(), True) for e in done_ids.tolist()]
+    assert torch.equal(a._motion_ids[done_ids].cpu(), torch.tensor([x[0] for x in d], dtype=torch.int64))
+    del cdf_w
 
 
 def test_device_sampled_reset_matches_restated_draws():
