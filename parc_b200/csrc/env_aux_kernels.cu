@@ -518,6 +518,34 @@ __device__ __forceinline__ T block_exclusive_scan(T v, T* warp_tot /* [32] smem 
     return r;
 }
 
+// Ascending in-place sort of a[0..n) by NT cooperating threads (t = 0..NT-1), any n: the normalised bitonic network (every
+// merge starts with a mirror step, all comparisons ascending), in which the virtual +inf elements past n never move.
+// sync() separates the steps: __syncwarp for a warp, __syncthreads for the block.
+template <typename SyncF>
+__device__ __forceinline__ void bitonic_sort_ints(int* __restrict__ a, int n, int t, int NT, SyncF sync) {
+    int np2 = 1;
+    while (np2 < n) np2 <<= 1;
+    const int half = np2 >> 1;
+    for (int size = 2; size <= np2; size <<= 1) {
+        const int hs = size >> 1;
+        for (int idx = t; idx < half; idx += NT) {
+            const int i = (idx / hs) * size + (idx % hs), p = i ^ (size - 1);
+            if (p < n) { const int x = a[i], y = a[p]; if (x > y) { a[i] = y; a[p] = x; } }
+        }
+        sync();
+        for (int stride = size >> 2; stride >= 1; stride >>= 1) {
+            for (int idx = t; idx < half; idx += NT) {
+                const int i = (idx / stride) * (2 * stride) + (idx % stride), p = i + stride;
+                if (p < n) { const int x = a[i], y = a[p]; if (x > y) { a[i] = y; a[p] = x; } }
+            }
+            sync();
+        }
+    }
+}
+constexpr int EMA_THREAD_MAX = 48;      // segments up to this many finished envs: one thread sorts (insertion) and applies
+constexpr int EMA_WARP_MAX = 2048;      // up to this many: one warp sorts, lane 0 applies; larger ones: the whole block sorts
+constexpr int EMA_BIG_LIST = 128;       // block-sorted segments per launch (more than that fall back to the warp tier)
+
 // Dynamic shared memory: [hist M | offs M] when `tables_in_smem`, then a bucket of `bucket_cap` entries; the global
 // scratch (2M + N ints) takes whatever does not fit. A bucket entry is env_id << 1 | failed, so that sorting the
 // entries sorts by env id and the apply loop needs no further global reads.
@@ -528,7 +556,10 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
     extern __shared__ int ema_smem[];
     __shared__ int warp_i[32];
     __shared__ float warp_f[32];
+    __shared__ int big_list[EMA_BIG_LIST];
+    __shared__ int big_count;
     const int t = threadIdx.x, T = blockDim.x;
+    if (t == 0) big_count = 0;
     const int n = min(*env.done_count, (int)env.num_envs);
     int* hist = tables_in_smem ? ema_smem : scratch;                 // [M]
     int* offs = hist + M;                                            // [M]
@@ -555,7 +586,11 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
             int sum = 0;
             for (int k = b; k < e; ++k) sum += hist[k];
             int run = block_exclusive_scan<int>(sum, warp_i, nullptr);
-            for (int k = b; k < e; ++k) { const int v = hist[k]; offs[k] = run; run += v; hist[k] = 0; }
+            for (int k = b; k < e; ++k) {
+                const int v = hist[k];
+                offs[k] = run; run += v; hist[k] = 0;
+                if (v > EMA_WARP_MAX) { const int slot = atomicAdd(&big_count, 1); if (slot < EMA_BIG_LIST) big_list[slot] = k; }
+            }
         }
         __syncthreads();
         // pass 2: scatter env_id << 1 | failed into the motion's segment
@@ -572,22 +607,49 @@ __global__ void __launch_bounds__(EMA_THREADS) fail_rate_ema_kernel(const __grid
         __syncthreads();
         const float w = cfg.ema_weight;
         const float keep = cfg.ema_keep;   // Python double (1.0 - 0.01) cast to fp32 when it meets the fp32 tensor
-        for (int m = t; m < M; m += T) {
-            const int cnt = hist[m];
-            if (cnt == 0) continue;
-            int* seg = bucket + offs[m];
-            for (int a = 1; a < cnt; ++a) {   // insertion sort by env id (segments are short)
-                const int v = seg[a];
-                int b = a - 1;
-                while (b >= 0 && seg[b] > v) { seg[b + 1] = seg[b]; --b; }
-                seg[b + 1] = v;
-            }
+        // the reference's rule, applied to one motion's finished envs in ascending env id (dm_env.py:648-660)
+        auto apply = [&](int m, const int* seg, int cnt) {
             float r = env.motion_id_fail_rates[m];
             for (int a = 0; a < cnt; ++a) {
                 r = __fmul_rn(r, keep);
                 if (seg[a] & 1) r = __fadd_rn(r, w);
             }
             env.motion_id_fail_rates[m] = r;
+        };
+        // tier 1: the many short segments, one thread per motion
+        for (int m = t; m < M; m += T) {
+            const int cnt = hist[m];
+            if (cnt == 0 || cnt > EMA_THREAD_MAX) continue;
+            int* seg = bucket + offs[m];
+            for (int a = 1; a < cnt; ++a) {   // insertion sort by env id
+                const int v = seg[a];
+                int b = a - 1;
+                while (b >= 0 && seg[b] > v) { seg[b + 1] = seg[b]; --b; }
+                seg[b + 1] = v;
+            }
+            apply(m, seg, cnt);
+        }
+        // tier 3: giant segments (few clips, many envs), the whole block sorts one after the other
+        const int n_big = min(big_count, EMA_BIG_LIST);
+        for (int k = 0; k < n_big; ++k) {
+            const int m = big_list[k];
+            bitonic_sort_ints(bucket + offs[m], hist[m], t, T, [] { __syncthreads(); });
+            if (t == 0) apply(m, bucket + offs[m], hist[m]);
+        }
+        // tier 2: one warp per medium segment
+        {
+            const int warp = t >> 5, lane = t & 31, nwarp = T >> 5;
+            for (int m = warp; m < M; m += nwarp) {
+                const int cnt = hist[m];
+                if (cnt <= EMA_THREAD_MAX) continue;
+                if (cnt > EMA_WARP_MAX) {
+                    bool listed = false;
+                    for (int k = 0; k < n_big; ++k) listed = listed || big_list[k] == m;
+                    if (listed) continue;          // already done by the block
+                }
+                bitonic_sort_ints(bucket + offs[m], cnt, lane, 32, [] { __syncwarp(); });
+                if (lane == 0) apply(m, bucket + offs[m], cnt);
+            }
         }
         __syncthreads();
     }

@@ -395,6 +395,40 @@ def test_reset_done_honours_offsets_start_fractions_demo_and_ignore_fail_rates()
     del cdf_w
 
 
+@pytest.mark.parametrize("M,n_done", [(1, 4096), (3, 6000), (7, 300), (1000, 28000), (40, 40)])
+def test_fail_rate_ema_is_sequential_in_env_order_for_any_segment_size(M, n_done):
+    """parc_b200_fail_rate_ema against the reference's host loop (dm_env.py:648-660: finished envs in ascending env id,
+    r <- r * (1 - w) [+ w on FAIL] in fp32) on forced done lists: one clip with 4,096 finishes (every entry in one segment),
+    a few clips with thousands each, the BASELINE configs[4] shape (28 k finishes over 1,000 clips), and tiny cases."""
+    from parc_b200 import _lib
+    sc = H.Scenario(num_envs=max(n_done + 100, 512), num_motions=M, ray="cone", seed=31, wrap_fraction=0.0, max_frames=70)
+    penv = sc.product_env(DEV)
+    N = sc.N
+    g = torch.Generator().manual_seed(M * 7 + n_done)
+    mids = torch.randint(0, M, (N,), generator=g)
+    done_envs = torch.randperm(N, generator=g)[:n_done]                 # unordered, as the step kernel appends them
+    code = torch.zeros(N, dtype=torch.uint8)
+    code[done_envs] = torch.where(torch.rand(n_done, generator=g) < 0.4, torch.tensor(1, dtype=torch.uint8), torch.tensor(2, dtype=torch.uint8))
+    rates0 = torch.rand(M, generator=g)
+    penv._motion_ids.copy_(mids.to(DEV))
+    penv._done_code.copy_(code.to(DEV))
+    penv._done_list[:n_done].copy_(done_envs.to(torch.int32).to(DEV))
+    penv._done_count.fill_(n_done)
+    penv._motion_id_fail_rates.copy_(rates0.to(DEV))
+    _lib.check(_lib.lib().parc_b200_fail_rate_ema(penv._cfg, penv._bufs, M, _lib.ptr(penv._cdf), _lib.ptr(penv._ema_scratch), penv._stream()))
+    torch.cuda.synchronize()
+    want = rates0.numpy().astype(np.float32).copy()
+    keep, w = np.float32(1.0 - 0.01), np.float32(0.01)
+    order = torch.sort(done_envs).values.tolist()
+    mi, co = mids.numpy(), code.numpy()
+    for e in order:
+        r = np.float32(want[mi[e]] * keep)
+        want[mi[e]] = np.float32(r + w) if co[e] == 1 else r
+    assert np.array_equal(penv._motion_id_fail_rates.cpu().numpy(), want), "the EMA must equal the sequential fp32 recurrence bit for bit"
+    cdf = np.cumsum(np.maximum(want, np.float32(0.01)) * penv._mlib._motion_weights.cpu().numpy(), dtype=np.float32)
+    assert_close(penv._cdf, cdf, rtol=1e-5, atol=1e-7, what="RSI CDF")
+
+
 def test_device_sampled_reset_matches_restated_draws():
     """parc_b200_env_reset_sampled: Philox + inverse-CDF draws are bit-exact against the CPU
     restatement (oracle.rsi_draws), and the resulting state equals an explicit reset with them."""
