@@ -49,6 +49,8 @@ def parse_args():
                     help="share of the envs the simulator stand-in pushes off their reference every step (they terminate and are "
                          "reset): 0.02 is the stationary BASELINE configs[1] workload, 0.1 with --envs 262144 is configs[4] (reset-heavy)")
     ap.add_argument("--chunks", type=int, default=6, help="row ranges of the host-fed step (upload of range c+1 overlaps the step of range c)")
+    ap.add_argument("--fail-rate-sync", type=int, default=10, help="multi-GPU runs: all-reduce the per-motion fail / pass counts every this many "
+                                                                   "steps so that every rank samples RSI motions from the same fail rates (0 = never)")
     ap.add_argument("--no-extra", action="store_true", help="skip the `extra` block (BASELINE configs[2], [3], [4] measured beside the headline)")
     ap.add_argument("--four-tensor-state", action="store_true", help="host-fed step with Isaac Gym's four state tensors instead of one interleaved row per env")
     return ap.parse_args()
@@ -361,6 +363,8 @@ def run_gpu_arm(args):
     world = build_world(args.motions)
     env = build_gpu_env(world, N, rank * N, n_gpus * N, dev, interleaved=not args.four_tensor_state)
     init_gpu_state(env, rank * N)
+    if distributed and args.fail_rate_sync > 0:
+        env.enable_fail_rate_sync(interval=args.fail_rate_sync)      # the only exchange besides the final statistics
     from parc_b200 import synth
     noise = synth.standin_noise(N, env._J, env._D, seed=5678 + rank * N, fail_fraction=args.fail_fraction).to(dev)   # simulator stand-in
 
@@ -514,6 +518,8 @@ def run_gpu_arm(args):
                        "ray_points": int(world["ray"].shape[0]), "resets_per_step": dl["done_per_step"],
                        "standin_fail_fraction": args.fail_fraction, "obs_dim": 871 + int(world["ray"].shape[0]),
                        "terrain_cells": list(world["hf"].shape), "parallelism": "env-sharded x%d, no data-path collective" % n_gpus,
+                       "fail_rate_sync": ("all-reduce of 2 x %d int64 outcome counts every %d steps (NCCL)" % (args.motions, args.fail_rate_sync))
+                                         if (distributed and args.fail_rate_sync > 0) else "none (one process)",
                        "l2": "per-step working set %.2f GB > 126 MB L2 (no flush needed)" % (roof["algorithmic_bytes_per_launch"] / 1e9)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

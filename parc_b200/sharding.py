@@ -55,10 +55,9 @@ def motion_outcome_counts(done_code: torch.Tensor, motion_ids: torch.Tensor, num
     EMA; the order of updates inside one step cannot follow global env ids across processes, so the
     combined update applies all passes then all fails of a step (documented in DESIGN.md)."""
     out = torch.zeros(2, num_motions, dtype=torch.int64, device=motion_ids.device)
-    for row, code in ((0, 1), (1, 2)):
-        sel = motion_ids[done_code == code]
-        if sel.numel():
-            out[row] = torch.bincount(sel, minlength=num_motions)
+    # scatter-add of 0/1 flags: no boolean indexing, hence no device -> host synchronisation on the step path
+    out[0].scatter_add_(0, motion_ids, (done_code == 1).to(torch.int64))
+    out[1].scatter_add_(0, motion_ids, (done_code == 2).to(torch.int64))
     return out
 
 
@@ -73,3 +72,31 @@ def apply_outcome_counts(fail_rates: torch.Tensor, counts: torch.Tensor, ema_wei
     kk = keep.pow(fails.float())
     fail_rates.copy_(r * kk + (1.0 - kk))
     return fail_rates
+
+
+class FailRateSync:
+    """Cross-rank fail rates for env-sharded runs. Each rank keeps applying the reference's sequential
+    EMA to its own envs every step (its RSI sampling needs fresh rates without waiting for anybody); every `interval` steps
+    the per-motion fail / pass counts accumulated since the last exchange are summed over the ranks with ONE all-reduce of
+    2 M int64 (NCCL over NVLink on the GPUs) and every rank replaces its rates by
+    apply_outcome_counts(rates at the last exchange, summed counts) -- "run the reference once per shard and combine the
+    counts". All ranks then hold the same rates again."""
+
+    def __init__(self, fail_rates: torch.Tensor, interval: int = 1, ema_weight: float = 0.01, group=None):
+        self.interval, self.w, self.group = max(int(interval), 1), float(ema_weight), group
+        self.base = fail_rates.clone()
+        self.acc = torch.zeros(2, fail_rates.shape[0], dtype=torch.int64, device=fail_rates.device)
+        self.steps = 0
+
+    def after_step(self, fail_rates, done_code, motion_ids):
+        """Call once per control step, after the local EMA. Returns True when the rates were replaced by the combined ones."""
+        self.acc += motion_outcome_counts(done_code, motion_ids, fail_rates.shape[0])
+        self.steps += 1
+        if self.steps % self.interval:
+            return False
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(self.acc, op=dist.ReduceOp.SUM, group=self.group)
+        apply_outcome_counts(self.base, self.acc, self.w)
+        fail_rates.copy_(self.base)
+        self.acc.zero_()
+        return True

@@ -260,6 +260,7 @@ class TrackingEnv:
         self._demo_mode = bool(env_config.get("demo_mode", False))
         self._root_pos_offset = None
         self._root_rot_offset = None
+        self._fail_rate_sync = None       # sharding.FailRateSync: cross-rank combination of the fail rates (enable_fail_rate_sync)
         self._kernel_events = None        # a list: post_physics_step appends (start, end) CUDA events around the fused step launch
         self._build_buffers_struct()
 
@@ -367,7 +368,21 @@ class TrackingEnv:
         if (parts & _lib.STEP_DONE) and update_fail_rates:
             _lib.check(L.parc_b200_fail_rate_ema(self._cfg, self._bufs, self._mlib.num_motions(), _lib.ptr(self._cdf),
                                                  _lib.ptr(self._ema_scratch), self._stream()))
+            self._sync_fail_rates()
         self._step_count += 1
+
+    def enable_fail_rate_sync(self, interval=1, group=None):
+        """Env-sharded runs (one process per GPU): combine the per-motion fail / pass counts of all ranks every `interval` steps
+        with one all-reduce, so that every rank samples RSI motions from the same fail rates (sharding.FailRateSync)."""
+        from . import sharding
+        self._fail_rate_sync = sharding.FailRateSync(self._motion_id_fail_rates, interval, float(self._cfg.ema_weight), group)
+
+    def _sync_fail_rates(self):
+        if self._fail_rate_sync is None:
+            return
+        if self._fail_rate_sync.after_step(self._motion_id_fail_rates, self._done_code, self._motion_ids):
+            w = torch.clamp(self._motion_id_fail_rates, min=float(self._cfg.min_motion_weight)) * self._mlib._motion_weights
+            self._cdf.copy_(torch.cumsum(w, 0))           # the RSI sampling CDF follows the replaced rates
 
     def reset_done(self):
         """env.reset(done_ids) of the rollout loop (base_agent.py:366-370) without leaving the
@@ -530,6 +545,7 @@ class TrackingEnv:
         if (parts & _lib.STEP_DONE) and update_fail_rates:
             _lib.check(L.parc_b200_fail_rate_ema(self._cfg, self._bufs, self._mlib.num_motions(), _lib.ptr(self._cdf),
                                                  _lib.ptr(self._ema_scratch), self._stream()))
+            self._sync_fail_rates()
         self._step_count += 1
 
     def step_host(self, host_state, host_results, num_chunks=6, standin_noise=None):
