@@ -294,6 +294,42 @@ def test_fused_step_vs_oracle_synthetic(variant):
         _compare_step(oenv, penv, what="%s step %d" % (variant, it))
 
 
+def _compare_step_strict(oenv, penv, what=""):
+    """north_star tolerances with no allowance: flags and time bit-exact, EVERY fp32 element inside rtol 1e-5 / atol 1e-6."""
+    assert torch.equal(penv._done_buf.cpu(), oenv.done_buf), what + ": done flags must be bit-exact"
+    assert torch.equal(penv._time_buf.cpu(), oenv.time_buf), what + ": time"
+    for k in ("root_pos", "body_pos", "root_rot", "root_vel", "root_ang_vel", "joint_rot", "dof_pos", "dof_vel", "contacts"):
+        assert_close(getattr(penv, "_ref_" + k), getattr(oenv, "ref_" + k), rtol=1e-5, atol=1e-6, what=what + " ref_" + k)
+    assert_close(penv._obs_buf, oenv.obs_buf, rtol=1e-5, atol=1e-6, what=what + " obs")
+    assert_close(penv._reward_terms[:, 0:7], oenv.reward_terms, rtol=1e-5, atol=1e-6, what=what + " reward terms")
+    assert_close(penv._reward_buf, oenv.reward_buf, rtol=1e-5, atol=1e-6, what=what + " reward")
+    assert_close(penv._motion_id_fail_rates, oenv.fail_rates, rtol=2e-6, atol=0, what=what + " fail rates")
+
+
+@pytest.mark.parametrize("variant", sorted(VARIANTS))
+def test_fused_step_strict_tolerance_near_the_origin(variant):
+    """The seven configurations of test_fused_step_vs_oracle_synthetic with env_offsets = 0 and the tile grid centred on the
+    origin (one clip: world coordinates stay within ~ +-7 m, one fp32 ulp <= 4.8e-7): without the 200 m world offsets the plain north_star
+    tolerance holds for 100 % of the elements, reward included -- the evidence behind assert_close_world's
+    "ulp of the world magnitude" allowance in the large-world tests."""
+    from parc_b200.tracking_env import default_env_config
+    ec = default_env_config()
+    ec.update(VARIANTS[variant])
+    sc = H.Scenario(num_envs=1531, num_motions=1, ray="grid" if variant != "fall_test" else "cone", seed=78,
+                    wrap_fraction=0.0, env_config=ec, max_frames=120)
+    sc.env_offsets = torch.zeros_like(sc.env_offsets)
+    assert float(sc.min_point.abs().max()) < 8.0
+    oenv = sc.oracle_env()
+    H.randomize_oracle_state(oenv, seed=31)
+    penv = sc.product_env(DEV)
+    H.copy_oracle_state_to_product(oenv, penv)
+    for it in range(2):
+        oenv.post_physics_step()
+        penv.post_physics_step()
+        torch.cuda.synchronize()
+        _compare_step_strict(oenv, penv, what="%s strict step %d" % (variant, it))
+
+
 def test_reset_subset_and_obs_refresh_vs_oracle():
     sc = H.Scenario(num_envs=700, num_motions=11, ray="cone", seed=9, wrap_fraction=0.2, max_frames=100)
     oenv = sc.oracle_env()
