@@ -62,7 +62,7 @@ def test_motion_loss_matches_reference_golden(tag):
     np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
     for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
         ref = d[tag + k]
-        np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+        np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))   # gradients <= 1e-4 relative (of the tensor scale)
 
 
 def _synthetic_batch(B, T, seed):
@@ -113,7 +113,7 @@ def test_batched_motion_loss_vs_oracle_per_motion():
         np.testing.assert_allclose(float(loss[b]), float(lo), rtol=3e-5)
         for g, go in zip(p, po):
             ref = go.grad.numpy()
-            np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+            np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))   # gradients <= 1e-4 relative (of the tensor scale)
 
 
 def test_config4_size_properties():
