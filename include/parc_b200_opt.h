@@ -26,7 +26,7 @@ enum {
     PARC_LOSS_PENETRATION = 4,
     PARC_LOSS_CONTACT = 5,
     PARC_LOSS_SLIDING = 6,
-    PARC_LOSS_BODY_CONSTRAINT = 7, /* always 0: body_constraints=None is the only supported setting */
+    PARC_LOSS_BODY_CONSTRAINT = 7, /* 0 unless parc_b200_motion_loss_constrained is given constraint records */
     PARC_LOSS_JERK = 8,
     PARC_NUM_LOSS_TERMS = 9
 };
@@ -76,6 +76,43 @@ int parc_b200_motion_loss(const parc_char_model_t* h_model, const parc_opt_confi
                           const float* body_points, void* workspace, int64_t workspace_bytes,
                           float* terms, float* loss, float* g_root_pos, float* g_root_rot, float* g_joint_dof,
                           void* stream);
+
+/* body_constraints of motion_terrain_contact_loss_localized (motion_optimization.py:581-609), flattened. The reference
+ * passes, per motion, one Python list of BodyConstraint{start_frame_idx, end_frame_idx, constraint_point} per body
+ * (:28-31, built by compute_approx_body_constraints :70-205); here every constraint is one record, the records of
+ * motion b being [motion_start[b], motion_start[b+1]). What a record does depends on the FIRST geom of its body:
+ *   sphere (:590-596)  term += sum over frames start..end of | |point - (rot * geom_offset + pos)| - radius |
+ *   box    (:598-602)  term += sum over frames start..end and the body's first `sole_points` sample points P of
+ *                      max(|point - P| - 1.25 * |box dims|, 0)
+ *   other              the record is ignored
+ * and, for sphere and box, the body's velocity / angular-velocity errors of velocity indices start..end drop out of the
+ * SLIDING term (:606-609; the smoothness term was summed before and keeps them). */
+enum { PARC_GEOM_NONE = 0, PARC_GEOM_SPHERE = 1, PARC_GEOM_BOX = 2 };
+typedef struct {
+    int32_t num;                                   /* records over all motions */
+    const int32_t* motion_start;                   /* [B+1] device */
+    const int32_t* body;                           /* [num] device */
+    const int32_t* start_frame;                    /* [num] device */
+    const int32_t* end_frame;                      /* [num] device, inclusive; frames past T-1 do not exist (Python slicing) */
+    const float* point;                            /* [num,3] device */
+    int32_t geom_kind[PARC_MAX_BODIES];            /* PARC_GEOM_* of body b's first geom */
+    float geom_radius[PARC_MAX_BODIES];            /* sphere: its radius; box: 1.25 * |dims| (:599) */
+    float geom_offset[PARC_MAX_BODIES][3];         /* sphere: the geom's offset in the body frame */
+    int32_t sole_points;                           /* 18 in the reference (:600) */
+} parc_opt_constraints_t;
+
+/* parc_b200_motion_loss with body constraints (h_constraints may be NULL = none; then identical to it). Fills
+ * terms[:, PARC_LOSS_BODY_CONSTRAINT], adds w[PARC_LOSS_BODY_CONSTRAINT] x term to the loss and its gradient to the g_*. */
+int parc_b200_motion_loss_constrained(const parc_char_model_t* h_model, const parc_opt_config_t* h_cfg,
+                                      const parc_opt_constraints_t* h_constraints, int64_t B, int64_t T,
+                                      const float* tgt_root_pos, const float* tgt_root_rot, const float* tgt_joint_dof,
+                                      const float* src_root_pos, const float* src_root_rot_quat, const float* src_joint_rot,
+                                      const float* src_body_vels, const float* src_body_rot_vels, const float* contacts,
+                                      const float* hf, int64_t hf_motion_stride, int32_t X, int32_t Y,
+                                      const float* min_point, int64_t min_point_motion_stride, float dx, float dy,
+                                      const float* body_points, void* workspace, int64_t workspace_bytes,
+                                      float* terms, float* loss, float* g_root_pos, float* g_root_rot, float* g_joint_dof,
+                                      void* stream);
 
 /* mdm_path.compute_motion_loss (PARC/motion_synthesis/procgen/mdm_path.py:31-127): the
  * forward-only penetration / contact score that ranks a batch of generated motions, against ONE terrain taken whole

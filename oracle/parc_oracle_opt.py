@@ -68,12 +68,14 @@ def frame_patches(points_xy, hf, min_point, dxdy):
 
 def motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, tgt_root_pos, tgt_root_rot, tgt_joint_dof,
                 src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts, weights,
-                contact_body_of_body=None):
-    """motion_terrain_contact_loss_localized (:426-656) without body constraints. `weights` =
+                contact_body_of_body=None, body_constraints=None, geoms=None):
+    """motion_terrain_contact_loss_localized (:426-656). `body_constraints` (:581-609): None or a list of records
+    (body, start_frame, end_frame, point[3]); `geoms[b]` = ("SPHERE", radius, offset[3]) | ("BOX", dims[3]) | anything else
+    (ignored), the first geom of body b. `weights` =
     [w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
     w_body_constraints, w_jerk, max_jerk]. body_points [Np,3] concatenated in body order with
     body_point_counts [J]. -> (loss, terms [9] in LOSS_NAMES order); differentiable in the tgt_* tensors."""
-    (w_root_pos, w_root_rot, w_joint_rot, w_smooth, w_pen, w_contact, w_slide, _w_bc, w_jerk, max_jerk) = [float(x) for x in weights]
+    (w_root_pos, w_root_rot, w_joint_rot, w_smooth, w_pen, w_contact, w_slide, w_bc, w_jerk, max_jerk) = [float(x) for x in weights]
     T, J = tgt_root_pos.shape[0], model.J
     root_pos_loss = (tgt_root_pos - src_root_pos).square().sum()
     tq = O.exp_map_to_quat(tgt_root_rot)
@@ -108,6 +110,28 @@ def motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, tgt_
             cb = b if contact_body_of_body is None else contact_body_of_body[b]
             if cb is not None and cb >= 0:
                 contact_loss = contact_loss + (closest * contacts[:, cb]).sum()
+    bc_loss = torch.zeros(())
+    if body_constraints is not None:
+        starts = [0]
+        for n in body_point_counts:
+            starts.append(starts[-1] + int(n))
+        vel_keep = torch.ones(T - 1, J)
+        for (b, s0, e0, pt) in body_constraints:
+            b, s0, e0 = int(b), int(s0), int(e0)
+            pt = torch.as_tensor(pt, dtype=torch.float32)
+            g = geoms[b]
+            if g[0] == "SPHERE":                               # :590-596: | |point - centre| - radius | per frame
+                centre = O.quat_rotate(body_rot[:, b], torch.as_tensor(g[2], dtype=torch.float32)[None].expand(T, -1)) + body_pos[:, b]
+                bc_loss = bc_loss + ((pt[None] - centre[s0:e0 + 1]).norm(dim=-1) - float(g[1])).abs().sum()
+            elif g[0] == "BOX":                                # :598-602: hinge on the first 18 sample points, ball of 1.25 |dims|
+                radius = torch.as_tensor(g[1], dtype=torch.float32).norm() * 1.25
+                sole = world[s0:e0 + 1, starts[b]:starts[b + 1]][:, 0:18].reshape(-1, 3)
+                bc_loss = bc_loss + torch.clamp((pt[None] - sole).norm(dim=-1) - radius, min=0.0).sum()
+            else:
+                continue
+            vel_keep[s0:e0 + 1, b] = 0.0                       # :606-609, after the smoothness sum: the sliding term only
+        vel_err_sq = vel_err_sq * vel_keep[..., None]
+        rvel_err_sq = rvel_err_sq * vel_keep
     slide_loss = torch.zeros(())
     if w_slide != 0.0 and both.shape[-1] == J:
         c, c2 = 0.03, 0.0009
@@ -115,10 +139,43 @@ def motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, tgt_
     acc = vel[1:] - vel[:-1]
     jerk = (acc[1:] - acc[:-1]).norm(dim=-1)
     jerk_loss = torch.clamp(jerk - max_jerk * (1.0 / 30.0) ** 3, min=0.0).sum()
-    terms = [root_pos_loss, root_rot_loss, joint_rot_loss, smooth_loss, pen_loss, contact_loss, slide_loss, torch.zeros(()), jerk_loss]
-    ws = [w_root_pos, w_root_rot, w_joint_rot, w_smooth, w_pen, w_contact, w_slide, 0.0, w_jerk]
+    terms = [root_pos_loss, root_rot_loss, joint_rot_loss, smooth_loss, pen_loss, contact_loss, slide_loss, bc_loss, jerk_loss]
+    ws = [w_root_pos, w_root_rot, w_joint_rot, w_smooth, w_pen, w_contact, w_slide, w_bc, w_jerk]
     loss = sum(w * t for w, t in zip(ws, terms))
     return loss, torch.stack([t.detach().double() for t in terms])
+
+
+def approx_body_constraints(model, root_pos, root_rot, joint_rot, contacts, hf, min_point, dxdy, bodies, box_offsets, iters=1000):
+    """compute_approx_body_constraints (:70-205). `bodies` = ids of (left_foot, right_foot, left_hand, right_hand);
+    `box_offsets[k]` = offset of the k-th body's box geom or None (hands). Returns records (body, start, end, point[3]) in
+    `bodies` order. Every run of consecutive frames with contact > 0.9 gives one record (a trailing run of ONE frame is
+    dropped, :94-95), its point = mean body position over the run, moved by `iters` SGD steps (lr 0.01) on the squared
+    solid-column distance to the whole terrain (base_z = min(hf) - 10)."""
+    body_pos, body_rot = model.forward_kinematics(root_pos, root_rot, joint_rot)
+    T = root_pos.shape[0]
+    base_z = float(hf.min()) - 10.0
+    records = []
+    for k, b in enumerate(bodies):
+        pos = body_pos[:, b]
+        if box_offsets[k] is not None:
+            pos = pos + O.quat_rotate(body_rot[:, b], torch.as_tensor(box_offsets[k], dtype=torch.float32)[None].expand(T, -1))
+        idx = torch.nonzero(contacts[:, b] > 0.9).flatten().tolist()
+        runs, cur = [], []
+        for i in idx:
+            if cur and i != cur[-1] + 1:
+                runs.append(cur)
+                cur = []
+            cur.append(i)
+        if len(cur) >= 2:                                      # the last run survives only with two or more frames
+            runs.append(cur)
+        for run in runs:
+            pt = pos[run].mean(dim=0).detach().clone().requires_grad_(True)
+            for _ in range(iters):
+                sd = points_hf_sdf(pt[None, None], hf[None], min_point[None], dxdy, base_z, False)
+                (g,) = torch.autograd.grad(sd.square().sum(), pt)
+                pt = (pt - 0.01 * g).detach().requires_grad_(True)
+            records.append((int(b), int(run[0]), int(run[-1]), pt.detach()))
+    return records
 
 
 # ------------------------------------------------------------------------------------------------

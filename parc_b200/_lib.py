@@ -191,6 +191,25 @@ class OptConfigStruct(C.Structure):
     ]
 
 
+GEOM_NONE, GEOM_SPHERE, GEOM_BOX = 0, 1, 2
+
+
+class OptConstraintsStruct(C.Structure):
+    """parc_opt_constraints_t (include/parc_b200_opt.h)."""
+    _fields_ = [
+        ("num", C.c_int32),
+        ("motion_start", C.c_void_p),
+        ("body", C.c_void_p),
+        ("start_frame", C.c_void_p),
+        ("end_frame", C.c_void_p),
+        ("point", C.c_void_p),
+        ("geom_kind", C.c_int32 * MAX_BODIES),
+        ("geom_radius", C.c_float * MAX_BODIES),
+        ("geom_offset", (C.c_float * 3) * MAX_BODIES),
+        ("sole_points", C.c_int32),
+    ]
+
+
 class ParcB200Error(RuntimeError):
     pass
 
@@ -241,6 +260,8 @@ def _declare(lib):
         "parc_b200_points_hf_sdf": [vp, i64, i64, vp, i32, i32, vp, f32, f32, f32, i32, vp, vp, vp],
         "parc_b200_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64] + [vp] * 9 + [vp, i64, i32, i32, vp, i64, f32, f32,
                                                                                                  vp, vp, i64, vp, vp, vp, vp, vp, vp],
+        "parc_b200_motion_loss_constrained": [P(CharModelStruct), P(OptConfigStruct), P(OptConstraintsStruct), i64, i64] + [vp] * 9 +
+                                             [vp, i64, i32, i32, vp, i64, f32, f32, vp, vp, i64, vp, vp, vp, vp, vp, vp],
         "parc_b200_selftest_div": [vp, i64, f32, vp, vp, vp],
         "parc_b200_selftest_cells": [vp, i64, f32, f32, f32, f32, f32, f32, f32, f32, i32, i32, vp, vp, vp],
         "parc_b200_record_agent_states": [P(CharModelStruct), P(MotionLibStruct), P(EnvConfigStruct), P(EnvBuffersStruct),

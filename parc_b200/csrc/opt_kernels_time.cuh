@@ -6,11 +6,15 @@ namespace parc {
 // ---- 3. smoothness, sliding, jerk (:460-471, 608-624) and their gradients ----------------------------
 // Lane = body j of frame t. The lane owns velocity index t (t <= T-2) and jerk index t (t <= T-4) for the
 // VALUES, and gathers every contribution to d loss / d body_pos[t,j], d loss / d body_rot[t,j].
-template <int G>
+// CONS: body-constraint records are present (:581-609). The lane scans its motion's records for its own body: frames inside a
+// record add the sphere / sole-point hinge (value + gradient w.r.t. this frame's body transform), and velocity indices
+// inside a record are masked out of the sliding term.
+template <int G, bool CONS>
 __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(const __grid_constant__ parc_char_model_t cm, const __grid_constant__ parc_opt_config_t cfg,
+                                                           const __grid_constant__ parc_opt_constraints_t cons,
                                                            long long n, long long T, const float* __restrict__ src_body_vels,
                                                            const float* __restrict__ src_body_rot_vels, const float* __restrict__ contacts,
-                                                           OptWs ws, int need_grad) {
+                                                           const float* __restrict__ body_points, OptWs ws, int need_grad) {
     const int J = cm.num_bodies;
     const int j = threadIdx.x & (G - 1);
     const bool active = j < J;
@@ -30,9 +34,63 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(
         const long long b = i / T;
         const int t = (int)(i - b * T);
         const int jj = active ? j : 0;
-        float v_smooth = 0.f, v_slide = 0.f, v_jerk = 0.f;
+        float v_smooth = 0.f, v_slide = 0.f, v_jerk = 0.f, v_cons = 0.f;
         Vec3 gP = make_vec3(0.f, 0.f, 0.f);
         Quat gR = make_quat(0.f, 0.f, 0.f, 0.f);
+        bool masked_t = false, masked_tm1 = false;      // velocity indices t and t-1 of this body sit inside a constraint
+        if (CONS && live) {
+            const int kind = cons.geom_kind[jj];
+            if (kind != PARC_GEOM_NONE) {
+                const float w_c = cfg.w[PARC_LOSS_BODY_CONSTRAINT];
+                const float* bp = ws.body_pos + (i * J + jj) * 3;
+                const Vec3 pos = make_vec3(bp[0], bp[1], bp[2]);
+                const Quat rot = quat_from_f4(reinterpret_cast<const float4*>(ws.body_rot)[i * J + jj]);
+                const float radius = cons.geom_radius[jj];
+                const int r1 = cons.motion_start[b + 1];
+                for (int r = cons.motion_start[b]; r < r1; ++r) {
+                    if (cons.body[r] != jj) continue;
+                    const int s0 = cons.start_frame[r], e0 = cons.end_frame[r];
+                    masked_t |= (t >= s0 && t <= e0);
+                    masked_tm1 |= (t - 1 >= s0 && t - 1 <= e0);
+                    if (t < s0 || t > e0) continue;
+                    const Vec3 cp = make_vec3(cons.point[r * 3], cons.point[r * 3 + 1], cons.point[r * 3 + 2]);
+                    if (kind == PARC_GEOM_SPHERE) {
+                        const Vec3 off = make_vec3(cons.geom_offset[jj][0], cons.geom_offset[jj][1], cons.geom_offset[jj][2]);
+                        const Vec3 ctr = quat_rotate(rot, off) + pos;
+                        const Vec3 dv = make_vec3(ctr.x - cp.x, ctr.y - cp.y, ctr.z - cp.z);
+                        const float m = sqrtf(dv.x * dv.x + dv.y * dv.y + dv.z * dv.z);
+                        const float d = m - radius;                                          // geom_util.sdSphere (:169-173)
+                        v_cons += fabsf(d);
+                        if (need_grad && m > 0.f && d != 0.f) {
+                            const float k = (d > 0.f ? w_c : -w_c) / m;
+                            const Vec3 g = make_vec3(k * dv.x, k * dv.y, k * dv.z);
+                            const Quat gq = rotate_bwd_q(rot, off, g);
+                            gP = gP + g;
+                            gR.x += gq.x; gR.y += gq.y; gR.z += gq.z; gR.w += gq.w;
+                        }
+                    } else {
+                        const int p0 = cfg.point_start[jj];
+                        const int p1 = min(cfg.point_start[jj + 1], p0 + cons.sole_points);
+                        for (int q = p0; q < p1; ++q) {
+                            const Vec3 lp = make_vec3(__ldg(body_points + q * 3), __ldg(body_points + q * 3 + 1), __ldg(body_points + q * 3 + 2));
+                            const Vec3 wp = quat_rotate(rot, lp) + pos;
+                            const Vec3 dv = make_vec3(wp.x - cp.x, wp.y - cp.y, wp.z - cp.z);
+                            const float m = sqrtf(dv.x * dv.x + dv.y * dv.y + dv.z * dv.z);
+                            const float d = m - radius;
+                            if (!(d > 0.f)) continue;
+                            v_cons += d;
+                            if (need_grad) {
+                                const float k = w_c / m;
+                                const Vec3 g = make_vec3(k * dv.x, k * dv.y, k * dv.z);
+                                const Quat gq = rotate_bwd_q(rot, lp, g);
+                                gP = gP + g;
+                                gR.x += gq.x; gR.y += gq.y; gR.z += gq.z; gR.w += gq.w;
+                            }
+                        }
+                    }
+                }
+            }
+        }
         if (live) {
             // positions of frames t-3 .. t+3 of this body
             Vec3 Pw[7];
@@ -64,7 +122,12 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(
                 const float S = ve.x * ve.x + ve.y * ve.y + ve.z * ve.z;
                 const float re = qda_value(rot_at(t + 1), rot_at(t)) - src_body_rot_vels[(b * (T - 1) + t) * J + jj];
                 v_smooth = S + re * re;
-                if (sliding) { const float bo = both_at(t); v_slide = (sqrtf(S + c2) - c0) * bo + (sqrtf(re * re + c2) - c0) * bo; }
+                if (sliding) {
+                    const float bo = both_at(t);
+                    // inside a constraint the errors were zeroed before the sliding sum (:606-609)
+                    v_slide = masked_t ? (sqrtf(c2) - c0) * bo + (sqrtf(c2) - c0) * bo
+                                       : (sqrtf(S + c2) - c0) * bo + (sqrtf(re * re + c2) - c0) * bo;
+                }
             }
             if (t <= T - 4) {
                 const Vec3 jv = jerk_vec(3);
@@ -76,7 +139,7 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(
                     if (tt < 0 || tt > T - 2) return make_vec3(0.f, 0.f, 0.f);
                     const Vec3 ve = vel_err(tt, k0);
                     float k = 2.0f * w_s;
-                    if (sliding) k += w_sl * both_at(tt) / sqrtf(ve.x * ve.x + ve.y * ve.y + ve.z * ve.z + c2);
+                    if (sliding && !(tt == t ? masked_t : masked_tm1)) k += w_sl * both_at(tt) / sqrtf(ve.x * ve.x + ve.y * ve.y + ve.z * ve.z + c2);
                     return make_vec3(k * ve.x, k * ve.y, k * ve.z);
                 };
                 // d loss / d jerk vector[s]
@@ -90,13 +153,13 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(
                 };
                 const Vec3 a = gvel(t - 1, 2), c = gvel(t, 3);
                 const Vec3 j3 = gjerk(t - 3, 0), j2 = gjerk(t - 2, 1), j1 = gjerk(t - 1, 2), j0 = gjerk(t, 3);
-                gP = make_vec3(a.x - c.x + j3.x - 3.f * j2.x + 3.f * j1.x - j0.x, a.y - c.y + j3.y - 3.f * j2.y + 3.f * j1.y - j0.y,
+                gP = gP + make_vec3(a.x - c.x + j3.x - 3.f * j2.x + 3.f * j1.x - j0.x, a.y - c.y + j3.y - 3.f * j2.y + 3.f * j1.y - j0.y,
                                a.z - c.z + j3.z - 3.f * j2.z + 3.f * j1.z - j0.z);
                 // rotational velocity: rvel[tt] = quat_diff_angle(rot[tt+1], rot[tt]) (:464)
                 auto g_angle = [&](int tt, Quat q0, Quat q1) {
                     const float re = qda_value(q0, q1) - src_body_rot_vels[(b * (T - 1) + tt) * J + jj];
                     float k = 2.0f * w_s * re;
-                    if (sliding) k += w_sl * both_at(tt) * re / sqrtf(re * re + c2);
+                    if (sliding && !(tt == t ? masked_t : masked_tm1)) k += w_sl * both_at(tt) * re / sqrtf(re * re + c2);
                     return k;
                 };
                 const Quat Rt = rot_at(t);
@@ -106,9 +169,11 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_temporal_kernel(
             }
         }
         v_smooth = group_sum<G>(v_smooth); v_slide = group_sum<G>(v_slide); v_jerk = group_sum<G>(v_jerk);
+        if (CONS) v_cons = group_sum<G>(v_cons);
         if (i0 < n && j == 0) {
             float* ft = ws.frame_terms + i * OPT_FT;
             ft[PARC_LOSS_SMOOTHNESS] = v_smooth; ft[PARC_LOSS_SLIDING] = v_slide; ft[PARC_LOSS_JERK] = v_jerk;
+            if (CONS) ft[PARC_LOSS_BODY_CONSTRAINT] = v_cons;
         }
         if (live && need_grad) {
             float* gp = ws.g_body_pos + (i * J + j) * 3;
@@ -184,7 +249,6 @@ __global__ void __launch_bounds__(256) opt_reduce_kernel(const __grid_constant__
         for (int k = 0; k < PARC_NUM_LOSS_TERMS; ++k) {
             double v = 0.0;
             for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += s[k][w];
-            if (k == PARC_LOSS_BODY_CONSTRAINT) v = 0.0;
             terms[b * PARC_NUM_LOSS_TERMS + k] = (float)v;
             total += (double)cfg.w[k] * v;
         }
@@ -212,8 +276,8 @@ extern "C" int64_t parc_b200_motion_loss_workspace_bytes(const parc_char_model_t
     return (int64_t)(opt_ws_floats(B * T, B, m->num_bodies) * sizeof(float));
 }
 
-extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_config_t* cfg, int64_t B, int64_t T,
-                                     const float* tgt_root_pos, const float* tgt_root_rot, const float* tgt_joint_dof,
+extern "C" int parc_b200_motion_loss_constrained(const parc_char_model_t* m, const parc_opt_config_t* cfg, const parc_opt_constraints_t* cons,
+                                     int64_t B, int64_t T, const float* tgt_root_pos, const float* tgt_root_rot, const float* tgt_joint_dof,
                                      const float* src_root_pos, const float* src_root_rot_quat, const float* src_joint_rot,
                                      const float* src_body_vels, const float* src_body_rot_vels, const float* contacts,
                                      const float* hf, int64_t hf_motion_stride, int32_t X, int32_t Y, const float* min_point,
@@ -233,6 +297,11 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
     PARC_REQUIRE(X > 0 && Y > 0 && dx > 0.f && dy > 0.f, "motion_loss: bad terrain");
     const bool need_grad = g_root_pos || g_root_rot || g_joint_dof;
     PARC_REQUIRE(!need_grad || (g_root_pos && g_root_rot && g_joint_dof), "motion_loss: pass all three gradient outputs or none");
+    const bool constrained = cons != nullptr && cons->num > 0;
+    if (constrained) {
+        PARC_REQUIRE(cons->motion_start && cons->body && cons->start_frame && cons->end_frame && cons->point, "motion_loss: NULL constraint array");
+        PARC_REQUIRE(cons->sole_points >= 0, "motion_loss: negative sole point count");
+    }
     const long long n = B * T;
     PARC_REQUIRE(workspace_bytes >= (int64_t)(opt_ws_floats(n, B, J) * sizeof(float)), "motion_loss: workspace too small");
     PARC_REQUIRE(n * (long long)J * 4 < (1ll << 40), "motion_loss: batch too large");
@@ -257,7 +326,14 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
     PARC_REQUIRE(pg_bytes <= 32 * 1024, "motion_loss: more than 1,170 body sample points");
     opt_sdf_kernel<<<(unsigned)n, OPT_SDF_THREADS, pg_bytes, st>>>(*m, *cfg, T, contacts, body_points, ter, ws, need_grad ? 1 : 0);
     if ((rc = check_launch("motion_loss (sdf)"))) return rc;
-    PARC_OPT_G(opt_temporal_kernel, *m, *cfg, n, T, src_body_vels, src_body_rot_vels, contacts, ws, need_grad ? 1 : 0);
+    if (constrained) {
+        if (G == 16) opt_temporal_kernel<16, true><<<blocks, 256, 0, st>>>(*m, *cfg, *cons, n, T, src_body_vels, src_body_rot_vels, contacts, body_points, ws, need_grad ? 1 : 0);
+        else opt_temporal_kernel<32, true><<<blocks, 256, 0, st>>>(*m, *cfg, *cons, n, T, src_body_vels, src_body_rot_vels, contacts, body_points, ws, need_grad ? 1 : 0);
+    } else {
+        const parc_opt_constraints_t none = {};
+        if (G == 16) opt_temporal_kernel<16, false><<<blocks, 256, 0, st>>>(*m, *cfg, none, n, T, src_body_vels, src_body_rot_vels, contacts, body_points, ws, need_grad ? 1 : 0);
+        else opt_temporal_kernel<32, false><<<blocks, 256, 0, st>>>(*m, *cfg, none, n, T, src_body_vels, src_body_rot_vels, contacts, body_points, ws, need_grad ? 1 : 0);
+    }
     if ((rc = check_launch("motion_loss (temporal)"))) return rc;
     if (need_grad) {
         rc = parc_b200_forward_kinematics_bwd(m, tgt_root_pos, ws.tq, ws.jq, n, ws.g_body_pos, ws.g_body_rot, ws.g_rp, ws.g_tq, ws.g_jq, stream);
@@ -271,6 +347,20 @@ extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_
 #undef PARC_OPT_G
     opt_reduce_kernel<<<(unsigned)B, 256, 0, st>>>(*cfg, T, ws, terms, loss);
     return check_launch("motion_loss (reduce)");
+}
+
+extern "C" int parc_b200_motion_loss(const parc_char_model_t* m, const parc_opt_config_t* cfg, int64_t B, int64_t T,
+                                     const float* tgt_root_pos, const float* tgt_root_rot, const float* tgt_joint_dof,
+                                     const float* src_root_pos, const float* src_root_rot_quat, const float* src_joint_rot,
+                                     const float* src_body_vels, const float* src_body_rot_vels, const float* contacts,
+                                     const float* hf, int64_t hf_motion_stride, int32_t X, int32_t Y, const float* min_point,
+                                     int64_t min_point_motion_stride, float dx, float dy, const float* body_points, void* workspace,
+                                     int64_t workspace_bytes, float* terms, float* loss, float* g_root_pos, float* g_root_rot,
+                                     float* g_joint_dof, void* stream) {
+    return parc_b200_motion_loss_constrained(m, cfg, nullptr, B, T, tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat,
+                                             src_joint_rot, src_body_vels, src_body_rot_vels, contacts, hf, hf_motion_stride, X, Y, min_point,
+                                             min_point_motion_stride, dx, dy, body_points, workspace, workspace_bytes, terms, loss, g_root_pos,
+                                             g_root_rot, g_joint_dof, stream);
 }
 
 // ---- mdm_path.compute_motion_loss: forward-only penetration / contact against a whole terrain ----

@@ -8,12 +8,14 @@ autograd history to `tgt_root_pos`, `tgt_root_rot`, `tgt_joint_dof`, so the refe
 Everything numeric happens in `parc_b200_motion_loss` (include/parc_b200_opt.h): value and gradient in
 one pass; `backward` only scales the stored gradients."""
 import enum
+from dataclasses import dataclass
 from typing import List
 
+import numpy as np
 import torch
 
 from . import _lib
-from .kin_char_model import KinCharModel
+from .kin_char_model import GeomType, KinCharModel
 
 
 class LossType(enum.Enum):      # motion_optimization.py:15-25
@@ -27,6 +29,125 @@ class LossType(enum.Enum):      # motion_optimization.py:15-25
     BODY_CONSTRAINT_LOSS = 7
     JERK_LOSS = 8
     LOOPING_LOSS = 9
+
+
+@dataclass
+class BodyConstraint:           # motion_optimization.py:27-31
+    start_frame_idx = 0
+    end_frame_idx = 0
+    constraint_point = None     # 3D torch vector
+
+
+SOLE_POINTS = 18                # the box (foot) term reads the body's first 18 sample points (:600)
+
+
+class PackedBodyConstraints:
+    """The reference's per-body Python lists of BodyConstraint (one list of lists per motion), flattened into the device
+    arrays parc_opt_constraints_t points at (include/parc_b200_opt.h). Pack once per optimisation, reuse every iteration."""
+
+    def __init__(self, per_motion: list, char_model: KinCharModel, device):
+        J = char_model.get_num_joints()
+        rows, starts = [], [0]
+        for body_constraints in per_motion:
+            if body_constraints is not None:
+                assert len(body_constraints) == J, "body_constraints holds one list per body"
+                for b, lst in enumerate(body_constraints):
+                    for c in lst:
+                        pt = c.constraint_point.detach().reshape(3).cpu().numpy().astype(np.float32)
+                        rows.append((b, int(c.start_frame_idx), int(c.end_frame_idx), pt))
+            starts.append(len(rows))
+        n = len(rows)
+        B = len(per_motion)
+        # one int32 buffer = one host-to-device copy: motion_start [B+1] | body [n] | start [n] | end [n] | point bits [n,3]
+        buf = np.zeros(B + 1 + 6 * max(n, 1), dtype=np.int32)
+        buf[:B + 1] = starts
+        o = B + 1
+        if n:
+            buf[o:o + n] = [r[0] for r in rows]
+            buf[o + n:o + 2 * n] = [r[1] for r in rows]
+            buf[o + 2 * n:o + 3 * n] = [r[2] for r in rows]
+            buf[o + 3 * n:o + 6 * n] = np.stack([r[3] for r in rows]).reshape(-1).view(np.int32)
+        self.num, self.num_motions = n, B
+        self.buffer = torch.from_numpy(buf).to(device)
+        st = _lib.OptConstraintsStruct()
+        st.num = n
+        base = self.buffer.data_ptr()
+        st.motion_start = base
+        st.body = base + 4 * o
+        st.start_frame = base + 4 * (o + n)
+        st.end_frame = base + 4 * (o + 2 * n)
+        st.point = base + 4 * (o + 3 * n)
+        for b in range(J):
+            geoms = char_model.get_geoms(b)
+            kind = _lib.GEOM_NONE
+            if geoms:
+                g = geoms[0]
+                if g._shape_type == GeomType.SPHERE:        # :590-592
+                    kind = _lib.GEOM_SPHERE
+                    st.geom_radius[b] = float(g._dims.reshape(-1)[0])
+                    for k in range(3):
+                        st.geom_offset[b][k] = float(g._offset[k])
+                elif g._shape_type == GeomType.BOX:         # :598-599
+                    kind = _lib.GEOM_BOX
+                    st.geom_radius[b] = float(torch.norm(g._dims.float()) * 1.25)
+            st.geom_kind[b] = kind
+        st.sole_points = SOLE_POINTS
+        self.struct = st
+
+
+def compute_approx_body_constraints(root_pos, root_rot, joint_rot, contacts, char_model: KinCharModel, terrain):
+    """motion_optimization.py:70-205. For each foot and hand: every run of consecutive frames whose contact label exceeds
+    0.9 becomes one BodyConstraint whose point is the body's mean position over the run (feet: the centre of the box
+    geom), pulled onto the terrain surface by 1,000 SGD steps (lr 0.01) on the squared heightfield distance.
+    Returns one list of BodyConstraint per body."""
+    def extract_consecutive_trues(flags):                     # :74-104
+        idx = torch.nonzero(flags.flatten(), as_tuple=True)[0]
+        if len(idx) == 0:
+            return []
+        breaks = [0] + (torch.nonzero(idx[1:] - idx[:-1] > 1, as_tuple=True)[0] + 1).tolist()
+        groups = [idx[breaks[i]:breaks[i + 1]].clone() for i in range(len(breaks) - 1)]
+        if breaks[-1] < idx.shape[0] - 1:                     # upstream drops a trailing run of a single frame
+            groups.append(idx[breaks[-1]:].clone())
+        return groups
+
+    body_pos, body_rot = char_model.forward_kinematics(root_pos, root_rot, joint_rot)
+    from .geom_util import _quat_rotate
+    dev = body_pos.device
+    ids = [char_model.get_body_id(n) for n in ("left_foot", "right_foot", "left_hand", "right_hand")]
+    points, frame_groups = [], []
+    for k, b in enumerate(ids):
+        pos = body_pos[:, b]
+        if k < 2:                                             # feet: centre of the box geom (:145-152)
+            off = char_model.get_geoms(b)[0]._offset.to(dev)
+            pos = pos + _quat_rotate(body_rot[:, b], off.unsqueeze(0).expand(pos.shape[0], -1))     # torch_util.quat_rotate, torch_util.py:62-67
+        groups = extract_consecutive_trues(contacts[:, b] > 0.9)          # :106-108
+        frame_groups.append(groups)
+        points.extend(torch.mean(pos[g], dim=0) for g in groups)         # :115
+    if points:
+        from . import terrain as _terrain
+        # every point descends independently (:123-143), so all of them share the 1,000 steps here
+        pts = torch.stack(points).detach().clone().unsqueeze(0).contiguous().requires_grad_(True)
+        base_z = terrain.hf.min().item() - 10.0
+        opt = torch.optim.SGD([pts], lr=0.01)
+        hf, mp = terrain.hf.unsqueeze(0), terrain.min_point.unsqueeze(0)
+        for _ in range(1000):
+            opt.zero_grad()
+            sd = _terrain.points_hf_sdf(pts, hf, mp, terrain.dxdy, base_z=base_z, inverted=False)
+            torch.sum(torch.square(sd)).backward()
+            opt.step()
+        pts = pts.detach()[0]
+    body_constraints = [[] for _ in range(char_model.get_num_joints())]
+    k = 0
+    for b, groups in zip(ids, frame_groups):
+        out = []
+        for g in groups:                                      # :185-193
+            c = BodyConstraint()
+            c.start_frame_idx, c.end_frame_idx = g[0].item(), g[-1].item()
+            c.constraint_point = pts[k].clone()
+            k += 1
+            out.append(c)
+        body_constraints[b] = out
+    return body_constraints
 
 
 def build_opt_config(char_model: KinCharModel, body_points: List[torch.Tensor], num_contact_cols: int, w_root_pos, w_root_rot,
@@ -58,7 +179,7 @@ def build_opt_config(char_model: KinCharModel, body_points: List[torch.Tensor], 
 
 class _MotionLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, tgt_root_pos, tgt_root_rot, tgt_joint_dof, char_model, cfg, consts, terrain_args, points):
+    def forward(ctx, tgt_root_pos, tgt_root_rot, tgt_joint_dof, char_model, cfg, consts, terrain_args, points, packed=None):
         (src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts) = consts
         hf, hf_stride, X, Y, min_point, mp_stride, dx, dy = terrain_args
         B, T = tgt_root_pos.shape[0], tgt_root_pos.shape[1]
@@ -75,10 +196,12 @@ class _MotionLossFn(torch.autograd.Function):
         loss = torch.empty(B, dtype=f32, device=dev)
         grads = [torch.empty_like(x) for x in p] if need_grad else [None, None, None]
         keep = [c(x) for x in (src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts)]
-        _lib.check(L.parc_b200_motion_loss(km, cfg, B, T, _lib.ptr(p[0]), _lib.ptr(p[1]), _lib.ptr(p[2]), *[_lib.ptr(x) for x in keep],
-                                           _lib.ptr(hf), hf_stride, X, Y, _lib.ptr(min_point), mp_stride, dx, dy, _lib.ptr(points),
-                                           _lib.ptr(ws), ws_bytes, _lib.ptr(terms), _lib.ptr(loss), _lib.ptr(grads[0]), _lib.ptr(grads[1]),
-                                           _lib.ptr(grads[2]), _lib.stream_ptr(dev)))
+        if packed is not None:
+            assert packed.num_motions == B and packed.buffer.device == dev, "constraints packed for another batch / device"
+        _lib.check(L.parc_b200_motion_loss_constrained(km, cfg, packed.struct if packed is not None else None, B, T, _lib.ptr(p[0]), _lib.ptr(p[1]), _lib.ptr(p[2]), *[_lib.ptr(x) for x in keep],
+                                                       _lib.ptr(hf), hf_stride, X, Y, _lib.ptr(min_point), mp_stride, dx, dy,
+                                                       _lib.ptr(points), _lib.ptr(ws), ws_bytes, _lib.ptr(terms), _lib.ptr(loss),
+                                                       _lib.ptr(grads[0]), _lib.ptr(grads[1]), _lib.ptr(grads[2]), _lib.stream_ptr(dev)))
         ctx.save_for_backward(*[g for g in grads if g is not None])
         ctx.has_grads = need_grad
         ctx.mark_non_differentiable(terms)
@@ -87,19 +210,20 @@ class _MotionLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, _g_terms):
         if not ctx.has_grads:
-            return (None,) * 8
+            return (None,) * 9
         g0, g1, g2 = ctx.saved_tensors
         s = g_loss.reshape(-1, 1, 1)
-        return s * g0, s * g1, s * g2, None, None, None, None, None
+        return s * g0, s * g1, s * g2, None, None, None, None, None, None
 
 
 def motion_loss_batched(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels,
                         src_body_rot_vels, contacts, hf, min_point, dxdy, body_points: List[torch.Tensor], char_model: KinCharModel,
                         w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints,
-                        w_jerk, max_jerk):
+                        w_jerk, max_jerk, body_constraints=None):
     """B independent motions of T frames: all motion tensors carry a leading [B, T(-1), ...]; `hf` is
-    [B, X, Y] with `min_point` [B, 2], or one shared [X, Y] / [2]. -> (loss [B], terms [B, 9]) with
-    autograd to the three tgt_* tensors."""
+    [B, X, Y] with `min_point` [B, 2], or one shared [X, Y] / [2]. `body_constraints`: None, a PackedBodyConstraints, or a
+    list with one entry per motion (None or the reference's list of BodyConstraint lists per body).
+    -> (loss [B], terms [B, 9]) with autograd to the three tgt_* tensors."""
     dev = tgt_root_pos.device
     assert tgt_root_pos.dim() == 3 and tgt_root_rot.shape == tgt_root_pos.shape and tgt_joint_dof.dim() == 3
     B, T = tgt_root_pos.shape[:2]
@@ -117,9 +241,12 @@ def motion_loss_batched(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos,
         assert hf.shape[0] == B and min_point.shape == (B, 2)
         X, Y, hf_stride, mp_stride = hf.shape[1], hf.shape[2], hf.shape[1] * hf.shape[2], 2
     points = torch.cat([p.to(device=dev, dtype=torch.float32) for p in body_points], dim=0).contiguous()
+    if body_constraints is not None and not isinstance(body_constraints, PackedBodyConstraints):
+        assert len(body_constraints) == B, "one body_constraints entry per motion"
+        body_constraints = PackedBodyConstraints(body_constraints, char_model, dev)
     return _MotionLossFn.apply(tgt_root_pos, tgt_root_rot, tgt_joint_dof, char_model, cfg,
                                (src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts),
-                               (hf, hf_stride, X, Y, min_point, mp_stride, float(dxdy[0]), float(dxdy[1])), points)
+                               (hf, hf_stride, X, Y, min_point, mp_stride, float(dxdy[0]), float(dxdy[1])), points, body_constraints)
 
 
 def motion_terrain_contact_loss_localized(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat, src_joint_rot,
@@ -127,14 +254,16 @@ def motion_terrain_contact_loss_localized(tgt_root_pos, tgt_root_rot, tgt_joint_
                                           char_model: KinCharModel, w_root_pos: float, w_root_rot: float, w_joint_rot: float,
                                           w_smoothness: float, w_penetration: float, w_contact: float, w_sliding: float,
                                           w_body_constraints: float, w_jerk: float, body_constraints: list, max_jerk: float):
-    """motion_optimization.py:426-656, one motion of T frames. Returns (loss, {LossType: float})."""
-    if body_constraints is not None:
-        raise NotImplementedError("body_constraints are not supported by the CUDA loss (pass None)")
+    """motion_optimization.py:426-656, one motion of T frames. Returns (loss, {LossType: float}). `body_constraints` is the
+    reference's list (one list of BodyConstraint per body), None, or a PackedBodyConstraints made once for the whole run."""
+    if body_constraints is not None and not isinstance(body_constraints, PackedBodyConstraints):
+        body_constraints = PackedBodyConstraints([body_constraints], char_model, tgt_root_pos.device)
     u = lambda t: t.unsqueeze(0)
     loss, terms = motion_loss_batched(u(tgt_root_pos), u(tgt_root_rot), u(tgt_joint_dof), u(src_root_pos), u(src_root_rot_quat),
                                       u(src_joint_rot), u(src_body_vels), u(src_body_rot_vels), u(contacts), terrain.hf,
                                       terrain.min_point, terrain.dxdy, body_points, char_model, w_root_pos, w_root_rot, w_joint_rot,
-                                      w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk)
+                                      w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk,
+                                      body_constraints=body_constraints)
     vals = terms[0].tolist()       # the reference also reads every term back with .item() (:626-643)
     losses = {t: vals[t.value] for t in list(LossType)[:9]}
     return loss[0], losses

@@ -13,6 +13,13 @@ UNMODIFIED PARC reference on CPU (oracle/ref_import.py; run in the authoring con
                         (its own terrain), targets = source + seeded perturbation, first half pushed 6 cm into the
                         ground, second half lifted 5 cm: total loss, the 9 loss terms, and autograd gradients w.r.t. the three
                         parameter tensors. Two weight sets (kin_gen defaults; contact/sliding off).
+                        Plus two body-constraint cases (motion_optimization.py:581-609) with the kin_gen weights:
+                        `cons`  = the lists compute_approx_body_constraints (:70-205) derives from the clip's contact labels
+                                  and terrain (its inputs are the src_* tensors above; its outputs are stored flattened as
+                                  cons_body / cons_start / cons_end / cons_point),
+                        `cons2` = hand-made lists that make every branch active (hinge on for the feet, both signs of the
+                                  sphere distance for the hands, overlapping ranges, a range that runs past the last frame,
+                                  a constraint on a capsule body, which the reference ignores).
 """
 import os
 import sys
@@ -107,6 +114,57 @@ def main():
                                                            "w_contact", "w_sliding", "w_body_constraints", "w_jerk", "max_jerk")])
         out[tag + "_g_root_pos"], out[tag + "_g_root_rot"], out[tag + "_g_joint_dof"] = p[0].grad, p[1].grad, p[2].grad
         print(tag, float(loss), {k.name: round(v, 6) if isinstance(v, float) else v for k, v in losses.items()})
+    # ---- body constraints ------------------------------------------------------------------------
+    def flatten(bc):
+        rows = [(b, c.start_frame_idx, c.end_frame_idx, c.constraint_point) for b, lst in enumerate(bc) for c in lst]
+        if not rows:
+            return np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros((0, 3), np.float32)
+        return (np.array([r[0] for r in rows], np.int64), np.array([r[1] for r in rows], np.int64), np.array([r[2] for r in rows], np.int64),
+                torch.stack([r[3] for r in rows]).numpy())
+
+    J = model.get_num_joints()
+    kinds, dims, offs = [], np.zeros((J, 3), np.float32), np.zeros((J, 3), np.float32)
+    for b in range(J):                                  # first geom of every body: all the constraint term looks at (:590, :598)
+        g0 = model.get_geoms(b)[0]
+        kinds.append(g0._shape_type.name)
+        dv = g0._dims.reshape(-1).numpy()
+        dims[b, :dv.shape[0]] = dv
+        offs[b] = g0._offset.numpy()
+    out["geom_kind"], out["geom_dims"], out["geom_offset"] = np.array(kinds), dims, offs
+    torch.manual_seed(0)
+    auto = ropt.compute_approx_body_constraints(src_root_pos, src_root_rot_quat, src_joint_rot, contacts, model, terrain)
+    tgt_body_pos, _ = model.forward_kinematics(tgt_root_pos, rtu.exp_map_to_quat(tgt_root_rot), model.dof_to_rot(tgt_joint_dof))
+
+    def mk(b, s, e, pt):
+        c = ropt.BodyConstraint()
+        c.start_frame_idx, c.end_frame_idx, c.constraint_point = s, e, pt.clone()
+        return b, c
+
+    lf, rf, lh, rh = (model.get_body_id(n) for n in ("left_foot", "right_foot", "left_hand", "right_hand"))
+    capsule_body = model.get_body_id("left_shin")
+    hand = [[] for _ in range(model.get_num_joints())]
+    for b, c in (mk(lf, 2, 9, tgt_body_pos[5, lf] + torch.tensor([0.25, -0.1, -0.05])),        # > 1.25 |dims| away: hinge active
+                 mk(lf, 7, 15, tgt_body_pos[11, lf] + torch.tensor([0.02, 0.01, -0.03])),      # overlaps the first; mostly inside the ball
+                 mk(rf, 0, 0, tgt_body_pos[0, rf] + torch.tensor([-0.2, 0.15, 0.1])),          # single frame at the start
+                 mk(rf, 18, 40, tgt_body_pos[20, rf] + torch.tensor([0.1, 0.2, -0.1])),        # runs past the last frame (Python slicing clips it)
+                 mk(lh, 3, 12, tgt_body_pos[8, lh] + torch.tensor([0.15, 0.0, 0.05])),         # outside the hand sphere
+                 mk(lh, 14, 20, tgt_body_pos[17, lh] + torch.tensor([0.005, 0.0, 0.0])),       # inside it
+                 mk(rh, 22, 23, tgt_body_pos[23, rh] + torch.tensor([0.0, -0.3, 0.0])),        # includes the last frame
+                 mk(capsule_body, 4, 10, tgt_body_pos[6, capsule_body])):                      # capsule geom: ignored (:603-604)
+        hand[b].append(c)
+    for tag, bc in (("cons", auto), ("cons2", hand)):
+        p = [t.clone().requires_grad_(True) for t in (tgt_root_pos, tgt_root_rot, tgt_joint_dof)]
+        loss, losses = ropt.motion_terrain_contact_loss_localized(
+            p[0], p[1], p[2], src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts, terrain,
+            body_points, model, body_constraints=bc, **KIN_GEN_WEIGHTS)
+        loss.backward()
+        out[tag + "_loss"] = loss.detach()
+        out[tag + "_terms"] = np.array([float(losses.get(t, 0.0)) for t in list(ropt.LossType)[:9]], dtype=np.float64)
+        out[tag + "_weights"] = out["full_weights"]
+        out[tag + "_g_root_pos"], out[tag + "_g_root_rot"], out[tag + "_g_joint_dof"] = p[0].grad, p[1].grad, p[2].grad
+        out[tag + "_body"], out[tag + "_start"], out[tag + "_end"], out[tag + "_point"] = flatten(bc)
+        print(tag, float(loss), {k.name: round(v, 6) if isinstance(v, float) else v for k, v in losses.items()},
+              list(zip(out[tag + "_body"].tolist(), out[tag + "_start"].tolist(), out[tag + "_end"].tolist())))
     npz("ref_opt_loss.npz", **out)
 
 

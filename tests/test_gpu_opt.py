@@ -41,11 +41,28 @@ def test_points_hf_sdf_matches_reference_values_and_oracle_gradient():
         torch.testing.assert_close(p.grad.cpu(), po.grad, rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("tag", ["full", "nocontact"])
+def _constraint_lists(d, tag, J, dev):
+    """golden records -> the reference's structure: one list of BodyConstraint per body"""
+    from parc_b200.motion_optimization import BodyConstraint
+    out = [[] for _ in range(J)]
+    for b, s0, e0, pt in zip(d[tag + "_body"], d[tag + "_start"], d[tag + "_end"], d[tag + "_point"]):
+        c = BodyConstraint()
+        c.start_frame_idx, c.end_frame_idx, c.constraint_point = int(s0), int(e0), _t(pt, dev)
+        out[int(b)].append(c)
+    return out
+
+
+def _geoms(d):
+    return [(str(k), (float(dm[0]) if str(k) == "SPHERE" else dm), off) for k, dm, off in zip(d["geom_kind"], d["geom_dims"], d["geom_offset"])]
+
+
+@pytest.mark.parametrize("tag", ["full", "nocontact", "cons", "cons2"])
 def test_motion_loss_matches_reference_golden(tag):
+    """`cons` / `cons2`: with body constraints (motion_optimization.py:581-609)."""
     from parc_b200.motion_optimization import LossType, motion_terrain_contact_loss_localized
     d = H.load_npz("ref_opt_loss.npz")
     model = H.product_model(DEV)
+    bc = _constraint_lists(d, tag, model.get_num_joints(), DEV) if tag.startswith("cons") else None
     pts, _ = _body_points(DEV)
     terrain = H.product_terrain(_t(d["hf"]), d["min_point"], float(d["dxdy"][0]), DEV)
     p = [_t(d[k], DEV).clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
@@ -55,14 +72,32 @@ def test_motion_loss_matches_reference_golden(tag):
     loss, losses = motion_terrain_contact_loss_localized(
         p[0], p[1], p[2], _t(d["src_root_pos"], DEV), _t(d["src_root_rot_quat"], DEV), _t(d["src_joint_rot"], DEV),
         _t(d["src_body_vels"], DEV), _t(d["src_body_rot_vels"], DEV), _t(d["contacts"], DEV), terrain, pts, model,
-        body_constraints=None, **kw)
+        body_constraints=bc, **kw)
     loss.backward()
     got = np.array([losses[t] for t in list(LossType)[:9]])
+    assert (got[7] > 1.0) == tag.startswith("cons")
     np.testing.assert_allclose(got, d[tag + "_terms"], rtol=2e-5, atol=2e-6)
     np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
     for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
         ref = d[tag + k]
         np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))   # gradients <= 1e-4 relative (of the tensor scale)
+
+
+def test_compute_approx_body_constraints_matches_reference():
+    """motion_optimization.py:70-205 on the golden clip: the same contact runs per foot / hand, and constraint points
+    (1,000 SGD steps through parc_b200_points_hf_sdf and its gradient) within 1e-5 m of the reference's."""
+    from parc_b200.motion_optimization import compute_approx_body_constraints
+    d = H.load_npz("ref_opt_loss.npz")
+    model = H.product_model(DEV)
+    terrain = H.product_terrain(_t(d["hf"]), d["min_point"], float(d["dxdy"][0]), DEV)
+    bc = compute_approx_body_constraints(_t(d["src_root_pos"], DEV), _t(d["src_root_rot_quat"], DEV), _t(d["src_joint_rot"], DEV),
+                                         _t(d["contacts"], DEV), model, terrain)
+    assert len(bc) == model.get_num_joints()
+    got = [(b, c.start_frame_idx, c.end_frame_idx) for b, lst in enumerate(bc) for c in lst]
+    want = list(zip(d["cons_body"].tolist(), d["cons_start"].tolist(), d["cons_end"].tolist()))
+    assert got == want and len(want) >= 3
+    pts = torch.stack([c.constraint_point for lst in bc for c in lst]).cpu().numpy()
+    np.testing.assert_allclose(pts, d["cons_point"], rtol=0, atol=1e-5)
 
 
 def _synthetic_batch(B, T, seed):
@@ -114,6 +149,67 @@ def test_batched_motion_loss_vs_oracle_per_motion():
         for g, go in zip(p, po):
             ref = go.grad.numpy()
             np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))   # gradients <= 1e-4 relative (of the tensor scale)
+
+
+def test_batched_motion_loss_with_body_constraints_vs_oracle_per_motion():
+    """Constraint records of a batch: a different number per motion (one motion has none, one passes None), feet and hands,
+    overlapping and clipped ranges; every motion against the pinned oracle evaluated alone."""
+    from parc_b200.motion_optimization import BodyConstraint, PackedBodyConstraints, motion_loss_batched
+    B, T = 4, 36
+    d, dx = _synthetic_batch(B, T, seed=57)
+    g4 = H.load_npz("ref_opt_loss.npz")
+    geoms = _geoms(g4)
+    model = H.product_model(DEV)
+    J = model.get_num_joints()
+    pts, bp = _body_points(DEV)
+    om = H.oracle_model()
+    w = [KIN_GEN[k] for k in ("w_root_pos", "w_root_rot", "w_joint_rot", "w_smoothness", "w_penetration", "w_contact", "w_sliding",
+                              "w_body_constraints", "w_jerk", "max_jerk")]
+    tq = torch.stack([H.O.exp_map_to_quat(d["tgt_root_rot"][b]) for b in range(B)])
+    gen = torch.Generator().manual_seed(3)
+    ends = [om.body_names.index(n) for n in ("left_foot", "right_foot", "left_hand", "right_hand", "head")]   # head: a sphere WITH an offset
+    records, lists = [], []
+    for b in range(B):
+        bpos, _ = om.forward_kinematics(d["tgt_root_pos"][b], tq[b], om.dof_to_rot(d["tgt_joint_dof"][b]))
+        rec = []
+        for k in range([5, 0, 9, 3][b]):
+            body = ends[int(torch.randint(0, 5, (1,), generator=gen))]
+            s0 = int(torch.randint(0, T - 2, (1,), generator=gen))
+            e0 = s0 + int(torch.randint(0, 12, (1,), generator=gen))          # may run past T-1
+            scale = 0.02 if k % 2 else 0.25
+            rec.append((body, s0, e0, bpos[min(s0 + 1, T - 1), body] + scale * torch.randn(3, generator=gen)))
+        records.append(rec)
+        if b == 1:
+            lists.append(None)
+            continue
+        per_body = [[] for _ in range(J)]
+        for body, s0, e0, pt in rec:
+            c = BodyConstraint()
+            c.start_frame_idx, c.end_frame_idx, c.constraint_point = s0, e0, pt.to(DEV)
+            per_body[body].append(c)
+        lists.append(per_body)
+    packed = PackedBodyConstraints(lists, model, torch.device(DEV))
+    assert packed.num == 17
+    p = [d[k].to(DEV).clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+    dxdy = torch.tensor([dx, dx])
+    loss, terms = motion_loss_batched(p[0], p[1], p[2], *[d[k].to(DEV) for k in ("src_root_pos", "src_root_rot_quat", "src_joint_rot",
+                                                                                 "src_body_vels", "src_body_rot_vels", "contacts")],
+                                      d["hf"].to(DEV), d["min_point"].to(DEV), dxdy, pts, model, body_constraints=packed, **KIN_GEN)
+    loss.sum().backward()
+    assert float(terms[1, 7]) == 0.0 and float(terms[0, 7]) > 0.1
+    for b in range(B):
+        po = [d[k][b].clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+        # the reference keeps per-body lists: records sorted by body, stable
+        rec = sorted(records[b], key=lambda r: r[0])
+        lo, to = OO.motion_loss(om, _t(bp["points"]), bp["counts"], d["hf"][b], d["min_point"][b], dxdy, po[0], po[1], po[2],
+                                d["src_root_pos"][b], d["src_root_rot_quat"][b], d["src_joint_rot"][b], d["src_body_vels"][b],
+                                d["src_body_rot_vels"][b], d["contacts"][b], w, body_constraints=rec, geoms=geoms)
+        lo.backward()
+        np.testing.assert_allclose(terms[b].cpu().numpy(), to.numpy(), rtol=3e-5, atol=3e-6)
+        np.testing.assert_allclose(float(loss[b]), float(lo), rtol=3e-5)
+        for g, go in zip(p, po):
+            ref = go.grad.numpy()
+            np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))
 
 
 def test_config4_size_properties():
