@@ -26,6 +26,18 @@ def golden_clip(name="clip_civilization.npz"):
                 fps=int(g["fps"]), loop_mode=int(g["loop_mode"]), hf=t(g["hf"]), min_point=t(g["min_point"]), dx=float(g["dx"]))
 
 
+def aug_extras(num_clips=2):
+    """What the heightfield augmenter reads beyond the clip files (tests/golden/clip_aug_extras.npz, written by
+    make_golden_sampler.py): -> (hf_maxmins [list of [X,Y,2]], mask_inds [list over clips of list over frames of [k,2] i64])"""
+    g = load_npz("clip_aug_extras.npz")
+    mms, masks = [], []
+    for k in range(num_clips):
+        mms.append(t(g["c%d_hf_maxmin" % k]))
+        st, cells = g["c%d_mask_start" % k], t(g["c%d_mask_cells" % k]).long()
+        masks.append([cells[int(st[f]):int(st[f + 1])] for f in range(len(st) - 1)])
+    return mms, masks
+
+
 def oracle_model():
     return O.CharModel(synth.humanoid_spec())
 
