@@ -101,7 +101,7 @@ def sample_motion_data(model: O.CharModel, lib: O.Library, cfg: SamplerConfig, m
     root_pos = O.quat_rotate(he, root_pos)
     body_pos, _ = model.forward_kinematics(root_pos, root_rot, joint_rot)                     # :241
     out.update(root_pos=root_pos, root_rot=root_rot, root_vel=root_vel, joint_pos=body_pos[..., 1:, :], joint_rot=joint_rot,
-               contacts=contacts, canon_pos=canon_pos, canon_heading_quat_inv=hinv)
+               contacts=contacts, canon_pos=canon_pos, canon_rot=canon_rot, canon_heading_quat_inv=hinv)
     if want_floor_heights:
         out["floor_heights"] = floor_heights(cfg, out["hfs"], root_pos)                       # :267-278
     if future_t is not None:                                                                  # :146-160
@@ -218,14 +218,20 @@ def augment_noise(mm, noise, cfg: SamplerConfig):
     return torch.clamp(noise * (cfg.max_h - cfg.min_h) + cfg.min_h, mm[..., 0], mm[..., 1])
 
 
+def grid_points_world(cfg: SamplerConfig, canon_pos, canon_rot):
+    """:367-374: the generic grid rotated by the heading of the reference frame and moved to its root -> [n,gx,gy,2]"""
+    n = canon_pos.shape[0]
+    pts = cfg.grid.unsqueeze(0).expand(n, -1, -1, -1)
+    heading = O.calc_heading(canon_rot).unsqueeze(-1).unsqueeze(-1).expand(-1, cfg.grid.shape[0], cfg.grid.shape[1])
+    return O.rotate_2d_vec(pts, heading) + canon_pos[:, 0:2].unsqueeze(1).unsqueeze(1)
+
+
 def local_heightmaps_augmented(lib: O.Library, hf_maxmins, mask_inds, cfg: SamplerConfig, motion_ids, start_times, canon_pos, canon_rot,
                                mode, rec_i=None, rec_f=None, noise=None):
     """get_hfs_from_data (:366-401) with the augmenter, then the clamp of sample_motion_data (:228). mode: "NOISE" |
     "MAXPOOL_AND_BOXES" | "NONE". -> hfs [n,gx,gy], center_h [n]"""
     n = motion_ids.shape[0]
-    pts = cfg.grid.unsqueeze(0).expand(n, -1, -1, -1)
-    heading = O.calc_heading(canon_rot).unsqueeze(-1).unsqueeze(-1).expand(-1, cfg.grid.shape[0], cfg.grid.shape[1])
-    pts = O.rotate_2d_vec(pts, heading) + canon_pos[:, 0:2].unsqueeze(1).unsqueeze(1)
+    pts = grid_points_world(cfg, canon_pos, canon_rot)
     hfs = torch.stack([lib.terrains[int(motion_ids[i])].height_at(pts[i]) for i in range(n)], dim=0)
     mms = window_maxmins(lib.terrains, hf_maxmins, mask_inds, cfg, motion_ids, start_times, pts)
     center_h = hfs[:, cfg.num_x_neg, cfg.num_y_neg].clone()

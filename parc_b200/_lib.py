@@ -56,6 +56,15 @@ class SamplerConfigStruct(C.Structure):     # parc_sampler_config_t, include/par
                 ("max_h", C.c_float), ("future_pos_noise_scale", C.c_float)]
 
 
+class HfAugStruct(C.Structure):              # parc_hf_aug_t, include/parc_b200_sampler.h
+    _fields_ = [("mode", C.c_int32), ("max_boxes", C.c_int32), ("max_terrain_cells", C.c_int32), ("timestep", C.c_float),
+                ("hf_maxmin", C.c_void_p), ("maxmin_offset", C.c_void_p), ("mask_frame_off", C.c_void_p), ("mask_start", C.c_void_p),
+                ("mask_cells", C.c_void_p), ("rec_i", C.c_void_p), ("rec_f", C.c_void_p), ("noise", C.c_void_p)]
+
+
+AUG_REC_INTS, AUG_BOX_FLOATS = 8, 7           # PARC_AUG_REC_INTS, PARC_AUG_BOX_FLOATS
+
+
 class RecordTapeStruct(C.Structure):         # parc_record_tape_t, include/parc_b200_env.h
     _fields_ = [("frames", C.c_void_p), ("contacts", C.c_void_p), ("obs", C.c_void_p), ("cursor", C.c_void_p), ("writing", C.c_void_p),
                 ("success", C.c_void_p), ("saved_list", C.c_void_p), ("saved_count", C.c_void_p), ("still_recording", C.c_void_p),
@@ -272,6 +281,8 @@ def _declare(lib):
         "parc_b200_path_motion_loss": [P(CharModelStruct), P(OptConfigStruct), i64, i64, vp, vp, vp, vp, i32, i32, vp, f32, f32, vp,
                                        f32, f32, vp, i64, vp, vp, vp, vp],
         "parc_b200_mdm_sample_motion_data": [P(CharModelStruct), P(MotionLibStruct), vp, P(SamplerConfigStruct), vp, vp, i64] + [vp] * 14,
+        "parc_b200_mdm_augment_hfs": [vp, P(SamplerConfigStruct), P(HfAugStruct), vp, vp, i64, vp, vp, vp, vp],
+        "parc_b200_mdm_floor_heights": [P(SamplerConfigStruct), f32, vp, vp, i64, vp, vp],
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32), P(i32)],
         "parc_b200_ray_points_lattice": [P(f32), i32, P(i32), P(i32)],
     }

@@ -138,9 +138,191 @@ __global__ void __launch_bounds__(PARC_MDM_THREADS, PARC_MDM_MINB) mdm_frames_ke
     }
 }
 
+// ---- heightfield augmenter (:304-364, :390-400): one block per window, the gx x gy patch and its bounds in shared memory ----
+// s_a / s_b ping-pong for the separable max-pools; the motion's masked terrain cells of the window's frames are OR-ed into a
+// bitmap first (CSR rows of consecutive frames are contiguous, so the union is one flat range of mask_cells).
+__global__ void __launch_bounds__(256) mdm_hf_augment_kernel(const __grid_constant__ parc_sampler_config_t cfg,
+                                                             const __grid_constant__ parc_hf_aug_t aug,
+                                                             const parc_terrain_t* __restrict__ terrains,
+                                                             const long long* __restrict__ motion_ids, const float* __restrict__ start_times,
+                                                             const long long n, const float* __restrict__ grid_xy,
+                                                             const float* __restrict__ canon, float* __restrict__ hfs) {
+    extern __shared__ float smem[];
+    const int gx = cfg.grid_dim_x, gy = cfg.grid_dim_y, P = gx * gy;
+    float* s_a = smem;
+    float* s_b = s_a + P;
+    float* s_max = s_b + P;
+    float* s_min = s_max + P;
+    unsigned* s_bits = reinterpret_cast<unsigned*>(s_min + P);
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const float span = __fsub_rn(cfg.max_h, cfg.min_h);                      // (self._max_h - self._min_h)
+    const float open_max = __fmul_rn(cfg.max_h, 2.0f), open_min = __fmul_rn(cfg.min_h, 2.0f);   // :354-355
+    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+        const long long mid = __ldg(motion_ids + i);
+        const parc_terrain_t tr = terrains[mid];
+        const int cells = tr.dim_x * tr.dim_y, words = (cells + 31) >> 5;
+        for (int w = tid; w < words; w += nt) s_bits[w] = 0u;
+        __syncthreads();
+        // frames of the window: round(start / timestep) + [0, T) (:213-216), sliced like a Python list (:348-349)
+        const long long f0 = (long long)rintf(__fdiv_rn(__ldg(start_times + i), aug.timestep));
+        const int row0 = __ldg(aug.mask_frame_off + mid), rows = __ldg(aug.mask_frame_off + mid + 1) - row0;
+        const long long lo = f0 < 0 ? 0 : (f0 > rows ? rows : f0);
+        long long hi = f0 + cfg.seq_len;
+        hi = hi < lo ? lo : (hi > rows ? rows : hi);
+        const int c0 = __ldg(aug.mask_start + row0 + lo), c1 = __ldg(aug.mask_start + row0 + hi);
+        for (int c = c0 + tid; c < c1; c += nt) {
+            const int cell = __ldg(aug.mask_cells + c);
+            if (cell >= 0 && cell < cells) atomicOr(&s_bits[cell >> 5], 1u << (cell & 31));
+        }
+        __syncthreads();
+        const float* cn = canon + i * CANON_W;
+        const float rx = __ldg(cn), ry = __ldg(cn + 1);
+        const float heading = calc_heading(make_quat(__ldg(cn + 3), __ldg(cn + 4), __ldg(cn + 5), __ldg(cn + 6)));
+        const float sh = sinf(heading), ch = cosf(heading);
+        const float base = cfg.relative_z_style == PARC_RELATIVE_TO_ROOT_FLOOR ? __ldg(cn + 11) : __ldg(cn + 2);    // :379-388
+        const float* mm = aug.hf_maxmin + __ldg(aug.maxmin_offset + mid);
+        for (int p = tid; p < P; p += nt) {
+            const float2 pt = __ldg(reinterpret_cast<const float2*>(grid_xy) + p);
+            const float wx = __fadd_rn(__fsub_rn(__fmul_rn(pt.x, ch), __fmul_rn(pt.y, sh)), rx);
+            const float wy = __fadd_rn(__fadd_rn(__fmul_rn(pt.x, sh), __fmul_rn(pt.y, ch)), ry);
+            const int ix = grid_index(wx, tr.min_x, tr.dx, tr.dim_x), iy = grid_index(wy, tr.min_y, tr.dy, tr.dim_y);
+            const int cell = ix * tr.dim_y + iy;
+            const bool masked = (s_bits[cell >> 5] >> (cell & 31)) & 1u;
+            s_a[p] = __fsub_rn(__ldg(tr.hf + cell), base);
+            s_max[p] = __fsub_rn(masked ? __ldg(mm + 2 * (long long)cell) : open_max, base);
+            s_min[p] = __fsub_rn(masked ? __ldg(mm + 2 * (long long)cell + 1) : open_min, base);
+        }
+        __syncthreads();
+        float* cur = s_a;
+        if (aug.mode == PARC_HF_AUG_NOISE) {
+            const float* u = aug.noise + i * P;
+            // torch.clamp(x, min = bound max, max = bound min) = min(max(x, bound max), bound min)  (:329)
+            for (int p = tid; p < P; p += nt)
+                s_a[p] = fminf(fmaxf(__fadd_rn(__fmul_rn(__ldg(u + p), span), cfg.min_h), s_max[p]), s_min[p]);
+        } else if (aug.mode == PARC_HF_AUG_MAXPOOL_AND_BOXES) {
+            const int* ri = aug.rec_i + i * PARC_AUG_REC_INTS;
+            const float* rf = aug.rec_f + i * (1 + PARC_AUG_BOX_FLOATS * aug.max_boxes);
+            if (__ldg(ri)) {                                                                         // :305-309
+                const float h = __ldg(rf);
+                for (int p = tid; p < P; p += nt) s_a[p] = h;
+            }
+            __syncthreads();
+            for (int k = 0; k < 3; ++k) {                                                            // :322-332
+                const int kind = __ldg(ri + 1 + 2 * k), size = __ldg(ri + 2 + 2 * k);
+                if (kind < 0) continue;
+                float* other = cur == s_a ? s_b : s_a;
+                if (kind == PARC_POOL_2D || kind == PARC_POOL_X) {                                   // along x (rows of the patch)
+                    const bool last = kind == PARC_POOL_X;
+                    for (int p = tid; p < P; p += nt) {
+                        const int x = p / gy, y = p - x * gy;
+                        const int x0 = max(x - size, 0), x1 = min(x + size, gx - 1);
+                        float v = cur[x0 * gy + y];
+                        for (int q = x0 + 1; q <= x1; ++q) v = fmaxf(v, cur[q * gy + y]);
+                        other[p] = last ? fminf(fmaxf(v, s_min[p]), s_max[p]) : v;                   // clamp(new, min, max), terrain_util.py:1513
+                    }
+                    __syncthreads();
+                    float* t = cur; cur = other; other = t;
+                }
+                if (kind == PARC_POOL_2D || kind == PARC_POOL_Y) {                                   // along y
+                    for (int p = tid; p < P; p += nt) {
+                        const int x = p / gy, y = p - x * gy;
+                        const int y0 = max(y - size, 0), y1 = min(y + size, gy - 1);
+                        float v = cur[x * gy + y0];
+                        for (int q = y0 + 1; q <= y1; ++q) v = fmaxf(v, cur[x * gy + q]);
+                        other[p] = fminf(fmaxf(v, s_min[p]), s_max[p]);
+                    }
+                    __syncthreads();
+                    float* t = cur; cur = other; other = t;
+                }
+            }
+            // add_boxes_to_hf2 (terrain_util.py:861-914): cells are independent, the boxes apply in order per cell
+            const int nb = min(__ldg(ri + 7), aug.max_boxes);
+            for (int p = tid; p < P; p += nt) {
+                const int x = p / gy, y = p - x * gy;
+                float v = cur[p];
+                for (int b = 0; b < nb; ++b) {
+                    const float* bx = rf + 1 + PARC_AUG_BOX_FLOATS * b;
+                    const float cx = __ldg(bx), cy = __ldg(bx + 1), hx = __fmul_rn(__ldg(bx + 2), 0.5f), hy = __fmul_rn(__ldg(bx + 3), 0.5f);
+                    const float c = __ldg(bx + 4), s = __ldg(bx + 5);
+                    const float dxv = __fsub_rn((float)x, cx), dyv = __fsub_rn((float)y, cy);
+                    const float qx = __fadd_rn(__fsub_rn(__fmul_rn(dxv, c), __fmul_rn(dyv, s)), cx);  // rotate_2d_vec(xy - centre) + centre
+                    const float qy = __fadd_rn(__fadd_rn(__fmul_rn(dxv, s), __fmul_rn(dyv, c)), cy);
+                    if (qx < __fadd_rn(cx, hx) && qx > __fsub_rn(cx, hx) && qy < __fadd_rn(cy, hy) && qy > __fsub_rn(cy, hy)) v = __ldg(bx + 6);
+                }
+                cur[p] = fminf(fmaxf(v, s_min[p]), s_max[p]);                                        // terrain_util.py:911-912
+            }
+        }
+        __syncthreads();
+        float* o = hfs + i * P;
+        for (int p = tid; p < P; p += nt) o[p] = fminf(fmaxf(cur[p], cfg.min_h), cfg.max_h);         // :228
+        __syncthreads();
+    }
+}
+
+// FLOOR_HEIGHTS (:267-278): thread per (i, j, t)
+__global__ void __launch_bounds__(256) mdm_floor_heights_kernel(const __grid_constant__ parc_sampler_config_t cfg, const float dx,
+                                                                const float* __restrict__ hfs, const float* __restrict__ root_pos,
+                                                                const long long n, float* __restrict__ out) {
+    const long long T = cfg.seq_len, total = n * n * T;
+    const float gmx = __fmul_rn((float)(-cfg.center_ix), dx), gmy = __fmul_rn((float)(-cfg.center_iy), dx);   // _grid_min_point, :72
+    const long long P = (long long)cfg.grid_dim_x * cfg.grid_dim_y;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
+        const long long i = k / (n * T), jt = k - i * (n * T);
+        const float x = __ldg(root_pos + jt * 3), y = __ldg(root_pos + jt * 3 + 1);
+        int ix = (int)rintf(__fdiv_rn(__fsub_rn(x, gmx), dx)), iy = (int)rintf(__fdiv_rn(__fsub_rn(y, gmy), dx));
+        ix = min(max(ix, 0), cfg.grid_dim_x - 1); iy = min(max(iy, 0), cfg.grid_dim_y - 1);
+        out[k] = __ldg(hfs + i * P + (long long)ix * cfg.grid_dim_y + iy);
+    }
+}
+
 }  // namespace parc
 
 using namespace parc;
+
+extern "C" int parc_b200_mdm_augment_hfs(const parc_terrain_t* terrains, const parc_sampler_config_t* cfg, const parc_hf_aug_t* aug,
+                                         const int64_t* motion_ids, const float* start_times, int64_t n, const float* grid_xy,
+                                         const float* canon, float* hfs, void* stream) {
+    PARC_REQUIRE(cfg && aug, "mdm_augment_hfs: NULL config");
+    PARC_REQUIRE(n >= 0, "mdm_augment_hfs: negative window count");
+    if (n == 0 || aug->mode == PARC_HF_AUG_NONE) return PARC_OK;
+    PARC_REQUIRE(terrains && motion_ids && start_times && grid_xy && canon && hfs, "mdm_augment_hfs: NULL input");
+    PARC_REQUIRE(aug->mode == PARC_HF_AUG_NOISE || aug->mode == PARC_HF_AUG_MAXPOOL_AND_BOXES, "mdm_augment_hfs: unknown mode %d", aug->mode);
+    PARC_REQUIRE(cfg->grid_dim_x > 0 && cfg->grid_dim_y > 0 && cfg->seq_len > 0, "mdm_augment_hfs: bad local grid / sequence length");
+    PARC_REQUIRE(aug->timestep > 0.f, "mdm_augment_hfs: timestep must be positive");
+    PARC_REQUIRE(aug->hf_maxmin && aug->maxmin_offset && aug->mask_frame_off && aug->mask_start && aug->mask_cells,
+                 "mdm_augment_hfs: NULL terrain bounds / mask tables");
+    if (aug->mode == PARC_HF_AUG_NOISE) PARC_REQUIRE(aug->noise != nullptr, "mdm_augment_hfs: NOISE mode without noise draws");
+    else PARC_REQUIRE(aug->rec_i && aug->rec_f && aug->max_boxes >= 0, "mdm_augment_hfs: MAXPOOL_AND_BOXES mode without records");
+    const size_t P = (size_t)cfg->grid_dim_x * cfg->grid_dim_y;
+    PARC_REQUIRE(aug->max_terrain_cells > 0, "mdm_augment_hfs: max_terrain_cells not set");
+    const size_t bytes = 4 * P * sizeof(float) + (((size_t)aug->max_terrain_cells + 31) / 32) * sizeof(unsigned);
+    PARC_REQUIRE(bytes <= 200 * 1024, "mdm_augment_hfs: %zu B of shared memory (local grid %zu points, terrains up to %d cells) exceed 200 KB",
+                 bytes, P, aug->max_terrain_cells);
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (bytes > 48 * 1024 && dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t ce = cudaFuncSetAttribute(mdm_hf_augment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (ce != cudaSuccess) { set_error("mdm_augment_hfs: %s", cudaGetErrorString(ce)); return PARC_ERR_CUDA; }
+        attr_set[dev] = true;
+    }
+    mdm_hf_augment_kernel<<<(unsigned)std::min<long long>(n, (long long)kNumSMs * 8), 256, bytes, as_stream(stream)>>>(
+        *cfg, *aug, terrains, (const long long*)motion_ids, start_times, n, grid_xy, canon, hfs);
+    return check_launch("mdm_augment_hfs");
+}
+
+extern "C" int parc_b200_mdm_floor_heights(const parc_sampler_config_t* cfg, float dx, const float* hfs, const float* root_pos, int64_t n,
+                                           float* out, void* stream) {
+    PARC_REQUIRE(cfg != nullptr, "mdm_floor_heights: NULL config");
+    PARC_REQUIRE(n >= 0, "mdm_floor_heights: negative window count");
+    if (n == 0) return PARC_OK;
+    PARC_REQUIRE(hfs && root_pos && out, "mdm_floor_heights: NULL pointer");
+    PARC_REQUIRE(dx > 0.f && cfg->grid_dim_x > 0 && cfg->grid_dim_y > 0 && cfg->seq_len > 0, "mdm_floor_heights: bad grid");
+    const long long total = n * n * cfg->seq_len;
+    mdm_floor_heights_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, (long long)kNumSMs * 16), 256, 0, as_stream(stream)>>>(
+        *cfg, dx, hfs, root_pos, n, out);
+    return check_launch("mdm_floor_heights");
+}
 
 extern "C" int parc_b200_mdm_sample_motion_data(const parc_char_model_t* m, const parc_motion_lib_t* lib, const parc_terrain_t* terrains,
                                                 const parc_sampler_config_t* cfg, const int64_t* motion_ids, const float* start_times,

@@ -6,12 +6,16 @@ same constructor config keys, same `sample_motion_data` signature and return str
 done by `parc_b200_mdm_sample_motion_data` (include/parc_b200_sampler.h) in two launches instead of a
 Python loop over samples. SURVEY.md section 8(f) rank 1.
 
-Not covered (raises NotImplementedError): the heightfield augmenter (`use_hf_augmentation`, :304-330 -- Python
-`random` + per-sample loops around maxpool/box edits) and the FLOOR_HEIGHTS / JOINT_VEL frame components.
-There is no CPU fallback.
+The heightfield augmenter (`use_hf_augmentation`, :304-364, :390-400) is a third launch, `parc_b200_mdm_augment_hfs`: the
+host draws what the reference draws (Python `random` for the pool / box schedule, torch's CPU generator for the boxes, in the
+reference's order, so equal seeds give equal augmentations) and ships them as one record per window. FLOOR_HEIGHTS
+(:267-278) is `parc_b200_mdm_floor_heights`. JOINT_VEL is accepted and, as upstream (whose loop :247-278 has no branch for
+it), produces no entry. There is no CPU fallback.
 """
 import enum
+import random
 
+import numpy as np
 import torch
 
 from . import _lib
@@ -97,9 +101,6 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
         super().__init__(cfg)
         self._canonicalize_samples = cfg["features"]["canonicalize_samples"]
         self._frame_components = [MDMFrameType[c] for c in cfg["features"]["frame_components"]]
-        for c in self._frame_components:
-            if c in (MDMFrameType.FLOOR_HEIGHTS, MDMFrameType.JOINT_VEL):
-                raise NotImplementedError("frame component %s is not produced by the CUDA sampler" % c.name)
         self._num_rb = self._kin_char_model.get_num_joints()
         self._fps = cfg["sequence_fps"]
         self._timestep = 1.0 / self._fps
@@ -130,8 +131,18 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
         self._max_h = hmap["max_h"]
         self._min_h = -self._max_h
         self._use_hf_augmentation = cfg["use_hf_augmentation"]
-        if self._use_hf_augmentation and self._hf_augmentation_mode != HFAugmentationMode.NONE:
-            raise NotImplementedError("heightfield augmentation (mode %s) is outside the CUDA sampler path" % self._hf_augmentation_mode.name)
+        if self._use_hf_augmentation:                                   # :90-97
+            self._max_num_boxes = cfg["max_num_boxes"]
+            self._box_min_len = cfg["box_min_len"]
+            self._box_max_len = cfg["box_max_len"]
+            self._hf_maxpool_chance = cfg["hf_maxpool_chance"]
+            self._hf_max_maxpool_size = cfg["hf_max_maxpool_size"]
+            self._hf_change_height_chance = cfg["hf_change_height_chance"]
+        self._angle_noise_scale = cfg["angle_noise_scale"]
+        self._pos_noise_scale = cfg["pos_noise_scale"]
+        if "custom_num_contacts" in cfg:
+            self._custom_num_contacts = cfg["custom_num_contacts"]
+        self._aug_tables = None
         self._future_window_min = cfg["future_window_min"]
         self._future_window_max = cfg["future_window_max"]
         self.check_init()
@@ -151,6 +162,103 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
             self._terrain_table = (host.to(self._device), [t.hf for t in ts])      # keep the heightfields alive
         return self._terrain_table[0]
 
+    # ---------------------------------------------------------------- heightfield augmenter
+    def _augmenter_tables(self):
+        """What get_hfs_from_data_helper (:332-364) reads per motion, flattened for the kernel: the terrains' hf_maxmin
+        concatenated, and MotionLib._hf_mask_inds as one CSR (row = frame) of packed cell indices."""
+        if self._aug_tables is None:
+            ts, masks = self._mlib._terrains, self._mlib._hf_mask_inds
+            M = len(ts)
+            assert len(masks) >= M and all(m is not None for m in masks[:M]), \
+                "use_hf_augmentation needs hf_mask_inds for every motion (the reference slices MotionLib._hf_mask_inds[id], :349)"
+            mm_off, o = [], 0
+            for t in ts:
+                mm_off.append(o)
+                o += t.hf_maxmin.numel()
+            maxmin = torch.cat([t.hf_maxmin.to(dtype=torch.float32).reshape(-1) for t in ts]).to(self._device).contiguous()
+            frame_off, starts, cells = [0], [0], []
+            for m in range(M):
+                dim_y = int(ts[m].hf.shape[1])
+                for fr in masks[m]:
+                    fr = torch.as_tensor(fr).reshape(-1, 2).to(dtype=torch.int64).cpu()
+                    cells.append((fr[:, 0] * dim_y + fr[:, 1]).to(torch.int32))
+                    starts.append(starts[-1] + int(fr.shape[0]))
+                frame_off.append(len(starts) - 1)
+            dev = self._device
+            self._aug_tables = dict(
+                maxmin=maxmin, maxmin_offset=torch.tensor(mm_off, dtype=torch.int64, device=dev),
+                frame_off=torch.tensor(frame_off, dtype=torch.int32, device=dev), starts=torch.tensor(starts, dtype=torch.int32, device=dev),
+                cells=(torch.cat(cells) if cells and starts[-1] > 0 else torch.zeros(1, dtype=torch.int32)).to(dev),
+                max_cells=max(int(t.hf.numel()) for t in ts))
+        return self._aug_tables
+
+    def _draw_box_aug_records(self, n):
+        """The draws of _box_hf_augmentation (:304-325) and add_boxes_to_hf2 (terrain_util.py:861-914) for n windows, window
+        after window: Python `random` for the schedule, torch's CPU generator for the boxes (upstream draws the boxes on
+        the sampler's device; here always on the host, so a CPU run of the reference with the same seeds is reproduced).
+        -> rec_i [n,8] int32, rec_f [n, 1 + 7 max_num_boxes] fp32 (layout: include/parc_b200_sampler.h)."""
+        nbmax = max(int(self._max_num_boxes), 1)
+        rec_i = np.full((n, _lib.AUG_REC_INTS), -1, dtype=np.int32)
+        rec_f = np.zeros((n, 1 + _lib.AUG_BOX_FLOATS * nbmax), dtype=np.float32)
+        shape = torch.tensor([float(self._grid_dim_x), float(self._grid_dim_y)], dtype=torch.float32)
+        ones = torch.ones(self._grid_dim_x, self._grid_dim_y)
+        span = self._max_h - self._min_h
+        for i in range(n):
+            change = random.random() < self._hf_change_height_chance
+            rec_i[i, 0] = int(change)
+            if change:
+                rec_f[i, 0] = random.random() * span + self._min_h
+            use = [random.random() < self._hf_maxpool_chance, random.random() < self._hf_maxpool_chance,
+                   random.random() < self._hf_maxpool_chance]
+            order = [0, 1, 2]                      # PARC_POOL_2D, _X, _Y = maxpool_hf, maxpool_hf_1d_x, maxpool_hf_1d_y (:314-316)
+            random.shuffle(order)
+            for k in range(3):
+                rec_i[i, 2 + 2 * k] = 0
+                if use[k]:
+                    rec_i[i, 1 + 2 * k] = order[k]
+                    rec_i[i, 2 + 2 * k] = random.randint(0, self._hf_max_maxpool_size)
+            nb = random.randint(0, self._max_num_boxes)
+            rec_i[i, 7] = nb
+            for b in range(nb):
+                center = torch.rand(size=(2,), dtype=torch.float32) * shape
+                side = torch.rand(size=(2,), dtype=torch.float32) * (self._box_max_len - self._box_min_len) + self._box_min_len
+                angle = (torch.rand(1) * (2.0 * torch.pi - 0.0) + 0.0) * ones          # upstream takes cos / sin over the whole grid
+                h = torch.rand(1) * span + self._min_h
+                o = 1 + _lib.AUG_BOX_FLOATS * b
+                rec_f[i, o:o + 7] = [float(center[0]), float(center[1]), float(side[0]), float(side[1]),
+                                     float(torch.cos(angle)[0, 0]), float(torch.sin(angle)[0, 0]), float(h[0])]
+        return torch.from_numpy(rec_i), torch.from_numpy(rec_f)
+
+    def _augment_hfs(self, motion_ids, motion_start_times, n, canon, hfs, hf_aug_records, hf_noise):
+        mode = self._hf_augmentation_mode
+        if mode == HFAugmentationMode.NONE:
+            return
+        tb = self._augmenter_tables()
+        dev, p = self._device, _lib.ptr
+        aug = _lib.HfAugStruct()
+        aug.mode, aug.max_terrain_cells, aug.timestep = mode.value, tb["max_cells"], self._timestep
+        aug.hf_maxmin, aug.maxmin_offset = p(tb["maxmin"]), p(tb["maxmin_offset"])
+        aug.mask_frame_off, aug.mask_start, aug.mask_cells = p(tb["frame_off"]), p(tb["starts"]), p(tb["cells"])
+        keep = []
+        if mode == HFAugmentationMode.NOISE:
+            if hf_noise is None:
+                hf_noise = torch.rand(n, self._grid_dim_x, self._grid_dim_y, device=dev, dtype=torch.float32)     # rand_like(hf), :328
+            hf_noise = hf_noise.to(device=dev, dtype=torch.float32).contiguous()
+            assert hf_noise.shape == (n, self._grid_dim_x, self._grid_dim_y)
+            aug.noise = p(hf_noise)
+            keep.append(hf_noise)
+        else:
+            rec_i, rec_f = self._draw_box_aug_records(n) if hf_aug_records is None else hf_aug_records
+            rec_i = rec_i.to(device=dev, dtype=torch.int32).contiguous()
+            rec_f = rec_f.to(device=dev, dtype=torch.float32).contiguous()
+            assert rec_i.shape == (n, _lib.AUG_REC_INTS) and rec_f.shape[0] == n and (rec_f.shape[1] - 1) % _lib.AUG_BOX_FLOATS == 0
+            aug.max_boxes = (rec_f.shape[1] - 1) // _lib.AUG_BOX_FLOATS
+            aug.rec_i, aug.rec_f = p(rec_i), p(rec_f)
+            keep += [rec_i, rec_f]
+        _lib.check(_lib.lib().parc_b200_mdm_augment_hfs(p(self._terrains_device()), self._cfg, aug, p(motion_ids), p(motion_start_times), n,
+                                                       p(self._generic_heightmap), p(canon), p(hfs), _lib.stream_ptr(dev)))
+        self._last_aug_inputs = keep                      # alive until the next call (the launch is asynchronous)
+
     def _sample_motion_future_times(self, motion_ids, start_times, future_window_min, future_window_max):
         """:133-144"""
         motion_full_lengths = self._mlib.get_motion_length(motion_ids)
@@ -158,10 +266,11 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
         return torch.rand_like(start_times) * remaining_time + start_times + future_window_min
 
     def sample_motion_data(self, motion_ids=None, num_samples=None, motion_start_times=None, ret_hf_obs=True, ret_target_info=True,
-                           future_times=None, future_pos_noise=None):
+                           future_times=None, future_pos_noise=None, hf_aug_records=None, hf_noise=None):
         """:197-302. `future_times` [n] / `future_pos_noise` [n,3] (standard normal) replace the draws of
         _sample_target_info (:146-160) when given (parity tests); otherwise they are drawn from torch's generator
-        on the device in the reference's order."""
+        on the device in the reference's order. Likewise `hf_aug_records` = (rec_i, rec_f) / `hf_noise` [n,gx,gy] replace
+        the augmenter's draws (_draw_box_aug_records / rand_like)."""
         if motion_ids is None:
             assert num_samples is not None
             motion_ids = self._mlib.sample_motions(num_samples)
@@ -174,6 +283,11 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
         motion_start_times = motion_start_times.to(device=dev, dtype=f32).contiguous()
         n, T, J = num_samples, self._seq_len, self._kin_char_model.get_num_joints()
         Cn = self._mlib._frame_contacts.shape[-1]
+        if ret_hf_obs and self._use_hf_augmentation and self._hf_augmentation_mode == HFAugmentationMode.MAXPOOL_AND_BOXES \
+                and hf_aug_records is None:
+            hf_aug_records = self._draw_box_aug_records(n)          # get_hfs_from_data (:226) draws before _sample_target_info (:297)
+        if ret_hf_obs and self._use_hf_augmentation and self._hf_augmentation_mode == HFAugmentationMode.NOISE and hf_noise is None:
+            hf_noise = torch.rand(n, self._grid_dim_x, self._grid_dim_y, device=dev, dtype=f32)
         if ret_target_info:
             if future_times is None:
                 future_times = self._sample_motion_future_times(motion_ids, motion_start_times, self._future_window_min,
@@ -200,6 +314,8 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
             p(root_pos), p(root_rot), p(joint_pos), p(joint_rot), p(contacts), p(hfs), p(fpos), p(frot), p(canon),
             _lib.stream_ptr(dev)))
         self._last_canon = canon
+        if ret_hf_obs and self._use_hf_augmentation:
+            self._augment_hfs(motion_ids, motion_start_times, n, canon, hfs, hf_aug_records, hf_noise)
         motion_ret = dict()
         for frame_type in self._frame_components:
             if frame_type == MDMFrameType.ROOT_POS:
@@ -212,6 +328,12 @@ class MDMHeightfieldContactMotionSampler(MotionSampler):
                 motion_ret[MDMFrameType.JOINT_ROT] = joint_rot
             if frame_type == MDMFrameType.CONTACTS:
                 motion_ret[MDMFrameType.CONTACTS] = contacts
+            if frame_type == MDMFrameType.FLOOR_HEIGHTS:            # :267-278, [n, n, T, 1] as upstream
+                assert ret_hf_obs
+                fh = e(n, n, T)
+                _lib.check(_lib.lib().parc_b200_mdm_floor_heights(self._cfg, float(self._dx), p(hfs), p(root_pos), n, p(fh),
+                                                                 _lib.stream_ptr(dev)))
+                motion_ret[MDMFrameType.FLOOR_HEIGHTS] = fh.unsqueeze(-1)
         if ret_hf_obs or ret_target_info:
             ret = [motion_ret]
             if ret_hf_obs:
