@@ -41,6 +41,8 @@ typedef struct {
     int32_t point_start[PARC_MAX_BODIES + 1];       /* body b owns points [point_start[b], point_start[b+1]) */
     int32_t contact_col[PARC_MAX_BODIES];           /* column of `contacts` for body b, or -1 (:575-579) */
     int32_t num_contact_cols;                       /* trailing dim of `contacts`; sliding needs == num_bodies (:608) */
+    int32_t whole_terrain;                          /* 0: motion_terrain_contact_loss_localized, per-frame windows (:507-551);
+                                                     * 1: motion_terrain_contact_loss (:207-423), every point against every cell */
 } parc_opt_config_t;
 
 /* terrain_util.points_hf_sdf without `radius`: points [B,N,3], hf [B,X,Y], min_box_center [B,2]

@@ -25,7 +25,7 @@ def sd_box(p, half):
     return outside + inside
 
 
-def points_hf_sdf(points, hf, min_box_center, dxdy, base_z=-10.0, inverted=True):
+def points_hf_sdf(points, hf, min_box_center, dxdy, base_z=-10.0, inverted=True, radius=None):
     """terrain_util.py:1736-1794. points [B,N,3], hf [B,X,Y], min_box_center [B,2], dxdy [2] -> [B,N].
     One axis-aligned box per cell, from base_z up to the cell height (solid terrain) or, inverted,
     from the cell height up to -base_z (the air above it; the result is negated), min over cells."""
@@ -43,7 +43,10 @@ def points_hf_sdf(points, hf, min_box_center, dxdy, base_z=-10.0, inverted=True)
     centers = torch.stack([cx, cy, cz], dim=-1).reshape(B, X * Y, 3)
     half = torch.stack([torch.full_like(hz, float(dxdy[0]) / 2.0), torch.full_like(hz, float(dxdy[1]) / 2.0), hz], dim=-1).reshape(B, X * Y, 3)
     rel = points[:, :, None, :] - centers[:, None, :, :]
-    sd = sd_box(rel, half[:, None, :, :]).min(dim=-1)[0]
+    sd = sd_box(rel, half[:, None, :, :])
+    if radius is not None:
+        sd = sd - radius                    # geom_util.sdRoundBox (geom_util.py:115-122): columns with rounded edges
+    sd = sd.min(dim=-1)[0]
     return -sd if inverted else sd
 
 
@@ -68,10 +71,11 @@ def frame_patches(points_xy, hf, min_point, dxdy):
 
 def motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, tgt_root_pos, tgt_root_rot, tgt_joint_dof,
                 src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts, weights,
-                contact_body_of_body=None, body_constraints=None, geoms=None):
+                contact_body_of_body=None, body_constraints=None, geoms=None, localized=True):
     """motion_terrain_contact_loss_localized (:426-656). `body_constraints` (:581-609): None or a list of records
     (body, start_frame, end_frame, point[3]); `geoms[b]` = ("SPHERE", radius, offset[3]) | ("BOX", dims[3]) | anything else
-    (ignored), the first geom of body b. `weights` =
+    (ignored), the first geom of body b. `localized=False` is motion_terrain_contact_loss (:207-423): the whole terrain for
+    every frame instead of the per-frame windows. `weights` =
     [w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
     w_body_constraints, w_jerk, max_jerk]. body_points [Np,3] concatenated in body order with
     body_point_counts [J]. -> (loss, terms [9] in LOSS_NAMES order); differentiable in the tgt_* tensors."""
@@ -93,6 +97,8 @@ def motion_loss(model, body_points, body_point_counts, hf, min_point, dxdy, tgt_
     body_of_point = torch.repeat_interleave(torch.arange(J), torch.as_tensor(body_point_counts))
     world = O.quat_rotate(body_rot[:, body_of_point], body_points[None].expand(T, -1, -1)) + body_pos[:, body_of_point]
     start, (px, py) = frame_patches(world[..., :2].detach(), hf, min_point, dxdy)
+    if not localized:
+        start, (px, py) = torch.zeros_like(start), (int(hf.shape[0]), int(hf.shape[1]))
     ix = start[:, 0, None] + torch.arange(px)[None]
     iy = start[:, 1, None] + torch.arange(py)[None]
     patches = hf[ix[:, :, None], iy[:, None, :]]

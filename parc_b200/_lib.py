@@ -197,6 +197,7 @@ class OptConfigStruct(C.Structure):
         ("point_start", C.c_int32 * (MAX_BODIES + 1)),
         ("contact_col", C.c_int32 * MAX_BODIES),
         ("num_contact_cols", C.c_int32),
+        ("whole_terrain", C.c_int32),
     ]
 
 

@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_pose_kernel(cons
             int g1x = (int)ceilf(__fmul_rn(__fsub_rn(__fadd_rn(hix, ter.dx * 2.0f), mpx), idx));
             int g1y = (int)ceilf(__fmul_rn(__fsub_rn(__fadd_rn(hiy, ter.dy * 2.0f), mpy), idy));
             g0x = max(g0x, 0); g0y = max(g0y, 0); g1x = min(g1x, ter.X - 1); g1y = min(g1y, ter.Y - 1);
+            if (cfg.whole_terrain) { g0x = 0; g0y = 0; g1x = ter.X - 1; g1y = ter.Y - 1; }       // motion_terrain_contact_loss (:273-276)
             ws.gmin[i * 2] = g0x; ws.gmin[i * 2 + 1] = g0y;
             atomicMax(&ws.patch[b * 2], g1x - g0x + 1);
             atomicMax(&ws.patch[b * 2 + 1], g1y - g0y + 1);

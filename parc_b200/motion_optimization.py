@@ -152,7 +152,7 @@ def compute_approx_body_constraints(root_pos, root_rot, joint_rot, contacts, cha
 
 def build_opt_config(char_model: KinCharModel, body_points: List[torch.Tensor], num_contact_cols: int, w_root_pos, w_root_rot,
                      w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk,
-                     base_z=-10.0) -> _lib.OptConfigStruct:
+                     base_z=-10.0, whole_terrain=False) -> _lib.OptConfigStruct:
     J = char_model.get_num_joints()
     assert len(body_points) == J, "body_points needs one tensor per body"
     cfg = _lib.OptConfigStruct()
@@ -174,6 +174,7 @@ def build_opt_config(char_model: KinCharModel, body_points: List[torch.Tensor], 
         if char_model.is_contact_body(name):
             cfg.contact_col[b] = int(char_model.get_contact_body_id(name))
     cfg.num_contact_cols = int(num_contact_cols)
+    cfg.whole_terrain = int(bool(whole_terrain))
     return cfg
 
 
@@ -219,10 +220,11 @@ class _MotionLossFn(torch.autograd.Function):
 def motion_loss_batched(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels,
                         src_body_rot_vels, contacts, hf, min_point, dxdy, body_points: List[torch.Tensor], char_model: KinCharModel,
                         w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints,
-                        w_jerk, max_jerk, body_constraints=None):
+                        w_jerk, max_jerk, body_constraints=None, localized=True):
     """B independent motions of T frames: all motion tensors carry a leading [B, T(-1), ...]; `hf` is
     [B, X, Y] with `min_point` [B, 2], or one shared [X, Y] / [2]. `body_constraints`: None, a PackedBodyConstraints, or a
-    list with one entry per motion (None or the reference's list of BodyConstraint lists per body).
+    list with one entry per motion (None or the reference's list of BodyConstraint lists per body). `localized`: per-frame
+    heightfield windows (motion_terrain_contact_loss_localized) or every cell of the terrain (motion_terrain_contact_loss).
     -> (loss [B], terms [B, 9]) with autograd to the three tgt_* tensors."""
     dev = tgt_root_pos.device
     assert tgt_root_pos.dim() == 3 and tgt_root_rot.shape == tgt_root_pos.shape and tgt_joint_dof.dim() == 3
@@ -231,7 +233,7 @@ def motion_loss_batched(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos,
     assert src_joint_rot.shape == (B, T, J - 1, 4) and src_body_vels.shape == (B, T - 1, J, 3) and src_body_rot_vels.shape == (B, T - 1, J)
     assert contacts.shape[:2] == (B, T)
     cfg = build_opt_config(char_model, body_points, contacts.shape[-1], w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration,
-                           w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk)
+                           w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk, whole_terrain=not localized)
     hf = hf.to(device=dev, dtype=torch.float32).contiguous()
     min_point = min_point.to(device=dev, dtype=torch.float32).contiguous()
     if hf.dim() == 2:
@@ -253,7 +255,8 @@ def motion_terrain_contact_loss_localized(tgt_root_pos, tgt_root_rot, tgt_joint_
                                           src_body_vels, src_body_rot_vels, contacts, terrain, body_points: List[torch.Tensor],
                                           char_model: KinCharModel, w_root_pos: float, w_root_rot: float, w_joint_rot: float,
                                           w_smoothness: float, w_penetration: float, w_contact: float, w_sliding: float,
-                                          w_body_constraints: float, w_jerk: float, body_constraints: list, max_jerk: float):
+                                          w_body_constraints: float, w_jerk: float, body_constraints: list, max_jerk: float,
+                                          _localized=True):
     """motion_optimization.py:426-656, one motion of T frames. Returns (loss, {LossType: float}). `body_constraints` is the
     reference's list (one list of BodyConstraint per body), None, or a PackedBodyConstraints made once for the whole run."""
     if body_constraints is not None and not isinstance(body_constraints, PackedBodyConstraints):
@@ -263,7 +266,20 @@ def motion_terrain_contact_loss_localized(tgt_root_pos, tgt_root_rot, tgt_joint_
                                       u(src_joint_rot), u(src_body_vels), u(src_body_rot_vels), u(contacts), terrain.hf,
                                       terrain.min_point, terrain.dxdy, body_points, char_model, w_root_pos, w_root_rot, w_joint_rot,
                                       w_smoothness, w_penetration, w_contact, w_sliding, w_body_constraints, w_jerk, max_jerk,
-                                      body_constraints=body_constraints)
+                                      body_constraints=body_constraints, localized=_localized)
     vals = terms[0].tolist()       # the reference also reads every term back with .item() (:626-643)
     losses = {t: vals[t.value] for t in list(LossType)[:9]}
     return loss[0], losses
+
+
+def motion_terrain_contact_loss(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat, src_joint_rot,
+                                src_body_vels, src_body_rot_vels, contacts, terrain, body_points: List[torch.Tensor],
+                                char_model: KinCharModel, w_root_pos: float, w_root_rot: float, w_joint_rot: float,
+                                w_smoothness: float, w_penetration: float, w_contact: float, w_sliding: float,
+                                w_body_constraints: float, w_jerk: float, body_constraints: list, max_jerk: float):
+    """motion_optimization.py:207-423: the same loss with every body point measured against EVERY cell of the terrain
+    instead of a per-frame window (the two differ when the nearest column lies outside the window)."""
+    return motion_terrain_contact_loss_localized(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_root_pos, src_root_rot_quat, src_joint_rot,
+                                                 src_body_vels, src_body_rot_vels, contacts, terrain, body_points, char_model, w_root_pos,
+                                                 w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
+                                                 w_body_constraints, w_jerk, body_constraints, max_jerk, _localized=False)

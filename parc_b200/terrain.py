@@ -150,14 +150,17 @@ class _PointsHfSdfFn(torch.autograd.Function):
 def points_hf_sdf(points, hf, hf_min_box_center, hf_dxdy, base_z=-10.0, inverted=True, radius=None):
     """terrain_util.points_hf_sdf (PARC/util/terrain_util.py:1736-1794): signed distance of points [B,N,3] to the
     box-per-cell heightfield hf [B,X,Y] whose (0,0) cell centre is hf_min_box_center [B,2]; differentiable in
-    `points`. `radius` (rounded boxes) is not supported."""
+    `points`. `radius` (:1782-1785, geom_util.sdRoundBox = sdBox - radius): every column's distance shrinks by the same
+    amount, so the minimum over the columns shifts by exactly `radius` (the sign flips with `inverted`)."""
     assert points.dim() == 3 and hf.dim() == 3 and hf_min_box_center.dim() == 2 and hf_dxdy.dim() == 1
-    if radius is not None:
-        raise NotImplementedError("points_hf_sdf: radius is not supported by the CUDA kernel")
     dev = points.device
     hf = hf.to(device=dev, dtype=torch.float32).contiguous()
     mc = hf_min_box_center.to(device=dev, dtype=torch.float32).contiguous()
-    return _PointsHfSdfFn.apply(points, hf, mc, float(hf_dxdy[0]), float(hf_dxdy[1]), float(base_z), bool(inverted))
+    sd = _PointsHfSdfFn.apply(points, hf, mc, float(hf_dxdy[0]), float(hf_dxdy[1]), float(base_z), bool(inverted))
+    if radius is not None:
+        assert isinstance(radius, float) and radius > 0.0          # :1783-1784
+        sd = sd + radius if inverted else sd - radius
+    return sd
 
 
 # ---- motion-aware terrain post-processing (SURVEY.md section 8f rank 4) -----------------------------------------

@@ -74,7 +74,10 @@ def main():
     pts[..., 2] = -1.5 + 3.0 * pts[..., 2]
     sd_inv = rterr.points_hf_sdf(pts, hf, min_c, dxdy, base_z=-10.0, inverted=True)
     sd_pos = rterr.points_hf_sdf(pts, hf, min_c, dxdy, base_z=-10.0, inverted=False)
-    npz("ref_hf_sdf.npz", points=pts, hf=hf, min_box_center=min_c, dxdy=dxdy, sd_inverted=sd_inv, sd_solid=sd_pos)
+    sd_inv_r = rterr.points_hf_sdf(pts, hf, min_c, dxdy, base_z=-10.0, inverted=True, radius=0.07)      # rounded columns (:1782-1785)
+    sd_pos_r = rterr.points_hf_sdf(pts, hf, min_c, dxdy, base_z=-10.0, inverted=False, radius=0.07)
+    npz("ref_hf_sdf.npz", points=pts, hf=hf, min_box_center=min_c, dxdy=dxdy, sd_inverted=sd_inv, sd_solid=sd_pos,
+        sd_inverted_r=sd_inv_r, sd_solid_r=sd_pos_r, radius=np.float64(0.07))
 
     # ---- motion_terrain_contact_loss_localized ----------------------------------------------------
     d = rfio.load_ms_file(ref_import.clip("dec2024_teaser_717_1_opt_dm.pkl"), device="cpu")
@@ -114,6 +117,24 @@ def main():
                                                            "w_contact", "w_sliding", "w_body_constraints", "w_jerk", "max_jerk")])
         out[tag + "_g_root_pos"], out[tag + "_g_root_rot"], out[tag + "_g_joint_dof"] = p[0].grad, p[1].grad, p[2].grad
         print(tag, float(loss), {k.name: round(v, 6) if isinstance(v, float) else v for k, v in losses.items()})
+    # ---- motion_terrain_contact_loss (:207-423): every cell of the terrain instead of per-frame windows; the root is
+    # raised so that for many points a neighbouring column is nearer than the ground below
+    p = [t.clone().requires_grad_(True) for t in (tgt_root_pos + torch.tensor([0.0, 0.0, 0.9]), tgt_root_rot, tgt_joint_dof)]
+    loss, losses = ropt.motion_terrain_contact_loss(
+        p[0], p[1], p[2], src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts, terrain,
+        body_points, model, body_constraints=None, **KIN_GEN_WEIGHTS)
+    loss.backward()
+    loc, loc_losses = ropt.motion_terrain_contact_loss_localized(
+        p[0].detach(), p[1].detach(), p[2].detach(), src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels,
+        contacts, terrain, body_points, model, body_constraints=None, **KIN_GEN_WEIGHTS)
+    out["whole_tgt_root_pos"] = p[0].detach()
+    out["whole_loss"] = loss.detach()
+    out["whole_terms"] = np.array([float(losses.get(t, 0.0)) for t in list(ropt.LossType)[:9]], dtype=np.float64)
+    out["whole_localized_terms"] = np.array([float(loc_losses.get(t, 0.0)) for t in list(ropt.LossType)[:9]], dtype=np.float64)
+    out["whole_weights"] = out["full_weights"]
+    out["whole_g_root_pos"], out["whole_g_root_rot"], out["whole_g_joint_dof"] = p[0].grad, p[1].grad, p[2].grad
+    print("whole", float(loss), "localized on the same input", float(loc), out["whole_terms"][4:6], out["whole_localized_terms"][4:6])
+
     # ---- body constraints ------------------------------------------------------------------------
     def flatten(bc):
         rows = [(b, c.start_frame_idx, c.end_frame_idx, c.constraint_point) for b, lst in enumerate(bc) for c in lst]

@@ -39,6 +39,9 @@ def test_points_hf_sdf_matches_reference_values_and_oracle_gradient():
         so = OO.points_hf_sdf(po, _t(d["hf"]), _t(d["min_box_center"]), _t(d["dxdy"]), -10.0, inverted)
         (so * w.cpu()).sum().backward()
         torch.testing.assert_close(p.grad.cpu(), po.grad, rtol=1e-4, atol=1e-5)
+        sd_r = points_hf_sdf(_t(d["points"], DEV), _t(d["hf"], DEV), _t(d["min_box_center"], DEV), _t(d["dxdy"]), -10.0, inverted,
+                             radius=float(d["radius"]))                       # rounded columns (terrain_util.py:1782-1785)
+        torch.testing.assert_close(sd_r.cpu(), _t(d[key + "_r"]), rtol=1e-5, atol=2e-6)
 
 
 def _constraint_lists(d, tag, J, dev):
@@ -77,7 +80,7 @@ def test_motion_loss_matches_reference_golden(tag):
     got = np.array([losses[t] for t in list(LossType)[:9]])
     assert (got[7] > 1.0) == tag.startswith("cons")
     np.testing.assert_allclose(got, d[tag + "_terms"], rtol=2e-5, atol=2e-6)
-    np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
+    np.testing.assert_allclose(float(loss.detach()), float(d[tag + "_loss"]), rtol=2e-5)
     for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
         ref = d[tag + k]
         np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))   # gradients <= 1e-4 relative (of the tensor scale)
@@ -98,6 +101,62 @@ def test_compute_approx_body_constraints_matches_reference():
     assert got == want and len(want) >= 3
     pts = torch.stack([c.constraint_point for lst in bc for c in lst]).cpu().numpy()
     np.testing.assert_allclose(pts, d["cons_point"], rtol=0, atol=1e-5)
+
+
+def test_whole_terrain_motion_loss_matches_reference_golden():
+    """motion_terrain_contact_loss (motion_optimization.py:207-423) through the mirror of the same name."""
+    from parc_b200.motion_optimization import LossType, motion_terrain_contact_loss
+    d = H.load_npz("ref_opt_loss.npz")
+    model = H.product_model(DEV)
+    pts, _ = _body_points(DEV)
+    terrain = H.product_terrain(_t(d["hf"]), d["min_point"], float(d["dxdy"][0]), DEV)
+    p = [_t(d[k], DEV).clone().requires_grad_(True) for k in ("whole_tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+    loss, losses = motion_terrain_contact_loss(
+        p[0], p[1], p[2], _t(d["src_root_pos"], DEV), _t(d["src_root_rot_quat"], DEV), _t(d["src_joint_rot"], DEV),
+        _t(d["src_body_vels"], DEV), _t(d["src_body_rot_vels"], DEV), _t(d["contacts"], DEV), terrain, pts, model,
+        body_constraints=None, **KIN_GEN)
+    loss.backward()
+    got = np.array([losses[t] for t in list(LossType)[:9]])
+    np.testing.assert_allclose(got, d["whole_terms"], rtol=2e-5, atol=2e-6)
+    np.testing.assert_allclose(float(loss.detach()), float(d["whole_loss"]), rtol=2e-5)
+    for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
+        ref = d["whole" + k]
+        np.testing.assert_allclose(g.grad.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))
+
+
+def test_whole_terrain_and_windowed_losses_match_their_oracles():
+    """32x32 terrains with 6 m walls every 7th row and the characters lifted 1.6 m, windowed and whole-terrain evaluation,
+    each against the oracle in the same mode (on these inputs the two agree to rounding: a motion's frames share its
+    largest window, which already holds every column that can be nearest)."""
+    from parc_b200.motion_optimization import motion_loss_batched
+    B, T = 2, 30
+    d, dx = _synthetic_batch(B, T, seed=13)
+    d["tgt_root_pos"] = d["tgt_root_pos"] + torch.tensor([0.0, 0.0, 1.6])
+    d["hf"][:, ::7, :] += 6.0
+    model = H.product_model(DEV)
+    pts, bp = _body_points(DEV)
+    om = H.oracle_model()
+    w = [KIN_GEN[k] for k in ("w_root_pos", "w_root_rot", "w_joint_rot", "w_smoothness", "w_penetration", "w_contact", "w_sliding",
+                              "w_body_constraints", "w_jerk", "max_jerk")]
+    dxdy = torch.tensor([dx, dx])
+    names = ("src_root_pos", "src_root_rot_quat", "src_joint_rot", "src_body_vels", "src_body_rot_vels", "contacts")
+    got = {}
+    for localized in (True, False):
+        p = [d[k].to(DEV).clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+        loss, terms = motion_loss_batched(p[0], p[1], p[2], *[d[k].to(DEV) for k in names], d["hf"].to(DEV), d["min_point"].to(DEV), dxdy, pts,
+                                          model, localized=localized, **KIN_GEN)
+        loss.sum().backward()
+        got[localized] = terms.cpu()
+        for b in range(B):
+            po = [d[k][b].clone().requires_grad_(True) for k in ("tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+            lo, to = OO.motion_loss(om, _t(bp["points"]), bp["counts"], d["hf"][b], d["min_point"][b], dxdy, po[0], po[1], po[2],
+                                    *[d[k][b] for k in names], w, localized=localized)
+            lo.backward()
+            np.testing.assert_allclose(terms[b].cpu().numpy(), to.numpy(), rtol=3e-5, atol=3e-6)
+            for g, go in zip(p, po):
+                ref = go.grad.numpy()
+                np.testing.assert_allclose(g.grad[b].cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * float(np.abs(ref).max()))
+    assert float(got[False][:, 4].min()) > 1.0 and float(got[False][:, 5].min()) > 1.0         # both terrain terms active
 
 
 def _synthetic_batch(B, T, seed):

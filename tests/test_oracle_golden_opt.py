@@ -16,6 +16,8 @@ def test_points_hf_sdf_matches_reference():
     for inverted, key in ((True, "sd_inverted"), (False, "sd_solid")):
         got = OO.points_hf_sdf(_t(d["points"]), _t(d["hf"]), _t(d["min_box_center"]), _t(d["dxdy"]), -10.0, inverted)
         torch.testing.assert_close(got, _t(d[key]), rtol=1e-6, atol=1e-6)
+        got = OO.points_hf_sdf(_t(d["points"]), _t(d["hf"]), _t(d["min_box_center"]), _t(d["dxdy"]), -10.0, inverted, radius=float(d["radius"]))
+        torch.testing.assert_close(got, _t(d[key + "_r"]), rtol=1e-6, atol=1e-6)
 
 
 def test_motion_loss_and_gradients_match_reference():
@@ -29,10 +31,26 @@ def test_motion_loss_and_gradients_match_reference():
                                      _t(d["src_body_rot_vels"]), _t(d["contacts"]), d[tag + "_weights"])
         loss.backward()
         np.testing.assert_allclose(terms.numpy(), d[tag + "_terms"], rtol=2e-5, atol=1e-6)
-        np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
+        np.testing.assert_allclose(float(loss.detach()), float(d[tag + "_loss"]), rtol=2e-5)
         for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
             ref = d[tag + k]
             np.testing.assert_allclose(g.grad.numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
+
+
+def test_whole_terrain_motion_loss_matches_reference():
+    """motion_terrain_contact_loss (motion_optimization.py:207-423): no per-frame windows."""
+    d = H.load_npz("ref_opt_loss.npz")
+    bp = H.load_npz("ref_body_points.npz")
+    model = H.oracle_model()
+    p = [_t(d[k]).clone().requires_grad_(True) for k in ("whole_tgt_root_pos", "tgt_root_rot", "tgt_joint_dof")]
+    loss, terms = OO.motion_loss(model, _t(bp["points"]), bp["counts"], _t(d["hf"]), _t(d["min_point"]), _t(d["dxdy"]), p[0], p[1], p[2],
+                                 _t(d["src_root_pos"]), _t(d["src_root_rot_quat"]), _t(d["src_joint_rot"]), _t(d["src_body_vels"]),
+                                 _t(d["src_body_rot_vels"]), _t(d["contacts"]), d["whole_weights"], localized=False)
+    loss.backward()
+    np.testing.assert_allclose(terms.numpy(), d["whole_terms"], rtol=2e-5, atol=1e-6)
+    for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
+        ref = d["whole" + k]
+        np.testing.assert_allclose(g.grad.numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
 
 
 def _geoms(d):
@@ -58,7 +76,7 @@ def test_motion_loss_with_body_constraints_matches_reference():
         loss.backward()
         assert d[tag + "_terms"][7] > 1.0
         np.testing.assert_allclose(terms.numpy(), d[tag + "_terms"], rtol=2e-5, atol=1e-6)
-        np.testing.assert_allclose(float(loss), float(d[tag + "_loss"]), rtol=2e-5)
+        np.testing.assert_allclose(float(loss.detach()), float(d[tag + "_loss"]), rtol=2e-5)
         for g, k in zip(p, ("_g_root_pos", "_g_root_rot", "_g_joint_dof")):
             ref = d[tag + k]
             np.testing.assert_allclose(g.grad.numpy(), ref, rtol=1e-3, atol=1e-3 * float(np.abs(ref).max()))
