@@ -18,6 +18,7 @@
 //   E  copy-out: cp.async.bulk (TMA) of each staged observation row and of the ref_* blocks, issued right after phase C
 //      so that the copies run under D / H; plain stores for partial tiles, row subsets and strided ref views
 #include <string.h>
+#include <type_traits>
 
 #include "parc_common.cuh"
 #include "parc_lanes.cuh"
@@ -33,7 +34,7 @@
 #define PARC_LATTICE_ROWS 8                   // lattice ray sets: lattice rows (= independent gathers) per lane and loop iteration
 #endif
 #ifndef PARC_HEIGHT_SPLIT
-#define PARC_HEIGHT_SPLIT 1                   // an env's sample points are handed out in this many pieces (load balance across the warps)
+#define PARC_HEIGHT_SPLIT 2                   // an env's sample points are handed out in this many pieces (load balance across the warps)
 #endif
 #ifndef PARC_PREFETCH_FRAMES
 #define PARC_PREFETCH_FRAMES 0                // 1: a separate stage prefetches the frame records before the pose loop (measured slower: the
@@ -59,6 +60,17 @@
 #ifndef PARC_STAGGER_NS
 #define PARC_STAGGER_NS 0                     // > 0: the second block of every SM's first wave starts this much later, so that the
 #endif                                        //      latency-bound phases of an SM's two resident blocks do not coincide
+#ifndef PARC_TAR_FAST_MATH
+#define PARC_TAR_FAST_MATH 0                  // 1 (measured: no gain, +0.3 %): the target poses (observation only, 1e-5 tolerance) use FMA-contracted quaternion products / rotations;
+#endif                                        //    the reference and character poses, which feed the termination flags, keep the reference's rounding
+#ifndef PARC_CELL_MAGIC
+#define PARC_CELL_MAGIC 1                     // 1: a sample's cell index is rounded by a magic-number addition (FMA pipe) instead of F2I (XU pipe)
+#endif
+#ifndef PARC_POSE_TAIL_COPIES
+#define PARC_POSE_TAIL_COPIES 1               // 1: the copies only the reference pose (velocity record) and the character pose (dof velocities, contact
+#endif                                        //    flags) make are asked for at the top of the pose and done after its joint loop with their loads batched;
+                                              //    0: done up front in rolled loops (each load's latency then sits on the block's critical path: those two warps
+                                              //    finish phase B last)
 #ifndef PARC_BULK_ROWS
 #define PARC_BULK_ROWS 1                      // 1: the tile's ref_* blocks leave through cp.async.bulk where alignment allows
 #endif
@@ -72,8 +84,10 @@ namespace parc {
 #ifdef PARC_STEP_TIMING
 __device__ long long g_step_stamps[16 * 16384];
 #define PARC_STAMP(k) do { if (threadIdx.x == 0 && blockIdx.x < 16384) g_step_stamps[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+#define PARC_STAMP_T(k, t) do { if (threadIdx.x == (t) && blockIdx.x < 16384) g_step_stamps[blockIdx.x * 16 + (k)] = clock64(); } while (0)
 #else
 #define PARC_STAMP(k) do { } while (0)
+#define PARC_STAMP_T(k, t) do { } while (0)
 #endif
 
 #ifndef PARC_STEP_TILE
@@ -402,6 +416,26 @@ __device__ __forceinline__ void tan_norm_exact(Quat q, float* __restrict__ o) {
     }
 }
 
+// FMA-contracted versions for values that only feed the observation (tolerance 1e-5, no flag or index depends on them)
+__device__ __forceinline__ Quat quat_mul_fast(Quat a, Quat b) {
+    return make_quat(fmaf(a.w, b.x, fmaf(a.x, b.w, fmaf(a.y, b.z, -a.z * b.y))), fmaf(a.w, b.y, fmaf(a.y, b.w, fmaf(a.z, b.x, -a.x * b.z))),
+                     fmaf(a.w, b.z, fmaf(a.z, b.w, fmaf(a.x, b.y, -a.y * b.x))), fmaf(a.w, b.w, -fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z))));
+}
+__device__ __forceinline__ Vec3 quat_rotate_fast(Quat q, Vec3 v) {      // v + 2 (w c + q_v x c), c = q_v x v
+    const float cx = fmaf(q.y, v.z, -q.z * v.y), cy = fmaf(q.z, v.x, -q.x * v.z), cz = fmaf(q.x, v.y, -q.y * v.x);
+    const float dx = fmaf(q.w, cx, fmaf(q.y, cz, -q.z * cy)), dy = fmaf(q.w, cy, fmaf(q.z, cx, -q.x * cz)), dz = fmaf(q.w, cz, fmaf(q.x, cy, -q.y * cx));
+    return make_vec3(fmaf(2.f, dx, v.x), fmaf(2.f, dy, v.y), fmaf(2.f, dz, v.z));
+}
+__device__ __forceinline__ void tan_norm_fast(Quat q, float* __restrict__ o) {      // R(q) x_hat, R(q) z_hat
+    const float x2 = q.x + q.x, y2 = q.y + q.y, z2 = q.z + q.z;
+    o[0] = 1.f - fmaf(q.y, y2, q.z * z2);
+    o[1] = fmaf(q.x, y2, q.w * z2);
+    o[2] = fmaf(q.x, z2, -q.w * y2);
+    o[3] = fmaf(q.x, z2, q.w * y2);
+    o[4] = fmaf(q.y, z2, -q.w * x2);
+    o[5] = 1.f - fmaf(q.x, x2, q.y * y2);
+}
+
 // (x - mn) / d for the nearest-cell index with d, 1/d uniform: q = x * rc; r = fma(-q, d, x);
 // q' = fma(r, rc, q) (Markstein) is the correctly rounded quotient for normal operands when rc is
 // the correctly rounded reciprocal; checked against div.rn by parc_b200_selftest_div.
@@ -426,8 +460,18 @@ __device__ __forceinline__ int packed_cell_ab(float2 a, float2 b, float2 g2, flo
     float2 q = __fmul2_rn(x, rd2);
     const float2 r = __ffma2_rn(q, nd2, x);
     q = __ffma2_rn(r, rd2, q);
+#if PARC_CELL_MAGIC
+    // round-half-even without the conversion unit (F2I runs on the XU pipe at a quarter of the FP32 rate, and the height samples
+    // are the only heavy user of it): q + 1.5 * 2^23 has its integer value in the low mantissa bits, rounded to nearest even by the
+    // addition itself -- exact for |q| < 2^22; beyond that the bit pattern still lands on the correct side of [0, dim - 1]
+    // (larger exponent -> large positive, smaller exponent -> negative), and NaN goes to dim - 1
+    const float2 m = __fadd2_rn(q, make_float2(12582912.0f, 12582912.0f));
+    const int ix = max(0, min(__float_as_int(m.x) - 0x4B400000, imx));
+    const int iy = max(0, min(__float_as_int(m.y) - 0x4B400000, imy));
+#else
     const int ix = max(0, min(__float2int_rn(q.x), imx));
     const int iy = max(0, min(__float2int_rn(q.y), imy));
+#endif
     return ix * dimy + iy;
 }
 __device__ __forceinline__ int packed_cell(float2 pt, float2 cs, float2 nsc, float2 g2, float2 nmn, float2 rd2, float2 nd2, int imx, int imy,
@@ -870,17 +914,21 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
                 o = refp(R.body_pos, 3 * J, el); o[0] = rpos.x; o[1] = rpos.y; o[2] = rpos.z;
             }
             // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
-            float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
-            PARC_COLD_LOOP
-            for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
-                const float4 x = ldg4(vrec + k);
-                const float xs[4] = {x.x, x.y, x.z, x.w};
+            if (PARC_POSE_TAIL_COPIES) {
+                if (part * 32 < 6 + D) asm volatile("prefetch.global.L1 [%0];" ::"l"(vrec + part * 32));
+            } else {
+                float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
+                PARC_COLD_LOOP
+                for (int k = 4 * part; k < 6 + D; k += 4 * NPART) {
+                    const float4 x = ldg4(vrec + k);
+                    const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const int kk = k + c;
-                    if (kk < 3) o_rv[kk] = xs[c];
-                    else if (kk < 6) o_rav[kk - 3] = xs[c];
-                    else if (kk < 6 + D) o_dv[kk - 6] = xs[c];
+                    for (int c = 0; c < 4; ++c) {
+                        const int kk = k + c;
+                        if (kk < 3) o_rv[kk] = xs[c];
+                        else if (kk < 6) o_rav[kk - 3] = xs[c];
+                        else if (kk < 6 + D) o_dv[kk - 6] = xs[c];
+                    }
                 }
             }
         } else if (is_tar) {
@@ -905,15 +953,23 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
                 o[6] = v.x; o[7] = v.y; o[8] = v.z; o[9] = w.x; o[10] = w.y; o[11] = w.z;
             }
             o_pose = o + 12; o_key = o + 12 + 6 * (J - 1) + D;
-            PARC_COLD_LOOP
-            for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
-            if (c_contact_info) {
-                // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+            if (PARC_POSE_TAIL_COPIES) {
+                // the rows read after the joint loop: 128-byte pieces of the dof-velocity span and of the contact-force row
+                const float* dv = env.char_dof_vel.ptr + u.e * env.char_dof_vel.row_stride;
+                if ((long long)part * 32 < (long long)D * env.char_dof_vel.elem_stride) asm volatile("prefetch.global.L1 [%0];" ::"l"(dv + part * 32));
+                if (c_contact_info && part * 32 < 3 * J)
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(env.char_contact_forces.ptr + u.e * env.char_contact_forces.row_stride + part * 32));
+            } else {
                 PARC_COLD_LOOP
-                for (int c = part; c < J; c += NPART) {
-                    const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
-                                fz = view_ld3(env.char_contact_forces, u.e, c, 2);
-                    row[L.o_charc + c] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
+                for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
+                if (c_contact_info) {
+                    // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+                    PARC_COLD_LOOP
+                    for (int c = part; c < J; c += NPART) {
+                        const float fx = view_ld3(env.char_contact_forces, u.e, c, 0), fy = view_ld3(env.char_contact_forces, u.e, c, 1),
+                                    fz = view_ld3(env.char_contact_forces, u.e, c, 2);
+                        row[L.o_charc + c] = (sqrtf(fx * fx + fy * fy + fz * fz) > cfg.contact_eps) ? 1.f : 0.f;
+                    }
                 }
             }
         }
@@ -951,6 +1007,8 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         float* o_jr = is_ref ? refp(R.joint_rot, 4 * (J - 1), el) : nullptr;
         float* o_bp = is_ref ? refp(R.body_pos, 3 * J, el) : nullptr;
         __syncwarp();
+        auto joint_loop = [&](auto fast_tag) {
+        constexpr bool FASTM = decltype(fast_tag)::value;
         PARC_COLD_LOOP
         for (int it = 0; it < n_iter; ++it) {
             const int entry = s_sched[it * NPART + part];
@@ -977,11 +1035,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
                     crot = make_quat(x[3 * NGROUP], x[4 * NGROUP], x[5 * NGROUP], x[6 * NGROUP]);
                 }
                 const float* jc = s_jc + 8 * j;
-                const Vec3 bpos = cpos + quat_rotate(crot, make_vec3(jc[0], jc[1], jc[2]));
+                const Vec3 bpos = cpos + (FASTM ? quat_rotate_fast(crot, make_vec3(jc[0], jc[1], jc[2])) : quat_rotate(crot, make_vec3(jc[0], jc[1], jc[2])));
                 cpos = bpos;
                 if (entry & SCHED_NEEDS_ROT) {
-                    const Quat cq = lrot_ident ? q : quat_mul(make_quat(jc[3], jc[4], jc[5], jc[6]), q);
-                    crot = quat_mul(crot, cq);
+                    const Quat lq = make_quat(jc[3], jc[4], jc[5], jc[6]);
+                    const Quat cq = lrot_ident ? q : (FASTM ? quat_mul_fast(lq, q) : quat_mul(lq, q));
+                    crot = FASTM ? quat_mul_fast(crot, cq) : quat_mul(crot, cq);
                     if (entry & SCHED_PUBLISH) {
                         float* x = gx + ((entry >> SCHED_WSLOT_SHIFT) & 31) * 7 * NGROUP;
                         x[0] = bpos.x; x[NGROUP] = bpos.y; x[2 * NGROUP] = bpos.z;
@@ -993,11 +1052,12 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
                     float* bp = o_bp + 3 * j;
                     bp[0] = bpos.x; bp[1] = bpos.y; bp[2] = bpos.z;
                 } else {
-                    tan_norm_exact(q, o_pose + 6 * (j - 1));
+                    if (FASTM) tan_norm_fast(q, o_pose + 6 * (j - 1));
+                    else tan_norm_exact(q, o_pose + 6 * (j - 1));
                     PARC_COLD_LOOP
                     for (unsigned km = (entry >> 8) & 0xffu; km; km &= km - 1) {
                         Vec3 kp = bpos - rpos;
-                        if (!c_global_obs) { kp = quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
+                        if (!c_global_obs) { kp = FASTM ? quat_rotate_fast(u.hinv, kp) : quat_rotate(u.hinv, kp); if (is_tar) kp = kp + rp_obs; }
                         float* kd = o_key + 3 * (__ffs(km) - 1);
                         kd[0] = kp.x; kd[1] = kp.y; kd[2] = kp.z;
                     }
@@ -1005,7 +1065,62 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
             __syncwarp();
         }
+        };
+        if (PARC_TAR_FAST_MATH && is_tar) joint_loop(std::true_type{});
+        else joint_loop(std::false_type{});
+        if (PARC_POSE_TAIL_COPIES && is_ref) {
+            // velocity record -> ref_root_vel | ref_root_ang_vel | ref_dof_vel: all of this lane's loads first, then the scatter
+            float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
+            constexpr int NX = FAST ? 3 : 2;                                       // pieces of 4 floats per lane and batch (humanoid: 34 floats = 3 / 2 / 2 / 2)
+            for (int k0 = 4 * part; k0 < 6 + D; k0 += 4 * NPART * NX) {
+                float4 x[NX];
+#pragma unroll
+                for (int i = 0; i < NX; ++i) if (k0 + 4 * NPART * i < 6 + D) x[i] = ldg4(vrec + k0 + 4 * NPART * i);
+#pragma unroll
+                for (int i = 0; i < NX; ++i) {
+                    if (k0 + 4 * NPART * i < 6 + D) {
+                        const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const int kk = k0 + 4 * NPART * i + c;
+                            if (kk < 3) o_rv[kk] = xs[c];
+                            else if (kk < 6) o_rav[kk - 3] = xs[c];
+                            else if (kk < 6 + D) o_dv[kk - 6] = xs[c];
+                        }
+                    }
+                }
+            }
+        }
+        if (PARC_POSE_TAIL_COPIES && is_char) {
+            float* o = row + L.root_h + 12 + 6 * (J - 1);
+            constexpr int ND = FAST ? (FastDims::D + NPART - 1) / NPART : 2;       // dof velocities of this lane per batch
+            for (int k0 = part; k0 < D; k0 += NPART * ND) {
+                float v[ND];
+#pragma unroll
+                for (int i = 0; i < ND; ++i) if (k0 + NPART * i < D) v[i] = view_ld(env.char_dof_vel, u.e, k0 + NPART * i);
+#pragma unroll
+                for (int i = 0; i < ND; ++i) if (k0 + NPART * i < D) o[k0 + NPART * i] = v[i];
+            }
+            if (c_contact_info) {
+                // _get_char_contact_state (ig_parkour_env.py:655-662): ||f|| > eps -> 0/1
+                constexpr int NC = FAST ? (FastDims::J + NPART - 1) / NPART : 1;
+                for (int c0 = part; c0 < J; c0 += NPART * NC) {
+                    float f[NC][3];
+#pragma unroll
+                    for (int i = 0; i < NC; ++i)
+                        if (c0 + NPART * i < J) {
+#pragma unroll
+                            for (int a = 0; a < 3; ++a) f[i][a] = view_ld3(env.char_contact_forces, u.e, c0 + NPART * i, a);
+                        }
+#pragma unroll
+                    for (int i = 0; i < NC; ++i)
+                        if (c0 + NPART * i < J)
+                            row[L.o_charc + c0 + NPART * i] = (sqrtf(f[i][0] * f[i][0] + f[i][1] * f[i][1] + f[i][2] * f[i][2]) > cfg.contact_eps) ? 1.f : 0.f;
+                }
+            }
+        }
     }
+    PARC_STAMP_T(9, 0); PARC_STAMP_T(10, 32); PARC_STAMP_T(11, 6 * 32); PARC_STAMP_T(12, 7 * 32);     // poses 0, 1, S, S + 1 of the first env group
     __syncthreads();
     PARC_STAMP(3);
 
