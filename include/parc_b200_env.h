@@ -237,6 +237,12 @@ int parc_b200_compute_tracking_error(const float* root_pos, const float* root_ro
 int parc_b200_fail_rate_ema(const parc_env_config_t* h_cfg, const parc_env_buffers_t* h_env,
                             int32_t num_motions, float* cdf, int32_t* scratch, void* stream);
 
+/* Env-sharded runs (no counterpart in the single-process reference): ADD to counts [2, num_motions]
+ * (int64, device) how many envs of the done list finished the last step as FAIL (row 0) / as time-out, success or motion end
+ * (row 1), per motion. One rank's input to the cross-rank fail-rate rule: the ranks sum their tables with one all-reduce
+ * and apply the closed form of dm_env.py:648-660 (parc_b200/sharding.py). Call after the step, before the reset. */
+int parc_b200_outcome_counts(const parc_env_buffers_t* h_env, int32_t num_motions, int64_t* counts, void* stream);
+
 /* Allocation-free variant of parc_b200_fail_rate_ema. It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid it). Same inputs, outputs and results as parc_b200_fail_rate_ema, but the scratch is a

@@ -284,6 +284,7 @@ def _declare(lib):
         "parc_b200_mdm_sample_motion_data": [P(CharModelStruct), P(MotionLibStruct), vp, P(SamplerConfigStruct), vp, vp, i64] + [vp] * 14,
         "parc_b200_mdm_augment_hfs": [vp, P(SamplerConfigStruct), P(HfAugStruct), vp, vp, i64, vp, vp, vp, vp],
         "parc_b200_mdm_floor_heights": [P(SamplerConfigStruct), f32, vp, vp, i64, vp, vp],
+        "parc_b200_outcome_counts": [P(EnvBuffersStruct), i32, vp, vp],
         "parc_b200_tree_parts": [P(CharModelStruct), P(i32), P(i32), P(i32), P(i32)],
         "parc_b200_ray_points_lattice": [P(f32), i32, P(i32), P(i32)],
     }

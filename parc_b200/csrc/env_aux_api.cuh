@@ -146,6 +146,15 @@ extern "C" int parc_b200_fail_rate_ema(const parc_env_config_t* cfg, const parc_
     return check_launch("fail_rate_ema");
 }
 
+extern "C" int parc_b200_outcome_counts(const parc_env_buffers_t* env, int32_t num_motions, int64_t* counts, void* stream) {
+    PARC_REQUIRE(env && num_motions > 0 && counts, "outcome_counts: bad arguments");
+    PARC_REQUIRE(env->done_count && env->done_list && env->done_code && env->motion_ids, "outcome_counts: done buffers not set");
+    const long long blocks = std::min<long long>((env->num_envs + 255) / 256, (long long)kNumSMs * 4);
+    outcome_counts_kernel<<<(unsigned)std::max<long long>(blocks, 1), 256, 0, as_stream(stream)>>>(*env, num_motions,
+                                                                                                   reinterpret_cast<unsigned long long*>(counts));
+    return check_launch("outcome_counts");
+}
+
 static int check_reset_views(const parc_env_buffers_t* env, const char* who) {
     PARC_REQUIRE(env->char_root_pos.ptr && env->char_root_rot.ptr && env->char_root_vel.ptr && env->char_root_ang_vel.ptr &&
                      env->char_dof_pos.ptr && env->char_dof_vel.ptr && env->ref_root_pos.ptr && env->ref_root_rot.ptr &&

@@ -720,6 +720,18 @@ __global__ void __launch_bounds__(PARC_STANDIN_THREADS, PARC_STANDIN_MINB) sim_s
 
 __global__ void zero_int_kernel(int* p) { *p = 0; }
 
+// Cross-rank fail rates: per motion, how many of this rank's envs finished the last step as FAIL (row 0) / otherwise
+// (row 1), ADDED to counts [2, M]. Reads the step kernel's done list, so it costs a handful of atomics per finished env.
+__global__ void outcome_counts_kernel(const __grid_constant__ parc_env_buffers_t env, const int num_motions, unsigned long long* __restrict__ counts) {
+    const int n = *env.done_count;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const long long e = env.done_list[i];
+        const int code = env.done_code[e];
+        const long long m = env.motion_ids[e];
+        if (code != 0 && m >= 0 && m < num_motions) atomicAdd(counts + (code == 1 ? 0 : num_motions) + m, 1ull);
+    }
+}
+
 }  // namespace parc
 
 #include "env_aux_api.cuh"

@@ -71,6 +71,12 @@
 #endif                                        //    flags) make are asked for at the top of the pose and done after its joint loop with their loads batched;
                                               //    0: done up front in rolled loops (each load's latency then sits on the block's critical path: those two warps
                                               //    finish phase B last)
+#ifndef PARC_REF_TAIL_BY_CHAR
+#define PARC_REF_TAIL_BY_CHAR 0               // 1 (measured 0.5 % slower: the target poses, not the reference pose, then end phase B): when both run, the character-pose warp (no slerps: it finishes phase B first) makes the reference pose's
+#endif                                        //    velocity-record copy and contact-label lerp, and asks L1 for the rigid-body rows phase C reads
+#ifndef PARC_PHASE_A_WIDE
+#define PARC_PHASE_A_WIDE 0                   // 1 (measured: phase A 5.2k -> 4.9k cycles, kernel time unchanged): phase A's tables and joint constants arrive as 16-byte parameter loads (a divergent parameter read costs one pass per
+#endif                                        //    distinct address), and the root chain's cos / inverse heading quaternion run in two further warps
 #ifndef PARC_BULK_ROWS
 #define PARC_BULK_ROWS 1                      // 1: the tile's ref_* blocks leave through cp.async.bulk where alignment allows
 #endif
@@ -189,7 +195,9 @@ struct StepPlan {
     int lrot_ident;                       // every _local_rotation is the identity
     int n_iter;                           // iterations of the joint schedule
     int root_slot;                        // >= 0: the root transform is published to this group slot before the joint loop
-    int sched[PARC_MAX_BODIES * NPART];   // [it][part]
+    alignas(16) int sched[PARC_MAX_BODIES * NPART];   // [it][part]
+    alignas(16) float jc[PARC_MAX_BODIES * 8];        // per joint: local translation[3] | local rotation[4] | 0 (copied to shared memory in phase A)
+    alignas(16) int jd[PARC_MAX_BODIES * 4];          // per joint: joint type | dof index << 8, hinge axis x, y, z (float bits): one 16-byte read in phase A
     float rdx, rdy;                       // correctly rounded 1/dx, 1/dy
     int lat_nx, lat_ny;                   // > 0: ray_xy_points is the lattice xs[i] x ys[j], point i * ny + j (cfg.ray_grid_*)
     int ref_fast;                         // every ref_* view is a contiguous, 16-byte aligned [N, w] tensor
@@ -360,6 +368,11 @@ inline StepPlan make_step_plan(const parc_char_model_t& cm, int C, const parc_en
     for (int j = 1; j < J; ++j)
         if (!(cm.local_rot[j][0] == 0.f && cm.local_rot[j][1] == 0.f && cm.local_rot[j][2] == 0.f && cm.local_rot[j][3] == 1.f)) sp.lrot_ident = 0;
     plan_schedule(cm, cfg, sp);
+    for (int j = 0; j < PARC_MAX_BODIES; ++j) {
+        for (int c = 0; c < 8; ++c) sp.jc[j * 8 + c] = j < J ? (c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f)) : 0.f;
+        sp.jd[j * 4] = j < J ? (cm.joint_type[j] | (cm.dof_idx[j] << 8)) : 0;
+        for (int c = 0; c < 3; ++c) { const float a = j < J ? cm.axis[j][c] : 0.f; memcpy(&sp.jd[j * 4 + 1 + c], &a, sizeof(float)); }
+    }
     // the lattice sampler gives lane l the lattice column l (32 columns) and walks PARC_LATTICE_ROWS rows per iteration
     const bool lat = cfg.ray_grid_nx > 0 && cfg.ray_grid_ny > 0 && cfg.ray_grid_nx * cfg.ray_grid_ny == cfg.num_ray_points &&
                      cfg.ray_grid_ny == LATTICE_NY && cfg.ray_grid_nx % PARC_LATTICE_ROWS == 0;
@@ -746,14 +759,20 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     if (PARC_STAGGER_NS > 0 && blockIdx.x >= kNumSMs && blockIdx.x < 2 * kNumSMs) __nanosleep(PARC_STAGGER_NS);
     // ================================ phase A ====================================================
     PARC_STAMP(0);
-    PARC_COLD_LOOP
-    for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_sched[k] = sp.sched[k];
-    PARC_COLD_LOOP
-    for (int k = tid; k < 8 * J; k += THREADS) {
-        const int j = k >> 3, c = k & 7;
-        s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
+    if (PARC_PHASE_A_WIDE) {
+        if (tid < NPART * PARC_MAX_BODIES / 4) reinterpret_cast<int4*>(s_sched)[tid] = reinterpret_cast<const int4*>(sp.sched)[tid];
+        else if (tid >= 32 && tid < 32 + 2 * J) reinterpret_cast<float4*>(s_jc)[tid - 32] = reinterpret_cast<const float4*>(sp.jc)[tid - 32];
+    } else {
+        PARC_COLD_LOOP
+        for (int k = tid; k < NPART * PARC_MAX_BODIES; k += THREADS) s_sched[k] = sp.sched[k];
+        PARC_COLD_LOOP
+        for (int k = tid; k < 8 * J; k += THREADS) {
+            const int j = k >> 3, c = k & 7;
+            s_jc[k] = c < 3 ? cm.local_trans[j][c] : (c < 7 ? cm.local_rot[j][c - 3] : 0.f);
+        }
     }
     if (tid == 0) *s_ctr = 0;
+    PARC_STAMP(13);
     if (do_heights) {
         if (LATTICE) {
             // xs[i] = x of point i * ny, ys[j] = y of point j
@@ -787,11 +806,26 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         u.eo = eo;
         u.g = c_pos + eo;                                              // ig_parkour_env.py:522
         const float heading = calc_heading(c_rot);
-        u.sh = sinf(heading); u.ch = cosf(heading);
-        u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
+        u.sh = sinf(heading);
+        if (!PARC_PHASE_A_WIDE) {
+            u.ch = cosf(heading);
+            u.hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
+        }
         u.flags = 0;
         u.row_shift = do_obs ? (int)(((reinterpret_cast<unsigned long long>(env.obs_buf) >> 2) + (unsigned long long)(e * env.obs_row_stride)) & 3ull) : 0;
         if (need_char_q) s_charq[el * J] = quat_to_f4(c_rot);
+        PARC_STAMP_T(14, THREADS - 32);
+      }
+    } else if (PARC_PHASE_A_WIDE && tid >= THREADS - 128 && tid < THREADS - 64) {
+      // the other two ends of the root chain, each in its own warp (the heading is recomputed: the same operations on the same
+      // quaternion): warp THREADS / 32 - 4 -> cos, warp THREADS / 32 - 3 -> inverse heading quaternion
+      const int el = tid & 31;
+      if (el < TILE) {
+        const long long row = row0 + (el < tile_rows ? el : 0);
+        const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
+        const float heading = calc_heading(view_ld_quat(env.char_root_rot, e));
+        if (tid < THREADS - 96) s_env[el].ch = cosf(heading);
+        else s_env[el].hinv = axis_angle_to_quat(make_vec3(0.f, 0.f, 1.f), -heading);   // calc_heading_quat_inv
       }
     } else if (tid >= THREADS - 64) {
       if (tid < THREADS - 64 + TILE) {
@@ -824,12 +858,18 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             const int el = it / (J - 1), j = 1 + (it - el * (J - 1));
             const long long row = row0 + (el < tile_rows ? el : 0);
             const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
-            const int jt = cm.joint_type[j], di = cm.dof_idx[j];
+            int jt, di; Vec3 ax;
+            if (PARC_PHASE_A_WIDE) {
+                const int4 d = reinterpret_cast<const int4*>(sp.jd)[j];
+                jt = d.x & 0xff; di = d.x >> 8; ax = make_vec3(__int_as_float(d.y), __int_as_float(d.z), __int_as_float(d.w));
+            } else {
+                jt = cm.joint_type[j]; di = cm.dof_idx[j]; ax = make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]);
+            }
             Quat q = quat_identity();
             if (jt == PARC_JOINT_SPHERICAL)
                 q = exp_map_to_quat(make_vec3(view_ld(env.char_dof_pos, e, di), view_ld(env.char_dof_pos, e, di + 1), view_ld(env.char_dof_pos, e, di + 2)));
             else if (jt == PARC_JOINT_HINGE)
-                q = axis_angle_to_quat(make_vec3(cm.axis[j][0], cm.axis[j][1], cm.axis[j][2]), view_ld(env.char_dof_pos, e, di));
+                q = axis_angle_to_quat(ax, view_ld(env.char_dof_pos, e, di));
             s_charq[el * J + j] = quat_to_f4(q);
         }
     }
@@ -874,6 +914,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     PARC_STAMP(2);
     static_assert(TILE % 8 == 0 && NPART == 4, "one warp = one pose of 8 of the tile's envs x NPART lanes");
     const bool pose_work = do_obs || need_ref_pose;
+    const bool ref_tail_by_char = PARC_REF_TAIL_BY_CHAR && PARC_POSE_TAIL_COPIES && do_obs && need_ref_pose;
     // warp w takes poses w, w + 8, ...; lane = (env, part). Rows past a partial tile hold a copy of the tile's first row
     // (phase A), so no lane leaves the loop early: the __syncwarp() of the joint schedule sees the whole warp.
     for (int pose = (tid >> 5) & 7; pose_work && pose < plan.n_pose; pose += 8) {
@@ -915,7 +956,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
             // velocities come from frame idx0 without interpolation (motion_lib.py:102-110)
             if (PARC_POSE_TAIL_COPIES) {
-                if (part * 32 < 6 + D) asm volatile("prefetch.global.L1 [%0];" ::"l"(vrec + part * 32));
+                if (!ref_tail_by_char && part * 32 < 6 + D) asm volatile("prefetch.global.L1 [%0];" ::"l"(vrec + part * 32));
             } else {
                 float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
                 PARC_COLD_LOOP
@@ -959,6 +1000,11 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
                 if ((long long)part * 32 < (long long)D * env.char_dof_vel.elem_stride) asm volatile("prefetch.global.L1 [%0];" ::"l"(dv + part * 32));
                 if (c_contact_info && part * 32 < 3 * J)
                     asm volatile("prefetch.global.L1 [%0];" ::"l"(env.char_contact_forces.ptr + u.e * env.char_contact_forces.row_stride + part * 32));
+                if (ref_tail_by_char) {
+                    // the reference pose's velocity record, copied by this warp after its joint loop
+                    const FrameBlend fb = calc_frame_blend(u.mm, u.t0);
+                    if (part * 32 < 6 + D) asm volatile("prefetch.global.L1 [%0];" ::"l"(lib.vel + fb.idx0 * vrec_f + part * 32));
+                }
             } else {
                 PARC_COLD_LOOP
                 for (int k = part; k < D; k += NPART) o[12 + 6 * (J - 1) + k] = view_ld(env.char_dof_vel, u.e, k);
@@ -974,7 +1020,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
         }
         // contact labels: lerp of the two records (motion_lib.py:121)
-        if (!is_char && C > 0 && (is_ref || c_contact_info)) {
+        if (!is_char && C > 0 && (is_ref ? !ref_tail_by_char : c_contact_info)) {
             float* oc = is_ref ? refp(R.contacts, C, el) : (row + L.o_tarc + (pose - 1) * C);
             const float* c0 = r0 + 4 * J + 4; const float* c1 = r1 + 4 * J + 4;
             PARC_COLD_LOOP
@@ -1068,7 +1114,26 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         };
         if (PARC_TAR_FAST_MATH && is_tar) joint_loop(std::true_type{});
         else joint_loop(std::false_type{});
-        if (PARC_POSE_TAIL_COPIES && is_ref) {
+        if (PARC_POSE_TAIL_COPIES && (is_ref ? !ref_tail_by_char : (is_char && ref_tail_by_char))) {
+            if (is_char) {
+                // the reference pose's frame pair again (same operations on the same uniforms as in that pose's warp)
+                const FrameBlend fb = calc_frame_blend(u.mm, u.t0);
+                vrec = lib.vel + fb.idx0 * vrec_f;
+                if (C > 0) {
+                    // contact labels of the reference pose: lerp of the two records (motion_lib.py:121)
+                    const float* c0 = lib.interp + fb.idx0 * irec_f + 4 * J + 4; const float* c1 = lib.interp + fb.idx1 * irec_f + 4 * J + 4;
+                    const float bb = fb.blend, ob = __fsub_rn(1.0f, bb);
+                    float* oc = refp(R.contacts, C, el);
+                    PARC_COLD_LOOP
+                    for (int c = 4 * part; c < C; c += 4 * NPART) {
+                        const float4 a = ldg4(c0 + c), d = ldg4(c1 + c);
+                        oc[c] = lerp_exact(ob, a.x, bb, d.x);
+                        if (c + 1 < C) oc[c + 1] = lerp_exact(ob, a.y, bb, d.y);
+                        if (c + 2 < C) oc[c + 2] = lerp_exact(ob, a.z, bb, d.z);
+                        if (c + 3 < C) oc[c + 3] = lerp_exact(ob, a.w, bb, d.w);
+                    }
+                }
+            }
             // velocity record -> ref_root_vel | ref_root_ang_vel | ref_dof_vel: all of this lane's loads first, then the scatter
             float* o_rv = refp(R.root_vel, 3, el); float* o_rav = refp(R.root_ang_vel, 3, el); float* o_dv = refp(R.dof_vel, D, el);
             constexpr int NX = FAST ? 3 : 2;                                       // pieces of 4 floats per lane and batch (humanoid: 34 floats = 3 / 2 / 2 / 2)
@@ -1092,6 +1157,8 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
         }
         if (PARC_POSE_TAIL_COPIES && is_char) {
+            if (PARC_REF_TAIL_BY_CHAR && (do_reward || do_done) && env.char_rigid_body_pos.ptr && (long long)part * 32 < (long long)J * env.char_rigid_body_pos.mid_stride)
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(env.char_rigid_body_pos.ptr + u.e * env.char_rigid_body_pos.row_stride + part * 32));   // read in phase C
             float* o = row + L.root_h + 12 + 6 * (J - 1);
             constexpr int ND = FAST ? (FastDims::D + NPART - 1) / NPART : 2;       // dof velocities of this lane per batch
             for (int k0 = part; k0 < D; k0 += NPART * ND) {

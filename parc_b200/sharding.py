@@ -65,11 +65,11 @@ def apply_outcome_counts(fail_rates: torch.Tensor, counts: torch.Tensor, ema_wei
     """Fail-rate EMA from reduced counts: rate <- rate * (1-w)^(passes+fails), then `fails` times
     rate <- rate + w applied after the decay of the later updates, i.e. the closed form of the
     reference's sequential rule with all passes first. In place; returns fail_rates."""
-    keep = torch.tensor(1.0 - ema_weight, dtype=torch.float32, device=fail_rates.device)
+    keep = float(torch.tensor(1.0 - ema_weight, dtype=torch.float32))     # the fp32 value of 1 - w, as a host scalar (no device copy, no sync)
     fails, passes = counts[0].to(fail_rates.device), counts[1].to(fail_rates.device)
-    r = fail_rates * keep.pow(passes.float())
+    r = fail_rates * torch.pow(keep, passes.float())
     # k fails in a row: r*keep^k + w*(1 + keep + ... + keep^(k-1)) = r*keep^k + (1 - keep^k)
-    kk = keep.pow(fails.float())
+    kk = torch.pow(keep, fails.float())
     fail_rates.copy_(r * kk + (1.0 - kk))
     return fail_rates
 
@@ -87,10 +87,19 @@ class FailRateSync:
         self.base = fail_rates.clone()
         self.acc = torch.zeros(2, fail_rates.shape[0], dtype=torch.int64, device=fail_rates.device)
         self.steps = 0
+        # the first collective of a process group sets up its communicator (tens of milliseconds with NCCL): do it here, on the
+        # zero table, not inside somebody's step loop. Every rank constructs its FailRateSync, so the call is collective.
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(self.acc, op=dist.ReduceOp.SUM, group=self.group)
 
-    def after_step(self, fail_rates, done_code, motion_ids):
-        """Call once per control step, after the local EMA. Returns True when the rates were replaced by the combined ones."""
-        self.acc += motion_outcome_counts(done_code, motion_ids, fail_rates.shape[0])
+    def after_step(self, fail_rates, done_code, motion_ids, accumulate=None):
+        """Call once per control step, after the local EMA. `accumulate(acc)`: adds this step's counts to `acc` on the device
+        (TrackingEnv passes parc_b200_outcome_counts: one launch, nothing on the host); without it the counts come from
+        motion_outcome_counts. Returns True when the rates were replaced by the combined ones."""
+        if accumulate is not None:
+            accumulate(self.acc)
+        else:
+            self.acc += motion_outcome_counts(done_code, motion_ids, fail_rates.shape[0])
         self.steps += 1
         if self.steps % self.interval:
             return False

@@ -380,7 +380,9 @@ class TrackingEnv:
     def _sync_fail_rates(self):
         if self._fail_rate_sync is None:
             return
-        if self._fail_rate_sync.after_step(self._motion_id_fail_rates, self._done_code, self._motion_ids):
+        M = int(self._motion_id_fail_rates.shape[0])
+        count = lambda acc: _lib.check(_lib.lib().parc_b200_outcome_counts(self._bufs, M, _lib.ptr(acc), self._stream()))
+        if self._fail_rate_sync.after_step(self._motion_id_fail_rates, self._done_code, self._motion_ids, accumulate=count):
             w = torch.clamp(self._motion_id_fail_rates, min=float(self._cfg.min_motion_weight)) * self._mlib._motion_weights
             self._cdf.copy_(torch.cumsum(w, 0))           # the RSI sampling CDF follows the replaced rates
 

@@ -35,6 +35,9 @@ for parts in (63, 2):
     print("parts = %d: mean cycles per phase over %d blocks (thread 0's view)" % (parts, nb))
     for k, nm in enumerate(names):
         print("  %-28s mean %8.0f  median %8.0f  p90 %8.0f" % (nm, d[:, k].mean(), np.median(d[:, k]), np.percentile(d[:, k], 90)))
+    for k, nm in ((13, "A: thread 0 after the table staging"), (14, "A: root chain done (last warp)")):
+        dd = out[:, k] - out[:, 0]
+        print("  %-36s mean %8.0f  median %8.0f  p90 %8.0f   (cycles since block start)" % (nm, dd.mean(), np.median(dd), np.percentile(dd, 90)))
     for k, nm in ((9, "B: reference pose done (warp 0)"), (10, "B: target pose 1 done (warp 1)"), (11, "B: target pose 6 done (warp 6)"), (12, "B: character pose done (warp 7)")):
         dd = out[:, k] - out[:, 2]
         print("  %-36s mean %8.0f  median %8.0f  p90 %8.0f   (cycles since the start of phase B)" % (nm, dd.mean(), np.median(dd), np.percentile(dd, 90)))

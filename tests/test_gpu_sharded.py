@@ -88,3 +88,24 @@ def test_two_ranks_step_their_shards_and_agree_on_the_fail_rates(tmp_path):
     want = sharding.apply_outcome_counts(torch.linspace(0.2, 0.9, M), counts, 0.01)
     np.testing.assert_allclose(r[0]["rates"], want.numpy(), rtol=1e-6, atol=0)
     assert not np.allclose(r[0]["rates"], np.linspace(0.2, 0.9, M))
+
+
+def test_outcome_counts_kernel_equals_the_torch_counts():
+    """parc_b200_outcome_counts (what FailRateSync accumulates on the device every step) against sharding.motion_outcome_counts
+    on the same finished envs, accumulated over two steps."""
+    from parc_b200 import _lib, sharding
+    sc = H.Scenario(num_envs=1003, num_motions=7, ray="grid", seed=4, wrap_fraction=0.2, max_frames=90)
+    oenv = sc.oracle_env()
+    H.randomize_oracle_state(oenv, seed=6, fail_fraction=0.3)
+    penv = sc.product_env("cuda:0")
+    H.copy_oracle_state_to_product(oenv, penv)
+    Mn = penv._mlib.num_motions()
+    acc = torch.zeros(2, Mn, dtype=torch.int64, device="cuda:0")
+    want = torch.zeros_like(acc)
+    for _ in range(2):
+        penv.post_physics_step(update_fail_rates=False)
+        want += sharding.motion_outcome_counts(penv._done_code, penv._motion_ids, Mn)
+        _lib.check(_lib.lib().parc_b200_outcome_counts(penv._bufs, Mn, _lib.ptr(acc), penv._stream()))
+        penv.reset_done()
+    assert int(want.sum()) > 0 and int(want[0].sum()) > 0 and int(want[1].sum()) >= 0
+    assert torch.equal(acc, want)
