@@ -77,6 +77,10 @@
 #ifndef PARC_PHASE_A_WIDE
 #define PARC_PHASE_A_WIDE 0                   // 1 (measured: phase A 5.2k -> 4.9k cycles, kernel time unchanged): phase A's tables and joint constants arrive as 16-byte parameter loads (a divergent parameter read costs one pass per
 #endif                                        //    distinct address), and the root chain's cos / inverse heading quaternion run in two further warps
+#ifndef PARC_EARLY_ROW_PREFETCH
+#define PARC_EARLY_ROW_PREFETCH 0             // 1 (measured 0.5 % slower): the L2 prefetch of the simulator rows phase C reads is issued by warps that idle in phase A (it sat between the
+#endif                                        //    phase-A barrier and the poses, on every warp's path); the character-pose warps, first to finish phase B, then ask
+                                              //    L1 for the rigid-body rows
 #ifndef PARC_BULK_ROWS
 #define PARC_BULK_ROWS 1                      // 1: the tile's ref_* blocks leave through cp.async.bulk where alignment allows
 #endif
@@ -851,6 +855,19 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         u.tox = __fsub_rn(__ldg(dmo), __ldg(env.env_offsets + e * 3)); u.toy = __fsub_rn(__ldg(dmo + 1), __ldg(env.env_offsets + e * 3 + 1));
       }
     }
+    if (PARC_EARLY_ROW_PREFETCH && (do_reward || do_done) && tid >= THREADS / 2 && tid < THREADS / 2 + TILE * 3 * 4) {
+        // simulator state read in phase C (rigid body positions, contact forces, dof velocities): 3 rows per env, asked for by
+        // threads that have nothing else to do in phase A
+        const int it = tid - THREADS / 2;
+        const int el = it / 12, w = (it >> 2) % 3, ln = it & 3;
+        if (el < tile_rows) {
+            const long long row = row0 + el;
+            const long long e = env_ids_ ? env_ids_[row] : (env_ids32_ ? (long long)env_ids32_[row] : row + first_env);
+            const parc_view3_t& v = w == 0 ? env.char_rigid_body_pos : (w == 1 ? env.char_contact_forces : env.char_dof_vel);
+            const long long span = (w == 2 ? (long long)D * v.elem_stride : (long long)J * v.mid_stride) * (long long)sizeof(float);
+            if (v.ptr && ln * 128 < span) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(v.ptr + e * v.row_stride) + ln * 128));
+        }
+    }
     // A.1 character joint rotations: KinCharModel.dof_to_rot (kin_char_model.py:586-599), one thread per (env, joint)
     if (need_char_q) {
         PARC_COLD_LOOP
@@ -878,7 +895,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
 
     // A.0b warm the frame records this tile is about to interpolate: one thread per (env, library pose) asks for
     //      the two adjacent interp records (and the velocity record of the reference pose)
-    if (do_reward || do_done) {
+    if (!PARC_EARLY_ROW_PREFETCH && (do_reward || do_done)) {
         // simulator state read in phase C (rigid body positions, contact forces, dof velocities): 3 rows per env
         PARC_COLD_LOOP
         for (int it = tid; it < TILE * 3 * 4; it += THREADS) {
@@ -1157,7 +1174,7 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             }
         }
         if (PARC_POSE_TAIL_COPIES && is_char) {
-            if (PARC_REF_TAIL_BY_CHAR && (do_reward || do_done) && env.char_rigid_body_pos.ptr && (long long)part * 32 < (long long)J * env.char_rigid_body_pos.mid_stride)
+            if ((PARC_REF_TAIL_BY_CHAR || PARC_EARLY_ROW_PREFETCH) && (do_reward || do_done) && env.char_rigid_body_pos.ptr && (long long)part * 32 < (long long)J * env.char_rigid_body_pos.mid_stride)
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(env.char_rigid_body_pos.ptr + u.e * env.char_rigid_body_pos.row_stride + part * 32));   // read in phase C
             float* o = row + L.root_h + 12 + 6 * (J - 1);
             constexpr int ND = FAST ? (FastDims::D + NPART - 1) / NPART : 2;       // dof velocities of this lane per batch
