@@ -651,8 +651,10 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     const long long* env_ids_ = FAST ? nullptr : env_ids;
     const int* env_ids32_ = FAST ? nullptr : env_ids32;
     const long long n_rows = n_rows_dev_ ? min((long long)*n_rows_dev_, n_rows_host) : n_rows_host;
-    const long long row0 = (long long)blockIdx.x * TILE;
-    if (row0 >= n_rows) return;
+    // A block owns one tile -- except in launches whose row count is only known on the device (the refresh of the reset rows):
+    // those use a small grid instead of one mostly empty block per possible tile, and a block walks its tiles here. The
+    // specialised instantiation never loops (`if (FAST) break` below), so its code is that of a single pass.
+    for (long long row0 = (long long)blockIdx.x * TILE; row0 < n_rows; row0 += (long long)gridDim.x * TILE) {
     const int tid = threadIdx.x;
     const int J = FAST ? FastDims::J : cm.num_bodies, D = FAST ? FastDims::D : cm.dof_size, C = FAST ? FastDims::C : lib.num_contacts;
     const int S = FAST ? FastDims::S : (cfg.enable_tar_obs ? cfg.num_tar_steps : 0);
@@ -1529,6 +1531,9 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
         }
     }
     if (bulk_pending) bulk_wait_read();   // the shared-memory sources must outlive the copies
+    if (FAST) break;
+    __syncthreads();                      // the block's next tile reuses the staging
+    }
     PARC_STAMP(8);
 #ifdef PARC_STEP_TIMING
     if (threadIdx.x == 0 && blockIdx.x < 16384) { unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); g_step_stamps[blockIdx.x * 16 + 15] = smid; }
@@ -1738,7 +1743,8 @@ int launch_env_step(const parc_char_model_t* m, const parc_motion_lib_t* lib, co
 #endif
         have = plan.total;
     }
-    const long long blocks = (max_rows + TILE - 1) / TILE;
+    long long blocks = (max_rows + TILE - 1) / TILE;
+    if (n_rows_dev) blocks = std::min<long long>(blocks, (long long)kNumSMs * 4);      // row count on the device: blocks loop over the tiles
     if (variant == 2)
         env_step_kernel<STEP_THREADS, true, true><<<(unsigned)blocks, STEP_THREADS, plan.total, as_stream(stream)>>>(
             *m, *lib, *terrain, *cfg, *env, sp, parts, (const long long*)env_ids, max_rows, env_ids32, n_rows_dev, first_env);
