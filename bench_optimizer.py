@@ -19,6 +19,7 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+LAST_EVALS = 0
 KIN_GEN = dict(w_root_pos=1.0, w_root_rot=10.0, w_joint_rot=1.0, w_smoothness=10.0, w_penetration=1000.0, w_contact=1000.0,
                w_sliding=10.0, w_body_constraints=1000.0, w_jerk=1000.0, max_jerk=1000.0)
 NAMES = ("src_root_pos", "src_root_rot_quat", "src_joint_rot", "src_body_vels", "src_body_rot_vels", "contacts")
@@ -90,6 +91,8 @@ def run(B=1024, T=300, steps=10, warmup=3, cpu_motions=2, dev=None, peak_gbs=Non
         loss.sum().backward()
         return loss, terms, p
 
+    global LAST_EVALS
+    LAST_EVALS = max(warmup, 3) + steps         # evaluations this call makes (profiles/opt_cells.py divides its counters by it)
     for _ in range(max(warmup, 3)):
         step()
     torch.cuda.synchronize(dev)
@@ -128,12 +131,26 @@ def run(B=1024, T=300, steps=10, warmup=3, cpu_motions=2, dev=None, peak_gbs=Non
         if os.path.exists(mp):
             peak_gbs = float(json.load(open(mp))["hbm_gbs"])
     achieved = alg_bytes / (ms * 1e-3) / 1e9
+    # fp32 side: cells evaluated per frame were counted once with a -DPARC_OPT_COUNT_CELLS build (profiles/opt_cells.py);
+    # one evaluated cell = both column distances (solid and air) = 2 x ~20 FLOP
+    fp32 = None
+    cells_json = os.path.join(ROOT, "profiles", "opt_sdf_cells.json")
+    if os.path.exists(cells_json) and (B, T) == (1024, 300):
+        cj = json.load(open(cells_json))
+        flop = frames * cj["cells_per_frame"] * 40.0
+        peak_tf = 148 * 128 * 2 * 1.965e9 / 1e12                       # FP32 FMA lanes x 2 x SM clock
+        fp32 = {"cells_per_scan": cj["cells_per_scan"], "scans_per_frame": cj["scans_per_frame"], "cells_per_frame": cj["cells_per_frame"],
+                "flop_per_eval": flop, "achieved": flop / (ms * 1e-3) / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": flop / (ms * 1e-3) / 1e12 / peak_tf,
+                "survey_formula_flop_per_eval": frames * 304 * cj["cells_per_scan"] * 2 * 20 * 3,
+                "source": "profiles/opt_sdf_cells.json (counting build, one evaluation of this workload)"}
     return {"metric": "optimizer loss fwd+bwd, motions/s (1,024 x 300 frames)", "value": B / (ms * 1e-3), "unit": "motions/s",
             "ms_per_eval": ms, "frames_per_s": frames / (ms * 1e-3),
             "config": {"workload": "BASELINE configs[3]: %d distinct synthetic motions x %d frames, own 32x32 terrains" % (B, T), "motions": B,
                        "frames": T, "body_points": int(sum(x.shape[0] for x in pts)), "terrain": list(d["hf"].shape[1:])},
             "roofline": {"bound": "fp32 ALU / shared memory (SURVEY 8d); HBM floor shown", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                         "frac": achieved / peak_gbs, "algorithmic_bytes_per_eval": alg_bytes, "hbm_floor_ms": alg_bytes / (peak_gbs * 1e9) * 1e3},
+                         "frac": achieved / peak_gbs, "algorithmic_bytes_per_eval": alg_bytes, "hbm_floor_ms": alg_bytes / (peak_gbs * 1e9) * 1e3,
+                         "fp32": fp32},
             "cpu_baseline": cpu,
             "stats": {"mean_loss": float(loss.mean()), "mean_penetration": float(terms[:, 4].mean())}}
 

@@ -131,6 +131,14 @@ __global__ void __launch_bounds__(256, PARC_OPT_LANES_MINB) opt_pose_kernel(cons
 //                 distance found so far: a point that cannot beat it does not matter); `solid_zlb` = how far the
 //                 point is above the highest column top of the window (0 if it is not).
 // Within those limits the result equals the reference's minimum over the whole window.
+// Debug build only (-DPARC_OPT_COUNT_CELLS, profiles/opt_cells.py): cells evaluated and scan_cells calls, for the mean cells
+// visited per sample point that the config-4 roofline is stated against.
+#ifdef PARC_OPT_COUNT_CELLS
+__device__ unsigned long long g_opt_cells[2];
+#define PARC_COUNT_CELLS(n) do { atomicAdd(&g_opt_cells[0], (unsigned long long)(n)); atomicAdd(&g_opt_cells[1], 1ull); } while (0)
+#else
+#define PARC_COUNT_CELLS(n) do { } while (0)
+#endif
 struct CellScan { float air, solid; int arg_air, arg_solid; };
 template <typename HF>
 __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float ox, float oy, float dx, float dy, float base_z,
@@ -143,12 +151,13 @@ __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float o
     out.air = r0.air; out.solid = r0.solid; out.arg_air = c0; out.arg_solid = c0;
     const float b_air = (need_air && out.air > 0.f) ? out.air : 0.f;
     const float b_solid = (need_solid && out.solid > 0.f) ? fminf(out.solid, solid_cap) : 0.f;
-    if (!(fmaxf(b_air, b_solid) > 0.f)) return out;
+    if (!(fmaxf(b_air, b_solid) > 0.f)) { PARC_COUNT_CELLS(1); return out; }
     // a point that is at least solid_zlb above every column top is, k columns away, at least
     // sqrt(((k - 1) dx)^2 + zlb^2) from a column: over flat ground only the neighbouring cells remain
     const float b_solid_xy = sqrtf(fmaxf(b_solid * b_solid - solid_zlb * solid_zlb, 0.f));
     const int r = (int)fminf(fmaxf(b_air, b_solid_xy) / fminf(dx, dy), 1.0e6f) + 1;
     const int x0 = max(ix0 - r, 0), x1 = min(ix0 + r, psx - 1), y0 = max(iy0 - r, 0), y1 = min(iy0 + r, psy - 1);
+    PARC_COUNT_CELLS(1 + (x1 - x0 + 1) * (y1 - y0 + 1));
     for (int cx = x0; cx <= x1; ++cx) {
         const float rx = P.x - (cx * dx + ox);
         for (int cy = y0; cy <= y1; ++cy) {

@@ -271,6 +271,14 @@ extern "C" int parc_b200_points_hf_sdf(const float* points, int64_t B, int64_t N
     return check_launch("points_hf_sdf");
 }
 
+#ifdef PARC_OPT_COUNT_CELLS
+extern "C" int parc_b200_debug_opt_cells(unsigned long long* h_out2, int reset) {
+    cudaError_t ce = cudaMemcpyFromSymbol(h_out2, g_opt_cells, sizeof(unsigned long long) * 2);
+    if (ce == cudaSuccess && reset) { const unsigned long long z[2] = {0ull, 0ull}; ce = cudaMemcpyToSymbol(g_opt_cells, z, sizeof(z)); }
+    return ce == cudaSuccess ? 0 : -3;
+}
+#endif
+
 extern "C" int64_t parc_b200_motion_loss_workspace_bytes(const parc_char_model_t* m, int64_t B, int64_t T) {
     if (!m || B <= 0 || T <= 0) return 0;
     return (int64_t)(opt_ws_floats(B * T, B, m->num_bodies) * sizeof(float));
