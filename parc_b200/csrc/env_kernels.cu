@@ -81,6 +81,9 @@
 #define PARC_EARLY_ROW_PREFETCH 0             // 1 (measured 0.5 % slower): the L2 prefetch of the simulator rows phase C reads is issued by warps that idle in phase A (it sat between the
 #endif                                        //    phase-A barrier and the poses, on every warp's path); the character-pose warps, first to finish phase B, then ask
                                               //    L1 for the rigid-body rows
+#ifndef PARC_REWARD_TWO_LANES
+#define PARC_REWARD_TWO_LANES 0               // 1 (measured 0.8 % slower): an env's reward is summed by two lanes of warp 0 (pose / key / root terms | dof-velocity and contact terms), the
+#endif                                        //    order inside every sum unchanged: warp 0 reaches the height samples sooner
 #ifndef PARC_BULK_ROWS
 #define PARC_BULK_ROWS 1                      // 1: the tile's ref_* blocks leave through cp.async.bulk where alignment allows
 #endif
@@ -1399,6 +1402,23 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
     PARC_STAMP(5);
     static_assert(TILE + NREF <= 32 && THREADS >= 96, "issuing lanes fit one warp; three warps take the tail roles");
     // 16 lanes each: the reward in warp 0, the termination flags in warp 2 (PARC_TAIL_ROLES; else both in warp 0)
+    constexpr bool RW2 = PARC_REWARD_TWO_LANES && 2 * TILE <= 32;
+    // second reward lane of an env (lanes TILE .. 2 TILE - 1 of warp 0): the two long sums, handed over by a shuffle
+    float vel_hi = 0.f, con_hi = 0.f;
+    if (RW2 && do_reward && (tid >> 5) == 0) {
+        const int lane = tid & 31;
+        if (lane >= TILE && lane - TILE < tile_rows) {
+            const float* tm = s_terms + (lane - TILE) * TP;
+#pragma unroll 4
+            for (int k = 0; k < D; ++k) vel_hi += tm[o_vel_t + k];
+            if (c_contact_info) {
+#pragma unroll 4
+                for (int k = 0; k < J; ++k) con_hi += tm[o_con_t + k];
+            }
+        }
+        vel_hi = __shfl_down_sync(FULL_MASK, vel_hi, TILE);
+        con_hi = __shfl_down_sync(FULL_MASK, con_hi, TILE);
+    }
     const bool run_reward = do_reward && (tid >> 5) == 0 && (tid & 31) < tile_rows;
     const bool run_done = do_done && (tid >> 5) == (PARC_TAIL_ROLES ? 2 : 0) && (tid & 31) < tile_rows;
     if (run_reward || run_done) {
@@ -1414,8 +1434,11 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             float pose_t = 0.f, vel_t = 0.f, key_t = 0.f, con_t = 0.f;
 #pragma unroll 4
             for (int k = 0; k < J - 1; ++k) pose_t += tm[o_pose_t + k];
+            if (RW2) vel_t = vel_hi;
+            else {
 #pragma unroll 4
-            for (int k = 0; k < D; ++k) vel_t += tm[o_vel_t + k];
+                for (int k = 0; k < D; ++k) vel_t += tm[o_vel_t + k];
+            }
             for (int k = 0; k < K; ++k) key_t += tm[o_key_t + k];
             Vec3 rpd = ref_rpos - u.c_pos;
             if (!c_track_root) { rpd.x = 0.f; rpd.y = 0.f; }
@@ -1445,8 +1468,11 @@ __global__ void __launch_bounds__(THREADS, PARC_STEP_MIN_BLOCKS) env_step_kernel
             float total = cfg.pose_w * pose_r + cfg.vel_w * vel_r + cfg.root_pos_w * root_pose_r + cfg.root_vel_w * root_vel_r + cfg.key_pos_w * key_r;
             float pen = 0.f;
             if (c_contact_info) {
+                if (RW2) con_t = con_hi;
+                else {
 #pragma unroll 4
-                for (int k = 0; k < J; ++k) con_t += tm[o_con_t + k];
+                    for (int k = 0; k < J; ++k) con_t += tm[o_con_t + k];
+                }
                 pen = con_t / (float)C;
                 total += pen;
             }
