@@ -144,7 +144,8 @@ template <typename HF>
 __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float ox, float oy, float dx, float dy, float base_z,
                                                bool need_air, bool need_solid, float solid_cap, float solid_zlb, HF height) {
     const float hx = dx * 0.5f, hy = dy * 0.5f;
-    const int ix0 = max(0, min(__float2int_rn((P.x - ox) / dx), psx - 1)), iy0 = max(0, min(__float2int_rn((P.y - oy) / dy), psy - 1));
+    // the cell to start from (any cell next to the point would do: the scan below is exact), hence the approximate division
+    const int ix0 = max(0, min(__float2int_rn(__fdividef(P.x - ox, dx)), psx - 1)), iy0 = max(0, min(__float2int_rn(__fdividef(P.y - oy, dy)), psy - 1));
     const int c0 = ix0 * psy + iy0;
     const CellSd r0 = cell_sd(P.x - (ix0 * dx + ox), P.y - (iy0 * dy + oy), P.z, height(ix0, iy0), hx, hy, base_z);
     CellScan out;
@@ -232,7 +233,10 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
     const float oy = __fadd_rn(ter.min_point[b * ter.mp_stride + 1], __fmul_rn((float)sy, ter.dy));
     const float hx = ter.dx * 0.5f, hy = ter.dy * 0.5f, top = -cfg.base_z;
     const bool want_contact = cfg.w[PARC_LOSS_CONTACT] != 0.f;
-    auto height = [&](int cx, int cy) { return staged ? s_h[cx * psy + cy] : hf[(sx + cx) * ter.Y + sy + cy]; };
+    // one base pointer + pitch for both homes of the window's heights (generic load): the staged copy or the terrain itself
+    const float* hbase = staged ? s_h : hf + (long long)sx * ter.Y + sy;
+    const int hpitch = staged ? psy : ter.Y;
+    auto height = [&](int cx, int cy) { return hbase[cx * hpitch + cy]; };
     float pen_sum = 0.f;
     // ---- pass 1: penetration (air columns) of every point; own-cell solid distance of the contact bodies' points
     for (int k = tid; k < cfg.num_points; k += blockDim.x) {
