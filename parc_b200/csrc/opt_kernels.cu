@@ -120,17 +120,26 @@ __device__ __forceinline__ float group_max(float v) {
 // sdBox (geom_util.py:124-145) for the air column [h, -base_z] and the solid column [base_z, h] of a cell
 // whose xy half extents are (hx, hy); rx, ry = point - cell centre. The two share the xy part.
 struct CellSd { float air, solid; };
+// AIR / SOLID: which of the two columns the caller needs (the other member is left at 0). The distances only feed minima and
+// clamped sums with a 2e-5 tolerance, so the square root is the approximate one (2 ulp).
+template <bool AIR, bool SOLID>
 __device__ __forceinline__ CellSd cell_sd(float rx, float ry, float pz, float h, float hx, float hy, float base_z) {
     const float qx = fabsf(rx) - hx, qy = fabsf(ry) - hy;
     const float ox = fmaxf(qx, 0.f), oy = fmaxf(qy, 0.f);
     const float oxy2 = ox * ox + oy * oy, mxy = fmaxf(qx, qy);
-    const float top = -base_z;
-    const float qa = fabsf(pz - (h + top) * 0.5f) - (top - h) * 0.5f;
-    const float qs = fabsf(pz - (h + base_z) * 0.5f) - (h - base_z) * 0.5f;
-    const float oa = fmaxf(qa, 0.f), os = fmaxf(qs, 0.f);
     CellSd r;
-    r.air = sqrtf(oxy2 + oa * oa) + fminf(fmaxf(mxy, qa), 0.f);
-    r.solid = sqrtf(oxy2 + os * os) + fminf(fmaxf(mxy, qs), 0.f);
+    r.air = 0.f; r.solid = 0.f;
+    if (AIR) {
+        const float top = -base_z;
+        const float qa = fabsf(pz - (h + top) * 0.5f) - (top - h) * 0.5f;
+        const float oa = fmaxf(qa, 0.f);
+        r.air = fast_sqrt(oxy2 + oa * oa) + fminf(fmaxf(mxy, qa), 0.f);
+    }
+    if (SOLID) {
+        const float qs = fabsf(pz - (h + base_z) * 0.5f) - (h - base_z) * 0.5f;
+        const float os = fmaxf(qs, 0.f);
+        r.solid = fast_sqrt(oxy2 + os * os) + fminf(fmaxf(mxy, qs), 0.f);
+    }
     return r;
 }
 // d sdBox / d point for the column (centre z cz, half height hz)
@@ -174,7 +183,7 @@ __global__ void __launch_bounds__(256) points_hf_sdf_kernel(const float* __restr
         const int lim = min(1024, cells - c0);
         for (int k = 0; k < lim; ++k) {
             const int c = c0 + k, cx = c / Y, cy = c - cx * Y;
-            const CellSd r = cell_sd(px - (cx * dx + mx), py - (cy * dy + my), pz, s_h[k], hx, hy, base_z);
+            const CellSd r = cell_sd<true, true>(px - (cx * dx + mx), py - (cy * dy + my), pz, s_h[k], hx, hy, base_z);
             const float v = inverted ? r.air : r.solid;
             if (v < best) { best = v; best_c = c; }
         }

@@ -140,14 +140,17 @@ __device__ unsigned long long g_opt_cells[2];
 #define PARC_COUNT_CELLS(n) do { } while (0)
 #endif
 struct CellScan { float air, solid; int arg_air, arg_solid; };
-template <typename HF>
+// AIR / SOLID: the column(s) whose minimum is wanted (compile time); OWN_BOTH: the own cell is evaluated for both (pass 1 keeps
+// the own-cell solid distance as the body's first bound). A member that is not scanned keeps its own-cell value.
+template <bool AIR, bool SOLID, bool OWN_BOTH, typename HF>
 __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float ox, float oy, float dx, float dy, float base_z,
-                                               bool need_air, bool need_solid, float solid_cap, float solid_zlb, HF height) {
+                                               float solid_cap, float solid_zlb, HF height) {
+    constexpr bool need_air = AIR, need_solid = SOLID;
     const float hx = dx * 0.5f, hy = dy * 0.5f;
     // the cell to start from (any cell next to the point would do: the scan below is exact), hence the approximate division
     const int ix0 = max(0, min(__float2int_rn(__fdividef(P.x - ox, dx)), psx - 1)), iy0 = max(0, min(__float2int_rn(__fdividef(P.y - oy, dy)), psy - 1));
     const int c0 = ix0 * psy + iy0;
-    const CellSd r0 = cell_sd(P.x - (ix0 * dx + ox), P.y - (iy0 * dy + oy), P.z, height(ix0, iy0), hx, hy, base_z);
+    const CellSd r0 = cell_sd<AIR || OWN_BOTH, SOLID || OWN_BOTH>(P.x - (ix0 * dx + ox), P.y - (iy0 * dy + oy), P.z, height(ix0, iy0), hx, hy, base_z);
     CellScan out;
     out.air = r0.air; out.solid = r0.solid; out.arg_air = c0; out.arg_solid = c0;
     const float b_air = (need_air && out.air > 0.f) ? out.air : 0.f;
@@ -163,10 +166,10 @@ __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float o
         const float rx = P.x - (cx * dx + ox);
         for (int cy = y0; cy <= y1; ++cy) {
             const int c = cx * psy + cy;
-            const CellSd v = cell_sd(rx, P.y - (cy * dy + oy), P.z, height(cx, cy), hx, hy, base_z);
+            const CellSd v = cell_sd<AIR, SOLID>(rx, P.y - (cy * dy + oy), P.z, height(cx, cy), hx, hy, base_z);
             // the lower cell index wins ties, as a scan in index order would
-            if (v.air < out.air || (v.air == out.air && c < out.arg_air)) { out.air = v.air; out.arg_air = c; }
-            if (v.solid < out.solid || (v.solid == out.solid && c < out.arg_solid)) { out.solid = v.solid; out.arg_solid = c; }
+            if (AIR && (v.air < out.air || (v.air == out.air && c < out.arg_air))) { out.air = v.air; out.arg_air = c; }
+            if (SOLID && (v.solid < out.solid || (v.solid == out.solid && c < out.arg_solid))) { out.solid = v.solid; out.arg_solid = c; }
         }
     }
     return out;
@@ -246,7 +249,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
         const Vec3 lp = make_vec3(__ldg(body_points + k * 3), __ldg(body_points + k * 3 + 1), __ldg(body_points + k * 3 + 2));
         const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
         const bool need_solid = s_cw[body] != 0.f;
-        const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, true, false, 0.f, 0.f, height);
+        const CellScan sc = scan_cells<true, false, true>(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, 0.f, 0.f, height);
         // penetration (:553-556): -min(-min_air, 0) = max(min_air, 0)
         pen_sum += fmaxf(sc.air, 0.f);
         Vec3 gP = make_vec3(0.f, 0.f, 0.f);
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
             // above every column by more than the body's best (1e-4 m of slack: the column distance is computed as
             // |z - centre| - half height, which rounds differently from z - top)
             if (P.z - hmax > cap + 1e-4f) continue;
-            const CellScan sc = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, cap, fmaxf(P.z - hmax - 1e-4f, 0.f), height);
+            const CellScan sc = scan_cells<false, true, false>(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, cap, fmaxf(P.z - hmax - 1e-4f, 0.f), height);
             const unsigned long long key = ((unsigned long long)__float_as_uint(fmaxf(sc.solid, 0.f)) << 32) | (unsigned)(k - cfg.point_start[body]);
             atomicMin(&s_key[body], key);
         }
@@ -308,7 +311,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
                 const Quat rot = quat_from_f4(s_brot[body]);
                 const Vec3 lp = make_vec3(__ldg(body_points + k * 3), __ldg(body_points + k * 3 + 1), __ldg(body_points + k * 3 + 2));
                 const Vec3 P = quat_rotate(rot, lp) + make_vec3(bp[0], bp[1], bp[2]);
-                const int arg_s = scan_cells(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, false, true, d * 1.00001f + 1e-6f, fmaxf(P.z - s_hmax - 1e-4f, 0.f), height).arg_solid;
+                const int arg_s = scan_cells<false, true, false>(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, d * 1.00001f + 1e-6f, fmaxf(P.z - s_hmax - 1e-4f, 0.f), height).arg_solid;
                 const int cx = arg_s / psy, cy = arg_s - cx * psy;
                 const float h = staged ? s_h[arg_s] : hf[(sx + cx) * ter.Y + sy + cy];
                 const Vec3 g = (cfg.w[PARC_LOSS_CONTACT] * cw) *
