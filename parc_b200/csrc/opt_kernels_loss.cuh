@@ -252,17 +252,18 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
         const CellScan sc = scan_cells<true, false, true>(P, psx, psy, ox, oy, ter.dx, ter.dy, cfg.base_z, 0.f, 0.f, height);
         // penetration (:553-556): -min(-min_air, 0) = max(min_air, 0)
         pen_sum += fmaxf(sc.air, 0.f);
-        Vec3 gP = make_vec3(0.f, 0.f, 0.f);
-        if (need_grad && sc.air > 0.f) {
-            const int cx = sc.arg_air / psy, cy = sc.arg_air - cx * psy;
-            const float h = height(cx, cy);
-            gP = cfg.w[PARC_LOSS_PENETRATION] * cell_sd_grad(P.x - (cx * ter.dx + ox), P.y - (cy * ter.dy + oy), P.z - (h + top) * 0.5f, hx, hy, (top - h) * 0.5f);
-        }
         if (need_solid) atomicMin(&s_bub[body], __float_as_uint(fmaxf(sc.solid, 0.f)));   // sc.solid here = the cell under the point
         if (need_grad) {
-            const Quat gq = rotate_bwd_q(rot, lp, gP);
             float* o = s_pg + k * 7;
-            o[0] = gP.x; o[1] = gP.y; o[2] = gP.z; o[3] = gq.x; o[4] = gq.y; o[5] = gq.z; o[6] = gq.w;
+            if (sc.air > 0.f) {      // only a penetrating point has a gradient (most do not: no chain through the rotation for them)
+                const int cx = sc.arg_air / psy, cy = sc.arg_air - cx * psy;
+                const float h = height(cx, cy);
+                const Vec3 gP = cfg.w[PARC_LOSS_PENETRATION] * cell_sd_grad(P.x - (cx * ter.dx + ox), P.y - (cy * ter.dy + oy), P.z - (h + top) * 0.5f, hx, hy, (top - h) * 0.5f);
+                const Quat gq = rotate_bwd_q(rot, lp, gP);
+                o[0] = gP.x; o[1] = gP.y; o[2] = gP.z; o[3] = gq.x; o[4] = gq.y; o[5] = gq.z; o[6] = gq.w;
+            } else {
+                o[0] = 0.f; o[1] = 0.f; o[2] = 0.f; o[3] = 0.f; o[4] = 0.f; o[5] = 0.f; o[6] = 0.f;
+            }
         }
     }
     __syncthreads();
