@@ -199,6 +199,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
     __shared__ unsigned char s_pbody[1184];         // body of each sample point (num_points <= 1170, checked by the caller)
     __shared__ float s_g[PARC_MAX_BODIES][8];
     __shared__ float s_red[16];
+    __shared__ int s_any[PARC_MAX_BODIES];          // body has at least one penetrating point (its per-point gradients are not all zero)
     extern __shared__ float s_pg[];          // [num_points][7] per-point gradient w.r.t. the body transform (need_grad)
     const long long i = blockIdx.x, b = i / T;
     const int J = cm.num_bodies, tid = threadIdx.x;
@@ -220,6 +221,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
     for (int k = tid; k < J; k += blockDim.x) {
         s_key[k] = ~0ull;
         s_bub[k] = 0x7f800000u;
+        s_any[k] = 0;
 #pragma unroll
         for (int c = 0; c < 8; ++c) s_g[k][c] = 0.f;
     }
@@ -261,6 +263,7 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
                 const Vec3 gP = cfg.w[PARC_LOSS_PENETRATION] * cell_sd_grad(P.x - (cx * ter.dx + ox), P.y - (cy * ter.dy + oy), P.z - (h + top) * 0.5f, hx, hy, (top - h) * 0.5f);
                 const Quat gq = rotate_bwd_q(rot, lp, gP);
                 o[0] = gP.x; o[1] = gP.y; o[2] = gP.z; o[3] = gq.x; o[4] = gq.y; o[5] = gq.z; o[6] = gq.w;
+                s_any[body] = 1;
             } else {
                 o[0] = 0.f; o[1] = 0.f; o[2] = 0.f; o[3] = 0.f; o[4] = 0.f; o[5] = 0.f; o[6] = 0.f;
             }
@@ -292,7 +295,8 @@ __global__ void __launch_bounds__(OPT_SDF_THREADS, PARC_OPT_SDF_MINB) opt_sdf_ke
         for (int k = tid; k < J * 7; k += blockDim.x) {
             const int body = k / 7, c = k - body * 7;
             float a = 0.f;
-            for (int q = cfg.point_start[body]; q < cfg.point_start[body + 1]; ++q) a += s_pg[q * 7 + c];
+            if (s_any[body])     // a body without a penetrating point sums zeros
+                for (int q = cfg.point_start[body]; q < cfg.point_start[body + 1]; ++q) a += s_pg[q * 7 + c];
             s_g[body][c] = a;
         }
         __syncthreads();
