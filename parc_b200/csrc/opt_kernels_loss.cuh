@@ -162,11 +162,13 @@ __device__ __forceinline__ CellScan scan_cells(Vec3 P, int psx, int psy, float o
     const int r = (int)fminf(fmaxf(b_air, b_solid_xy) / fminf(dx, dy), 1.0e6f) + 1;
     const int x0 = max(ix0 - r, 0), x1 = min(ix0 + r, psx - 1), y0 = max(iy0 - r, 0), y1 = min(iy0 + r, psy - 1);
     PARC_COUNT_CELLS(1 + (x1 - x0 + 1) * (y1 - y0 + 1));
+    const float fy0 = (float)y0;
     for (int cx = x0; cx <= x1; ++cx) {
         const float rx = P.x - (cx * dx + ox);
-        for (int cy = y0; cy <= y1; ++cy) {
-            const int c = cx * psy + cy;
-            const CellSd v = cell_sd<AIR, SOLID>(rx, P.y - (cy * dy + oy), P.z, height(cx, cy), hx, hy, base_z);
+        float fy = fy0;                                 // cy as a float, stepped exactly (no int -> float conversion per cell)
+        int c = cx * psy + y0;
+        for (int cy = y0; cy <= y1; ++cy, ++c, fy += 1.0f) {
+            const CellSd v = cell_sd<AIR, SOLID>(rx, P.y - (fy * dy + oy), P.z, height(cx, cy), hx, hy, base_z);
             // the lower cell index wins ties, as a scan in index order would
             if (AIR && (v.air < out.air || (v.air == out.air && c < out.arg_air))) { out.air = v.air; out.arg_air = c; }
             if (SOLID && (v.solid < out.solid || (v.solid == out.solid && c < out.arg_solid))) { out.solid = v.solid; out.arg_solid = c; }
