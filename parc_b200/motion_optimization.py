@@ -283,3 +283,92 @@ def motion_terrain_contact_loss(tgt_root_pos, tgt_root_rot, tgt_joint_dof, src_r
                                                  src_body_vels, src_body_rot_vels, contacts, terrain, body_points, char_model, w_root_pos,
                                                  w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
                                                  w_body_constraints, w_jerk, body_constraints, max_jerk, _localized=False)
+
+
+# ---- set-up conversions of the optimisation loop (run once per motion, elementwise torch on the caller's device) --------------
+def _quat_axis_angle(q):
+    """torch_util.quat_to_axis_angle (torch_util.py:69-91): w made non-negative, angle = 2 atan2(|xyz|, w), axis z below 1e-5."""
+    q = torch.where(q[..., 3:] < 0, -q, q)
+    ln = torch.linalg.vector_norm(q[..., :3], dim=-1)
+    angle = 2.0 * torch.atan2(ln, q[..., 3])
+    axis = q[..., :3] / ln.unsqueeze(-1).clamp(min=1e-6)
+    small = ln <= 1e-5
+    z = torch.zeros_like(axis)
+    z[..., 2] = 1.0
+    return torch.where(small.unsqueeze(-1), z, axis), torch.where(small, torch.zeros_like(angle), angle)
+
+
+def _quat_to_exp_map(q):                     # torch_util.py:372-376
+    axis, angle = _quat_axis_angle(q)
+    return axis * angle.unsqueeze(-1)
+
+
+def _quat_mul(a, b):                         # Hamilton product, xyzw
+    ax, ay, az, aw = a.unbind(-1)
+    bx, by, bz, bw = b.unbind(-1)
+    return torch.stack([aw * bx + ax * bw + ay * bz - az * by, aw * by - ax * bz + ay * bw + az * bx,
+                        aw * bz + ax * by - ay * bx + az * bw, aw * bw - ax * bx - ay * by - az * bz], dim=-1)
+
+
+def _quat_diff_angle(q0, q1):                # torch_util.py:453-462: angle of q1 * conj(q0)
+    conj = torch.cat([-q0[..., :3], q0[..., 3:]], dim=-1)
+    return _quat_axis_angle(_quat_mul(q1, conj))[1]
+
+
+def _exp_map_to_quat(e):
+    """torch_util.exp_map_to_quat (:426-450): angle = |e| normalised to (-pi, pi], axis e / |e| (z below 1e-5), unit quaternion."""
+    angle = torch.linalg.vector_norm(e, dim=-1)
+    axis = e / angle.unsqueeze(-1)
+    angle = torch.atan2(torch.sin(angle), torch.cos(angle))
+    small = angle.abs() <= 1e-5
+    z = torch.zeros_like(e)
+    z[..., 2] = 1.0
+    axis = torch.where(small.unsqueeze(-1), z, axis)
+    angle = torch.where(small, torch.zeros_like(angle), angle)
+    axis = axis / torch.linalg.vector_norm(axis, dim=-1, keepdim=True).clamp(min=1e-9)
+    q = torch.cat([axis * torch.sin(angle / 2).unsqueeze(-1), torch.cos(angle / 2).unsqueeze(-1)], dim=-1)
+    return q / torch.linalg.vector_norm(q, dim=-1, keepdim=True).clamp(min=1e-9)
+
+
+def motion_contact_optimization(src_motion_frames, body_points: list, terrain, char_model: KinCharModel, num_iters: int, step_size: float,
+                                w_root_pos: float, w_root_rot: float, w_joint_rot: float, w_smoothness: float, w_penetration: float,
+                                w_contact: float, w_sliding: float, w_body_constraints: float, w_jerk: float, body_constraints: list,
+                                max_jerk: float, exp_name: str = None, use_wandb: bool = False, log_file: str = None, log=None):
+    """motion_optimization.py:721-823: Adam on (root position, root exp map, joint dofs) of one motion against the CUDA loss.
+    Same arguments and return (a MotionFrames with the optimised root_pos / root_rot / joint_rot and the source contacts).
+    Every iteration is one call of parc_b200_motion_loss_constrained (value + gradient) and torch's Adam step; the constraint
+    lists are packed once. Logging: every 25 iterations `log(iteration, loss, {LossType: value})` if given, and a line per log
+    step into `log_file`; `use_wandb` is accepted and ignored (wandb is outside this path)."""
+    from .file_io import MotionFrames
+    src_root_pos, src_root_rot_quat, src_joint_rot = src_motion_frames.root_pos, src_motion_frames.root_rot, src_motion_frames.joint_rot
+    assert src_root_pos.dim() == 2 and src_root_rot_quat.dim() == 2 and src_joint_rot.dim() == 3, "one motion: [T,3], [T,4], [T,J-1,4]"
+    contacts = src_motion_frames.contacts
+    src_root_rot = _quat_to_exp_map(src_root_rot_quat)
+    src_joint_dof = char_model.rot_to_dof(src_joint_rot)
+    src_body_pos, src_body_rot = char_model.forward_kinematics(src_root_pos, src_root_rot_quat, src_joint_rot)
+    src_body_vels = src_body_pos[1:] - src_body_pos[:-1]
+    src_body_rot_vels = _quat_diff_angle(src_body_rot[1:], src_body_rot[:-1])
+    params = [src_root_pos.clone().requires_grad_(True), src_root_rot.clone().requires_grad_(True), src_joint_dof.clone().requires_grad_(True)]
+    optimizer = torch.optim.Adam(params, lr=step_size)
+    packed = None
+    if body_constraints is not None:
+        packed = body_constraints if isinstance(body_constraints, PackedBodyConstraints) else \
+            PackedBodyConstraints([body_constraints], char_model, src_root_pos.device)
+    out = open(log_file, "w") if log_file is not None else None
+    for it in range(num_iters):
+        optimizer.zero_grad()
+        loss, loss_dict = motion_terrain_contact_loss_localized(
+            params[0], params[1], params[2], src_root_pos, src_root_rot_quat, src_joint_rot, src_body_vels, src_body_rot_vels, contacts,
+            terrain, body_points, char_model, w_root_pos, w_root_rot, w_joint_rot, w_smoothness, w_penetration, w_contact, w_sliding,
+            w_body_constraints, w_jerk, packed, max_jerk)
+        loss.backward()
+        optimizer.step()
+        if it % 25 == 0 and (log is not None or out is not None):
+            if log is not None:
+                log(it, float(loss.detach()), loss_dict)
+            if out is not None:
+                out.write("%d %.6f %s\n" % (it, float(loss.detach()), " ".join("%s=%.6f" % (k.name, v) for k, v in loss_dict.items())))
+    if out is not None:
+        out.close()
+    return MotionFrames(root_pos=params[0].detach(), root_rot=_exp_map_to_quat(params[1].detach()),
+                        joint_rot=char_model.dof_to_rot(params[2].detach()), contacts=contacts.clone())

@@ -186,6 +186,16 @@ def main():
         out[tag + "_body"], out[tag + "_start"], out[tag + "_end"], out[tag + "_point"] = flatten(bc)
         print(tag, float(loss), {k.name: round(v, 6) if isinstance(v, float) else v for k, v in losses.items()},
               list(zip(out[tag + "_body"].tolist(), out[tag + "_start"].tolist(), out[tag + "_end"].tolist())))
+    # ---- motion_contact_optimization (:721-823): 40 Adam iterations (kin_gen step size) on the 24 frames, the source pushed
+    # 4 cm into the ground so that the penetration / contact terms drive the update, with the auto-derived constraints
+    import parc.util.motion_util as rmu
+    src = rmu.MotionFrames(root_pos=src_root_pos + torch.tensor([0.0, 0.0, -0.04]), root_rot=src_root_rot_quat.clone(),
+                           joint_rot=src_joint_rot.clone(), contacts=contacts.clone())
+    ret = ropt.motion_contact_optimization(src, body_points, terrain, model, num_iters=40, step_size=0.001, body_constraints=auto,
+                                           exp_name=None, use_wandb=False, log_file=None, **KIN_GEN_WEIGHTS)
+    out["optim_src_root_pos"] = src.root_pos
+    out["optim_root_pos"], out["optim_root_rot"], out["optim_joint_rot"] = ret.root_pos, ret.root_rot, ret.joint_rot
+    print("optim: root moved by", float((ret.root_pos - src.root_pos).abs().max()), "joints by", float((ret.joint_rot - src.joint_rot).abs().max()))
     npz("ref_opt_loss.npz", **out)
 
 
