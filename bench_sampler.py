@@ -41,6 +41,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--cpu-samples", type=int, default=2048)
+    ap.add_argument("--augment", action="store_true", help="also time the call with the heightfield augmenter (MAXPOOL_AND_BOXES, "
+                    "parc_1_train_gen_default.yaml values), records drawn once beforehand")
     args = ap.parse_args()
     assert torch.cuda.is_available(), "needs a CUDA device (no CPU fallback on the product path)"
     dev = torch.device("cuda", 0)
@@ -87,6 +89,46 @@ def main():
     if os.path.exists(pk):
         peak = float(json.load(open(pk))["hbm_gbs"])
     achieved = n * b_win / (ms * 1e-3) / 1e9
+    aug = None
+    if args.augment:
+        # what the augmenter reads per clip: hf_maxmin (here hf +- 0.25 m) and the per-frame cells under the body (the product's own
+        # compute_hf_mask_inds, the function scripts/parc_2_kin_gen.py runs when it writes a clip)
+        from parc_b200 import geom_util
+        from parc_b200.file_io import MotionFrames
+        from parc_b200.terrain import compute_hf_mask_inds
+        pts = geom_util.get_char_point_samples(model)
+        masks = []
+        for k, c in enumerate(pc):
+            t_ = c["terrain"]
+            t_.hf_maxmin = torch.stack([t_.hf + 0.25, t_.hf - 0.25], dim=-1).contiguous()
+            fr = MotionFrames(root_pos=c["root_pos"].to(dev), root_rot=c["root_rot"].to(dev), joint_rot=c["joint_rot"].to(dev))
+            masks.append([x.cpu() for x in compute_hf_mask_inds(fr, t_, model, pts)[0]])
+        lib._hf_mask_inds = masks
+        cfg_a = sampler_cfg(lib, dev)
+        cfg_a.update(use_hf_augmentation=True, hf_augmentation_mode="MAXPOOL_AND_BOXES", max_num_boxes=4, box_min_len=2, box_max_len=12,
+                     hf_maxpool_chance=0.15, hf_max_maxpool_size=10, hf_change_height_chance=0.1)
+        sa = MDMHeightfieldContactMotionSampler(cfg_a)
+        t0 = time.perf_counter()
+        rec = sa._draw_box_aug_records(n)
+        draw_s = time.perf_counter() - t0
+        rec = (rec[0].to(dev), rec[1].to(dev))
+
+        def step_a():
+            return sa.sample_motion_data(motion_ids=ids, motion_start_times=starts, future_times=ft, future_pos_noise=z, hf_aug_records=rec)
+
+        for _ in range(3):
+            step_a()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(args.steps):
+            step_a()
+        e1.record()
+        torch.cuda.synchronize()
+        ms_a = e0.elapsed_time(e1) / args.steps
+        aug = {"ms_per_call": ms_a, "augment_ms": ms_a - ms, "windows_per_s": n / (ms_a * 1e-3),
+               "bytes_per_window_augment": 31 * 31 * 4 * 2 + 4 * (8 + 29), "host_draw_s": draw_s,
+               "note": "MAXPOOL_AND_BOXES with parc_1_train_gen_default.yaml chances; augment_ms = the third launch (mask bitmap, bounds, pools, "
+                       "boxes in shared memory); host_draw_s = Python random / torch draws of the records for all windows, outside the timed calls"}
     cpu = None
     if args.cpu_samples > 0:
         from oracle import parc_oracle as O
@@ -108,7 +150,7 @@ def main():
                       "unit": "windows/s", "ms_per_call": ms, "frames_per_s": n * T / (ms * 1e-3),
                       "config": {"workload": "SURVEY 8f rank 1", "windows": n, "clips": args.motions, "seq_len": T, "grid": [31, 31]},
                       "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                   "bytes_per_window": b_win}, "cpu_baseline": cpu}))
+                                   "bytes_per_window": b_win}, "augmenter": aug, "cpu_baseline": cpu}))
 
 
 if __name__ == "__main__":

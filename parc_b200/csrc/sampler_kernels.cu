@@ -177,8 +177,14 @@ __global__ void __launch_bounds__(256) mdm_hf_augment_kernel(const __grid_consta
         __syncthreads();
         const float* cn = canon + i * CANON_W;
         const float rx = __ldg(cn), ry = __ldg(cn + 1);
-        const float heading = calc_heading(make_quat(__ldg(cn + 3), __ldg(cn + 4), __ldg(cn + 5), __ldg(cn + 6)));
-        const float sh = sinf(heading), ch = cosf(heading);
+        // heading of the reference frame: once per window (the same calls as mdm_canon_hf_kernel), shared through s_trig
+        __shared__ float s_trig[2];
+        if (tid == 0) {
+            const float heading = calc_heading(make_quat(__ldg(cn + 3), __ldg(cn + 4), __ldg(cn + 5), __ldg(cn + 6)));
+            s_trig[0] = sinf(heading); s_trig[1] = cosf(heading);
+        }
+        __syncthreads();
+        const float sh = s_trig[0], ch = s_trig[1];
         const float base = cfg.relative_z_style == PARC_RELATIVE_TO_ROOT_FLOOR ? __ldg(cn + 11) : __ldg(cn + 2);    // :379-388
         const float* mm = aug.hf_maxmin + __ldg(aug.maxmin_offset + mid);
         for (int p = tid; p < P; p += nt) {
